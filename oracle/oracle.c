@@ -1,0 +1,293 @@
+/*
+ * oracle/oracle.c -- CPU ORACLE (TEST INFRASTRUCTURE, NOT PRODUCT CODE).
+ *
+ * Plain-C restatement of the ensemble-update hot path of jmatta1/MCMCpp, used
+ * ONLY as the checker by tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline leg.  The product path (mcmcpp_b200/csrc) never links, loads or
+ * calls anything in this directory.
+ *
+ * Parity status: PINNED.  This file is checked (tests/test_oracle_*.py)
+ *   - against the pcg-cpp upstream known-answer vectors
+ *     (MCMCpp/Utility/pcg-cpp/test-high/expected/check-pcg64.out, check-pcg32.out),
+ *   - against golden vectors generated in the build container by running the
+ *     UNMODIFIED reference headers (oracle/ref_driver.cpp -> oracle/_ref/,
+ *     fixtures + generating script under tests/golden/),
+ *   - and, when oracle/_ref/ is present, live against the compiled reference.
+ *
+ * Every function cites the reference file:line it follows (paths relative to
+ * /root/reference).  Build: gcc -O2 -ffp-contract=off -fPIC -shared (see Makefile);
+ * contraction must stay off, the reference trajectory depends on it.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef unsigned __int128 u128;
+
+/* ------------------------------------------------------------------ pcg64 */
+/* MCMCpp/Utility/pcg-cpp/include/pcg_random.hpp:161-162 (128-bit default multiplier) */
+#define PCG128_MULT ((((u128)2549297995355413924ULL) << 64) | (u128)4865540595714422341ULL)
+
+typedef struct { u128 state; u128 inc; } pcg64_t;
+
+/* pcg_random.hpp:335-339 (set_stream: inc=(stream<<1)|1), :480-487 (seed ctor:
+ * state = bump(seed + increment)), :399-402 (bump = state*mult + inc).
+ * MCMCpp passes 64-bit seed/stream zero-extended (Utility/MultiSampler.h:54). */
+void oracle_pcg64_seed(pcg64_t* g, uint64_t seed, uint64_t stream)
+{
+    g->inc = (((u128)stream) << 1) | 1u;
+    g->state = ((u128)seed + g->inc) * PCG128_MULT + g->inc;
+}
+
+/* pcg_random.hpp:984-1011 (xsl_rr_mixin::output), pcg_extras.hpp:303-312 (rotr) */
+static inline uint64_t pcg64_output(u128 s)
+{
+    unsigned rot = (unsigned)(s >> 122);
+    uint64_t x = (uint64_t)(s >> 64) ^ (uint64_t)s;
+    return (x >> rot) | (x << ((-rot) & 63u));
+}
+
+/* pcg_random.hpp:417-423 with output_previous=false for 128-bit state (:742):
+ * advance first, then output the NEW state. */
+uint64_t oracle_pcg64_next(pcg64_t* g)
+{
+    g->state = g->state * PCG128_MULT + g->inc;
+    return pcg64_output(g->state);
+}
+
+/* pcg_random.hpp:622-651 (engine::advance, square-and-multiply over (mult,plus)) */
+void oracle_pcg64_advance(pcg64_t* g, u128 delta)
+{
+    u128 acc_mult = 1, acc_plus = 0, cur_mult = PCG128_MULT, cur_plus = g->inc;
+    while (delta > 0) {
+        if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+        cur_plus = (cur_mult + 1) * cur_plus;
+        cur_mult *= cur_mult;
+        delta >>= 1;
+    }
+    g->state = acc_mult * g->state + acc_plus;
+}
+void oracle_pcg64_advance_u64(pcg64_t* g, uint64_t delta) { oracle_pcg64_advance(g, (u128)delta); }
+/* backstep(n) == advance(2^128 - n): pcg_random.hpp:445-448 */
+void oracle_pcg64_backstep_u64(pcg64_t* g, uint64_t delta) { oracle_pcg64_advance(g, (u128)0 - (u128)delta); }
+
+/* pcg_extras.hpp:514-525 (bounded_rand); *rejections counts redraws */
+uint64_t oracle_pcg64_bounded(pcg64_t* g, uint64_t bound, int* rejections)
+{
+    uint64_t threshold = (0 - bound) % bound;
+    for (;;) {
+        uint64_t r = oracle_pcg64_next(g);
+        if (r >= threshold) return r % bound;
+        if (rejections) ++*rejections;
+    }
+}
+
+/* ------------------------------------------------------------------ pcg32 */
+/* pcg_random.hpp:158-159 (64-bit multiplier / default increment), :470-475
+ * (one-arg ctor), :808-836 (xsh_rr output on the OLD state). Used by the
+ * reference only for test-side initial positions and AutoCorrCalc subsampling. */
+typedef struct { uint64_t state; uint64_t inc; } pcg32_t;
+#define PCG64_MULT 6364136223846793005ULL
+#define PCG64_DEFAULT_INC 1442695040888963407ULL
+void oracle_pcg32_seed(pcg32_t* g, uint64_t seed) /* pcg32 eng(seed) */
+{
+    g->inc = PCG64_DEFAULT_INC;
+    g->state = (seed + g->inc) * PCG64_MULT + g->inc;
+}
+void oracle_pcg32_seed_stream(pcg32_t* g, uint64_t seed, uint64_t stream) /* pcg32 eng(seed, stream) */
+{
+    g->inc = (stream << 1) | 1u;
+    g->state = (seed + g->inc) * PCG64_MULT + g->inc;
+}
+uint32_t oracle_pcg32_next(pcg32_t* g)
+{
+    uint64_t old = g->state;
+    g->state = old * PCG64_MULT + g->inc;
+    unsigned rot = (unsigned)(old >> 59);
+    uint32_t x = (uint32_t)(((old >> 18) ^ old) >> 27);
+    return (x >> rot) | (x << ((-rot) & 31u));
+}
+
+/* ------------------------------------------------- libstdc++ distributions */
+/* std::generate_canonical<double,53>(pcg64) (libstdc++ 13 bits/random.tcc:3346-3381):
+ * one 64-bit draw, sum = double(r) (RNE), ret = sum / 2^64, clamp to nextafter(1,0).
+ * std::uniform_real_distribution<double>(0,1) is the identity on it
+ * (Utility/MultiSampler.h:121, bits/random.h:1779+). */
+double oracle_u64_to_unit(uint64_t r)
+{
+    double u = (double)r * 0x1.0p-64;
+    if (u >= 1.0) u = 0x1.fffffffffffffp-1;
+    return u;
+}
+
+/* Utility/GwDistribution.h:45-58: z = (Term1*u + InvSqrtAlpha)^2 with
+ * Alpha = num/denom, SqrtAlpha = sqrt(Alpha), InvSqrtAlpha = 1/sqrt(Alpha),
+ * Term1 = SqrtAlpha - InvSqrtAlpha. */
+void oracle_gw_constants(int alpha_num, int alpha_denom, double* term1, double* inv_sqrt_alpha)
+{
+    double alpha = (double)alpha_num / (double)alpha_denom;
+    double sa = sqrt(alpha);
+    double isa = 1.0 / sqrt(alpha);
+    *inv_sqrt_alpha = isa;
+    *term1 = sa - isa;
+}
+double oracle_gw_sample(double u, double term1, double inv_sqrt_alpha)
+{
+    double t = term1 * u + inv_sqrt_alpha;
+    return t * t;
+}
+/* Utility/MultiSampler.h:86 getNegExponentialReal = -expDist(engine);
+ * std::exponential_distribution (bits/random.h:4897-4905): -log(1-u)/lambda, lambda=1 */
+double oracle_neg_exponential(double u) { return -(-log(1.0 - u) / 1.0); }
+
+/* ---------------------------------------------------------------- targets */
+/* Target kinds.  Kind 0 is the reference's only in-repo Calculator; kinds 1-4
+ * are the synthetic BASELINE.json configs; their arithmetic
+ * order is DEFINED here and in include/mcmcpp_b200/targets.h identically. */
+enum { T_SKEWED_GAUSS_2D = 0, T_ROSENBROCK_2D = 1, T_DIAG_GAUSS = 2, T_DENSE_GAUSS = 3, T_LINREG = 4 };
+
+/* params: kind 0: {eps}; 1: {}; 2: iv[D]; 3: P[D*D] row-major; 4: {M, prior_var, X[M*D] row-major, y[M]} */
+
+/* test/sequential/SkewedGaussian/Common/SkewedGaussian.h:52-57 */
+static double logp_skewed(const double* x, double eps)
+{
+    double t1 = x[0] / 2.0 - x[1];
+    double t2 = x[0] / 2.0 + x[1];
+    return (((t1 * t1) / eps) + (t2 * t2)) / -2.0;
+}
+/* -(100 (y-x^2)^2 + (1-x)^2)/20 */
+static double logp_rosenbrock(const double* x)
+{
+    double t1 = x[1] - x[0] * x[0];
+    double t2 = 1.0 - x[0];
+    return ((100.0 * (t1 * t1)) + (t2 * t2)) / -20.0;
+}
+/* canonical 64-way strided sum + xor-butterfly tree: term d goes to partial
+ * d%64 (in increasing d); s[l]=p[2l]+p[2l+1]; then s[l]+=s[l^off] for
+ * off=16,8,4,2,1.  This is the order one warp (lane l owns elements 64k+2l,
+ * 64k+2l+1) produces, so host and device agree bit for bit. */
+static double canonical64_finish(double* p)
+{
+    double s[32], t[32];
+    for (int l = 0; l < 32; ++l) s[l] = p[2 * l] + p[2 * l + 1];
+    for (int off = 16; off >= 1; off >>= 1) {
+        for (int l = 0; l < 32; ++l) t[l] = s[l] + s[l ^ off];
+        memcpy(s, t, sizeof s);
+    }
+    return s[0];
+}
+/* -1/2 sum_d x_d^2 iv_d */
+static double logp_diag(const double* x, const double* iv, int D)
+{
+    double p[64];
+    for (int l = 0; l < 64; ++l) p[l] = 0.0;
+    for (int d = 0; d < D; ++d) p[d & 63] += (x[d] * x[d]) * iv[d];
+    return -0.5 * canonical64_finish(p);
+}
+/* -1/2 x^T P x, y_i = sum_j P_ij x_j then sum_i x_i y_i */
+static double logp_dense(const double* x, const double* P, int D)
+{
+    double q = 0.0;
+    for (int i = 0; i < D; ++i) {
+        double y = 0.0;
+        for (int j = 0; j < D; ++j) y += P[(size_t)i * D + j] * x[j];
+        q += x[i] * y;
+    }
+    return -0.5 * q;
+}
+/* -1/2 ||y - X th||^2 - 1/2 ||th||^2 / prior_var */
+static double logp_linreg(const double* th, const double* p, int D)
+{
+    long M = (long)p[0];
+    double pv = p[1];
+    const double* X = p + 2;
+    const double* y = X + (size_t)M * D;
+    double ss = 0.0, tt = 0.0;
+    for (long m = 0; m < M; ++m) {
+        double r = 0.0;
+        for (int j = 0; j < D; ++j) r += X[(size_t)m * D + j] * th[j];
+        r = y[m] - r;
+        ss += r * r;
+    }
+    for (int j = 0; j < D; ++j) tt += th[j] * th[j];
+    return -0.5 * ss - 0.5 * (tt / pv);
+}
+
+double oracle_logp(int kind, int D, const double* params, const double* x)
+{
+    switch (kind) {
+    case T_SKEWED_GAUSS_2D: return logp_skewed(x, params[0]);
+    case T_ROSENBROCK_2D:   return logp_rosenbrock(x);
+    case T_DIAG_GAUSS:      return logp_diag(x, params, D);
+    case T_DENSE_GAUSS:     return logp_dense(x, params, D);
+    case T_LINREG:          return logp_linreg(x, params, D);
+    }
+    return NAN;
+}
+
+/* --------------------------------------------------------- the hot path */
+typedef struct {
+    int32_t j;          /* complementary index (StretchMove.h:102) */
+    int32_t accept;     /* Metropolis decision (StretchMove.h:113) */
+    double z;           /* scalingFactor (StretchMove.h:104) */
+    double e;           /* log(1-u) = getNegExponentialReal() (StretchMove.h:113) */
+    double newp;        /* calcLogPostProb(proposal) (StretchMove.h:111) */
+    double diff;        /* logProbDiff (StretchMove.h:112) */
+} oracle_trace_t;
+
+/*
+ * Sequential-order restatement of EnsembleSampler::runMCMC / performStep
+ * (EnsembleSampler.h:284-310, 341-360) with StretchMove::updateWalker
+ * (Movers/StretchMove.h:100-123) and Walker bookkeeping (Walker/Walker.h:105,162-179).
+ *
+ *  pos   [W*D]  AoS [walker][param]; walkers 0..K-1 red, K..W-1 black (EnsembleSampler.h:225-226)
+ *  logp  [W]    aux data (current log posterior)
+ *  acc/tot [W]  per-walker accepted / total counters.  The caller mirrors
+ *               setInitialWalkerPos by starting them at 1 (Walker.h:76,162-170).
+ *  nsteps       number of STORED steps; each is `interval` ensemble steps of which
+ *               only the last is stored (EnsembleSampler.h:296-308)
+ *  chain [nsteps*W*D] AoS [step][walker][param] or NULL (Chain/ChainBlock.h:125-131)
+ *  trace [nsteps*interval*W] in update order, or NULL
+ *  rng state is carried in *g so that successive calls continue the stream.
+ * Returns the number of bounded_rand rejections seen (shifts the 3-draws/update cadence).
+ */
+int oracle_stretch_run(pcg64_t* g, int kind, const double* tparams, int W, int D,
+                       int alpha_num, int alpha_denom,
+                       double* pos, double* logp, int64_t* acc, int64_t* tot,
+                       int nsteps, int interval, double* chain, oracle_trace_t* trace)
+{
+    const int K = W / 2;
+    double term1, isa;
+    oracle_gw_constants(alpha_num, alpha_denom, &term1, &isa);
+    double* prop = (double*)malloc(sizeof(double) * (size_t)D);
+    int rejections = 0;
+    size_t tr = 0;
+    for (int s = 0; s < nsteps; ++s) {
+        for (int sub = 0; sub < interval; ++sub) {
+            int store = (sub == interval - 1);
+            for (int h = 0; h < 2; ++h) {
+                const int own0 = h * K, oth0 = (1 - h) * K;
+                for (int i = 0; i < K; ++i) {
+                    const int w = own0 + i;
+                    int j = (int)oracle_pcg64_bounded(g, (uint64_t)K, &rejections);
+                    const double* sel = pos + (size_t)(oth0 + j) * D;
+                    double* cur = pos + (size_t)w * D;
+                    double z = oracle_gw_sample(oracle_u64_to_unit(oracle_pcg64_next(g)), term1, isa);
+                    for (int d = 0; d < D; ++d) prop[d] = sel[d] + z * (cur[d] - sel[d]);
+                    double scaling = log(z) * (double)(D - 1);
+                    double newp = oracle_logp(kind, D, tparams, prop);
+                    double diff = scaling + newp - logp[w];
+                    double e = oracle_neg_exponential(oracle_u64_to_unit(oracle_pcg64_next(g)));
+                    int a = (e < diff);
+                    if (a) { memcpy(cur, prop, sizeof(double) * (size_t)D); logp[w] = newp; ++acc[w]; }
+                    ++tot[w];
+                    if (trace) { oracle_trace_t* t = &trace[tr++]; t->j = j; t->accept = a; t->z = z; t->e = e; t->newp = newp; t->diff = diff; }
+                    if (store && chain) memcpy(chain + ((size_t)s * W + w) * D, cur, sizeof(double) * (size_t)D);
+                }
+            }
+        }
+    }
+    free(prop);
+    return rejections;
+}

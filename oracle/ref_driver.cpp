@@ -1,0 +1,173 @@
+/*
+ * oracle/ref_driver.cpp -- TEST INFRASTRUCTURE (oracle), not product code.
+ *
+ * Thin extern "C" driver around the UNMODIFIED reference headers under
+ * /root/reference/MCMCpp (never copied into this repo).  Built by oracle/Makefile
+ * into oracle/_ref/ (git-ignored):
+ *   libmcmcpp_ref.so        reference headers as they lie (BlockSize 10000)  -> parity + goldens
+ *   libmcmcpp_ref_small.so  shadow copy whose only change is Chain::Detail::BlockSize
+ *                           (Chain/ChainBlock.h:31) so W >= ~2e4 can be allocated -> CPU timing
+ * Single TU on purpose: MCMCpp/Utility/Misc.h:34-67 defines non-inline functions.
+ */
+#include <chrono>
+#include <cstring>
+#include <thread>
+#include "EnsembleSampler.h"              /* MCMCpp/EnsembleSampler.h */
+#include "ParallelEnsembleSampler.h"      /* MCMCpp/ParallelEnsembleSampler.h */
+#include "Movers/StretchMove.h"           /* MCMCpp/Movers/StretchMove.h */
+#include "Common/SkewedGaussian.h"        /* test/sequential/SkewedGaussian/Common/SkewedGaussian.h */
+#include "mcmcpp_b200/targets.h"          /* HD functors for the synthetic configs (kinds 1-4) */
+
+namespace {
+
+/* Run `nsteps` stored steps on a sequential reference sampler; copy chain rows out. */
+template <class Calc>
+int runSequential(const Calc& calc, int W, int D, int seed, double* initPos, double* initAux,
+                  int nsteps, int interval, double* chainOut,
+                  unsigned long long* acc, unsigned long long* tot)
+{
+    typedef MCMC::Mover::StretchMove<double, Calc> Mover;
+    Mover mover(D, seed, calc);
+    /* chain cap large enough for nsteps+1 rows in 10000-step blocks */
+    unsigned long long blocks = (unsigned long long)(nsteps + 1) / MCMC::Chain::Detail::BlockSize + 2ULL;
+    unsigned long long maxBytes = blocks * sizeof(double) * D * MCMC::Chain::Detail::BlockSize * (unsigned long long)W;
+    MCMC::EnsembleSampler<double, Mover> sampler(seed, W, D, mover, maxBytes);
+    if (interval > 1) sampler.setSlicingMode(true, interval);
+    sampler.setInitialWalkerPos(initPos, initAux);
+    bool ok = sampler.runMCMC(nsteps);
+    *acc = sampler.getAcceptedSteps();
+    *tot = sampler.getTotalSteps();
+    if (chainOut) {
+        auto it = sampler.getStepIttBegin();
+        auto end = sampler.getStepIttEnd();
+        size_t row = (size_t)W * D;
+        int s = 0;
+        for (; it != end && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
+    }
+    return ok ? sampler.getStoredSteps() : -sampler.getStoredSteps();
+}
+
+/* Throughput run: steps are issued in bursts that fit one chain block, reset() in between
+ * (EnsembleSampler.h:312-322 keeps walker positions).  threads==0 -> sequential sampler. */
+template <class Calc>
+double runTimed(const Calc& calc, int W, int D, int seed, double* initPos, double* initAux,
+                int nsteps, int threads, unsigned long long* acc, unsigned long long* tot)
+{
+    typedef MCMC::Mover::StretchMove<double, Calc> Mover;
+    Mover mover(D, seed, calc);
+    const int burst = MCMC::Chain::Detail::BlockSize - 1;
+    unsigned long long maxBytes = 2ULL * sizeof(double) * D * MCMC::Chain::Detail::BlockSize * (unsigned long long)W;
+    double secs = 0.0;
+    unsigned long long a = 0, t = 0;
+    if (threads <= 0) {
+        MCMC::EnsembleSampler<double, Mover> sampler(seed, W, D, mover, maxBytes);
+        sampler.setInitialWalkerPos(initPos, initAux);
+        for (int done = 0; done < nsteps;) {
+            int n = (nsteps - done < burst) ? nsteps - done : burst;
+            sampler.reset();
+            auto t0 = std::chrono::steady_clock::now();
+            sampler.runMCMC(n);
+            secs += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            a += sampler.getAcceptedSteps(); t += sampler.getTotalSteps();
+            done += n;
+        }
+    } else {
+        MCMC::ParallelEnsembleSampler<double, Mover, MCMC::Utility::NoAction<double>, true> sampler(seed, threads, W, D, mover, maxBytes);
+        sampler.setInitialWalkerPos(initPos, initAux);
+        for (int done = 0; done < nsteps;) {
+            int n = (nsteps - done < burst) ? nsteps - done : burst;
+            sampler.reset();
+            auto t0 = std::chrono::steady_clock::now();
+            sampler.runMCMC(n);
+            secs += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            /* the parallel sampler only exposes the fraction (ParallelEnsembleSampler.h:171) */
+            unsigned long long tt = (unsigned long long)W * n;
+            a += (unsigned long long)(sampler.getAcceptanceFraction() * (double)tt + 0.5); t += tt;
+            done += n;
+        }
+    }
+    *acc = a; *tot = t;
+    return secs;
+}
+
+} // namespace
+
+/* kind / params encoding is the one of oracle/oracle.c: 0 {eps}; 1 {}; 2 iv[D];
+ * 3 P[D*D]; 4 {M, priorVar, X[M*D], y[M]} */
+#define DISPATCH(CALL)                                                                             \
+    switch (kind) {                                                                                \
+    case 0: { SkewedGaussianTwoDim<double> c(p[0]); return CALL(c); }                              \
+    case 1: { MCMC::Targets::RosenbrockTwoDim<double> c; return CALL(c); }                         \
+    case 2: { MCMC::Targets::DiagGaussian<double> c(p, D); return CALL(c); }                       \
+    case 3: { MCMC::Targets::DenseGaussian<double> c(p, D); return CALL(c); }                      \
+    case 4: { long M = (long)p[0]; const double* X = p + 2;                                        \
+              MCMC::Targets::LinearRegression<double> c(X, X + (size_t)M * D, M, D, p[1]); return CALL(c); } \
+    }
+
+extern "C" {
+
+int ref_block_size() { return MCMC::Chain::Detail::BlockSize; }
+int ref_hardware_concurrency() { return (int)std::thread::hardware_concurrency(); }
+
+/* log posterior through the functor the reference mover would call (StretchMove.h:111) */
+double ref_logp(int kind, int D, const double* p, double* x)
+{
+#define CALL_LOGP(c) c.calcLogPostProb(x)
+    DISPATCH(CALL_LOGP)
+    return 0.0;
+}
+
+/* Sequential EnsembleSampler (EnsembleSampler.h:284-310).  chainOut: (nsteps+1) rows of W*D
+ * (row 0 = initial positions, EnsembleSampler.h:220-230) or NULL.  Returns stored steps
+ * (negative if runMCMC returned false). */
+int ref_stretch_run(int kind, const double* p, int W, int D, int seed, double* initPos, double* initAux,
+                    int nsteps, int interval, double* chainOut, unsigned long long* acc, unsigned long long* tot)
+{
+#define CALL_RUN(c) runSequential(c, W, D, seed, initPos, initAux, nsteps, interval, chainOut, acc, tot)
+    DISPATCH(CALL_RUN)
+    return 0;
+}
+
+/* Timed run; threads==0 -> EnsembleSampler on one core, else ParallelEnsembleSampler<..., true>
+ * with `threads` workers (ParallelEnsembleSampler.h:228-291).  Returns seconds inside runMCMC. */
+double ref_stretch_time(int kind, const double* p, int W, int D, int seed, double* initPos, double* initAux,
+                        int nsteps, int threads, unsigned long long* acc, unsigned long long* tot)
+{
+#define CALL_TIME(c) runTimed(c, W, D, seed, initPos, initAux, nsteps, threads, acc, tot)
+    DISPATCH(CALL_TIME)
+    return -1.0;
+}
+
+/* Test-side initial positions exactly as the survey KAT / reference tests make them:
+ * pcg32 eng(seed) + std::normal_distribution<double>(0,1), filled in order
+ * (test/sequential/SkewedGaussian/StretchMove/src/main.cpp:146). */
+void ref_init_normal(unsigned long long seed, double* out, long n)
+{
+    pcg32 eng(seed);
+    std::normal_distribution<double> nd(0.0, 1.0);
+    for (long i = 0; i < n; ++i) out[i] = nd(eng);
+}
+
+/* raw MultiSampler draws in StretchMove order (j, z, log(1-u)) for n updates
+ * (Utility/MultiSampler.h:60,86,99) */
+void ref_draws(long long seed, long long stream, int K, long n, int* j, double* z, double* e)
+{
+    MCMC::Utility::MultiSampler<double, MCMC::Utility::GwDistribution<double, 2, 1> > ms;
+    ms.setPrng(seed, stream);
+    for (long i = 0; i < n; ++i) { j[i] = ms.getNonOffSetInt(K); z[i] = ms.getCustomSample(); e[i] = ms.getNegExponentialReal(); }
+}
+
+/* raw pcg64 / pcg32 outputs */
+void ref_pcg64_raw(unsigned long long seed, unsigned long long stream, unsigned long long skip, unsigned long long* out, long n)
+{
+    pcg64 g(seed, stream);
+    g.advance(skip);
+    for (long i = 0; i < n; ++i) out[i] = g();
+}
+void ref_pcg32_raw(unsigned long long seed, unsigned long long stream, unsigned int* out, long n)
+{
+    pcg32 g(seed, stream);
+    for (long i = 0; i < n; ++i) out[i] = g();
+}
+
+} /* extern "C" */
