@@ -1,0 +1,185 @@
+/*
+ * include/mcmcpp_b200/capi.h -- C-ABI of libmcmcpp_b200.so, the B200 (sm_100a) runtime behind
+ * MCMCpp's ensemble-update hot path.
+ *
+ * Plain C: opaque handle, plain pointers and sizes, int status returns (0 = ok).  No torch,
+ * no C++ types.  Each entry point names the reference interface it replaces (paths relative to
+ * the reference checkout, jmatta1/MCMCpp).  The C++ drop-in templates in
+ * include/mcmcpp_b200/EnsembleSampler.h and the Python mirror in mcmcpp_b200/sampler.py are thin
+ * callers of exactly these functions; INTEGRATION.md shows the binding a maintainer adds.
+ *
+ * There is no CPU fallback: every call fails with MCMCPP_ERR_CUDA when no sm_100-class device
+ * is usable.
+ */
+#ifndef MCMCPP_B200_CAPI_H
+#define MCMCPP_B200_CAPI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mcmcpp_sampler mcmcpp_sampler;
+
+enum {
+    MCMCPP_OK = 0,
+    MCMCPP_CHAIN_FULL = 1,      /* runMCMC would return false (EnsembleSampler.h:293,306) */
+    MCMCPP_ERR_ARG = -1,        /* the reference asserts (EnsembleSampler.h:207-208,327,335-336) */
+    MCMCPP_ERR_CUDA = -2,
+    MCMCPP_ERR_NCCL = -3,
+    MCMCPP_ERR_STATE = -4,      /* call order (e.g. run before set_initial) */
+    MCMCPP_ERR_UNSUPPORTED = -5
+};
+
+/* RNG modes.  SEQUENTIAL reproduces EnsembleSampler's single pcg64 stream (seed, stream 0)
+ * consumed in walker order (EnsembleSampler.h:217,345-354): walker slot i of half h at step t
+ * uses draws 3(tW + hK + i)+1..+3, reached by jump-ahead, so results are bit-identical to the
+ * sequential reference and independent of the GPU count.  PER_WALKER gives walker w its own
+ * stream pcg64(seed, w) (the per-thread streams of RedBlkUpdater.h:86 taken to one walker per
+ * "thread"); its oracle is one reference StretchMove per walker. */
+enum { MCMCPP_RNG_SEQUENTIAL = 0, MCMCPP_RNG_PER_WALKER = 1 };
+
+/* How one ensemble is spread over `world` GPUs (one process per GPU):
+ *   NONE       world == 1
+ *   ALLGATHER  walker-index shards; after each half-step the updated half is all-gathered with
+ *              NCCL so every rank holds the full ensemble (BASELINE.json north_star)
+ *   PEER       walker-index shards; partner rows are read straight from the owning GPU's HBM
+ *              over NVLink (peer-mapped memory) inside the update kernel, one device-side
+ *              barrier per half-step, no bulk exchange */
+enum { MCMCPP_SHARD_NONE = 0, MCMCPP_SHARD_ALLGATHER = 1, MCMCPP_SHARD_PEER = 2 };
+
+/* built-in Calculators (include/mcmcpp_b200/targets.h); params layout as in oracle/oracle.c */
+enum {
+    MCMCPP_TARGET_SKEWED_GAUSS_2D = 0, /* params {eps}             test/sequential/SkewedGaussian/Common/SkewedGaussian.h:52-57 */
+    MCMCPP_TARGET_ROSENBROCK_2D = 1,   /* params {}                */
+    MCMCPP_TARGET_DIAG_GAUSS = 2,      /* params iv[D]             */
+    MCMCPP_TARGET_DENSE_GAUSS = 3,     /* params P[D*D] row-major  */
+    MCMCPP_TARGET_LINREG = 4           /* params {M, priorVar, X[M*D] row-major, y[M]} */
+};
+
+typedef struct {
+    int32_t num_walkers;       /* numWalker: even, > 2*num_params  (EnsembleSampler.h:66,207-208) */
+    int32_t num_params;        /* numParameter */
+    int64_t seed;              /* randSeed -> setPrng(seed, stream)  (EnsembleSampler.h:217) */
+    int32_t rng_mode;          /* MCMCPP_RNG_* */
+    int32_t alpha_num;         /* GwDistribution<ParamType, AlphaNum, AlphaDenom>  (Utility/GwDistribution.h:45) */
+    int32_t alpha_denom;
+    int32_t device;            /* CUDA device ordinal */
+    int32_t rank;              /* this process's shard */
+    int32_t world;             /* number of shards (GPUs) */
+    int32_t shard_mode;        /* MCMCPP_SHARD_* */
+    int32_t trace_updates;     /* >0: record (j, accept, z, e, newp, diff) for the first n updates (tests) */
+    uint64_t max_chain_bytes;  /* maxChainSizeBytes (EnsembleSampler.h:67); 0 = keep no chain */
+} mcmcpp_config;
+
+/* One row of the optional trace, in the sequential update order (step, half, slot). */
+typedef struct {
+    int32_t j;
+    int32_t accept;
+    double z, e, newp, diff;
+} mcmcpp_trace;
+
+/*
+ * Arguments of one half-step launch.  A "launcher" is a host function that enqueues the
+ * update kernel for the owned slots of one colour on `stream`; the runtime owns every buffer.
+ * Launchers for user Calculators are instantiated in the user's CUDA translation unit by
+ * include/mcmcpp_b200/stretch_kernels.cuh (MCMC::Device::HalfStepLauncher<Calc>::launch);
+ * launchers for the built-in targets live inside the library.
+ *
+ * Layout: walker-major rows.  pos[w*D + d], walkers 0..K-1 red, K..W-1 black
+ * (EnsembleSampler.h:225-226) -- the reference's own chain-row layout (ChainBlock.h:125-131),
+ * so a stored step is a plain copy of the state.
+ */
+typedef struct {
+    double* pos;               /* [W*D] local full-ensemble array (own rows always valid; all rows valid unless PEER) */
+    double* logp;              /* [W]   auxData of owned walkers */
+    uint64_t* rng_state;       /* [W*2] pcg64 state (lo,hi) per walker, positioned at its next draw */
+    double* chain_row;         /* device chain slot [W*D] for this step, or NULL when the step is not stored */
+    unsigned long long* accept_slots; /* [grid] per-CTA accepted-proposal partial sums */
+    int32_t* flags;            /* [0]: count of bounded_rand redraws seen (sequential-stream cadence broken) */
+    mcmcpp_trace* trace;       /* trace row of slot 0 of this half-step, or NULL */
+    const double* const* peer_pos; /* PEER mode: [world] device pointers to every rank's pos array, else NULL */
+    int32_t W, D, K;
+    int32_t half;              /* 0 red, 1 black */
+    int32_t slot_begin;        /* first owned slot in [0,K) */
+    int32_t slot_count;        /* owned slots */
+    int32_t slots_per_rank;    /* K / world (PEER owner lookup) */
+    int32_t rng_mode;
+    uint64_t bound_threshold;  /* (2^64 - K) mod K   (pcg_extras.hpp:517) */
+    uint64_t bound_recip;      /* floor(2^64 / K) */
+    uint64_t skip_mult[2];     /* SEQUENTIAL: affine jump by 3W-3 draws applied after a walker's 3 draws */
+    uint64_t skip_plus[2];
+    double gw_term1;           /* GwDistribution constants */
+    double gw_inv_sqrt_alpha;
+    int32_t max_grid;          /* size of accept_slots */
+    int32_t trace_rows;        /* rows available at `trace` (slots >= trace_rows are not recorded) */
+} mcmcpp_halfstep_args;
+
+typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);
+
+/* ---- life cycle: EnsembleSampler ctor/dtor (EnsembleSampler.h:199-218,72) -------------------- */
+/* `calculator` is copied by value (calc_bytes); it must be trivially copyable and any pointers in
+ * it must be device pointers (the Calculator "view" convention of targets.h). */
+int mcmcpp_sampler_create(const mcmcpp_config* cfg, mcmcpp_halfstep_fn launcher, const void* calculator,
+                          size_t calc_bytes, mcmcpp_sampler** out);
+/* Built-in Calculator: `params` (host) is uploaded and viewed by the functor. */
+int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, const double* params, size_t num_params_values,
+                                  mcmcpp_sampler** out);
+int mcmcpp_sampler_destroy(mcmcpp_sampler* s);
+
+/* ---- setInitialWalkerPos (EnsembleSampler.h:220-230): AoS [walker][param] + aux[walker];
+ *      counts as one accepted step per walker and stores chain row 0 (Walker.h:76,162-170) -------- */
+int mcmcpp_sampler_set_initial(mcmcpp_sampler* s, const double* positions_host, const double* aux_host);
+/* same with device-resident inputs (no host copy) */
+int mcmcpp_sampler_set_initial_device(mcmcpp_sampler* s, const double* positions_dev, const double* aux_dev);
+
+/* ---- setSlicingMode / setSamplingMode (EnsembleSampler.h:324-330, ParallelEnsembleSampler.h:322-330) */
+int mcmcpp_sampler_set_slicing(mcmcpp_sampler* s, int use_slicing, int interval);
+
+/* ---- runMCMC (EnsembleSampler.h:284-310): num_steps STORED steps (x interval when slicing).
+ *      Returns MCMCPP_CHAIN_FULL where the reference returns false.  Blocking; the chain rows of
+ *      the call are on the host when it returns.  device_ms (may be NULL) receives the CUDA-event
+ *      time of the update kernels + exchanges on the sampler's stream. */
+int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms);
+
+/* ---- getAcceptedSteps / getTotalSteps / getAcceptanceFraction (EnsembleSampler.h:244-282);
+ *      ensemble-wide (summed over ranks by the caller when world > 1: values are this rank's) ---- */
+int mcmcpp_sampler_get_counts(mcmcpp_sampler* s, unsigned long long* accepted, unsigned long long* total);
+int mcmcpp_sampler_get_stored_steps(mcmcpp_sampler* s);                  /* getStoredSteps (EnsembleSampler.h:150) */
+
+/* ---- reset / storeCurrentWalkerPositions / sliceAndBurnChain (EnsembleSampler.h:312-322,232-242,332-339) */
+int mcmcpp_sampler_reset(mcmcpp_sampler* s);
+int mcmcpp_sampler_store_current(mcmcpp_sampler* s);
+int mcmcpp_sampler_slice_and_burn(mcmcpp_sampler* s, int interval, int burn_in);
+
+/* ---- chain read side: contiguous host rows [stored][W][D], the layout ChainStepIterator
+ *      dereferences to (ChainStepIterator.h:125).  Valid until reset/slice/destroy/run. ---------- */
+int mcmcpp_sampler_chain(mcmcpp_sampler* s, const double** rows_host, long long* stored_steps);
+
+/* ---- current walker state (Walker::getCurrState / getCurrAuxData, Walker.h:128,134) ---------- */
+int mcmcpp_sampler_get_state(mcmcpp_sampler* s, double* positions_host, double* aux_host);
+int mcmcpp_sampler_state_device(mcmcpp_sampler* s, double** positions_dev, double** aux_dev);
+
+/* ---- diagnostics -------------------------------------------------------------------------- */
+int mcmcpp_sampler_get_trace(mcmcpp_sampler* s, mcmcpp_trace* out, int max_rows, int* rows);
+int mcmcpp_sampler_rng_redraws(mcmcpp_sampler* s, int* redraws);
+int mcmcpp_sampler_launch_count(mcmcpp_sampler* s, unsigned long long* kernel_launches);
+void* mcmcpp_sampler_stream(mcmcpp_sampler* s);      /* cudaStream_t the kernels are launched on */
+const char* mcmcpp_last_error(void);
+int mcmcpp_device_count(void);
+
+/* ---- multi-GPU plumbing (one process per GPU) -------------------------------------------------
+ *      ALLGATHER: rank 0 makes an id, the host layer broadcasts the 128 bytes, every rank joins.
+ *      PEER: every rank exports a 64-byte IPC handle of its pos array (and of a barrier word), the
+ *      host layer all-gathers them, every rank imports the others'. */
+int mcmcpp_comm_unique_id(void* id128);
+int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128);
+int mcmcpp_sampler_peer_export(mcmcpp_sampler* s, void* handle64);
+int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_ranks);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

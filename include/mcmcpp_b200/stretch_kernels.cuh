@@ -1,0 +1,400 @@
+/*
+ * include/mcmcpp_b200/stretch_kernels.cuh -- the red/black half-ensemble stretch move as sm_100a
+ * kernels, templated on the user's Calculator (the reference's log-posterior plug-in concept,
+ * MCMCpp/Movers/StretchMove.h:47-53, in __host__ __device__ form).
+ *
+ * One launch = one colour of EnsembleSampler::performStep (MCMCpp/EnsembleSampler.h:345-354):
+ * every owned walker of that colour runs StretchMove::updateWalker (Movers/StretchMove.h:100-123)
+ * against the frozen other colour:
+ *     j  = bounded pcg64 draw            (Utility/MultiSampler.h:99)
+ *     z  = g(z) inverse CDF              (Utility/MultiSampler.h:60, Utility/GwDistribution.h:58)
+ *     prop[d] = sel[d] + z*(cur[d]-sel[d])
+ *     q  = log(z)*(D-1) + logp(prop) - logp(cur)
+ *     accept iff log(1-u) < q            (Utility/MultiSampler.h:86)
+ *     accept: state <- prop, aux <- logp(prop), ++accepted   (Walker/Walker.h:172-179)
+ *     stored step: chain row <- current state, accepted or not (Walker/Walker.h:105, Chain/ChainBlock.h:125-131)
+ *
+ * Two kernels:
+ *   stretchHalfStepThread<Calc,D>      one thread per walker, D <= 8: row, partner row and proposal live in
+ *                                      registers; 16-byte vector loads/stores of the walker-major rows.
+ *   stretchHalfStepWarp<Calc,NCHUNK>   one warp per walker, D <= 64*NCHUNK: lane l owns elements 64c+2l, 64c+2l+1
+ *                                      (one double2 per chunk), the row pair is streamed once HBM -> registers,
+ *                                      the log-posterior of a SEPARABLE Calculator (term()/finish()) is reduced
+ *                                      in the canonical 64-way order of targets.h (bit-identical to its host form);
+ *                                      any other Calculator gets its proposal staged in shared memory and is
+ *                                      evaluated by lane 0 in the reference's sequential order.
+ * All arithmetic on the parity path is written with explicit round-to-nearest intrinsics (no FMA contraction);
+ * compile user Calculators with -fmad=false to keep them contraction-free too.
+ */
+#ifndef MCMCPP_B200_STRETCH_KERNELS_CUH
+#define MCMCPP_B200_STRETCH_KERNELS_CUH
+
+#include <cuda_runtime.h>
+#include "mcmcpp_b200/capi.h"
+#include "mcmcpp_b200/device_rng.cuh"
+
+namespace MCMC
+{
+namespace Device
+{
+
+enum { ThreadKernelMaxDim = 8, ThreadKernelThreads = 128, WarpKernelThreads = 256, WarpKernelMaxChunks = 16 };
+
+/* ---- Calculator traits --------------------------------------------------------------------- */
+template <class Calc>
+struct IsSeparable
+{
+    template <class C> static char test(decltype(&C::term), decltype(&C::finish));
+    template <class C> static long test(...);
+    static const bool value = sizeof(test<Calc>(0, 0)) == sizeof(char);
+};
+
+/* ---- small helpers -------------------------------------------------------------------------- */
+__device__ __forceinline__ double stretchPoint(double sel, double cur, double z)
+{
+    return __dadd_rn(sel, __dmul_rn(z, __dsub_rn(cur, sel)));
+}
+
+template <int D>
+__device__ __forceinline__ void loadRow(const double* __restrict__ row, double (&out)[D])
+{
+    if ((D & 1) == 0) {
+        const double2* r2 = reinterpret_cast<const double2*>(row);
+#pragma unroll
+        for (int d = 0; d < D / 2; ++d) { double2 v = r2[d]; out[2 * d] = v.x; out[2 * d + 1] = v.y; }
+    } else {
+#pragma unroll
+        for (int d = 0; d < D; ++d) out[d] = row[d];
+    }
+}
+
+template <int D>
+__device__ __forceinline__ void loadRowReadOnly(const double* __restrict__ row, double (&out)[D])
+{
+    if ((D & 1) == 0) {
+        const double2* r2 = reinterpret_cast<const double2*>(row);
+#pragma unroll
+        for (int d = 0; d < D / 2; ++d) { double2 v = __ldg(r2 + d); out[2 * d] = v.x; out[2 * d + 1] = v.y; }
+    } else {
+#pragma unroll
+        for (int d = 0; d < D; ++d) out[d] = __ldg(row + d);
+    }
+}
+
+template <int D>
+__device__ __forceinline__ void storeRow(double* __restrict__ row, const double (&in)[D])
+{
+    if ((D & 1) == 0) {
+        double2* r2 = reinterpret_cast<double2*>(row);
+#pragma unroll
+        for (int d = 0; d < D / 2; ++d) r2[d] = make_double2(in[2 * d], in[2 * d + 1]);
+    } else {
+#pragma unroll
+        for (int d = 0; d < D; ++d) row[d] = in[d];
+    }
+}
+
+struct WalkerRng
+{
+    U128 state, inc;
+};
+
+__device__ __forceinline__ WalkerRng loadRng(const mcmcpp_halfstep_args& a, int w)
+{
+    WalkerRng r;
+    ulonglong2 s = reinterpret_cast<const ulonglong2*>(a.rng_state)[w];
+    r.state.lo = s.x;
+    r.state.hi = s.y;
+    /* SEQUENTIAL: the sampler's one stream 0 (EnsembleSampler.h:217); PER_WALKER: stream = walker index */
+    r.inc.lo = (a.rng_mode == MCMCPP_RNG_PER_WALKER) ? ((((uint64_t)w) << 1) | 1ULL) : 1ULL;
+    r.inc.hi = 0;
+    return r;
+}
+
+/* leave the state at this walker's next draw: SEQUENTIAL jumps over the other W-1 walkers' draws */
+__device__ __forceinline__ void storeRng(const mcmcpp_halfstep_args& a, int w, WalkerRng r)
+{
+    if (a.rng_mode == MCMCPP_RNG_SEQUENTIAL) {
+        Affine128 m;
+        m.mult.lo = a.skip_mult[0]; m.mult.hi = a.skip_mult[1];
+        m.plus.lo = a.skip_plus[0]; m.plus.hi = a.skip_plus[1];
+        r.state = applyAffine(m, r.state);
+    }
+    reinterpret_cast<ulonglong2*>(a.rng_state)[w] = make_ulonglong2(r.state.lo, r.state.hi);
+}
+
+__device__ __forceinline__ const double* partnerBase(const mcmcpp_halfstep_args& a, int j)
+{
+    /* PEER sharding: the partner row lives in the HBM of the rank that owns slot j (NVLink load) */
+    return a.peer_pos ? a.peer_pos[j / a.slots_per_rank] : a.pos;
+}
+
+__device__ __forceinline__ GwConstants gwOf(const mcmcpp_halfstep_args& a)
+{
+    GwConstants g;
+    g.term1 = a.gw_term1;
+    g.invSqrtAlpha = a.gw_inv_sqrt_alpha;
+    return g;
+}
+
+/* ---- kernel 1: one thread per walker ---------------------------------------------------------- */
+template <class Calc, int D, bool TRACE>
+__global__ void __launch_bounds__(ThreadKernelThreads) stretchHalfStepThread(const mcmcpp_halfstep_args a, const Calc calcIn)
+{
+    const int i = blockIdx.x * ThreadKernelThreads + threadIdx.x;
+    int accepted = 0;
+    if (i < a.slot_count) {
+        Calc calc = calcIn;
+        const int slot = a.slot_begin + i;
+        const int w = a.half * a.K + slot;
+        const int other0 = (1 - a.half) * a.K;
+
+        WalkerRng rng = loadRng(a, w);
+        StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+        storeRng(a, w, rng);
+        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+
+        double cur[D], prop[D];
+        double* ownRow = a.pos + (size_t)w * D;
+        loadRow<D>(ownRow, cur);
+        loadRowReadOnly<D>(partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D, prop);
+#pragma unroll
+        for (int d = 0; d < D; ++d) prop[d] = stretchPoint(prop[d], cur[d], dr.z);
+
+        const double scaling = __dmul_rn(log(dr.z), (double)(D - 1));
+        const double newp = calc.calcLogPostProb(prop);
+        const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
+        accepted = dr.logOneMinusU < diff ? 1 : 0;
+        if (accepted) {
+            storeRow<D>(ownRow, prop);
+            a.logp[w] = newp;
+        }
+        if (a.chain_row) {
+            double* chainRow = a.chain_row + (size_t)w * D;
+            if (accepted) storeRow<D>(chainRow, prop); else storeRow<D>(chainRow, cur);
+        }
+        if (TRACE) {
+            if (slot < a.trace_rows) {
+                mcmcpp_trace t;
+                t.j = dr.j; t.accept = accepted; t.z = dr.z; t.e = dr.logOneMinusU; t.newp = newp; t.diff = diff;
+                a.trace[slot] = t;
+            }
+        }
+    }
+    /* acceptance counter: one CTA-wide popcount, one plain add per CTA into its own slot */
+    const int blockAccepted = __syncthreads_count(accepted);
+    if (threadIdx.x == 0 && blockAccepted) a.accept_slots[blockIdx.x] += (unsigned long long)blockAccepted;
+}
+
+/* ---- kernel 2: one warp per walker ------------------------------------------------------------ */
+template <class Calc, bool SEPARABLE>
+struct WarpLogp;
+
+/* separable Calculator: canonical 64-way strided partial sums + xor butterfly (targets.h canonical64Finish) */
+template <class Calc>
+struct WarpLogp<Calc, true>
+{
+    template <int NCHUNK>
+    static __device__ __forceinline__ double eval(Calc& calc, const double2 (&prop)[NCHUNK], int D, int lane, double*)
+    {
+        double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+        for (int c = 0; c < NCHUNK; ++c) {
+            const int d = 64 * c + 2 * lane;
+            if (d < D) p0 = __dadd_rn(p0, calc.term(prop[c].x, d));
+            if (d + 1 < D) p1 = __dadd_rn(p1, calc.term(prop[c].y, d + 1));
+        }
+        double s = __dadd_rn(p0, p1);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) s = __dadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
+        return calc.finish(s);
+    }
+};
+
+/* any other Calculator: proposal staged in shared memory, lane 0 evaluates in the reference's order */
+template <class Calc>
+struct WarpLogp<Calc, false>
+{
+    template <int NCHUNK>
+    static __device__ __forceinline__ double eval(Calc& calc, const double2 (&prop)[NCHUNK], int D, int lane, double* stage)
+    {
+#pragma unroll
+        for (int c = 0; c < NCHUNK; ++c) {
+            const int d = 64 * c + 2 * lane;
+            if (d < D) stage[d] = prop[c].x;
+            if (d + 1 < D) stage[d + 1] = prop[c].y;
+        }
+        __syncwarp();
+        double v = 0.0;
+        if (lane == 0) v = calc.calcLogPostProb(stage);
+        v = __shfl_sync(0xffffffffu, v, 0);
+        __syncwarp();
+        return v;
+    }
+};
+
+template <class Calc, int NCHUNK, bool VEC, bool TRACE>
+__global__ void __launch_bounds__(WarpKernelThreads) stretchHalfStepWarp(const mcmcpp_halfstep_args a, const Calc calcIn)
+{
+    extern __shared__ double stageAll[];
+    const int lane = threadIdx.x & 31;
+    const int warpInBlock = threadIdx.x >> 5;
+    const int i = blockIdx.x * (WarpKernelThreads / 32) + warpInBlock;
+    if (i >= a.slot_count) return;          /* warp-uniform */
+    Calc calc = calcIn;
+    const int D = a.D;
+    const int slot = a.slot_begin + i;
+    const int w = a.half * a.K + slot;
+    const int other0 = (1 - a.half) * a.K;
+
+    /* every lane replays the same three draws (cheaper than a broadcast of six registers) */
+    WalkerRng rng = loadRng(a, w);
+    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+
+    double* ownRow = a.pos + (size_t)w * D;
+    const double* selRow = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
+    double2 cur[NCHUNK], prop[NCHUNK];
+#pragma unroll
+    for (int c = 0; c < NCHUNK; ++c) {
+        const int d = 64 * c + 2 * lane;
+        cur[c] = make_double2(0.0, 0.0);
+        prop[c] = make_double2(0.0, 0.0);
+        if (VEC) {
+            if (d < D) {
+                cur[c] = *reinterpret_cast<const double2*>(ownRow + d);
+                prop[c] = __ldg(reinterpret_cast<const double2*>(selRow + d));
+            }
+        } else {
+            if (d < D) { cur[c].x = ownRow[d]; prop[c].x = __ldg(selRow + d); }
+            if (d + 1 < D) { cur[c].y = ownRow[d + 1]; prop[c].y = __ldg(selRow + d + 1); }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NCHUNK; ++c) {
+        prop[c].x = stretchPoint(prop[c].x, cur[c].x, dr.z);
+        prop[c].y = stretchPoint(prop[c].y, cur[c].y, dr.z);
+    }
+
+    const double scaling = __dmul_rn(log(dr.z), (double)(D - 1));
+    const double newp = WarpLogp<Calc, IsSeparable<Calc>::value>::template eval<NCHUNK>(calc, prop, D, lane, stageAll + (size_t)warpInBlock * D);
+    const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
+    const bool accepted = dr.logOneMinusU < diff;
+
+    if (accepted) {
+#pragma unroll
+        for (int c = 0; c < NCHUNK; ++c) {
+            const int d = 64 * c + 2 * lane;
+            if (VEC) {
+                if (d < D) *reinterpret_cast<double2*>(ownRow + d) = prop[c];
+            } else {
+                if (d < D) ownRow[d] = prop[c].x;
+                if (d + 1 < D) ownRow[d + 1] = prop[c].y;
+            }
+        }
+    }
+    if (a.chain_row) {
+        double* chainRow = a.chain_row + (size_t)w * D;
+#pragma unroll
+        for (int c = 0; c < NCHUNK; ++c) {
+            const int d = 64 * c + 2 * lane;
+            const double2 v = accepted ? prop[c] : cur[c];
+            if (VEC) {
+                if (d < D) *reinterpret_cast<double2*>(chainRow + d) = v;
+            } else {
+                if (d < D) chainRow[d] = v.x;
+                if (d + 1 < D) chainRow[d + 1] = v.y;
+            }
+        }
+    }
+    if (lane == 0) {
+        storeRng(a, w, rng);
+        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+        if (accepted) {
+            a.logp[w] = newp;
+            atomicAdd(a.accept_slots + blockIdx.x, 1ULL);
+        }
+        if (TRACE) {
+            if (slot < a.trace_rows) {
+                mcmcpp_trace t;
+                t.j = dr.j; t.accept = accepted ? 1 : 0; t.z = dr.z; t.e = dr.logOneMinusU; t.newp = newp; t.diff = diff;
+                a.trace[slot] = t;
+            }
+        }
+    }
+}
+
+/* ---- launchers ---------------------------------------------------------------------------------- */
+inline int launchStatus()
+{
+    return cudaGetLastError() == cudaSuccess ? MCMCPP_OK : MCMCPP_ERR_CUDA;
+}
+
+template <class Calc, int D>
+int launchThreadKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream)
+{
+    const int grid = (a.slot_count + ThreadKernelThreads - 1) / ThreadKernelThreads;
+    if (grid > a.max_grid) return MCMCPP_ERR_ARG;
+    if (a.trace) stretchHalfStepThread<Calc, D, true><<<grid, ThreadKernelThreads, 0, stream>>>(a, calc);
+    else stretchHalfStepThread<Calc, D, false><<<grid, ThreadKernelThreads, 0, stream>>>(a, calc);
+    return launchStatus();
+}
+
+template <class Calc, int NCHUNK>
+int launchWarpKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream)
+{
+    const int warpsPerBlock = WarpKernelThreads / 32;
+    const int grid = (a.slot_count + warpsPerBlock - 1) / warpsPerBlock;
+    if (grid > a.max_grid) return MCMCPP_ERR_ARG;
+    const size_t smem = IsSeparable<Calc>::value ? 0 : sizeof(double) * (size_t)a.D * warpsPerBlock;
+    const bool vec = (a.D % 2) == 0;
+#define MCMCPP_LAUNCH_WARP(V, T)                                                                             \
+    do {                                                                                                     \
+        if (smem > 48 * 1024)                                                                                \
+            cudaFuncSetAttribute(stretchHalfStepWarp<Calc, NCHUNK, V, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        stretchHalfStepWarp<Calc, NCHUNK, V, T><<<grid, WarpKernelThreads, smem, stream>>>(a, calc);         \
+    } while (0)
+    if (vec) { if (a.trace) MCMCPP_LAUNCH_WARP(true, true); else MCMCPP_LAUNCH_WARP(true, false); }
+    else     { if (a.trace) MCMCPP_LAUNCH_WARP(false, true); else MCMCPP_LAUNCH_WARP(false, false); }
+#undef MCMCPP_LAUNCH_WARP
+    return launchStatus();
+}
+
+/* FixedD > 0 restricts the thread kernel to one dimension (2-D test targets); 0 = any D. */
+template <class Calc, int FixedD = 0>
+struct HalfStepLauncher
+{
+    static int launch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)
+    {
+        const mcmcpp_halfstep_args& a = *args;
+        const Calc& calc = *static_cast<const Calc*>(calculator);
+        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
+        if (a.slot_count <= 0) return MCMCPP_OK;
+        if constexpr (FixedD > 0) {
+            if (a.D != FixedD) return MCMCPP_ERR_ARG;
+            return launchThreadKernel<Calc, FixedD>(a, calc, stream);
+        } else {
+            switch (a.D) {
+            case 1: return launchThreadKernel<Calc, 1>(a, calc, stream);
+            case 2: return launchThreadKernel<Calc, 2>(a, calc, stream);
+            case 3: return launchThreadKernel<Calc, 3>(a, calc, stream);
+            case 4: return launchThreadKernel<Calc, 4>(a, calc, stream);
+            case 5: return launchThreadKernel<Calc, 5>(a, calc, stream);
+            case 6: return launchThreadKernel<Calc, 6>(a, calc, stream);
+            case 7: return launchThreadKernel<Calc, 7>(a, calc, stream);
+            case 8: return launchThreadKernel<Calc, 8>(a, calc, stream);
+            default: break;
+            }
+            const int chunks = (a.D + 63) / 64;
+            if (chunks <= 1) return launchWarpKernel<Calc, 1>(a, calc, stream);
+            if (chunks <= 2) return launchWarpKernel<Calc, 2>(a, calc, stream);
+            if (chunks <= 4) return launchWarpKernel<Calc, 4>(a, calc, stream);
+            if (chunks <= 8) return launchWarpKernel<Calc, 8>(a, calc, stream);
+            if (chunks <= 16) return launchWarpKernel<Calc, 16>(a, calc, stream);
+            return MCMCPP_ERR_UNSUPPORTED;   /* D > 1024: not built yet */
+        }
+    }
+};
+
+}
+}
+#endif

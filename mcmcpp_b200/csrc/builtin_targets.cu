@@ -1,0 +1,66 @@
+/*
+ * mcmcpp_b200/csrc/builtin_targets.cu -- half-step launchers for the built-in Calculators
+ * (BASELINE.json configs; include/mcmcpp_b200/targets.h).  Each is an instantiation of the same
+ * templates a user's CUDA translation unit instantiates for its own Calculator
+ * (MCMC::Device::HalfStepLauncher<Calc>, include/mcmcpp_b200/stretch_kernels.cuh).
+ */
+#include <cstring>
+#include "builtin_targets.h"
+#include "mcmcpp_b200/stretch_kernels.cuh"
+#include "mcmcpp_b200/targets.h"
+
+namespace
+{
+template <class Calc>
+void storeCalc(const Calc& c, std::vector<char>* blob)
+{
+    blob->resize(sizeof(Calc));
+    std::memcpy(blob->data(), &c, sizeof(Calc));
+}
+}
+
+int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t nValues, const double* devParams,
+                        mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux)
+{
+    using namespace MCMC::Targets;
+    (void)W;
+    *aux = nullptr;
+    switch (kind) {
+    case MCMCPP_TARGET_SKEWED_GAUSS_2D: {
+        if (D != 2 || nValues != 1) return MCMCPP_ERR_ARG;
+        storeCalc(SkewedGaussianTwoDim<double>(hostParams[0]), calculator);
+        *launcher = &MCMC::Device::HalfStepLauncher<SkewedGaussianTwoDim<double>, 2>::launch;
+        return MCMCPP_OK;
+    }
+    case MCMCPP_TARGET_ROSENBROCK_2D: {
+        if (D != 2) return MCMCPP_ERR_ARG;
+        storeCalc(RosenbrockTwoDim<double>(), calculator);
+        *launcher = &MCMC::Device::HalfStepLauncher<RosenbrockTwoDim<double>, 2>::launch;
+        return MCMCPP_OK;
+    }
+    case MCMCPP_TARGET_DIAG_GAUSS: {
+        if (nValues != (size_t)D) return MCMCPP_ERR_ARG;
+        storeCalc(DiagGaussian<double>(devParams, D), calculator);
+        *launcher = &MCMC::Device::HalfStepLauncher<DiagGaussian<double> >::launch;
+        return MCMCPP_OK;
+    }
+    case MCMCPP_TARGET_DENSE_GAUSS: {
+        if (nValues != (size_t)D * (size_t)D) return MCMCPP_ERR_ARG;
+        storeCalc(DenseGaussian<double>(devParams, D), calculator);
+        *launcher = &MCMC::Device::HalfStepLauncher<DenseGaussian<double> >::launch;
+        return MCMCPP_OK;
+    }
+    case MCMCPP_TARGET_LINREG: {
+        if (nValues < 2) return MCMCPP_ERR_ARG;
+        const long M = (long)hostParams[0];
+        if (M <= 0 || nValues != 2 + (size_t)M * (size_t)D + (size_t)M) return MCMCPP_ERR_ARG;
+        const double* X = devParams + 2;
+        storeCalc(LinearRegression<double>(X, X + (size_t)M * D, M, D, hostParams[1]), calculator);
+        *launcher = &MCMC::Device::HalfStepLauncher<LinearRegression<double> >::launch;
+        return MCMCPP_OK;
+    }
+    default: return MCMCPP_ERR_ARG;
+    }
+}
+
+void mcmcpp_builtin_release(void* aux) { (void)aux; }

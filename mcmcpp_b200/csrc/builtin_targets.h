@@ -1,0 +1,16 @@
+/*
+ * mcmcpp_b200/csrc/builtin_targets.h -- internal: binds a built-in Calculator (include/mcmcpp_b200/targets.h)
+ * to its half-step launcher.  Not part of the C-ABI.
+ */
+#ifndef MCMCPP_B200_BUILTIN_TARGETS_H
+#define MCMCPP_B200_BUILTIN_TARGETS_H
+#include <cstddef>
+#include <vector>
+#include "mcmcpp_b200/capi.h"
+
+/* hostParams/nValues: the caller's parameter vector; devParams: its device copy (viewed by the functor).
+ * Fills *launcher and the by-value calculator blob; *aux receives optional scratch owned by the target. */
+int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t nValues, const double* devParams,
+                        mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux);
+void mcmcpp_builtin_release(void* aux);
+#endif

@@ -1,0 +1,629 @@
+/*
+ * mcmcpp_b200/csrc/runtime.cu -- the non-template runtime behind include/mcmcpp_b200/capi.h.
+ *
+ * Owns what the reference's EnsembleSampler owns (MCMCpp/EnsembleSampler.h:178-195: walkers, chain,
+ * counters, sampling mode) as device buffers, and drives EnsembleSampler::runMCMC / performStep
+ * (EnsembleSampler.h:284-310,341-360) as two kernel launches per ensemble step on one CUDA stream:
+ *   walker state   pos[W][D] walker-major rows + logp[W]               (Walker/Walker.h:142-149)
+ *   rng            one 128-bit pcg64 state per walker, pre-positioned  (Utility/MultiSampler.h:120)
+ *   chain          2-slot device ring of step rows, each streamed to a pinned host array
+ *                  [stored][W][D] on a side stream                      (Chain/Chain.h:93,204-236)
+ *   counters       per-CTA accepted partial sums, reduced on query     (Walker/Walker.h:111-122)
+ * The update kernels themselves are launched through the `launcher` function pointer supplied at
+ * creation: built-in Calculators (builtin_targets.cu) or a user instantiation of
+ * MCMC::Device::HalfStepLauncher<Calc> (include/mcmcpp_b200/stretch_kernels.cuh).
+ */
+#include <cuda_runtime.h>
+#include <nccl.h>
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "mcmcpp_b200/capi.h"
+#include "mcmcpp_b200/device_rng.cuh"
+#include "builtin_targets.h"
+
+using MCMC::Device::U128;
+
+namespace
+{
+
+thread_local std::string g_lastError;
+
+int fail(int code, const std::string& what)
+{
+    g_lastError = what;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                \
+    do {                                                                                              \
+        cudaError_t err__ = (expr);                                                                   \
+        if (err__ != cudaSuccess)                                                                     \
+            return fail(MCMCPP_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(err__));      \
+    } while (0)
+
+#define NCCL_TRY(expr)                                                                                \
+    do {                                                                                              \
+        ncclResult_t err__ = (expr);                                                                  \
+        if (err__ != ncclSuccess)                                                                     \
+            return fail(MCMCPP_ERR_NCCL, std::string(#expr) + ": " + ncclGetErrorString(err__));      \
+    } while (0)
+
+enum { ChainSlots = 2 };
+
+/* every walker's pcg64 state at its first draw */
+__global__ void initRngKernel(uint64_t* rngState, int W, int K, uint64_t seed, int rngMode)
+{
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= W) return;
+    MCMC::Device::Pcg64 g;
+    if (rngMode == MCMCPP_RNG_PER_WALKER) {
+        g = MCMC::Device::pcg64Seed(seed, (uint64_t)w);
+    } else {
+        /* sequential order inside step 0: red slots 0..K-1 then black slots 0..K-1, 3 draws each;
+         * walker index w = h*K + i is exactly that order (EnsembleSampler.h:345-354) */
+        g = MCMC::Device::pcg64Seed(seed, 0);
+        MCMC::Device::Affine128 m = MCMC::Device::pcg64AdvanceMap(g.inc, 3ULL * (uint64_t)w, 0);
+        g.state = MCMC::Device::applyAffine(m, g.state);
+    }
+    reinterpret_cast<ulonglong2*>(rngState)[w] = make_ulonglong2(g.state.lo, g.state.hi);
+}
+
+__global__ void sumSlotsKernel(const unsigned long long* slots, int n, unsigned long long* out)
+{
+    __shared__ unsigned long long partial[256];
+    unsigned long long s = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += slots[i];
+    partial[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if (threadIdx.x < off) partial[threadIdx.x] += partial[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = partial[0];
+}
+
+}  // namespace
+
+struct mcmcpp_sampler
+{
+    mcmcpp_config cfg;
+    int W = 0, D = 0, K = 0;
+    int slotBegin = 0, slotCount = 0;      /* owned slots of each colour */
+    mcmcpp_halfstep_fn launcher = nullptr;
+    std::vector<char> calculator;
+    double* dParams = nullptr;             /* built-in target parameters */
+    void* builtinAux = nullptr;            /* built-in target scratch (dense kernels) */
+
+    cudaStream_t stream = nullptr, copyStream = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    cudaEvent_t slotReady[ChainSlots] = {nullptr, nullptr}, slotFree[ChainSlots] = {nullptr, nullptr};
+    bool slotBusy[ChainSlots] = {false, false};
+
+    double* dPos = nullptr;
+    double* dLogp = nullptr;
+    uint64_t* dRng = nullptr;
+    unsigned long long* dAcceptSlots = nullptr;
+    unsigned long long* dAcceptSum = nullptr;
+    int32_t* dFlags = nullptr;
+    mcmcpp_trace* dTrace = nullptr;
+    double* dChain[ChainSlots] = {nullptr, nullptr};
+    int maxGrid = 0;
+
+    double* hChain = nullptr;              /* pinned [capacityRows][W][D] */
+    long long hChainRows = 0;              /* allocated rows */
+    long long capRows = 0;                 /* byte cap in rows (0 = chain off) */
+    long long stored = 0;                  /* storedSteps (EnsembleSampler.h:190) */
+
+    bool subSampling = false;
+    int interval = 1;
+    bool initialised = false;
+    unsigned long long acceptedBase = 0;   /* initial placement counts as accepted (Walker.h:162-170) */
+    unsigned long long totalSteps = 0;     /* per-walker totals summed over owned walkers */
+    long long ensembleSteps = 0;           /* ensemble steps since set_initial (trace indexing) */
+    unsigned long long launches = 0;
+
+    mcmcpp_halfstep_args base;             /* constant part of the launch arguments */
+
+    ncclComm_t comm = nullptr;
+    int32_t* dBarrier = nullptr;
+    std::vector<void*> peerOpened;
+    const double** dPeerPos = nullptr;
+};
+
+namespace
+{
+
+size_t rowDoubles(const mcmcpp_sampler* s) { return (size_t)s->W * (size_t)s->D; }
+
+int ensureHostChain(mcmcpp_sampler* s, long long rowsNeeded)
+{
+    if (s->capRows == 0) return MCMCPP_OK;
+    rowsNeeded = std::min(rowsNeeded, s->capRows);
+    if (rowsNeeded <= s->hChainRows) return MCMCPP_OK;
+    long long newRows = std::min(s->capRows, std::max(rowsNeeded, s->hChainRows * 2));
+    double* fresh = nullptr;
+    CUDA_TRY(cudaMallocHost(&fresh, sizeof(double) * rowDoubles(s) * (size_t)newRows));
+    if (s->hChain) {
+        std::memcpy(fresh, s->hChain, sizeof(double) * rowDoubles(s) * (size_t)std::min(s->stored, s->hChainRows));
+        cudaFreeHost(s->hChain);
+    }
+    s->hChain = fresh;
+    s->hChainRows = newRows;
+    return MCMCPP_OK;
+}
+
+int ensureDeviceChain(mcmcpp_sampler* s)
+{
+    if (s->capRows == 0 || s->dChain[0]) return MCMCPP_OK;
+    for (int i = 0; i < ChainSlots; ++i) {
+        CUDA_TRY(cudaMalloc(&s->dChain[i], sizeof(double) * rowDoubles(s)));
+        /* rows of walkers this rank does not own stay zero so the host layer can sum shards */
+        CUDA_TRY(cudaMemsetAsync(s->dChain[i], 0, sizeof(double) * rowDoubles(s), s->stream));
+    }
+    return MCMCPP_OK;
+}
+
+/* one colour: kernel launch (+ the exchange that makes the updated half visible to every rank) */
+int halfStep(mcmcpp_sampler* s, int half, double* chainRow)
+{
+    mcmcpp_halfstep_args a = s->base;
+    a.half = half;
+    a.chain_row = chainRow;
+    a.trace = nullptr;
+    a.trace_rows = 0;
+    if (s->dTrace) {
+        long long first = s->ensembleSteps * (long long)s->W + (long long)half * s->K;
+        long long rows = (long long)s->cfg.trace_updates - first;
+        if (rows > 0) {
+            a.trace = s->dTrace + first;
+            a.trace_rows = (int32_t)std::min<long long>(rows, s->K);
+        }
+    }
+    int rc = s->launcher(&a, s->calculator.data(), s->stream);
+    if (rc != MCMCPP_OK) return fail(rc, std::string("half-step launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+    ++s->launches;
+    if (s->cfg.world > 1) {
+        if (s->cfg.shard_mode == MCMCPP_SHARD_ALLGATHER) {
+            /* in-place all-gather of the colour just updated: contiguous rows [half*K, half*K+K) */
+            double* halfBase = s->dPos + (size_t)half * s->K * s->D;
+            NCCL_TRY(ncclAllGather(halfBase + (size_t)s->slotBegin * s->D, halfBase, (size_t)s->slotCount * s->D,
+                                   ncclDouble, s->comm, s->stream));
+        } else if (s->cfg.shard_mode == MCMCPP_SHARD_PEER) {
+            /* stream-ordered rendezvous: nobody starts the other colour before everyone finished this one */
+            NCCL_TRY(ncclAllReduce(s->dBarrier, s->dBarrier, 1, ncclInt32, ncclSum, s->comm, s->stream));
+        }
+    }
+    return MCMCPP_OK;
+}
+
+int appendRowFromDeviceSlot(mcmcpp_sampler* s, int slot)
+{
+    /* side stream: wait for the black half-step, copy the row to its place in the pinned host chain */
+    CUDA_TRY(cudaEventRecord(s->slotReady[slot], s->stream));
+    CUDA_TRY(cudaStreamWaitEvent(s->copyStream, s->slotReady[slot], 0));
+    CUDA_TRY(cudaMemcpyAsync(s->hChain + rowDoubles(s) * (size_t)s->stored, s->dChain[slot], sizeof(double) * rowDoubles(s),
+                             cudaMemcpyDeviceToHost, s->copyStream));
+    CUDA_TRY(cudaEventRecord(s->slotFree[slot], s->copyStream));
+    s->slotBusy[slot] = true;
+    return MCMCPP_OK;
+}
+
+int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
+{
+    if (!cfg || !out) return fail(MCMCPP_ERR_ARG, "null argument");
+    const int W = cfg->num_walkers, D = cfg->num_params;
+    /* the reference's ctor asserts (EnsembleSampler.h:207-208) */
+    if (W <= 0 || D <= 0 || (W % 2) != 0 || W <= 2 * D) return fail(MCMCPP_ERR_ARG, "numWalkers must be even and exceed 2*numParams");
+    if (cfg->alpha_num <= 0 || cfg->alpha_denom <= 0) return fail(MCMCPP_ERR_ARG, "alpha must be positive");
+    if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world) return fail(MCMCPP_ERR_ARG, "bad rank/world");
+    if ((W / 2) % cfg->world != 0) return fail(MCMCPP_ERR_ARG, "walkers per colour must divide evenly over the GPUs");
+    if (cfg->world > 1 && cfg->shard_mode == MCMCPP_SHARD_NONE) return fail(MCMCPP_ERR_ARG, "world > 1 needs a shard mode");
+
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        return fail(MCMCPP_ERR_CUDA, "no CUDA device: mcmcpp_b200 has no CPU fallback");
+    if (cfg->device < 0 || cfg->device >= count) return fail(MCMCPP_ERR_ARG, "bad device ordinal");
+    CUDA_TRY(cudaSetDevice(cfg->device));
+
+    mcmcpp_sampler* s = new mcmcpp_sampler();
+    s->cfg = *cfg;
+    s->W = W; s->D = D; s->K = W / 2;
+    s->slotCount = s->K / cfg->world;
+    s->slotBegin = cfg->rank * s->slotCount;
+    s->capRows = (long long)(cfg->max_chain_bytes / (sizeof(double) * (unsigned long long)W * (unsigned long long)D));
+    *out = s;   /* destroy() cleans up on later failure */
+
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->copyStream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreate(&s->evStart));
+    CUDA_TRY(cudaEventCreate(&s->evStop));
+    for (int i = 0; i < ChainSlots; ++i) {
+        CUDA_TRY(cudaEventCreateWithFlags(&s->slotReady[i], cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->slotFree[i], cudaEventDisableTiming));
+    }
+    s->maxGrid = s->K;   /* upper bound for any launcher: one CTA per walker */
+    CUDA_TRY(cudaMalloc(&s->dPos, sizeof(double) * rowDoubles(s)));
+    CUDA_TRY(cudaMalloc(&s->dLogp, sizeof(double) * (size_t)W));
+    CUDA_TRY(cudaMalloc(&s->dRng, sizeof(uint64_t) * 2 * (size_t)W));
+    CUDA_TRY(cudaMalloc(&s->dAcceptSlots, sizeof(unsigned long long) * (size_t)s->maxGrid));
+    CUDA_TRY(cudaMalloc(&s->dAcceptSum, sizeof(unsigned long long)));
+    CUDA_TRY(cudaMalloc(&s->dFlags, sizeof(int32_t) * 4));
+    CUDA_TRY(cudaMalloc(&s->dBarrier, sizeof(int32_t)));
+    CUDA_TRY(cudaMemset(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid));
+    CUDA_TRY(cudaMemset(s->dFlags, 0, sizeof(int32_t) * 4));
+    CUDA_TRY(cudaMemset(s->dBarrier, 0, sizeof(int32_t)));
+    CUDA_TRY(cudaMemset(s->dPos, 0, sizeof(double) * rowDoubles(s)));
+    if (cfg->trace_updates > 0) {
+        CUDA_TRY(cudaMalloc(&s->dTrace, sizeof(mcmcpp_trace) * (size_t)cfg->trace_updates));
+        CUDA_TRY(cudaMemset(s->dTrace, 0, sizeof(mcmcpp_trace) * (size_t)cfg->trace_updates));
+    }
+
+    /* constant launch arguments */
+    mcmcpp_halfstep_args& a = s->base;
+    std::memset(&a, 0, sizeof a);
+    a.pos = s->dPos; a.logp = s->dLogp; a.rng_state = s->dRng;
+    a.accept_slots = s->dAcceptSlots; a.flags = s->dFlags;
+    a.W = W; a.D = D; a.K = s->K;
+    a.slot_begin = s->slotBegin; a.slot_count = s->slotCount; a.slots_per_rank = s->slotCount;
+    a.rng_mode = cfg->rng_mode;
+    const uint64_t K64 = (uint64_t)s->K;
+    a.bound_threshold = (0ULL - K64) % K64;                                    /* pcg_extras.hpp:517 */
+    a.bound_recip = (K64 == 1) ? ~0ULL : (uint64_t)((((unsigned __int128)1) << 64) / K64);
+    U128 inc; inc.lo = 1; inc.hi = 0;                                          /* stream 0 */
+    MCMC::Device::Affine128 skip = MCMC::Device::pcg64AdvanceMap(inc, 3ULL * (uint64_t)W - 3ULL, 0);
+    a.skip_mult[0] = skip.mult.lo; a.skip_mult[1] = skip.mult.hi;
+    a.skip_plus[0] = skip.plus.lo; a.skip_plus[1] = skip.plus.hi;
+    MCMC::Device::GwConstants gw = MCMC::Device::makeGwConstants(cfg->alpha_num, cfg->alpha_denom);
+    a.gw_term1 = gw.term1; a.gw_inv_sqrt_alpha = gw.invSqrtAlpha;
+    a.max_grid = s->maxGrid;
+    return MCMCPP_OK;
+}
+
+int afterInitialState(mcmcpp_sampler* s, const double* hostRowOrNull)
+{
+    /* rng positioned for step 0; counters as after Walker::setFirstPoint (Walker.h:76,162-170) */
+    initRngKernel<<<(s->W + 255) / 256, 256, 0, s->stream>>>(s->dRng, s->W, s->K, (uint64_t)s->cfg.seed, s->cfg.rng_mode);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemsetAsync(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid, s->stream));
+    CUDA_TRY(cudaMemsetAsync(s->dFlags, 0, sizeof(int32_t) * 4, s->stream));
+    const unsigned long long owned = 2ULL * (unsigned long long)s->slotCount;
+    s->acceptedBase += owned;
+    s->totalSteps += owned;
+    s->ensembleSteps = 0;
+    /* chain row for the initial placement + incrementChainStep (EnsembleSampler.h:228-229) */
+    if (s->capRows > 0 && s->stored < s->capRows) {
+        int rc = ensureHostChain(s, s->stored + 1);
+        if (rc != MCMCPP_OK) return rc;
+        double* dst = s->hChain + rowDoubles(s) * (size_t)s->stored;
+        if (hostRowOrNull) std::memcpy(dst, hostRowOrNull, sizeof(double) * rowDoubles(s));
+        else CUDA_TRY(cudaMemcpyAsync(dst, s->dPos, sizeof(double) * rowDoubles(s), cudaMemcpyDeviceToHost, s->stream));
+    }
+    ++s->stored;
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->initialised = true;
+    return MCMCPP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* mcmcpp_last_error(void) { return g_lastError.c_str(); }
+
+int mcmcpp_device_count(void)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
+    return count;
+}
+
+int mcmcpp_sampler_create(const mcmcpp_config* cfg, mcmcpp_halfstep_fn launcher, const void* calculator, size_t calc_bytes,
+                          mcmcpp_sampler** out)
+{
+    if (!launcher || (!calculator && calc_bytes)) return fail(MCMCPP_ERR_ARG, "null launcher/calculator");
+    int rc = createCommon(cfg, out);
+    if (rc != MCMCPP_OK) { if (out && *out) { mcmcpp_sampler_destroy(*out); *out = nullptr; } return rc; }
+    (*out)->launcher = launcher;
+    (*out)->calculator.assign((const char*)calculator, (const char*)calculator + calc_bytes);
+    if ((*out)->calculator.empty()) (*out)->calculator.resize(1);
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, const double* params, size_t num_params_values,
+                                  mcmcpp_sampler** out)
+{
+    int rc = createCommon(cfg, out);
+    if (rc != MCMCPP_OK) { if (out && *out) { mcmcpp_sampler_destroy(*out); *out = nullptr; } return rc; }
+    mcmcpp_sampler* s = *out;
+    if (num_params_values) {
+        if (!params) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(MCMCPP_ERR_ARG, "null params"); }
+        cudaError_t e = cudaMalloc(&s->dParams, sizeof(double) * num_params_values);
+        if (e == cudaSuccess) e = cudaMemcpy(s->dParams, params, sizeof(double) * num_params_values, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(MCMCPP_ERR_CUDA, cudaGetErrorString(e)); }
+    }
+    rc = mcmcpp_builtin_bind(target_kind, s->W, s->D, params, num_params_values, s->dParams, &s->launcher, &s->calculator,
+                             &s->builtinAux);
+    if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "unknown built-in target or bad parameter count"); }
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
+{
+    if (!s) return MCMCPP_OK;
+    cudaSetDevice(s->cfg.device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->copyStream) cudaStreamSynchronize(s->copyStream);
+    if (s->comm) ncclCommDestroy(s->comm);
+    for (void* p : s->peerOpened) cudaIpcCloseMemHandle(p);
+    cudaFree(s->dPeerPos);
+    cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
+    cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
+    mcmcpp_builtin_release(s->builtinAux);
+    for (int i = 0; i < ChainSlots; ++i) {
+        cudaFree(s->dChain[i]);
+        if (s->slotReady[i]) cudaEventDestroy(s->slotReady[i]);
+        if (s->slotFree[i]) cudaEventDestroy(s->slotFree[i]);
+    }
+    if (s->hChain) cudaFreeHost(s->hChain);
+    if (s->evStart) cudaEventDestroy(s->evStart);
+    if (s->evStop) cudaEventDestroy(s->evStop);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    if (s->copyStream) cudaStreamDestroy(s->copyStream);
+    delete s;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_set_initial(mcmcpp_sampler* s, const double* positions_host, const double* aux_host)
+{
+    if (!s || !positions_host || !aux_host) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    CUDA_TRY(cudaMemcpyAsync(s->dPos, positions_host, sizeof(double) * rowDoubles(s), cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->dLogp, aux_host, sizeof(double) * (size_t)s->W, cudaMemcpyHostToDevice, s->stream));
+    return afterInitialState(s, positions_host);
+}
+
+int mcmcpp_sampler_set_initial_device(mcmcpp_sampler* s, const double* positions_dev, const double* aux_dev)
+{
+    if (!s || !positions_dev || !aux_dev) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    CUDA_TRY(cudaMemcpyAsync(s->dPos, positions_dev, sizeof(double) * rowDoubles(s), cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->dLogp, aux_dev, sizeof(double) * (size_t)s->W, cudaMemcpyDeviceToDevice, s->stream));
+    return afterInitialState(s, nullptr);
+}
+
+int mcmcpp_sampler_set_slicing(mcmcpp_sampler* s, int use_slicing, int interval)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (interval <= 0) return fail(MCMCPP_ERR_ARG, "slicing interval must be positive");   /* EnsembleSampler.h:327 */
+    s->subSampling = use_slicing != 0;
+    s->interval = interval;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (!s->initialised) return fail(MCMCPP_ERR_STATE, "runMCMC before setInitialWalkerPos");
+    if (num_steps <= 0) return fail(MCMCPP_ERR_ARG, "numSteps must be positive");           /* RedBlkCtrlerSpinLock.h:188 */
+    if (s->cfg.world > 1 && !s->comm) return fail(MCMCPP_ERR_STATE, "world > 1 but no communicator (mcmcpp_sampler_comm_init)");
+    if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_PEER && !s->dPeerPos)
+        return fail(MCMCPP_ERR_STATE, "PEER sharding needs mcmcpp_sampler_peer_import");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    const bool chainOn = s->capRows > 0;
+    int rc = MCMCPP_OK;
+    if (chainOn) {
+        if ((rc = ensureHostChain(s, s->stored + num_steps)) != MCMCPP_OK) return rc;
+        if ((rc = ensureDeviceChain(s)) != MCMCPP_OK) return rc;
+    }
+    const int perStored = s->subSampling ? s->interval : 1;
+    int status = MCMCPP_OK;
+    CUDA_TRY(cudaEventRecord(s->evStart, s->stream));
+    for (int i = 0; i < num_steps; ++i) {
+        /* the interval-1 unsaved steps come first (EnsembleSampler.h:300-303) */
+        for (int j = 1; j < perStored; ++j) {
+            if ((rc = halfStep(s, 0, nullptr)) != MCMCPP_OK) return rc;
+            if ((rc = halfStep(s, 1, nullptr)) != MCMCPP_OK) return rc;
+            ++s->ensembleSteps;
+        }
+        const bool keepRow = chainOn && s->stored < s->capRows;
+        const int slot = (int)(s->stored % ChainSlots);
+        if (keepRow && s->slotBusy[slot]) {
+            CUDA_TRY(cudaStreamWaitEvent(s->stream, s->slotFree[slot], 0));
+            s->slotBusy[slot] = false;
+        }
+        double* row = keepRow ? s->dChain[slot] : nullptr;
+        if ((rc = halfStep(s, 0, row)) != MCMCPP_OK) return rc;
+        if ((rc = halfStep(s, 1, row)) != MCMCPP_OK) return rc;
+        ++s->ensembleSteps;
+        if (keepRow && (rc = appendRowFromDeviceSlot(s, slot)) != MCMCPP_OK) return rc;
+        ++s->stored;
+        s->totalSteps += 2ULL * (unsigned long long)s->slotCount * (unsigned long long)perStored;
+        if (chainOn && s->stored >= s->capRows) {   /* incrementChainStep() == EndOfChain (Chain.h:229-233) */
+            status = MCMCPP_CHAIN_FULL;
+            break;
+        }
+    }
+    CUDA_TRY(cudaEventRecord(s->evStop, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->copyStream));
+    if (device_ms) CUDA_TRY(cudaEventElapsedTime(device_ms, s->evStart, s->evStop));
+    return status;
+}
+
+int mcmcpp_sampler_get_counts(mcmcpp_sampler* s, unsigned long long* accepted, unsigned long long* total)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    sumSlotsKernel<<<1, 256, 0, s->stream>>>(s->dAcceptSlots, s->maxGrid, s->dAcceptSum);
+    CUDA_TRY(cudaGetLastError());
+    unsigned long long sum = 0;
+    CUDA_TRY(cudaMemcpyAsync(&sum, s->dAcceptSum, sizeof sum, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (accepted) *accepted = s->acceptedBase + sum;
+    if (total) *total = s->totalSteps;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_get_stored_steps(mcmcpp_sampler* s) { return s ? (int)s->stored : 0; }
+
+int mcmcpp_sampler_reset(mcmcpp_sampler* s)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    /* storedSteps = 0, chain reset, walker counters zeroed; positions kept (EnsembleSampler.h:312-322) */
+    s->stored = 0;
+    s->acceptedBase = 0;
+    s->totalSteps = 0;
+    CUDA_TRY(cudaMemsetAsync(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_store_current(mcmcpp_sampler* s)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (!s->initialised) return fail(MCMCPP_ERR_STATE, "no walker positions yet");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    if (s->capRows > 0 && s->stored < s->capRows) {
+        int rc = ensureHostChain(s, s->stored + 1);
+        if (rc != MCMCPP_OK) return rc;
+        CUDA_TRY(cudaMemcpyAsync(s->hChain + rowDoubles(s) * (size_t)s->stored, s->dPos, sizeof(double) * rowDoubles(s),
+                                 cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    }
+    ++s->stored;    /* EnsembleSampler.h:240-241 */
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_slice_and_burn(mcmcpp_sampler* s, int interval, int burn_in)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (interval <= 0 || burn_in < 0) return fail(MCMCPP_ERR_ARG, "interval must be > 0 and burnIn >= 0");  /* EnsembleSampler.h:335-336 */
+    /* Chain::resetChainForSubSampling (Chain/Chain.h:268-305) on the contiguous host rows */
+    const long long steps = std::min(s->stored, s->hChainRows > 0 ? s->hChainRows : s->stored);
+    if (burn_in == 0 && interval == 1) return MCMCPP_OK;
+    if ((steps - burn_in) < interval || steps <= burn_in) { s->stored = 0; return MCMCPP_OK; }
+    long long kept = 0;
+    const size_t row = rowDoubles(s);
+    for (long long r = burn_in; r < steps; r += interval, ++kept) {
+        if (s->hChain && r != kept) std::memmove(s->hChain + row * (size_t)kept, s->hChain + row * (size_t)r, sizeof(double) * row);
+    }
+    s->stored = kept;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_chain(mcmcpp_sampler* s, const double** rows_host, long long* stored_steps)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (rows_host) *rows_host = s->hChain;
+    if (stored_steps) *stored_steps = s->capRows > 0 ? std::min(s->stored, s->capRows) : 0;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_get_state(mcmcpp_sampler* s, double* positions_host, double* aux_host)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    if (positions_host)
+        CUDA_TRY(cudaMemcpyAsync(positions_host, s->dPos, sizeof(double) * rowDoubles(s), cudaMemcpyDeviceToHost, s->stream));
+    if (aux_host) CUDA_TRY(cudaMemcpyAsync(aux_host, s->dLogp, sizeof(double) * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_state_device(mcmcpp_sampler* s, double** positions_dev, double** aux_dev)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (positions_dev) *positions_dev = s->dPos;
+    if (aux_dev) *aux_dev = s->dLogp;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_get_trace(mcmcpp_sampler* s, mcmcpp_trace* out, int max_rows, int* rows)
+{
+    if (!s || !out) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    long long have = std::min<long long>(s->cfg.trace_updates, s->ensembleSteps * (long long)s->W);
+    int n = (int)std::min<long long>(have, max_rows);
+    if (n > 0) {
+        CUDA_TRY(cudaMemcpyAsync(out, s->dTrace, sizeof(mcmcpp_trace) * (size_t)n, cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    }
+    if (rows) *rows = n;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_rng_redraws(mcmcpp_sampler* s, int* redraws)
+{
+    if (!s || !redraws) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    CUDA_TRY(cudaMemcpyAsync(redraws, s->dFlags, sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_launch_count(mcmcpp_sampler* s, unsigned long long* kernel_launches)
+{
+    if (!s || !kernel_launches) return fail(MCMCPP_ERR_ARG, "null argument");
+    *kernel_launches = s->launches;
+    return MCMCPP_OK;
+}
+
+void* mcmcpp_sampler_stream(mcmcpp_sampler* s) { return s ? (void*)s->stream : nullptr; }
+
+/* ---- multi-GPU ---------------------------------------------------------------------------------- */
+int mcmcpp_comm_unique_id(void* id128)
+{
+    if (!id128) return fail(MCMCPP_ERR_ARG, "null id");
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    NCCL_TRY(ncclGetUniqueId(&id));
+    std::memcpy(id128, &id, sizeof id);
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128)
+{
+    if (!s || !id128) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    ncclUniqueId id;
+    std::memcpy(&id, id128, sizeof id);
+    NCCL_TRY(ncclCommInitRank(&s->comm, s->cfg.world, id, s->cfg.rank));
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_peer_export(mcmcpp_sampler* s, void* handle64)
+{
+    if (!s || !handle64) return fail(MCMCPP_ERR_ARG, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, s->dPos));
+    std::memcpy(handle64, &h, sizeof h);
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_ranks)
+{
+    if (!s || !handles64_all_ranks) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    std::vector<const double*> ptrs((size_t)s->cfg.world, nullptr);
+    for (int r = 0; r < s->cfg.world; ++r) {
+        if (r == s->cfg.rank) { ptrs[(size_t)r] = s->dPos; continue; }
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, (const char*)handles64_all_ranks + 64 * (size_t)r, sizeof h);
+        void* p = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        s->peerOpened.push_back(p);
+        ptrs[(size_t)r] = (const double*)p;
+    }
+    CUDA_TRY(cudaMalloc(&s->dPeerPos, sizeof(double*) * (size_t)s->cfg.world));
+    CUDA_TRY(cudaMemcpy(s->dPeerPos, ptrs.data(), sizeof(double*) * (size_t)s->cfg.world, cudaMemcpyHostToDevice));
+    s->base.peer_pos = s->dPeerPos;
+    return MCMCPP_OK;
+}
+
+}  /* extern "C" */
