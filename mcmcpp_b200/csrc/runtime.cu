@@ -14,7 +14,8 @@
  * MCMC::Device::HalfStepLauncher<Calc> (include/mcmcpp_b200/stretch_kernels.cuh).
  */
 #include <cuda_runtime.h>
-#include <nccl.h>
+#include <nccl.h>      /* types only: the library is bound at run time (see NcclApi) */
+#include <dlfcn.h>
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
@@ -44,11 +45,46 @@ int fail(int code, const std::string& what)
             return fail(MCMCPP_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(err__));      \
     } while (0)
 
+/*
+ * NCCL is bound with dlopen/dlsym the first time a communicator is needed, preferring a libnccl.so.2 that
+ * is already in the process (a Python host that imported torch has torch's own NCCL loaded; linking a second
+ * copy at load time would clash with it).  Single-GPU use never touches NCCL.
+ */
+struct NcclApi
+{
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+
+NcclApi& nccl()
+{
+    static NcclApi api;
+    if (api.ok) return api;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+    if (!h) return api;
+    *(void**)&api.GetUniqueId = dlsym(h, "ncclGetUniqueId");
+    *(void**)&api.CommInitRank = dlsym(h, "ncclCommInitRank");
+    *(void**)&api.CommDestroy = dlsym(h, "ncclCommDestroy");
+    *(void**)&api.AllGather = dlsym(h, "ncclAllGather");
+    *(void**)&api.AllReduce = dlsym(h, "ncclAllReduce");
+    *(void**)&api.GetErrorString = dlsym(h, "ncclGetErrorString");
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.AllReduce && api.GetErrorString;
+    return api;
+}
+
 #define NCCL_TRY(expr)                                                                                \
     do {                                                                                              \
+        if (!nccl().ok) return fail(MCMCPP_ERR_NCCL, "libnccl.so.2 could not be loaded");             \
         ncclResult_t err__ = (expr);                                                                  \
         if (err__ != ncclSuccess)                                                                     \
-            return fail(MCMCPP_ERR_NCCL, std::string(#expr) + ": " + ncclGetErrorString(err__));      \
+            return fail(MCMCPP_ERR_NCCL, std::string(#expr) + ": " + nccl().GetErrorString(err__));   \
     } while (0)
 
 enum { ChainSlots = 2 };
@@ -189,11 +225,11 @@ int halfStep(mcmcpp_sampler* s, int half, double* chainRow)
         if (s->cfg.shard_mode == MCMCPP_SHARD_ALLGATHER) {
             /* in-place all-gather of the colour just updated: contiguous rows [half*K, half*K+K) */
             double* halfBase = s->dPos + (size_t)half * s->K * s->D;
-            NCCL_TRY(ncclAllGather(halfBase + (size_t)s->slotBegin * s->D, halfBase, (size_t)s->slotCount * s->D,
+            NCCL_TRY(nccl().AllGather(halfBase + (size_t)s->slotBegin * s->D, halfBase, (size_t)s->slotCount * s->D,
                                    ncclDouble, s->comm, s->stream));
         } else if (s->cfg.shard_mode == MCMCPP_SHARD_PEER) {
             /* stream-ordered rendezvous: nobody starts the other colour before everyone finished this one */
-            NCCL_TRY(ncclAllReduce(s->dBarrier, s->dBarrier, 1, ncclInt32, ncclSum, s->comm, s->stream));
+            NCCL_TRY(nccl().AllReduce(s->dBarrier, s->dBarrier, 1, ncclInt32, ncclSum, s->comm, s->stream));
         }
     }
     return MCMCPP_OK;
@@ -356,7 +392,7 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     cudaSetDevice(s->cfg.device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->copyStream) cudaStreamSynchronize(s->copyStream);
-    if (s->comm) ncclCommDestroy(s->comm);
+    if (s->comm && nccl().ok) nccl().CommDestroy(s->comm);
     for (void* p : s->peerOpened) cudaIpcCloseMemHandle(p);
     cudaFree(s->dPeerPos);
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
@@ -580,7 +616,7 @@ int mcmcpp_comm_unique_id(void* id128)
     if (!id128) return fail(MCMCPP_ERR_ARG, "null id");
     static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
     ncclUniqueId id;
-    NCCL_TRY(ncclGetUniqueId(&id));
+    NCCL_TRY(nccl().GetUniqueId(&id));
     std::memcpy(id128, &id, sizeof id);
     return MCMCPP_OK;
 }
@@ -591,7 +627,7 @@ int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128)
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     ncclUniqueId id;
     std::memcpy(&id, id128, sizeof id);
-    NCCL_TRY(ncclCommInitRank(&s->comm, s->cfg.world, id, s->cfg.rank));
+    NCCL_TRY(nccl().CommInitRank(&s->comm, s->cfg.world, id, s->cfg.rank));
     return MCMCPP_OK;
 }
 

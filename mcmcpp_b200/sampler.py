@@ -1,0 +1,260 @@
+"""Python mirror of the reference's sampler front-ends for the ensemble-update hot path.
+
+Same names, argument meaning and error behaviour as
+  MCMC::EnsembleSampler           (MCMCpp/EnsembleSampler.h:39-197)
+  MCMC::ParallelEnsembleSampler   (MCMCpp/ParallelEnsembleSampler.h:78-226)
+  MCMC::Mover::StretchMove        (MCMCpp/Movers/StretchMove.h:40-131)
+so the parity tests read like the reference's own test programs
+(test/sequential/SkewedGaussian/StretchMove/src/main.cpp:22-80).  Everything below the method
+names is a call into the C-ABI (include/mcmcpp_b200/capi.h); nothing here computes on the CPU.
+The C++ drop-in with the same names is include/mcmcpp_b200/EnsembleSampler.h.
+"""
+import ctypes as C
+import numpy as np
+
+from . import _capi
+from ._capi import check
+
+
+# ---- Calculators (include/mcmcpp_b200/targets.h); params layout of the C-ABI built-ins ---------
+class _Calculator:
+    kind = None
+
+    def params(self):
+        return np.zeros(0)
+
+
+class SkewedGaussianTwoDim(_Calculator):
+    """test/sequential/SkewedGaussian/Common/SkewedGaussian.h:52-57"""
+    kind = "skewed_gauss_2d"
+
+    def __init__(self, eps):
+        self.eps = float(eps)
+
+    def params(self):
+        return np.array([self.eps])
+
+
+class RosenbrockTwoDim(_Calculator):
+    kind = "rosenbrock_2d"
+
+
+class DiagGaussian(_Calculator):
+    kind = "diag_gauss"
+
+    def __init__(self, inv_var):
+        self.iv = np.ascontiguousarray(inv_var, dtype=np.float64)
+
+    def params(self):
+        return self.iv
+
+
+class DenseGaussian(_Calculator):
+    kind = "dense_gauss"
+
+    def __init__(self, precision):
+        self.P = np.ascontiguousarray(precision, dtype=np.float64)
+
+    def params(self):
+        return self.P.reshape(-1)
+
+
+class LinearRegression(_Calculator):
+    kind = "linreg"
+
+    def __init__(self, X, y, prior_var):
+        self.X = np.ascontiguousarray(X, dtype=np.float64)
+        self.y = np.ascontiguousarray(y, dtype=np.float64)
+        self.prior_var = float(prior_var)
+
+    def params(self):
+        M = self.X.shape[0]
+        return np.concatenate([[float(M), self.prior_var], self.X.reshape(-1), self.y])
+
+
+class StretchMove:
+    """MCMC::Mover::StretchMove<ParamType, Calculator, GwDistribution<ParamType, alphaNum, alphaDenom>>.
+    As in the reference (StretchMove.h:74-78, EnsembleSampler.h:217) `prngInit` is not what seeds the
+    run: the sampler re-seeds its copy of the mover with (randSeed, stream)."""
+
+    def __init__(self, numParams, prngInit, calc, alphaNum=2, alphaDenom=1):
+        self.numParams = int(numParams)
+        self.prngInit = int(prngInit)
+        self.calc = calc
+        self.alpha = (int(alphaNum), int(alphaDenom))
+
+
+class EnsembleSampler:
+    """MCMC::EnsembleSampler<double, StretchMove<...>> on one B200 (or one shard of an ensemble
+    spread over `world` GPUs, one process per GPU).
+
+    Extra keyword arguments have no counterpart in the reference and default to its behaviour:
+      rngMode      "sequential" (bit parity with the reference's single stream) | "per_walker"
+      traceUpdates record the first n updates' (j, accept, z, e, newp, diff) for tests
+      device/rank/world/shardMode  multi-GPU placement (see capi.h)
+    """
+
+    def __init__(self, randSeed, numWalker, numParameter, move, maxChainSizeBytes=2147483648, stepAct=None,
+                 rngMode="sequential", traceUpdates=0, device=0, rank=0, world=1, shardMode="none"):
+        if not isinstance(move, StretchMove):
+            raise TypeError("the B200 path implements Mover::StretchMove only")
+        if move.numParams != numParameter:
+            raise ValueError("mover and sampler disagree on numParams")
+        self._lib = _capi.lib()
+        self.numWalkers, self.numParams = int(numWalker), int(numParameter)
+        self.stepAction = stepAct
+        self.rank, self.world = int(rank), int(world)
+        cfg = _capi.Config(
+            num_walkers=self.numWalkers, num_params=self.numParams, seed=int(randSeed),
+            rng_mode={"sequential": _capi.RNG_SEQUENTIAL, "per_walker": _capi.RNG_PER_WALKER}[rngMode],
+            alpha_num=move.alpha[0], alpha_denom=move.alpha[1], device=int(device), rank=self.rank, world=self.world,
+            shard_mode={"none": _capi.SHARD_NONE, "allgather": _capi.SHARD_ALLGATHER, "peer": _capi.SHARD_PEER}[shardMode],
+            trace_updates=int(traceUpdates), max_chain_bytes=int(maxChainSizeBytes))
+        self.shardMode = shardMode
+        params = np.ascontiguousarray(move.calc.params(), dtype=np.float64)
+        self._h = C.c_void_p()
+        # the reference asserts on bad walker counts (EnsembleSampler.h:207-208); here: ERR_ARG -> exception
+        check(self._lib.mcmcpp_sampler_create_builtin(C.byref(cfg), _capi.TARGET[move.calc.kind],
+                                                      params.ctypes.data_as(C.POINTER(C.c_double)), params.size,
+                                                      C.byref(self._h)))
+        self.lastDeviceMs = 0.0
+
+    # -- life cycle --------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.mcmcpp_sampler_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- EnsembleSampler.h:220-230 -----------------------------------------------------------
+    def setInitialWalkerPos(self, positions, auxValues):
+        pos = np.ascontiguousarray(positions, dtype=np.float64).reshape(self.numWalkers, self.numParams)
+        aux = np.ascontiguousarray(auxValues, dtype=np.float64).reshape(self.numWalkers)
+        check(self._lib.mcmcpp_sampler_set_initial(self._h, pos.ctypes.data, aux.ctypes.data))
+
+    def setInitialWalkerPosDevice(self, positionsPtr, auxPtr):
+        """Device-resident inputs (raw device pointers, e.g. torch tensor .data_ptr())."""
+        check(self._lib.mcmcpp_sampler_set_initial_device(self._h, positionsPtr, auxPtr))
+
+    def setInitialWalkerPosPinned(self, positionsPtr, auxPtr):
+        """Host inputs given as raw pointers (e.g. pinned torch tensors)."""
+        check(self._lib.mcmcpp_sampler_set_initial(self._h, positionsPtr, auxPtr))
+
+    # -- EnsembleSampler.h:232-242, 312-322 --------------------------------------------------
+    def storeCurrentWalkerPositions(self):
+        check(self._lib.mcmcpp_sampler_store_current(self._h))
+
+    def reset(self):
+        check(self._lib.mcmcpp_sampler_reset(self._h))
+
+    # -- EnsembleSampler.h:284-310 ------------------------------------------------------------
+    def runMCMC(self, numSteps):
+        """True if the sampling went to the end before the max chain size was reached."""
+        ms = C.c_float(0.0)
+        rc = check(self._lib.mcmcpp_sampler_run(self._h, int(numSteps), C.byref(ms)))
+        self.lastDeviceMs = float(ms.value)
+        if self.stepAction is not None:
+            # end-of-call hook (the per-step hook of EnsembleSampler.h:356-359 stays on the host)
+            self.stepAction.performAction(self.getChain())
+        return rc != _capi.CHAIN_FULL
+
+    # -- EnsembleSampler.h:244-282 ------------------------------------------------------------
+    def _counts(self):
+        a, t = C.c_ulonglong(), C.c_ulonglong()
+        check(self._lib.mcmcpp_sampler_get_counts(self._h, C.byref(a), C.byref(t)))
+        return a.value, t.value
+
+    def getAcceptedSteps(self):
+        return self._counts()[0]
+
+    def getTotalSteps(self):
+        return self._counts()[1]
+
+    def getAcceptanceFraction(self):
+        a, t = self._counts()
+        return float(a) / float(t)
+
+    # -- EnsembleSampler.h:324-339, 150 --------------------------------------------------------
+    def setSlicingMode(self, useSlicing=False, slicingInterval=1):
+        check(self._lib.mcmcpp_sampler_set_slicing(self._h, int(bool(useSlicing)), int(slicingInterval)))
+
+    def sliceAndBurnChain(self, slicingInterval, burnIn):
+        check(self._lib.mcmcpp_sampler_slice_and_burn(self._h, int(slicingInterval), int(burnIn)))
+
+    def getStoredSteps(self):
+        return self._lib.mcmcpp_sampler_get_stored_steps(self._h)
+
+    # -- read side: what ChainStepIterator / ChainPsetIterator walk (ChainStepIterator.h:125) --
+    def getChain(self):
+        """[stored][W][D] view of the pinned host chain (valid until reset/slice/run/close)."""
+        rows, n = C.POINTER(C.c_double)(), C.c_longlong()
+        check(self._lib.mcmcpp_sampler_chain(self._h, C.byref(rows), C.byref(n)))
+        if n.value == 0 or not rows:
+            return np.zeros((0, self.numWalkers, self.numParams))
+        return np.ctypeslib.as_array(rows, shape=(n.value, self.numWalkers, self.numParams))
+
+    def getStepIttBegin(self):
+        return iter(self.getChain())
+
+    def getParamSetIttBegin(self):
+        return iter(self.getChain().reshape(-1, self.numParams))
+
+    # -- walker state (Walker::getCurrState / getCurrAuxData) ---------------------------------
+    def getWalkerState(self):
+        pos = np.empty((self.numWalkers, self.numParams))
+        aux = np.empty(self.numWalkers)
+        check(self._lib.mcmcpp_sampler_get_state(self._h, pos.ctypes.data, aux.ctypes.data))
+        return pos, aux
+
+    # -- diagnostics -----------------------------------------------------------------------------
+    def getTrace(self, maxRows):
+        buf = (_capi.Trace * int(maxRows))()
+        n = C.c_int()
+        check(self._lib.mcmcpp_sampler_get_trace(self._h, buf, int(maxRows), C.byref(n)))
+        dt = np.dtype([("j", "<i4"), ("accept", "<i4"), ("z", "<f8"), ("e", "<f8"), ("newp", "<f8"), ("diff", "<f8")])
+        return np.frombuffer(buf, dtype=dt, count=n.value).copy()
+
+    def getRngRedraws(self):
+        n = C.c_int()
+        check(self._lib.mcmcpp_sampler_rng_redraws(self._h, C.byref(n)))
+        return n.value
+
+    def getLaunchCount(self):
+        n = C.c_ulonglong()
+        check(self._lib.mcmcpp_sampler_launch_count(self._h, C.byref(n)))
+        return n.value
+
+    # -- multi-GPU plumbing (torch.distributed carries the handles; see parallel.py) -------------
+    def commInit(self, uniqueId):
+        check(self._lib.mcmcpp_sampler_comm_init(self._h, uniqueId))
+
+    def peerExport(self):
+        buf = C.create_string_buffer(64)
+        check(self._lib.mcmcpp_sampler_peer_export(self._h, buf))
+        return buf.raw
+
+    def peerImport(self, handles):
+        check(self._lib.mcmcpp_sampler_peer_import(self._h, b"".join(handles)))
+
+
+class ParallelEnsembleSampler(EnsembleSampler):
+    """MCMC::ParallelEnsembleSampler (ParallelEnsembleSampler.h:119-120): same surface plus a
+    thread count.  On the GPU every walker of a colour is updated concurrently, so `threadCount`
+    only selects the RNG discipline: 1 -> the sequential stream (the reference is bit-identical to
+    the sequential sampler with one thread), >1 -> one stream per walker (the reference is
+    non-deterministic there, ParallelEnsembleSampler.h:71-76)."""
+
+    def __init__(self, randSeed, threadCount, numWalker, numParameter, move, maxChainSizeBytes=2147483648, stepAct=None,
+                 **kw):
+        kw.setdefault("rngMode", "sequential" if int(threadCount) <= 1 else "per_walker")
+        super().__init__(randSeed, numWalker, numParameter, move, maxChainSizeBytes, stepAct, **kw)
+        self.threadCount = int(threadCount)
+
+    def setSamplingMode(self, useSubSampling=False, subSamplingInt=1, burnIn=0):
+        # sequential-sampler subsampling semantics (the parallel controller's own are broken)
+        self.setSlicingMode(useSubSampling, subSamplingInt)

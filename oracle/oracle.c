@@ -291,3 +291,61 @@ int oracle_stretch_run(pcg64_t* g, int kind, const double* tparams, int W, int D
     free(prop);
     return rejections;
 }
+
+/*
+ * PER_WALKER rng discipline: walker w owns pcg64(seed, stream = w), i.e. one reference mover per
+ * walker re-seeded with setPrng(seed, w) (Movers/StretchMove.h:90, the per-thread streams of
+ * Threading/RedBlkUpdater.h:86 taken to one walker per stream).  Same update arithmetic and the
+ * same red-then-black order as oracle_stretch_run; rng [W] carries every walker's engine.
+ */
+void oracle_pcg64_seed_many(pcg64_t* g, uint64_t seed, int W)
+{
+    for (int w = 0; w < W; ++w) oracle_pcg64_seed(&g[w], seed, (uint64_t)w);
+}
+
+int oracle_stretch_run_per_walker(pcg64_t* rng, int kind, const double* tparams, int W, int D,
+                                  int alpha_num, int alpha_denom,
+                                  double* pos, double* logp, int64_t* acc, int64_t* tot,
+                                  int nsteps, int interval, double* chain, oracle_trace_t* trace)
+{
+    const int K = W / 2;
+    double term1, isa;
+    oracle_gw_constants(alpha_num, alpha_denom, &term1, &isa);
+    double* prop = (double*)malloc(sizeof(double) * (size_t)D);
+    int rejections = 0;
+    size_t tr = 0;
+    for (int s = 0; s < nsteps; ++s) {
+        for (int sub = 0; sub < interval; ++sub) {
+            int store = (sub == interval - 1);
+            for (int h = 0; h < 2; ++h) {
+                const int own0 = h * K, oth0 = (1 - h) * K;
+                for (int i = 0; i < K; ++i) {
+                    const int w = own0 + i;
+                    pcg64_t* g = &rng[w];
+                    int j = (int)oracle_pcg64_bounded(g, (uint64_t)K, &rejections);
+                    const double* sel = pos + (size_t)(oth0 + j) * D;
+                    double* cur = pos + (size_t)w * D;
+                    double z = oracle_gw_sample(oracle_u64_to_unit(oracle_pcg64_next(g)), term1, isa);
+                    for (int d = 0; d < D; ++d) prop[d] = sel[d] + z * (cur[d] - sel[d]);
+                    double scaling = log(z) * (double)(D - 1);
+                    double newp = oracle_logp(kind, D, tparams, prop);
+                    double diff = scaling + newp - logp[w];
+                    double e = oracle_neg_exponential(oracle_u64_to_unit(oracle_pcg64_next(g)));
+                    int a = (e < diff);
+                    if (a) { memcpy(cur, prop, sizeof(double) * (size_t)D); logp[w] = newp; ++acc[w]; }
+                    ++tot[w];
+                    if (trace) { oracle_trace_t* t = &trace[tr++]; t->j = j; t->accept = a; t->z = z; t->e = e; t->newp = newp; t->diff = diff; }
+                    if (store && chain) memcpy(chain + ((size_t)s * W + w) * D, cur, sizeof(double) * (size_t)D);
+                }
+            }
+        }
+    }
+    free(prop);
+    return rejections;
+}
+
+/* batched log posterior (tests + timing helpers) */
+void oracle_logp_many(int kind, int D, const double* params, const double* x, long n, double* out)
+{
+    for (long i = 0; i < n; ++i) out[i] = oracle_logp(kind, D, params, x + (size_t)i * D);
+}

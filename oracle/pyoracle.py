@@ -66,6 +66,11 @@ class Port:
         L.oracle_stretch_run.argtypes = [C.c_void_p, C.c_int, c_dp, C.c_int, C.c_int, C.c_int, C.c_int,
                                          c_dp, c_dp, C.c_void_p, C.c_void_p, C.c_int, C.c_int, c_dp, C.c_void_p]
 
+        L.oracle_stretch_run_per_walker.restype = C.c_int
+        L.oracle_stretch_run_per_walker.argtypes = L.oracle_stretch_run.argtypes
+        L.oracle_pcg64_seed_many.argtypes = [C.c_void_p, c_u64, C.c_int]
+        L.oracle_logp_many.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_long, c_dp]
+
     # --- rng -----------------------------------------------------------
     def pcg64(self, seed, stream):
         g = Pcg64()
@@ -101,27 +106,35 @@ class Port:
     # --- targets ---------------------------------------------------------
     def logp(self, kind, params, x):
         x = np.ascontiguousarray(x, dtype=np.float64)
-        params = np.ascontiguousarray(params, dtype=np.float64)
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
         D = x.shape[-1]
-        flat = x.reshape(-1, D)
-        out = np.array([self.lib.oracle_logp(KIND[kind], D, _dp(params), _dp(flat[i])) for i in range(flat.shape[0])])
+        flat = np.ascontiguousarray(x.reshape(-1, D))
+        out = np.empty(flat.shape[0])
+        self.lib.oracle_logp_many(KIND[kind], D, _dp(params), _dp(flat), flat.shape[0], _dp(out))
         return out.reshape(x.shape[:-1])
 
     # --- hot path ----------------------------------------------------------
     def run(self, kind, params, pos, logp, nsteps, interval=1, seed=0, stream=0, alpha=(2, 1),
-            want_chain=True, want_trace=False, rng=None, acc=None, tot=None):
+            want_chain=True, want_trace=False, rng=None, acc=None, tot=None, per_walker=False):
         """Sequential-order stretch-move run.  pos [W,D] and logp [W] are NOT modified;
         returns dict(pos, logp, acc, tot, chain[(nsteps),W,D], trace, rejections, rng)."""
         pos = np.array(pos, dtype=np.float64, order="C")
         logp = np.array(logp, dtype=np.float64)
         W, D = pos.shape
         params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
-        g = rng if rng is not None else self.pcg64(seed, stream)
+        if per_walker:
+            g = rng
+            if g is None:
+                g = (Pcg64 * W)()
+                self.lib.oracle_pcg64_seed_many(g, seed & (2**64 - 1), W)
+        else:
+            g = rng if rng is not None else self.pcg64(seed, stream)
         acc = np.ones(W, np.int64) if acc is None else np.array(acc, np.int64)
         tot = np.ones(W, np.int64) if tot is None else np.array(tot, np.int64)
         chain = np.empty((nsteps, W, D)) if want_chain else None
         trace = np.zeros(nsteps * interval * W, dtype=TRACE_DTYPE) if want_trace else None
-        rej = self.lib.oracle_stretch_run(C.byref(g), KIND[kind], _dp(params), W, D, alpha[0], alpha[1],
+        fn = self.lib.oracle_stretch_run_per_walker if per_walker else self.lib.oracle_stretch_run
+        rej = fn(C.byref(g), KIND[kind], _dp(params), W, D, alpha[0], alpha[1],
                                           _dp(pos), _dp(logp), acc.ctypes.data, tot.ctypes.data, nsteps, interval,
                                           _dp(chain), trace.ctypes.data if want_trace else None)
         return dict(pos=pos, logp=logp, acc=acc, tot=tot, chain=chain, trace=trace, rejections=rej, rng=g)

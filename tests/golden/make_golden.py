@@ -1,0 +1,61 @@
+"""Regenerates tests/golden/*.npz by running the UNMODIFIED reference (oracle/_ref, built from
+/root/reference by oracle/Makefile).  Run in the build container only:  python tests/golden/make_golden.py
+Every fixture holds the inputs (init positions/logp, target params) and the reference outputs
+(chain rows, ensemble accepted/total), so tests need neither /root/reference nor oracle/_ref."""
+import os
+import sys
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle.pyoracle import Ref, build  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def corr_precision(D, rho=0.9):
+    idx = np.arange(D)
+    cov = rho ** np.abs(idx[:, None] - idx[None, :])
+    return np.linalg.inv(cov)
+
+
+def main():
+    build()
+    R = Ref()
+    out = {}
+
+    def case(name, kind, params, W, D, nsteps, interval=1, seed=0, init_seed=53, scale=1.0, keep_rows=None):
+        init = (R.init_normal(init_seed, W * D) * scale).reshape(W, D)
+        params = np.asarray(params if params is not None else [0.0], dtype=np.float64)
+        lp = R.logp(kind, params, init)
+        r = R.run(kind, params, init, lp, nsteps, interval=interval, seed=seed)
+        chain = r["chain"]            # (nsteps+1, W, D), row 0 = initial positions
+        rows = np.arange(chain.shape[0]) if keep_rows is None else np.asarray(keep_rows)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), kind=kind, params=params, W=W, D=D, nsteps=nsteps,
+                            interval=interval, seed=seed, init=init, logp=lp, rows=rows, chain=chain[rows],
+                            acc=r["acc"], tot=r["tot"], stored=r["stored"])
+        out[name] = (r["acc"], r["tot"])
+
+    # C1: the survey KAT (BASELINE config 1): acc 228883/320032, walker 0 of the last row pinned
+    case("c1_skewed_w32", "skewed_gauss_2d", [0.13], 32, 2, 10000, keep_rows=[0, 1, 2, 100, 5000, 9999, 10000])
+    # the reference test's walker count, with slicing (test/sequential/SkewedGaussian/StretchMove/src/main.cpp:22-41)
+    case("skewed_w320_slice3", "skewed_gauss_2d", [0.13], 320, 2, 200, interval=3, keep_rows=[0, 1, 50, 200])
+    case("rosenbrock_w512", "rosenbrock_2d", None, 512, 2, 100, keep_rows=[0, 1, 100])
+    iv = 1.0 / (1.0 + (np.arange(100) % 10))
+    case("diag_d100_w256", "diag_gauss", iv, 256, 100, 20, keep_rows=[0, 1, 20])
+    iv37 = 1.0 / (1.0 + (np.arange(37) % 10))
+    case("diag_d37_w128", "diag_gauss", iv37, 128, 37, 20, keep_rows=[0, 1, 20])
+    iv5 = 1.0 / (1.0 + (np.arange(5) % 10))
+    case("diag_d5_w64", "diag_gauss", iv5, 64, 5, 50, keep_rows=[0, 1, 50])
+    case("dense_d12_w64", "dense_gauss", corr_precision(12).reshape(-1), 64, 12, 30, keep_rows=[0, 1, 30])
+    rng = np.random.default_rng(1234)
+    M, P = 40, 3
+    X = rng.standard_normal((M, P)); th = rng.standard_normal(P); y = X @ th + rng.standard_normal(M)
+    lin = np.concatenate([[float(M), 100.0], X.reshape(-1), y])
+    case("linreg_p3_w16", "linreg", lin, 16, 3, 50, scale=0.3, keep_rows=[0, 1, 50])
+    for k, v in out.items():
+        print(k, v)
+
+
+if __name__ == "__main__":
+    main()
