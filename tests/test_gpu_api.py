@@ -1,0 +1,115 @@
+"""GPU tests of the sampler surface the reference's call sites use (EnsembleSampler.h:89-176):
+chain cap / runMCMC's bool, reset, storeCurrentWalkerPositions, sliceAndBurnChain, argument checks,
+and full-size runs of the BASELINE shapes checked through size-independent properties."""
+import numpy as np
+import pytest
+from conftest import load_golden
+from test_gpu_parity import make_sampler, seeded_init
+
+pytestmark = pytest.mark.gpu
+
+
+def test_argument_checks_mirror_the_reference_asserts():
+    from mcmcpp_b200._capi import McmcppError, ERR_ARG
+    for W, D in ((31, 2), (4, 2), (6, 3)):          # odd; W <= 2D (EnsembleSampler.h:207-208)
+        with pytest.raises(McmcppError) as ei:
+            make_sampler("diag_gauss", np.ones(D), W, D)
+        assert ei.value.code == ERR_ARG
+    s = make_sampler("skewed_gauss_2d", [0.13], 32, 2)
+    with pytest.raises(McmcppError):
+        s.runMCMC(5)                                   # before setInitialWalkerPos
+    with pytest.raises(McmcppError):
+        s.setSlicingMode(True, 0)                      # EnsembleSampler.h:327
+    with pytest.raises(McmcppError):
+        s.sliceAndBurnChain(0, 0)                      # EnsembleSampler.h:335
+    s.close()
+
+
+def test_chain_cap_returns_false_like_runMCMC(port):
+    g = load_golden("c1_skewed_w32")
+    rows = 11
+    s = make_sampler(g["kind"], g["params"], g["W"], g["D"], maxChainSizeBytes=rows * g["W"] * g["D"] * 8)
+    s.setInitialWalkerPos(g["init"], g["logp"])
+    assert s.runMCMC(5) is True
+    assert s.runMCMC(50) is False                      # cap reached (EnsembleSampler.h:293)
+    assert s.getStoredSteps() == rows and s.getChain().shape[0] == rows
+    o = port.run(g["kind"], g["params"], g["init"], g["logp"], rows - 1)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    s.close()
+
+
+def test_reset_store_current_and_counters(port):
+    g = load_golden("c1_skewed_w32")
+    W = g["W"]
+    s = make_sampler(g["kind"], g["params"], W, g["D"])
+    s.setInitialWalkerPos(g["init"], g["logp"])
+    assert s.getAcceptedSteps() == W and s.getTotalSteps() == W        # Walker.h:162-170
+    s.runMCMC(40)
+    o = port.run(g["kind"], g["params"], g["init"], g["logp"], 40)
+    s.reset()                                                           # EnsembleSampler.h:312-322
+    assert s.getStoredSteps() == 0 and s.getTotalSteps() == 0 and s.getAcceptedSteps() == 0
+    s.storeCurrentWalkerPositions()                                     # EnsembleSampler.h:232-242
+    assert s.getStoredSteps() == 1 and np.array_equal(s.getChain()[0], o["pos"])
+    s.runMCMC(10)
+    o2 = port.run(g["kind"], g["params"], o["pos"], o["logp"], 10, rng=o["rng"], acc=np.zeros(W), tot=np.zeros(W))
+    assert np.array_equal(s.getChain()[1:], o2["chain"])
+    assert (s.getAcceptedSteps(), s.getTotalSteps()) == (int(o2["acc"].sum()), 10 * W)
+    s.close()
+
+
+@pytest.mark.parametrize("interval,burn", [(1, 0), (3, 5), (7, 0), (1, 20), (50, 10), (2, 59), (5, 80)])
+def test_slice_and_burn_matches_chain_reset_semantics(interval, burn):
+    g = load_golden("c1_skewed_w32")
+    s = make_sampler(g["kind"], g["params"], g["W"], g["D"])
+    s.setInitialWalkerPos(g["init"], g["logp"])
+    s.runMCMC(59)
+    full = s.getChain().copy()
+    n = full.shape[0]
+    s.sliceAndBurnChain(interval, burn)
+    if burn == 0 and interval == 1:
+        expect = full
+    elif (n - burn) < interval or n <= burn:           # Chain.h:272-273 -> resetChain
+        expect = full[:0]
+    else:
+        expect = full[burn::interval]
+    assert s.getStoredSteps() == expect.shape[0]
+    assert np.array_equal(s.getChain(), expect)
+    s.close()
+
+
+def test_c2_full_size_rosenbrock_million_walkers(port):
+    """BASELINE config 2 at full size: 2^20 walkers; the oracle finishes 3 steps in seconds."""
+    W, D = 1 << 20, 2
+    init, lp = seeded_init(port, "rosenbrock_2d", None, W, D, 2)
+    s = make_sampler("rosenbrock_2d", [], W, D, maxChainSizeBytes=0)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(3)
+    o = port.run("rosenbrock_2d", None, init, lp, 3, want_chain=False)
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum()) and s.getTotalSteps() == 4 * W
+    assert s.getChain().shape[0] == 0                  # chain off
+    s.close()
+
+
+def test_c4_shape_properties_at_65536_walkers(port):
+    """BASELINE config 4 row shape (D=1000) at a size the oracle checks directly, plus properties that hold
+    at any size: logp[w] == logp(pos[w]); a rejected walker's row is untouched; counters add up."""
+    W, D = 1 << 16, 1000
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    rng = np.random.default_rng(4)
+    init = rng.standard_normal((W, D))
+    lp = port.logp("diag_gauss", iv, init)
+    s = make_sampler("diag_gauss", iv, W, D, maxChainSizeBytes=0, traceUpdates=W)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(1)
+    pos, aux = s.getWalkerState()
+    o = port.run("diag_gauss", iv, init, lp, 1, want_chain=False, want_trace=True)
+    assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+    tr = s.getTrace(W)
+    assert np.array_equal(tr["accept"], o["trace"]["accept"]) and np.array_equal(tr["j"], o["trace"]["j"])
+    rejected = tr["accept"] == 0
+    assert np.array_equal(pos[rejected], init[rejected])
+    assert np.array_equal(aux, port.logp("diag_gauss", iv, pos))
+    assert s.getAcceptedSteps() == W + int(tr["accept"].sum()) and s.getTotalSteps() == 2 * W
+    s.close()

@@ -1,0 +1,160 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the Python mirror -> C-ABI, against the
+CPU oracle (oracle/oracle.c, pinned by tests/test_oracle_cpu.py) and the golden fixtures made from
+the unmodified reference.  Bar: bit-exact positions, log-probs, partner indices and accept bits
+(tier A); log(1-u) and the Metropolis difference within 4 ulp (device log vs glibc
+log differ in the last bit on a few inputs; neither enters the stored state)."""
+import numpy as np
+import pytest
+from conftest import load_golden, golden_names
+
+pytestmark = pytest.mark.gpu
+
+CALC = {
+    "skewed_gauss_2d": lambda m, p, D: m.SkewedGaussianTwoDim(p[0]),
+    "rosenbrock_2d": lambda m, p, D: m.RosenbrockTwoDim(),
+    "diag_gauss": lambda m, p, D: m.DiagGaussian(p),
+    "dense_gauss": lambda m, p, D: m.DenseGaussian(p.reshape(D, D)),
+    "linreg": lambda m, p, D: m.LinearRegression(p[2:2 + int(p[0]) * D].reshape(int(p[0]), D), p[2 + int(p[0]) * D:], p[1]),
+}
+
+
+def make_sampler(kind, params, W, D, seed=0, **kw):
+    import mcmcpp_b200 as m
+    calc = CALC[kind](m, np.asarray(params, dtype=np.float64), D)
+    return m.EnsembleSampler(seed, W, D, m.StretchMove(D, seed, calc), **kw)
+
+
+def ulp_close(a, b, ulps=4):
+    a = np.asarray(a); b = np.asarray(b)
+    return np.all(np.abs(a - b) <= ulps * np.spacing(np.maximum(np.abs(a), np.abs(b))))
+
+
+def assert_trace_equal(dev, ref):
+    assert np.array_equal(dev["j"], ref["j"])
+    assert np.array_equal(dev["accept"], ref["accept"])
+    assert np.array_equal(dev["z"], ref["z"])
+    assert np.array_equal(dev["newp"], ref["newp"])
+    assert ulp_close(dev["e"], ref["e"]) and ulp_close(dev["diff"], ref["diff"], 16)
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_golden_fixtures_bit_exact(name):
+    """Every fixture generated from the unmodified reference: chain rows, counters."""
+    g = load_golden(name)
+    s = make_sampler(g["kind"], g["params"], g["W"], g["D"], seed=g["seed"])
+    if g["interval"] > 1:
+        s.setSlicingMode(True, g["interval"])
+    s.setInitialWalkerPos(g["init"], g["logp"])
+    assert s.runMCMC(g["nsteps"]) is True
+    chain = s.getChain()
+    assert chain.shape == (g["nsteps"] + 1, g["W"], g["D"]) and s.getStoredSteps() == g["stored"]
+    assert np.array_equal(chain[g["rows"]], g["chain"])
+    assert (s.getAcceptedSteps(), s.getTotalSteps()) == (g["acc"], g["tot"])
+    assert s.getRngRedraws() == 0
+    s.close()
+
+
+def test_c1_full_chain_and_trace_against_oracle(port):
+    """BASELINE config 1: W=32, D=2, 10,000 stored steps; the whole chain and the first 64,000 updates."""
+    g = load_golden("c1_skewed_w32")
+    ntr = 64000
+    s = make_sampler(g["kind"], g["params"], g["W"], g["D"], traceUpdates=ntr)
+    s.setInitialWalkerPos(g["init"], g["logp"])
+    assert s.runMCMC(g["nsteps"])
+    o = port.run(g["kind"], g["params"], g["init"], g["logp"], g["nsteps"], want_trace=True)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+    assert s.getAcceptedSteps() == 228883 and s.getTotalSteps() == 320032
+    assert abs(s.getAcceptanceFraction() - 228883 / 320032) < 1e-15
+    assert_trace_equal(s.getTrace(ntr), o["trace"][:ntr])
+    assert [float.hex(v) for v in s.getChain()[-1, 0]] == ["0x1.754c17069f6f6p+0", "0x1.22e26142efda4p+0"]
+    s.close()
+
+
+def seeded_init(port, kind, params, W, D, seed, scale=1.0):
+    rng = np.random.default_rng(seed)
+    init = rng.standard_normal((W, D)) * scale
+    return init, port.logp(kind, params, init)
+
+
+@pytest.mark.parametrize("W,D,steps,interval", [(4096, 2, 60, 1), (1 << 16, 2, 8, 2)])
+def test_rosenbrock_thread_kernel(port, W, D, steps, interval):
+    init, lp = seeded_init(port, "rosenbrock_2d", None, W, D, 11)
+    s = make_sampler("rosenbrock_2d", [], W, D, seed=3, traceUpdates=W * 2)
+    s.setSlicingMode(interval > 1, interval)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run("rosenbrock_2d", None, init, lp, steps, interval=interval, seed=3, want_trace=True)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum()) and s.getTotalSteps() == int(o["tot"].sum())
+    assert_trace_equal(s.getTrace(W * 2), o["trace"][:W * 2])
+    s.close()
+
+
+@pytest.mark.parametrize("W,D,steps", [(64, 3, 20), (64, 8, 20), (256, 9, 10), (256, 64, 10), (256, 65, 10), (128, 127, 6),
+                                       (512, 200, 6), (2048, 500, 3), (4096, 1000, 3), (4096, 1023, 2), (4096, 1024, 2)])
+def test_diag_gauss_every_kernel_shape(port, W, D, steps):
+    """thread kernel (D<=8), warp kernel with 1..16 chunks, odd D (scalar loads) and ragged tails:
+    the separable log-posterior is reduced in the canonical order, so everything is bit-exact."""
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    init, lp = seeded_init(port, "diag_gauss", iv, W, D, 100 + D)
+    s = make_sampler("diag_gauss", iv, W, D, seed=1, traceUpdates=W)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run("diag_gauss", iv, init, lp, steps, seed=1, want_trace=True)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum())
+    assert_trace_equal(s.getTrace(W), o["trace"][:W])
+    s.close()
+
+
+def test_generic_calculator_in_warp_kernel(port):
+    """non-separable Calculator, D > 8: proposal staged in shared memory, evaluated in the reference's order."""
+    D, W = 24, 128
+    idx = np.arange(D)
+    P = np.linalg.inv(0.9 ** np.abs(idx[:, None] - idx[None, :]))
+    init, lp = seeded_init(port, "dense_gauss", P.reshape(-1), W, D, 5)
+    s = make_sampler("dense_gauss", P.reshape(-1), W, D, seed=2)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(15)
+    o = port.run("dense_gauss", P.reshape(-1), init, lp, 15, seed=2)
+    assert np.array_equal(s.getChain()[1:], o["chain"]) and s.getAcceptedSteps() == int(o["acc"].sum())
+    s.close()
+
+
+def test_per_walker_rng_mode(port):
+    W, D = 2048, 2
+    init, lp = seeded_init(port, "skewed_gauss_2d", [0.13], W, D, 21)
+    s = make_sampler("skewed_gauss_2d", [0.13], W, D, seed=77, rngMode="per_walker", traceUpdates=W * 3)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(25)
+    o = port.run("skewed_gauss_2d", [0.13], init, lp, 25, seed=77, per_walker=True, want_trace=True)
+    assert np.array_equal(s.getChain()[1:], o["chain"]) and s.getAcceptedSteps() == int(o["acc"].sum())
+    assert_trace_equal(s.getTrace(W * 3), o["trace"][:W * 3])
+    s.close()
+
+
+def test_alpha_other_than_two(port):
+    import mcmcpp_b200 as m
+    W, D = 512, 2
+    init, lp = seeded_init(port, "skewed_gauss_2d", [0.13], W, D, 8)
+    s = m.EnsembleSampler(4, W, D, m.StretchMove(D, 4, m.SkewedGaussianTwoDim(0.13), alphaNum=3, alphaDenom=2))
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(30)
+    o = port.run("skewed_gauss_2d", [0.13], init, lp, 30, seed=4, alpha=(3, 2))
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    s.close()
+
+
+def test_successive_runs_continue_the_stream(port):
+    g = load_golden("c1_skewed_w32")
+    s = make_sampler(g["kind"], g["params"], g["W"], g["D"])
+    s.setInitialWalkerPos(g["init"], g["logp"])
+    for n in (7, 1, 92):
+        assert s.runMCMC(n)
+    o = port.run(g["kind"], g["params"], g["init"], g["logp"], 100)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    s.close()
