@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py -- walker-updates/s of the ensemble-update hot path on N B200s (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c1] [--shard allgather|peer]
+  python bench.py --impl reference ...       the reference's own CPU implementation on the host cores
+
+A "step" is one ensemble step (EnsembleSampler::performStep, MCMCpp/EnsembleSampler.h:341-360): every one of
+the W walkers is updated once (red half then black half) = W walker-updates.  One JSON line on stdout (rank 0).
+Default workload = BASELINE.json configs[3] ("1000-D Gaussian, 1M walkers"), the configuration north_star
+quotes its target on and the one that is sharded over 1/2/4/8 GPUs; it fits one GPU (8 GB of state).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "walker-updates/sec"
+UNIT = "walker-updates/s"
+
+WORKLOADS = {
+    # name: (description, kind, W, D, cpu sample walkers, cpu sample steps)
+    "c4": ("BASELINE configs[3]: 1000-D diagonal Gaussian, 2^20 walkers, stretch move a=2", "diag_gauss", 1 << 20, 1000, 4096, 40),
+    "c2": ("BASELINE configs[1]: Rosenbrock 2-D banana, 2^20 walkers, stretch move a=2", "rosenbrock_2d", 1 << 20, 2, 65536, 300),
+    "c1": ("BASELINE configs[0]: 2-D skewed Gaussian, 32 walkers", "skewed_gauss_2d", 32, 2, 32, 20000),
+}
+
+
+def target_params(kind, D):
+    if kind == "diag_gauss":
+        return 1.0 / (1.0 + (np.arange(D) % 10))
+    if kind == "skewed_gauss_2d":
+        return np.array([0.13])
+    return np.zeros(0)
+
+
+def algorithmic_bytes_per_update(D, stored):
+    """own row read + partner row read + own row write (+ chain row) + logp read/write."""
+    return 8 * D * (3 + (1 if stored else 0)) + 16
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop, self.thread = index, [], threading.Event(), None
+
+    def _loop(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.thread.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+# ---- CPU arm: the reference's own implementation on the host cores (oracle/ is the checker; this is the one
+# ---- place bench.py executes it, as the thing that is the BASELINE, never as the product) -------------------
+def cpu_reference_run(workload, steps, warmup, seed=0):
+    """Times EnsembleSampler (1 core) and ParallelEnsembleSampler (all host threads) of the unmodified reference
+    (oracle/_ref, compiled from /root/reference by oracle/Makefile) on a bounded sample of the workload; falls
+    back to the plain-C port (kind "port", 1 core) when oracle/_ref is absent."""
+    from oracle.pyoracle import Port, Ref
+    desc, kind, W, D, Wc, _ = WORKLOADS[workload]
+    params = target_params(kind, D)
+    rng = np.random.default_rng(1)
+    init = rng.standard_normal((Wc, D))
+    port = Port()
+    lp = port.logp(kind, params, init)
+    cores = os.cpu_count() or 1
+    updates = float(Wc) * steps
+    if Ref.available(small=True):
+        R = Ref(small=True)
+        if warmup:
+            R.time(kind, params, init, lp, warmup, threads=0, seed=seed)
+        t_seq, _, _ = R.time(kind, params, init, lp, steps, threads=0, seed=seed)
+        t_par, _, _ = R.time(kind, params, init, lp, steps, threads=cores, seed=seed)
+        par_threads = cores
+        if cores > 16:      # spin barriers can lose to fewer threads on many-core hosts: try 16 too, keep the better
+            t16, _, _ = R.time(kind, params, init, lp, steps, threads=16, seed=seed)
+            if t16 < t_par:
+                t_par, par_threads = t16, 16
+        seq, par = updates / t_seq, updates / t_par
+        best, used, secs = (par, par_threads, t_par) if par >= seq else (seq, 1, t_seq)
+        cores = par_threads
+        return {"value": best, "unit": UNIT, "cores": used, "kind": "reference", "seconds": secs,
+                "sample": "%d walkers x %d steps, D=%d (%s); EnsembleSampler 1 core %.4g/s, ParallelEnsembleSampler "
+                          "%d threads %.4g/s; unmodified reference headers, chain BlockSize=%d, -O3 -march=x86-64-v3 "
+                          "-ffp-contract=off" % (Wc, steps, D, kind, seq, cores, par, R.block_size)}
+    t0 = time.perf_counter()
+    port.run(kind, params, init, lp, steps, seed=seed, want_chain=False)
+    secs = time.perf_counter() - t0
+    return {"value": updates / secs, "unit": UNIT, "cores": 1, "kind": "port", "seconds": secs,
+            "sample": "%d walkers x %d steps, D=%d (%s); plain-C port oracle/oracle.c, 1 core" % (Wc, steps, D, kind)}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    desc, kind, W, D, Wc, _ = WORKLOADS[args.workload]
+    r = cpu_reference_run(args.workload, args.steps, args.warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * r["seconds"] / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "walkers": W, "params": D, "cpu_sample_walkers": Wc,
+                       "note": "CPU throughput per update does not depend on W beyond cache effects (SURVEY.md s.8(d))"},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---- GPU arm ------------------------------------------------------------------------------------------------
+def device_inputs(torch, kind, W, D, params, device):
+    """Synthetic initial ensemble created in HBM: x ~ N(0, I), aux = log posterior (the caller's
+    job in the reference API, EnsembleSampler.h:220).  Same seed on every rank -> identical ensembles."""
+    g = torch.Generator(device=device)
+    g.manual_seed(1234)
+    pos = torch.randn((W, D), dtype=torch.float64, device=device, generator=g)
+    aux = torch.empty(W, dtype=torch.float64, device=device)
+    chunk = max(1, (1 << 24) // D)
+    if kind == "diag_gauss":
+        iv = torch.tensor(params, dtype=torch.float64, device=device)
+        for b in range(0, W, chunk):
+            x = pos[b:b + chunk]
+            aux[b:b + chunk] = -0.5 * (x * x * iv).sum(dim=1)
+    elif kind == "rosenbrock_2d":
+        x, y = pos[:, 0], pos[:, 1]
+        aux = -(100.0 * (y - x * x) ** 2 + (1.0 - x) ** 2) / 20.0
+    elif kind == "skewed_gauss_2d":
+        t1, t2 = pos[:, 0] / 2 - pos[:, 1], pos[:, 0] / 2 + pos[:, 1]
+        aux = -((t1 * t1) / float(params[0]) + t2 * t2) / 2.0
+    else:
+        raise ValueError(kind)
+    return pos, aux.contiguous()
+
+
+def make_calc(m, kind, params):
+    return {"diag_gauss": lambda: m.DiagGaussian(params), "rosenbrock_2d": lambda: m.RosenbrockTwoDim(),
+            "skewed_gauss_2d": lambda: m.SkewedGaussianTwoDim(params[0])}[kind]()
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import mcmcpp_b200 as m
+    from mcmcpp_b200 import parallel
+    rank, world, local = parallel.env_rank_world()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    if world != args.gpus and rank == 0:
+        print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
+    desc, kind, W, D, Wc, cpu_steps = WORKLOADS[args.workload]
+    params = target_params(kind, D)
+    shard = "none" if world == 1 else args.shard
+    rng_mode = args.rng
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def new_sampler():
+        s = m.EnsembleSampler(0, W, D, m.StretchMove(D, 0, make_calc(m, kind, params)), maxChainSizeBytes=0,
+                              rngMode=rng_mode, device=local, rank=rank, world=world, shardMode=shard)
+        parallel.connect(s)
+        return s
+
+    pos, aux = device_inputs(torch, kind, W, D, params, device)
+
+    # ---- value: inputs resident in HBM, K steps timed with CUDA events on the sampler's stream ------------
+    s = new_sampler()
+    s.setInitialWalkerPosDevice(pos.data_ptr(), aux.data_ptr())
+    s.runMCMC(max(3, args.warmup))
+    launches0 = s.getLaunchCount()
+    barrier()
+    with ClockSampler(local) as clocks:
+        wall0 = time.perf_counter()
+        s.runMCMC(args.steps)
+        barrier()
+        wall = time.perf_counter() - wall0
+    ms = torch.tensor([s.lastDeviceMs], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    launches = s.getLaunchCount() - launches0
+    accepted, total = parallel.reduce_counts(s)
+    redraws = s.getRngRedraws()
+    s.close()
+    value = float(W) * args.steps / (ms * 1e-3)
+
+    # ---- e2e: the call a user makes, HOST buffers in, HOST buffers out, copies inside the timed region --------
+    host_pos = torch.empty((W, D), dtype=torch.float64, pin_memory=True)
+    host_aux = torch.empty(W, dtype=torch.float64, pin_memory=True)
+    host_pos.copy_(pos)
+    host_aux.copy_(aux)
+    del pos, aux
+    torch.cuda.empty_cache()
+    s = new_sampler()
+    barrier()
+    t0 = time.perf_counter()
+    s.setInitialWalkerPosPinned(host_pos.data_ptr(), host_aux.data_ptr())
+    ok = s.runMCMC(args.steps)
+    s.getWalkerStateInto(host_pos.data_ptr(), host_aux.data_ptr())
+    e2e_acc, e2e_tot = s._counts()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    s.close()
+    state_bytes = W * D * 8 + W * 8
+    e2e = {"value": float(W) * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": state_bytes / args.steps,
+           "d2h_bytes_per_step": (state_bytes + 16) / args.steps, "seconds": e2e_s,
+           "what": "setInitialWalkerPos(pinned host) + runMCMC(%d) + walker state and counters back to pinned host, per rank"
+                   % args.steps}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peaks()
+    per_launch_updates = (W // 2) // world
+    launch_ms = ms / max(1, launches)
+    alg_bytes = per_launch_updates * algorithmic_bytes_per_update(D, False)
+    achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(args.workload)
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "kernel": "stretchHalfStepWarp" if D > 8 else "stretchHalfStepThread", "peak_source": peak_src,
+                "algorithmic_bytes_per_update": algorithmic_bytes_per_update(D, False), "updates_per_launch": per_launch_updates,
+                "launch_ms": launch_ms,
+                "note": "launch_ms = CUDA-event time of the timed region / launches" + ("" if world == 1 else " (includes the per-half-step exchange)")}
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        cpu = cpu_reference_run(args.workload, cpu_steps, 1)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": desc, "walkers": W, "params": D, "rng": rng_mode, "shard": shard, "chain": "off",
+                       "l2": "inputs (%.1f GB of walker rows) far exceed the 126 MB L2; no flush needed" % (W * D * 8 / 1e9)
+                       if W * D * 8 > (1 << 29) else "state fits L2: L2-resident steady state is the workload itself"},
+            "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches) * world, "roofline": roofline,
+            "cpu_baseline": cpu, "wall_s_timed_region": wall,
+            "acceptance": {"accepted": accepted, "total": total, "rng_redraws": redraws, "e2e_ok": bool(ok), "e2e_accepted": e2e_acc}}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--shard", default="allgather", choices=["allgather", "peer"])
+    ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.steps <= 0:
+        raise SystemExit("--steps must be positive")
+    return reference_arm(args) if args.impl == "reference" else gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,71 @@
+"""One ensemble over the GPUs of one box, one process per GPU (torchrun).
+
+torch.distributed is the plumbing only: it carries the 128-byte NCCL id and the 64-byte CUDA IPC
+handles between the ranks; the exchanges themselves (NCCL all-gather of the updated colour, or NVLink
+peer loads inside the update kernel) are issued by the C-ABI runtime on the sampler's own stream.
+Host-side shard arithmetic lives here so it can be tested on CPU with gloo.
+"""
+import ctypes as C
+import os
+
+from . import _capi
+
+
+def shard_slots(num_walkers, rank, world):
+    """Owned slots [begin, end) of each colour for `rank`: contiguous walker-index shards of
+    the K = W/2 walkers per colour (MCMCpp/EnsembleSampler.h:225-226 numbering)."""
+    K = num_walkers // 2
+    if K % world:
+        raise ValueError("walkers per colour (%d) must divide evenly over %d GPUs" % (K, world))
+    n = K // world
+    return rank * n, (rank + 1) * n
+
+
+def owned_walkers(num_walkers, rank, world):
+    """Global walker indices this rank updates (red slice then black slice)."""
+    K = num_walkers // 2
+    b, e = shard_slots(num_walkers, rank, world)
+    return list(range(b, e)) + list(range(K + b, K + e))
+
+
+def sequential_draw_index(step, half, slot, num_walkers):
+    """First (0-based) draw of the sampler's single pcg64 stream used by (step, colour, slot):
+    3 draws per update in red-then-black walker order -- independent of the GPU count."""
+    return 3 * (step * num_walkers + half * (num_walkers // 2) + slot)
+
+
+def env_rank_world():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def connect(sampler, group=None):
+    """Collective over all ranks: give `sampler` (created with rank/world/shardMode) its NCCL
+    communicator and, for PEER sharding, the other ranks' position arrays."""
+    import torch.distributed as dist
+    if sampler.world == 1:
+        return
+    ident = [None]
+    if sampler.rank == 0:
+        buf = C.create_string_buffer(128)
+        _capi.check(_capi.lib().mcmcpp_comm_unique_id(buf))
+        ident[0] = buf.raw
+    dist.broadcast_object_list(ident, src=0, group=group)
+    sampler.commInit(ident[0])
+    if sampler.shardMode == "peer":
+        handles = [None] * sampler.world
+        dist.all_gather_object(handles, sampler.peerExport(), group=group)
+        sampler.peerImport(handles)
+    dist.barrier(group=group)
+
+
+def reduce_counts(sampler, group=None):
+    """Ensemble-wide (accepted, total): the C-ABI returns this rank's owned walkers only."""
+    import torch
+    import torch.distributed as dist
+    a, t = sampler._counts()
+    if sampler.world == 1:
+        return a, t
+    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    v = torch.tensor([a, t], dtype=torch.int64, device=dev)
+    dist.all_reduce(v, group=group)
+    return int(v[0]), int(v[1])

@@ -211,6 +211,10 @@ class EnsembleSampler:
         check(self._lib.mcmcpp_sampler_get_state(self._h, pos.ctypes.data, aux.ctypes.data))
         return pos, aux
 
+    def getWalkerStateInto(self, positionsPtr, auxPtr):
+        """Same, into caller-owned host buffers given as raw pointers (e.g. pinned torch tensors)."""
+        check(self._lib.mcmcpp_sampler_get_state(self._h, positionsPtr, auxPtr))
+
     # -- diagnostics -----------------------------------------------------------------------------
     def getTrace(self, maxRows):
         buf = (_capi.Trace * int(maxRows))()

@@ -34,7 +34,9 @@ def assert_trace_equal(dev, ref):
     assert np.array_equal(dev["accept"], ref["accept"])
     assert np.array_equal(dev["z"], ref["z"])
     assert np.array_equal(dev["newp"], ref["newp"])
-    assert ulp_close(dev["e"], ref["e"]) and ulp_close(dev["diff"], ref["diff"], 16)
+    assert ulp_close(dev["e"], ref["e"])
+    # diff = log(z)(D-1) + newp - logp cancels: bound it by the size of its terms, not of the result
+    assert np.all(np.abs(dev["diff"] - ref["diff"]) <= 1e-14 * (1.0 + np.abs(ref["newp"]) + np.abs(ref["diff"])))
 
 
 @pytest.mark.parametrize("name", golden_names())
