@@ -94,7 +94,7 @@ def test_rosenbrock_thread_kernel(port, W, D, steps, interval):
     s.close()
 
 
-@pytest.mark.parametrize("W,D,steps", [(64, 3, 20), (64, 8, 20), (256, 9, 10), (256, 64, 10), (256, 65, 10), (128, 127, 6),
+@pytest.mark.parametrize("W,D,steps", [(64, 3, 20), (64, 8, 20), (256, 9, 10), (256, 64, 10), (256, 65, 10), (256, 127, 6),
                                        (512, 200, 6), (2048, 500, 3), (4096, 1000, 3), (4096, 1023, 2), (4096, 1024, 2)])
 def test_diag_gauss_every_kernel_shape(port, W, D, steps):
     """thread kernel (D<=8), warp kernel with 1..16 chunks, odd D (scalar loads) and ragged tails:
