@@ -30,6 +30,7 @@
 #define MCMCPP_B200_STRETCH_KERNELS_CUH
 
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include "mcmcpp_b200/capi.h"
 #include "mcmcpp_b200/device_rng.cuh"
 
@@ -323,6 +324,136 @@ __global__ void __launch_bounds__(WarpKernelThreads) stretchHalfStepWarp(const m
     }
 }
 
+/* ---- kernel 3: one warp per walker, rows staged HBM -> shared memory by TMA bulk copies ---------------- */
+/*
+ * For wide rows (D > 128) the register kernel above holds both rows in registers (187 regs/thread at D=1000,
+ * 8 warps/SM) and cannot keep enough bytes in flight to saturate HBM (ncu r01: 56% of DRAM peak).  Here lane 0
+ * issues two cp.async.bulk copies (own row, partner row; 8*D bytes each) that complete on an mbarrier; no
+ * register is tied up while the data is in flight and up to 12 walkers (192 KB) per SM are outstanding.
+ * The proposal is built in place of the partner row in shared memory, so a generic Calculator can be evaluated
+ * on it directly; a separable one is reduced in the canonical 64-way order (bit-identical to its host form).
+ * Needs 16-byte aligned rows: D even.
+ */
+__device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbarExpectTx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void bulkLoad(uint32_t dstSmem, const void* srcGlobal, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dstSmem), "l"(srcGlobal), "r"(bytes), "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t phase)
+{
+    asm volatile("{\n"
+                 ".reg .pred P1;\n"
+                 "LAB_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+                 "@P1 bra DONE;\n"
+                 "bra LAB_WAIT;\n"
+                 "DONE:\n"
+                 "}" ::"r"(bar), "r"(phase) : "memory");
+}
+
+enum { BulkKernelMinDim = 130 };
+
+template <class Calc, int WARPS, bool TRACE>
+__global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride)
+{
+    extern __shared__ __align__(128) unsigned char bulkSmem[];
+    const int lane = threadIdx.x & 31;
+    const int warpInBlock = threadIdx.x >> 5;
+    const int i = blockIdx.x * WARPS + warpInBlock;
+    if (i >= a.slot_count) return;          /* warp-uniform; warps of a CTA never synchronise with each other */
+    Calc calc = calcIn;
+    const int D = a.D;
+    const uint32_t rowBytes = (uint32_t)D * 8u;
+    double* ownS = reinterpret_cast<double*>(bulkSmem + (size_t)warpInBlock * 2u * rowStride);
+    double* selS = reinterpret_cast<double*>(bulkSmem + (size_t)warpInBlock * 2u * rowStride + rowStride);
+    const uint32_t bar = smemAddr(bulkSmem + (size_t)WARPS * 2u * rowStride + 8u * warpInBlock);
+    const int slot = a.slot_begin + i;
+    const int w = a.half * a.K + slot;
+    const int other0 = (1 - a.half) * a.K;
+
+    WalkerRng rng = loadRng(a, w);
+    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    double* ownRow = a.pos + (size_t)w * D;
+    const double* selRow = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
+    if (lane == 0) {
+        mbarInit(bar, 1);
+        mbarExpectTx(bar, 2u * rowBytes);
+        bulkLoad(smemAddr(ownS), ownRow, rowBytes, bar);
+        bulkLoad(smemAddr(selS), selRow, rowBytes, bar);
+    }
+    __syncwarp();
+    /* overlapped with the copies: the scalar part of the update */
+    const double scaling = __dmul_rn(log(dr.z), (double)(D - 1));
+    const double oldp = a.logp[w];
+    mbarWait(bar, 0);
+
+    double p0 = 0.0, p1 = 0.0;
+    for (int d = 2 * lane; d < D; d += 64) {
+        const double2 c = *reinterpret_cast<const double2*>(ownS + d);
+        const double2 s = *reinterpret_cast<const double2*>(selS + d);
+        double2 p;
+        p.x = stretchPoint(s.x, c.x, dr.z);
+        p.y = stretchPoint(s.y, c.y, dr.z);
+        *reinterpret_cast<double2*>(selS + d) = p;       /* the proposal replaces the partner row */
+        if constexpr (IsSeparable<Calc>::value) {
+            p0 = __dadd_rn(p0, calc.term(p.x, d));
+            p1 = __dadd_rn(p1, calc.term(p.y, d + 1));
+        }
+    }
+    double newp;
+    if constexpr (IsSeparable<Calc>::value) {
+        double s = __dadd_rn(p0, p1);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) s = __dadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
+        newp = calc.finish(s);
+    } else {
+        __syncwarp();
+        double v = 0.0;
+        if (lane == 0) v = calc.calcLogPostProb(selS);
+        newp = __shfl_sync(0xffffffffu, v, 0);
+    }
+    const double diff = __dsub_rn(__dadd_rn(scaling, newp), oldp);
+    const bool accepted = dr.logOneMinusU < diff;
+
+    if (accepted) {
+        for (int d = 2 * lane; d < D; d += 64) *reinterpret_cast<double2*>(ownRow + d) = *reinterpret_cast<const double2*>(selS + d);
+    }
+    if (a.chain_row) {
+        double* chainRow = a.chain_row + (size_t)w * D;
+        const double* src = accepted ? selS : ownS;
+        for (int d = 2 * lane; d < D; d += 64) *reinterpret_cast<double2*>(chainRow + d) = *reinterpret_cast<const double2*>(src + d);
+    }
+    if (lane == 0) {
+        storeRng(a, w, rng);
+        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+        if (accepted) {
+            a.logp[w] = newp;
+            atomicAdd(a.accept_slots + blockIdx.x, 1ULL);
+        }
+        if (TRACE) {
+            if (slot < a.trace_rows) {
+                mcmcpp_trace t;
+                t.j = dr.j; t.accept = accepted ? 1 : 0; t.z = dr.z; t.e = dr.logOneMinusU; t.newp = newp; t.diff = diff;
+                a.trace[slot] = t;
+            }
+        }
+    }
+}
+
 /* ---- launchers ---------------------------------------------------------------------------------- */
 inline int launchStatus()
 {
@@ -359,6 +490,41 @@ int launchWarpKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream
     return launchStatus();
 }
 
+template <class Calc, int WARPS>
+int launchBulkKernelW(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
+{
+    const int grid = (a.slot_count + WARPS - 1) / WARPS;
+    if (grid > a.max_grid) return MCMCPP_ERR_ARG;
+    const size_t smem = (size_t)WARPS * 2u * rowStride + 8u * WARPS;
+    static bool attrDone[2] = {false, false};
+    if (a.trace) {
+        if (!attrDone[1]) { cudaFuncSetAttribute(stretchHalfStepBulk<Calc, WARPS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attrDone[1] = true; }
+        stretchHalfStepBulk<Calc, WARPS, true><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
+    } else {
+        if (!attrDone[0]) { cudaFuncSetAttribute(stretchHalfStepBulk<Calc, WARPS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attrDone[0] = true; }
+        stretchHalfStepBulk<Calc, WARPS, false><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
+    }
+    return launchStatus();
+}
+
+/* warps per CTA chosen so that >= 3 CTAs (12 walkers, 2 rows each) fit the 227 KB of one SM when rows allow */
+template <class Calc>
+int launchBulkKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream)
+{
+    const uint32_t rowStride = ((uint32_t)a.D * 8u + 127u) & ~127u;
+    const size_t perWarp = 2u * (size_t)rowStride + 8u;
+    if (4 * perWarp <= 74 * 1024) return launchBulkKernelW<Calc, 4>(a, calc, stream, rowStride);
+    if (2 * perWarp <= 74 * 1024) return launchBulkKernelW<Calc, 2>(a, calc, stream, rowStride);
+    if (perWarp <= 226 * 1024) return launchBulkKernelW<Calc, 1>(a, calc, stream, rowStride);
+    return MCMCPP_ERR_UNSUPPORTED;
+}
+
+inline bool bulkKernelDisabled()
+{
+    static const bool off = [] { const char* e = getenv("MCMCPP_B200_NO_BULK"); return e && e[0] == '1'; }();
+    return off;
+}
+
 /* FixedD > 0 restricts the thread kernel to one dimension (2-D test targets); 0 = any D. */
 template <class Calc, int FixedD = 0>
 struct HalfStepLauncher
@@ -384,6 +550,7 @@ struct HalfStepLauncher
             case 8: return launchThreadKernel<Calc, 8>(a, calc, stream);
             default: break;
             }
+            if (a.D >= BulkKernelMinDim && (a.D % 2) == 0 && !bulkKernelDisabled()) return launchBulkKernel<Calc>(a, calc, stream);
             const int chunks = (a.D + 63) / 64;
             if (chunks <= 1) return launchWarpKernel<Calc, 1>(a, calc, stream);
             if (chunks <= 2) return launchWarpKernel<Calc, 2>(a, calc, stream);
