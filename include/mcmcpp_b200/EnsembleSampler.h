@@ -1,0 +1,277 @@
+/*
+ * include/mcmcpp_b200/EnsembleSampler.h -- C++ drop-in for the reference's sampler front-ends on the
+ * ensemble-update path.  Same namespaces, class names, template parameters and member signatures as
+ *   MCMC::EnsembleSampler            MCMCpp/EnsembleSampler.h:39-197
+ *   MCMC::ParallelEnsembleSampler    MCMCpp/ParallelEnsembleSampler.h:78-226
+ *   MCMC::Mover::StretchMove         MCMCpp/Movers/StretchMove.h:40-131
+ *   MCMC::Utility::GwDistribution    MCMCpp/Utility/GwDistribution.h:33-61
+ *   MCMC::Utility::NoAction          MCMCpp/Utility/NoAction.h:34-46
+ *   MCMC::Chain::ChainStepIterator / ChainPsetIterator (read side, MCMCpp/Chain/ChainStepIterator.h:125,251-272)
+ * so a call site such as test/sequential/SkewedGaussian/StretchMove/src/main.cpp:22-80 compiles unchanged when
+ * built with nvcc (the Calculator must have a __host__ __device__ calcLogPostProb and be trivially copyable;
+ * pointers inside it must be device pointers).  Everything forwards to the C-ABI (capi.h); the update kernels for
+ * the user's Calculator are instantiated HERE, in the user's translation unit.
+ * Compile:  nvcc -std=c++17 -gencode arch=compute_100a,code=sm_100a -fmad=false -I<repo>/include user.cu -L<repo>/mcmcpp_b200 -lmcmcpp_b200
+ */
+#ifndef MCMCPP_B200_ENSEMBLESAMPLER_H
+#define MCMCPP_B200_ENSEMBLESAMPLER_H
+
+#include <cassert>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include "mcmcpp_b200/capi.h"
+#include "mcmcpp_b200/stretch_kernels.cuh"
+
+namespace MCMC
+{
+
+namespace Utility
+{
+/* g(z) ~ 1/sqrt(z) on [1/a, a], a = AlphaNum/AlphaDenom, by inverse CDF (GwDistribution.h:45-58) */
+template <class ParamType, int AlphaNum = 2, int AlphaDenom = 1>
+struct GwDistribution
+{
+    static const int alphaNum = AlphaNum;
+    static const int alphaDenom = AlphaDenom;
+    ParamType operator()(ParamType u) const
+    {
+        const ParamType alpha = static_cast<ParamType>(AlphaNum) / static_cast<ParamType>(AlphaDenom);
+        const ParamType invSqrt = static_cast<ParamType>(1) / std::sqrt(alpha);
+        const ParamType t = (std::sqrt(alpha) - invSqrt) * u + invSqrt;
+        return t * t;
+    }
+};
+}
+
+namespace Chain
+{
+/* Read-side views over the contiguous host chain [step][walker][param] the runtime fills; same operator surface
+ * as the reference iterators the tests and Analysis classes use. */
+template <class ParamType>
+class ChainStepIterator
+{
+public:
+    ChainStepIterator() : row(nullptr), stride(0) {}
+    ChainStepIterator(ParamType* r, long long cellsPerStep) : row(r), stride(cellsPerStep) {}
+    ParamType* operator*() const { return row; }
+    ChainStepIterator& operator++() { row += stride; return *this; }
+    ChainStepIterator operator++(int) { ChainStepIterator t(*this); row += stride; return t; }
+    ChainStepIterator& operator--() { row -= stride; return *this; }
+    ChainStepIterator operator--(int) { ChainStepIterator t(*this); row -= stride; return t; }
+    ChainStepIterator& operator+=(int n) { row += stride * n; return *this; }
+    ChainStepIterator& operator-=(int n) { row -= stride * n; return *this; }
+    bool operator==(const ChainStepIterator& o) const { return row == o.row; }
+    bool operator!=(const ChainStepIterator& o) const { return row != o.row; }
+private:
+    ParamType* row;
+    long long stride;
+};
+
+template <class ParamType>
+class ChainPsetIterator
+{
+public:
+    ChainPsetIterator() : row(nullptr), stride(0) {}
+    ChainPsetIterator(ParamType* r, int cellsPerWalker) : row(r), stride(cellsPerWalker) {}
+    ParamType* operator*() const { return row; }
+    ChainPsetIterator& operator++() { row += stride; return *this; }
+    ChainPsetIterator operator++(int) { ChainPsetIterator t(*this); row += stride; return t; }
+    ChainPsetIterator& operator--() { row -= stride; return *this; }
+    bool operator==(const ChainPsetIterator& o) const { return row == o.row; }
+    bool operator!=(const ChainPsetIterator& o) const { return row != o.row; }
+private:
+    ParamType* row;
+    int stride;
+};
+}
+
+namespace Utility
+{
+template <class ParamType>
+struct NoAction
+{
+    typedef Chain::ChainStepIterator<ParamType> StepItt;
+    void performAction(const StepItt&, const StepItt&) {}
+};
+}
+
+namespace Mover
+{
+/* Holds what the reference mover holds that matters on the device path: the parameter count and a copy of the
+ * Calculator (StretchMove.h:62-66).  As in the reference the prngInit argument does not seed the run: the sampler
+ * re-seeds its copy with (randSeed, stream) (StretchMove.h:74-78, EnsembleSampler.h:217). */
+template <class ParamType, class Calculator, class CustomDistribution = Utility::GwDistribution<ParamType, 2, 1> >
+class StretchMove
+{
+public:
+    typedef Calculator CalculatorType;
+    typedef CustomDistribution DistributionType;
+    StretchMove(int numParams, long long prngInit, const Calculator& orig) : paramCount(numParams), seed(prngInit), stream(0), calc(orig) {}
+    void setPrng(long long s, long long st) { seed = s; stream = st; }
+    int getParamCount() const { return paramCount; }
+    const Calculator& getCalculator() const { return calc; }
+private:
+    int paramCount;
+    long long seed, stream;
+    Calculator calc;
+};
+}
+
+namespace Detail
+{
+inline void checkStatus(int rc, const char* what)
+{
+    /* the reference has no exceptions: hard errors are asserts (EnsembleSampler.h:207-208,327,335-336) */
+    if (rc < 0) {
+        std::fprintf(stderr, "mcmcpp_b200: %s failed (%d): %s\n", what, rc, mcmcpp_last_error());
+        std::abort();
+    }
+}
+
+/* Shared implementation of both front-ends; RngMode is the only thing that differs. */
+template <class ParamType, class Mover, class PostStepAction>
+class DeviceSamplerBase
+{
+public:
+    typedef Chain::ChainPsetIterator<ParamType> PsetItt;
+    typedef Chain::ChainStepIterator<ParamType> StepItt;
+    typedef typename Mover::CalculatorType Calculator;
+    typedef typename Mover::DistributionType Distribution;
+
+    DeviceSamplerBase(int randSeed, int rngMode, int numWalker, int numParameter, const Mover& move,
+                      unsigned long long maxChainSizeBytes, PostStepAction* stepAct)
+        : stepAction(stepAct), moveProposer(move), numParams(numParameter), numWalkers(numWalker), handle(nullptr)
+    {
+        static_assert(sizeof(ParamType) == sizeof(double), "the B200 path computes in FP64 (ParamType = double)");
+        assert(numWalkers % 2 == 0);
+        assert(numWalkers > (2 * numParams));
+        mcmcpp_config cfg;
+        cfg.num_walkers = numWalker; cfg.num_params = numParameter; cfg.seed = randSeed; cfg.rng_mode = rngMode;
+        cfg.alpha_num = Distribution::alphaNum; cfg.alpha_denom = Distribution::alphaDenom;
+        cfg.device = 0; cfg.rank = 0; cfg.world = 1; cfg.shard_mode = MCMCPP_SHARD_NONE; cfg.trace_updates = 0;
+        cfg.max_chain_bytes = maxChainSizeBytes;
+        if (const char* dev = std::getenv("MCMCPP_B200_DEVICE")) cfg.device = std::atoi(dev);
+        Calculator calc = moveProposer.getCalculator();
+        /* the kernels for THIS Calculator are instantiated here, in the user's translation unit */
+        checkStatus(mcmcpp_sampler_create(&cfg, &Device::HalfStepLauncher<Calculator>::launch, &calc, sizeof(Calculator), &handle),
+                    "EnsembleSampler()");
+    }
+    ~DeviceSamplerBase() { mcmcpp_sampler_destroy(handle); }
+    DeviceSamplerBase(const DeviceSamplerBase&) = delete;
+    DeviceSamplerBase& operator=(const DeviceSamplerBase&) = delete;
+
+    void setInitialWalkerPos(ParamType* positions, ParamType* auxValues)
+    {
+        checkStatus(mcmcpp_sampler_set_initial(handle, positions, auxValues), "setInitialWalkerPos");
+    }
+    void storeCurrentWalkerPositions() { checkStatus(mcmcpp_sampler_store_current(handle), "storeCurrentWalkerPositions"); }
+    bool runMCMC(int numSteps)
+    {
+        int rc = mcmcpp_sampler_run(handle, numSteps, nullptr);
+        checkStatus(rc, "runMCMC");
+        /* end-of-call hook over the rows stored so far; the reference calls it once per step (EnsembleSampler.h:356-359) */
+        if (stepAction != nullptr) stepAction->performAction(getStepIttBegin(), getStepIttEnd());
+        return rc != MCMCPP_CHAIN_FULL;
+    }
+    void reset() { checkStatus(mcmcpp_sampler_reset(handle), "reset"); }
+    ParamType getAcceptanceFraction()
+    {
+        return static_cast<ParamType>(getAcceptedSteps()) / static_cast<ParamType>(getTotalSteps());
+    }
+    unsigned long long getAcceptedSteps()
+    {
+        unsigned long long a = 0, t = 0;
+        checkStatus(mcmcpp_sampler_get_counts(handle, &a, &t), "getAcceptedSteps");
+        return a;
+    }
+    unsigned long long getTotalSteps()
+    {
+        unsigned long long a = 0, t = 0;
+        checkStatus(mcmcpp_sampler_get_counts(handle, &a, &t), "getTotalSteps");
+        return t;
+    }
+    void sliceAndBurnChain(int slicingInterval, int burnIn)
+    {
+        assert(slicingInterval > 0);
+        assert(burnIn >= 0);
+        checkStatus(mcmcpp_sampler_slice_and_burn(handle, slicingInterval, burnIn), "sliceAndBurnChain");
+    }
+    int getStoredSteps() { return mcmcpp_sampler_get_stored_steps(handle); }
+
+    PsetItt getParamSetIttBegin() { return PsetItt(rows(), numParams); }
+    PsetItt getParamSetIttEnd() { return PsetItt(rows() + cellsStored(), numParams); }
+    StepItt getStepIttBegin() { return StepItt(rows(), (long long)numWalkers * numParams); }
+    StepItt getStepIttEnd() { return StepItt(rows() + cellsStored(), (long long)numWalkers * numParams); }
+
+    /* not in the reference: current walker state back to the host (Walker::getCurrState / getCurrAuxData) */
+    void getWalkerState(ParamType* positions, ParamType* auxValues)
+    {
+        checkStatus(mcmcpp_sampler_get_state(handle, positions, auxValues), "getWalkerState");
+    }
+    mcmcpp_sampler* nativeHandle() { return handle; }
+
+protected:
+    void setSubSampling(bool use, int interval)
+    {
+        assert(interval > 0);
+        checkStatus(mcmcpp_sampler_set_slicing(handle, use ? 1 : 0, interval), "setSlicingMode");
+    }
+    ParamType* rows()
+    {
+        const double* r = nullptr; long long n = 0;
+        mcmcpp_sampler_chain(handle, &r, &n);
+        return const_cast<ParamType*>(reinterpret_cast<const ParamType*>(r));
+    }
+    long long cellsStored()
+    {
+        const double* r = nullptr; long long n = 0;
+        mcmcpp_sampler_chain(handle, &r, &n);
+        return n * (long long)numWalkers * numParams;
+    }
+    PostStepAction* stepAction;
+    Mover moveProposer;
+    int numParams, numWalkers;
+    mcmcpp_sampler* handle;
+};
+}
+
+/* MCMCpp/EnsembleSampler.h:39-197 */
+template <class ParamType, class Mover, class PostStepAction = Utility::NoAction<ParamType> >
+class EnsembleSampler : public Detail::DeviceSamplerBase<ParamType, Mover, PostStepAction>
+{
+    typedef Detail::DeviceSamplerBase<ParamType, Mover, PostStepAction> Base;
+public:
+    EnsembleSampler(int randSeed, int numWalker, int numParameter, const Mover& move,
+                    unsigned long long maxChainSizeBytes = 2147483648ULL, PostStepAction* stepAct = nullptr)
+        : Base(randSeed, MCMCPP_RNG_SEQUENTIAL, numWalker, numParameter, move, maxChainSizeBytes, stepAct) {}
+    void setSlicingMode(bool useSlicing = false, int slicingInterval = 1) { this->setSubSampling(useSlicing, slicingInterval); }
+};
+
+/* MCMCpp/ParallelEnsembleSampler.h:78-226.  One thread reproduces the sequential sampler bit for bit (as the
+ * reference does); more threads select one RNG stream per walker (the reference is non-deterministic there,
+ * ParallelEnsembleSampler.h:71-76).  UseSpinLocks has no meaning on the device and is accepted for source compatibility. */
+template <class ParamType, class Mover, class PostStepAction = Utility::NoAction<ParamType>, bool UseSpinLocks = true>
+class ParallelEnsembleSampler : public Detail::DeviceSamplerBase<ParamType, Mover, PostStepAction>
+{
+    typedef Detail::DeviceSamplerBase<ParamType, Mover, PostStepAction> Base;
+public:
+    ParallelEnsembleSampler(int randSeed, int threadCount, int numWalker, int numParameter, const Mover& move,
+                            unsigned long long maxChainSizeBytes = 2147483648ULL, PostStepAction* stepAct = nullptr)
+        : Base(randSeed, threadCount <= 1 ? MCMCPP_RNG_SEQUENTIAL : MCMCPP_RNG_PER_WALKER, numWalker, numParameter, move,
+               maxChainSizeBytes, stepAct) {}
+    /* ParallelEnsembleSampler.h:178,322-330: sets the interval for later runs and thins/burns what is already stored.
+     * Later runs follow the sequential sampler's subsampling (interval-1 unsaved steps, then one saved); the parallel
+     * controller's own subsampling is broken. */
+    void setSamplingMode(int subSamplingInt = 1, int burnIn = 0)
+    {
+        assert(subSamplingInt > 0);
+        assert(burnIn >= 0);
+        this->setSubSampling(subSamplingInt > 1, subSamplingInt);
+        this->sliceAndBurnChain(subSamplingInt, burnIn);
+    }
+    void setSlicingMode(bool useSlicing = false, int slicingInterval = 1) { this->setSubSampling(useSlicing, slicingInterval); }
+};
+
+}
+#endif

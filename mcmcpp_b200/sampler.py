@@ -259,6 +259,8 @@ class ParallelEnsembleSampler(EnsembleSampler):
         super().__init__(randSeed, numWalker, numParameter, move, maxChainSizeBytes, stepAct, **kw)
         self.threadCount = int(threadCount)
 
-    def setSamplingMode(self, useSubSampling=False, subSamplingInt=1, burnIn=0):
-        # sequential-sampler subsampling semantics (the parallel controller's own are broken)
-        self.setSlicingMode(useSubSampling, subSamplingInt)
+    def setSamplingMode(self, subSamplingInt=1, burnIn=0):
+        """ParallelEnsembleSampler.h:178,322-330: interval for later runs + thin/burn what is already stored.
+        Later runs use the sequential sampler's subsampling (the parallel controller's own is broken)."""
+        self.setSlicingMode(subSamplingInt > 1, subSamplingInt)
+        self.sliceAndBurnChain(subSamplingInt, burnIn)

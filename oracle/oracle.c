@@ -349,3 +349,35 @@ void oracle_logp_many(int kind, int D, const double* params, const double* x, lo
 {
     for (long i = 0; i < n; ++i) out[i] = oracle_logp(kind, D, params, x + (size_t)i * D);
 }
+
+/*
+ * One colour of one ensemble step restricted to slots [slot_begin, slot_begin+slot_count): what ONE RANK of a
+ * walker-sharded ensemble does.  Each update positions its own copy of the sampler's stream (seed, stream 0) at
+ * draw 3(step*W + half*K + slot) by jump-ahead (pcg_random.hpp:622-651) -- the restatement of the design the
+ * survey validated (SURVEY.md s.8(c) "Design validation").  Reads only the other colour; updates pos/logp/acc in place.
+ */
+void oracle_stretch_half_slots(uint64_t seed, int kind, const double* tparams, int W, int D, int alpha_num, int alpha_denom,
+                               double* pos, double* logp, int64_t* acc, long step, int half, int slot_begin, int slot_count)
+{
+    const int K = W / 2;
+    double term1, isa;
+    oracle_gw_constants(alpha_num, alpha_denom, &term1, &isa);
+    double* prop = (double*)malloc(sizeof(double) * (size_t)D);
+    const int own0 = half * K, oth0 = (1 - half) * K;
+    for (int i = slot_begin; i < slot_begin + slot_count; ++i) {
+        pcg64_t g;
+        oracle_pcg64_seed(&g, seed, 0);
+        oracle_pcg64_advance(&g, (u128)3 * ((u128)step * (u128)W + (u128)half * (u128)K + (u128)i));
+        const int w = own0 + i;
+        int j = (int)oracle_pcg64_bounded(&g, (uint64_t)K, NULL);
+        const double* sel = pos + (size_t)(oth0 + j) * D;
+        double* cur = pos + (size_t)w * D;
+        double z = oracle_gw_sample(oracle_u64_to_unit(oracle_pcg64_next(&g)), term1, isa);
+        for (int d = 0; d < D; ++d) prop[d] = sel[d] + z * (cur[d] - sel[d]);
+        double newp = oracle_logp(kind, D, tparams, prop);
+        double diff = log(z) * (double)(D - 1) + newp - logp[w];
+        double e = oracle_neg_exponential(oracle_u64_to_unit(oracle_pcg64_next(&g)));
+        if (e < diff) { memcpy(cur, prop, sizeof(double) * (size_t)D); logp[w] = newp; if (acc) ++acc[w]; }
+    }
+    free(prop);
+}

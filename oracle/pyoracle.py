@@ -70,6 +70,9 @@ class Port:
         L.oracle_stretch_run_per_walker.argtypes = L.oracle_stretch_run.argtypes
         L.oracle_pcg64_seed_many.argtypes = [C.c_void_p, c_u64, C.c_int]
         L.oracle_logp_many.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_long, c_dp]
+        L.oracle_stretch_half_slots.restype = None
+        L.oracle_stretch_half_slots.argtypes = [c_u64, C.c_int, c_dp, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp,
+                                                C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int]
 
     # --- rng -----------------------------------------------------------
     def pcg64(self, seed, stream):
@@ -138,6 +141,15 @@ class Port:
                                           _dp(pos), _dp(logp), acc.ctypes.data, tot.ctypes.data, nsteps, interval,
                                           _dp(chain), trace.ctypes.data if want_trace else None)
         return dict(pos=pos, logp=logp, acc=acc, tot=tot, chain=chain, trace=trace, rejections=rej, rng=g)
+
+
+    def half_slots(self, kind, params, pos, logp, acc, step, half, slot_begin, slot_count, seed=0, alpha=(2, 1)):
+        """In-place update of one colour's slots [slot_begin, +slot_count) with jump-ahead draws (one rank's work)."""
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        assert pos.flags.c_contiguous and logp.flags.c_contiguous and acc.dtype == np.int64
+        self.lib.oracle_stretch_half_slots(seed & (2**64 - 1), KIND[kind], _dp(params), W, D, alpha[0], alpha[1], _dp(pos),
+                                           _dp(logp), acc.ctypes.data, step, half, slot_begin, slot_count)
 
 
 class Ref:

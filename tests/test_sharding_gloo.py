@@ -1,0 +1,82 @@
+"""N>1 host-side logic on CPU (gloo, world_size 2): the walker-index shard arithmetic of mcmcpp_b200.parallel and the
+jump-ahead draw indexing make a sharded ensemble reproduce the sequential reference bit for bit.  Each rank plays one
+GPU: it updates its slots of a colour (oracle restatement of one rank's kernel launch), then the colour is all-gathered
+in place exactly as the runtime's ncclAllGather does (runtime.cu halfStep)."""
+import os
+import sys
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port_no, W, D, steps, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port_no)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle.pyoracle import Port
+    from mcmcpp_b200 import parallel
+    port = Port()
+    K = W // 2
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    rng = np.random.default_rng(5)
+    pos = rng.standard_normal((W, D))
+    logp = port.logp("diag_gauss", iv, pos)
+    acc = np.zeros(W, np.int64)
+    b, e = parallel.shard_slots(W, rank, world)
+    n = e - b
+    for t in range(steps):
+        for h in (0, 1):
+            port.half_slots("diag_gauss", iv, pos, logp, acc, t, h, b, n, seed=3)
+            mine = torch.from_numpy(pos[h * K + b:h * K + e].copy())
+            parts = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(parts, mine)                       # the in-place all-gather of the updated colour
+            pos[h * K:(h + 1) * K] = torch.cat(parts).numpy()
+    # ensemble-wide counters, as parallel.reduce_counts does
+    owned = parallel.owned_walkers(W, rank, world)
+    tot = torch.tensor([int(acc[owned].sum())])
+    dist.all_reduce(tot)
+    lp_parts = [torch.empty(2 * n, dtype=torch.float64) for _ in range(world)]
+    dist.all_gather(lp_parts, torch.from_numpy(logp[owned].copy()))
+    if rank == 0:
+        np.savez(os.path.join(out_dir, "sharded.npz"), pos=pos, acc=int(tot), logp_owned=torch.stack(lp_parts).numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("W,D,steps", [(64, 6, 5)])
+def test_two_rank_sharded_ensemble_equals_sequential_reference(tmp_path, port, W, D, steps):
+    world = 2
+    port_no = 29500 + (os.getpid() % 400)
+    mp.spawn(_worker, args=(world, port_no, W, D, steps, str(tmp_path)), nprocs=world, join=True)
+    z = np.load(tmp_path / "sharded.npz")
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    rng = np.random.default_rng(5)
+    init = rng.standard_normal((W, D))
+    o = port.run("diag_gauss", iv, init, port.logp("diag_gauss", iv, init), steps, seed=3, acc=np.zeros(W), tot=np.zeros(W))
+    assert np.array_equal(z["pos"], o["pos"])
+    assert int(z["acc"]) == int(o["acc"].sum())
+    from mcmcpp_b200 import parallel
+    for r in range(world):
+        assert np.array_equal(z["logp_owned"][r], o["logp"][parallel.owned_walkers(W, r, world)])
+
+
+def test_shard_arithmetic():
+    from mcmcpp_b200 import parallel
+    W = 48
+    for world in (1, 2, 4, 8):
+        K = W // 2
+        if K % world:
+            with pytest.raises(ValueError):
+                parallel.shard_slots(W, 0, world)
+            continue
+        seen = []
+        for r in range(world):
+            seen += parallel.owned_walkers(W, r, world)
+        assert sorted(seen) == list(range(W))
+    assert parallel.sequential_draw_index(0, 0, 0, W) == 0
+    assert parallel.sequential_draw_index(2, 1, 5, W) == 3 * (2 * W + W // 2 + 5)
