@@ -157,7 +157,7 @@ def device_inputs(torch, kind, W, D, params, device):
     g.manual_seed(1234)
     pos = torch.randn((W, D), dtype=torch.float64, device=device, generator=g)
     aux = torch.empty(W, dtype=torch.float64, device=device)
-    chunk = max(1, (1 << 24) // D)
+    chunk = max(1, (1 << 27) // D)
     if kind == "diag_gauss":
         iv = torch.tensor(params, dtype=torch.float64, device=device)
         for b in range(0, W, chunk):
@@ -306,7 +306,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
-    ap.add_argument("--shard", default="allgather", choices=["allgather", "peer"])
+    ap.add_argument("--shard", default="peer", choices=["allgather", "peer"])
     ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

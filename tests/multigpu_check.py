@@ -20,7 +20,7 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     port = Port()
     failures = 0
-    cases = [("rosenbrock_2d", 4096, 2, 12), ("diag_gauss", 512, 100, 6), ("diag_gauss", 1024, 1000, 4), ("diag_gauss", 256, 37, 5)]
+    cases = [("rosenbrock_2d", 4096, 2, 12), ("diag_gauss", 512, 100, 6), ("diag_gauss", 2048, 1000, 4), ("diag_gauss", 256, 37, 5)]
     for kind, W, D, steps in cases:
         params = 1.0 / (1.0 + (np.arange(D) % 10)) if kind == "diag_gauss" else np.zeros(0)
         rng = np.random.default_rng(17)

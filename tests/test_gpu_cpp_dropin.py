@@ -22,7 +22,8 @@ def run_example(*args):
     assert os.path.exists(EXE), "examples/skewed_gaussian missing: run __graft_entry__.build()"
     out = subprocess.run([EXE, *map(str, args)], check=True, capture_output=True, text=True, timeout=300).stdout
     acc, tot, stored = map(int, re.search(r"accepted (\d+) total (\d+) stored (\d+)", out).groups())
-    last = [float.fromhex(x) for x in re.search(r"last (\S+) (\S+)", out).groups()]
+    mlast = re.search(r"last (\S+) (\S+)", out)
+    last = [float.fromhex(x) for x in mlast.groups()] if mlast else None
     cov = [float(x) for x in re.search(r"cov (\S+) (\S+) (\S+)", out).groups()]
     return acc, tot, stored, last, cov, out
 
