@@ -29,6 +29,8 @@ WORKLOADS = {
     # name: (description, kind, W, D, cpu sample walkers, cpu sample steps)
     "c4": ("BASELINE configs[3]: 1000-D diagonal Gaussian, 2^20 walkers, stretch move a=2", "diag_gauss", 1 << 20, 1000, 4096, 40),
     "c2": ("BASELINE configs[1]: Rosenbrock 2-D banana, 2^20 walkers, stretch move a=2", "rosenbrock_2d", 1 << 20, 2, 65536, 300),
+    "c3": ("BASELINE configs[2]: 100-D correlated Gaussian (dense precision, rho=0.9), 65,536 walkers, FP64 tensor-core quadratic form",
+           "dense_gauss", 1 << 16, 100, 4096, 60),
     "c1": ("BASELINE configs[0]: 2-D skewed Gaussian, 32 walkers", "skewed_gauss_2d", 32, 2, 32, 20000),
 }
 
@@ -38,6 +40,9 @@ def target_params(kind, D):
         return 1.0 / (1.0 + (np.arange(D) % 10))
     if kind == "skewed_gauss_2d":
         return np.array([0.13])
+    if kind == "dense_gauss":
+        idx = np.arange(D)
+        return np.linalg.inv(0.9 ** np.abs(idx[:, None] - idx[None, :])).reshape(-1)
     return np.zeros(0)
 
 
@@ -163,6 +168,9 @@ def device_inputs(torch, kind, W, D, params, device):
         for b in range(0, W, chunk):
             x = pos[b:b + chunk]
             aux[b:b + chunk] = -0.5 * (x * x * iv).sum(dim=1)
+    elif kind == "dense_gauss":
+        P = torch.tensor(params, dtype=torch.float64, device=device).reshape(D, D)
+        aux = -0.5 * ((pos @ P) * pos).sum(dim=1)
     elif kind == "rosenbrock_2d":
         x, y = pos[:, 0], pos[:, 1]
         aux = -(100.0 * (y - x * x) ** 2 + (1.0 - x) ** 2) / 20.0
@@ -175,7 +183,8 @@ def device_inputs(torch, kind, W, D, params, device):
 
 
 def make_calc(m, kind, params):
-    return {"diag_gauss": lambda: m.DiagGaussian(params), "rosenbrock_2d": lambda: m.RosenbrockTwoDim(),
+    return {"diag_gauss": lambda: m.DiagGaussian(params), "dense_gauss": lambda: m.DenseGaussian(params.reshape(int(round(params.size ** 0.5)), -1)),
+            "rosenbrock_2d": lambda: m.RosenbrockTwoDim(),
             "skewed_gauss_2d": lambda: m.SkewedGaussianTwoDim(params[0])}[kind]()
 
 
@@ -280,6 +289,18 @@ def gpu_arm(args):
                 "algorithmic_bytes_per_update": algorithmic_bytes_per_update(D, False), "updates_per_launch": per_launch_updates,
                 "launch_ms": launch_ms,
                 "note": "launch_ms = CUDA-event time of the timed region / launches" + ("" if world == 1 else " (includes the per-half-step exchange)")}
+    if kind == "dense_gauss":
+        # compute-bound: FP64 tensor cores (DMMA); flops/update = 2D^2 + 5D; peak measured on this GPU
+        import ctypes
+        from mcmcpp_b200 import _capi
+        tf = ctypes.c_double()
+        _capi.check(_capi.lib().mcmcpp_fp64_tensor_peak(local, ctypes.byref(tf)))
+        flops = per_launch_updates * (2.0 * D * D + 5.0 * D)
+        ach = flops / (launch_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value, "traffic": traffic,
+                    "kernel": "denseGaussHalfStep (mma.sync.m8n8k4.f64)", "peak_source": "measured here: mcmcpp_fp64_tensor_peak (register-resident DMMA chains); MEASURED_PEAKS.json has no FP64 entry",
+                    "flops_per_update": 2 * D * D + 5 * D, "updates_per_launch": per_launch_updates, "launch_ms": launch_ms,
+                    "hbm_view": {"achieved_gbs": achieved, "frac_of_hbm_peak": achieved / peak}}
     cpu = None
     if world == 1 and not args.no_cpu:
         cpu = cpu_reference_run(args.workload, cpu_steps, 1)

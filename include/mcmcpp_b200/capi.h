@@ -169,6 +169,8 @@ int mcmcpp_sampler_launch_count(mcmcpp_sampler* s, unsigned long long* kernel_la
 void* mcmcpp_sampler_stream(mcmcpp_sampler* s);      /* cudaStream_t the kernels are launched on */
 const char* mcmcpp_last_error(void);
 int mcmcpp_device_count(void);
+/* measured FP64 tensor-core (DMMA m8n8k4) peak of `device` in TFLOP/s: the roofline denominator of the dense-likelihood kernels */
+int mcmcpp_fp64_tensor_peak(int device, double* tflops);
 
 /* ---- multi-GPU plumbing (one process per GPU) -------------------------------------------------
  *      ALLGATHER: rank 0 makes an id, the host layer broadcasts the 128 bytes, every rank joins.

@@ -46,6 +46,7 @@ int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t
     }
     case MCMCPP_TARGET_DENSE_GAUSS: {
         if (nValues != (size_t)D * (size_t)D) return MCMCPP_ERR_ARG;
+        if (mcmcpp_dense_bind(D, devParams, launcher, calculator)) return MCMCPP_OK;
         storeCalc(DenseGaussian<double>(devParams, D), calculator);
         *launcher = &MCMC::Device::HalfStepLauncher<DenseGaussian<double> >::launch;
         return MCMCPP_OK;

@@ -13,4 +13,6 @@
 int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t nValues, const double* devParams,
                         mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux);
 void mcmcpp_builtin_release(void* aux);
+/* dense_gauss.cu: FP64 tensor-core half-step for the dense Gaussian; false = use the generic launcher */
+bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);
 #endif

@@ -1,0 +1,283 @@
+/*
+ * mcmcpp_b200/csrc/dense_gauss.cu -- BASELINE config 3: stretch-move half-step for the dense-covariance Gaussian
+ * log-posterior  logp(x) = -1/2 x^T P x  (include/mcmcpp_b200/targets.h DenseGaussian), with the batched quadratic
+ * form evaluated on the FP64 tensor cores.
+ *
+ * Same update as StretchMove::updateWalker (MCMCpp/Movers/StretchMove.h:100-123); what changes is how
+ * calc.calcLogPostProb(proposal) (StretchMove.h:111) is evaluated: a CTA takes a tile of TM walkers, builds the TM
+ * proposals in shared memory, computes Y = Xprop * P as a [TM x D] x [D x D] contraction with
+ * mma.sync.m8n8k4.f64 (DMMA; tcgen05 has no FP64 kind) against P resident in shared memory, and folds the row dot
+ * q_i = sum_j Xprop_ij * Y_ij into the MMA epilogue.  Draws, partner choice and proposals are bit-identical to the
+ * reference; the log-posterior is summed in tensor-core order, so it carries the tolerance tier (<= 1e-12 relative,
+ * SURVEY.md s.8(c) tier B) and decisions agree unless one lands within that distance of its threshold.
+ *
+ * Persistent CTAs (one per SM, P loaded once), 8 warps: warp w owns rows 8w..8w+7 of the tile and all D/8 column
+ * blocks (accumulators in registers).  Shared-memory row stride = 4 mod 16 doubles -> conflict-free fragment loads.
+ */
+#include <cuda_runtime.h>
+#include <cstring>
+#include "builtin_targets.h"
+#include "mcmcpp_b200/stretch_kernels.cuh"
+#include "mcmcpp_b200/targets.h"
+
+namespace
+{
+using namespace MCMC::Device;
+
+enum { DenseTileRows = 64, DenseThreads = 256 };
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+__host__ __device__ inline int denseStride(int Dp)
+{
+    int s = Dp;
+    while ((s & 15) != 4) ++s;
+    return s;
+}
+
+/* NB = number of 8-wide column blocks (padded dimension Dp = 8*NB) */
+template <int NB, bool TRACE>
+__global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P)
+{
+    constexpr int Dp = 8 * NB;
+    extern __shared__ __align__(16) double denseSmem[];
+    const int stride = denseStride(Dp);
+    double* Ps = denseSmem;                                   /* [Dp][stride] */
+    double* Xs = Ps + (size_t)Dp * stride;                    /* [TM][stride] proposals */
+    double* sZ = Xs + (size_t)DenseTileRows * stride;         /* per-row scalars */
+    double* sE = sZ + DenseTileRows;
+    double* sQ = sE + DenseTileRows;
+    int* sJ = reinterpret_cast<int*>(sQ + DenseTileRows);
+    int* sAcc = sJ + DenseTileRows;
+
+    const int D = a.D;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int other0 = (1 - a.half) * a.K;
+
+    /* P -> shared, zero padded (rows/cols >= D contribute nothing) */
+    for (int idx = tid; idx < Dp * stride; idx += DenseThreads) {
+        const int r = idx / stride, c = idx - r * stride;
+        Ps[idx] = (r < D && c < D) ? P[(size_t)r * D + c] : 0.0;
+    }
+    unsigned long long ctaAccepted = 0;
+    const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
+
+    for (int tile = blockIdx.x; tile < numTiles; tile += gridDim.x) {
+        const int row0 = tile * DenseTileRows;
+        __syncthreads();                                      /* previous tile fully committed; Ps visible */
+        /* (a) draws: one thread per walker of the tile */
+        if (tid < DenseTileRows) {
+            const int i = row0 + tid;
+            if (i < a.slot_count) {
+                const int w = a.half * a.K + a.slot_begin + i;
+                WalkerRng rng = loadRng(a, w);
+                StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+                storeRng(a, w, rng);
+                if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+                sJ[tid] = dr.j; sZ[tid] = dr.z; sE[tid] = dr.logOneMinusU;
+            } else {
+                sJ[tid] = 0; sZ[tid] = 1.0; sE[tid] = 0.0;
+            }
+        }
+        __syncthreads();
+        /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic */
+        for (int r = warp; r < DenseTileRows; r += DenseThreads / 32) {
+            const int i = row0 + r;
+            double* xr = Xs + (size_t)r * stride;
+            if (i < a.slot_count) {
+                const int w = a.half * a.K + a.slot_begin + i;
+                const int j = sJ[r];
+                const double z = sZ[r];
+                const double* own = a.pos + (size_t)w * D;
+                const double* sel = partnerBase(a, j) + (size_t)(other0 + j) * D;
+                for (int d = lane; d < Dp; d += 32) xr[d] = (d < D) ? stretchPoint(__ldg(sel + d), own[d], z) : 0.0;
+            } else {
+                for (int d = lane; d < Dp; d += 32) xr[d] = 0.0;
+            }
+        }
+        __syncthreads();
+        /* (c) Y = Xs * Ps on the FP64 tensor cores; warp owns 8 rows x all NB column blocks */
+        {
+            double acc[NB][2];
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb) { acc[nb][0] = 0.0; acc[nb][1] = 0.0; }
+            const int g = lane >> 2, t = lane & 3;
+            const double* arow = Xs + (size_t)(warp * 8 + g) * stride + t;
+            const double* bcol = Ps + (size_t)t * stride + g;
+#pragma unroll 2
+            for (int k = 0; k < Dp; k += 4) {
+                const double av = arow[k];
+                const double* bk = bcol + (size_t)k * stride;
+#pragma unroll
+                for (int nb = 0; nb < NB; ++nb) dmma884(acc[nb][0], acc[nb][1], av, bk[nb * 8]);
+            }
+            /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols nb*8 + 2t, +1 of row g */
+            const double* xrow = Xs + (size_t)(warp * 8 + g) * stride + 2 * t;
+            double q = 0.0;
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb) {
+                const double2 xv = *reinterpret_cast<const double2*>(xrow + nb * 8);
+                q = fma(xv.x, acc[nb][0], q);
+                q = fma(xv.y, acc[nb][1], q);
+            }
+            q += __shfl_xor_sync(0xffffffffu, q, 1);
+            q += __shfl_xor_sync(0xffffffffu, q, 2);
+            if (t == 0) sQ[warp * 8 + g] = q;
+        }
+        __syncthreads();
+        /* (d) Metropolis decision, one thread per walker */
+        if (tid < DenseTileRows) {
+            const int i = row0 + tid;
+            int accepted = 0;
+            if (i < a.slot_count) {
+                const int slot = a.slot_begin + i;
+                const int w = a.half * a.K + slot;
+                const double z = sZ[tid];
+                const double scaling = __dmul_rn(log(z), (double)(D - 1));
+                const double newp = -0.5 * sQ[tid];
+                const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
+                accepted = sE[tid] < diff ? 1 : 0;
+                if (accepted) a.logp[w] = newp;
+                if (TRACE) {
+                    if (slot < a.trace_rows) {
+                        mcmcpp_trace tr;
+                        tr.j = sJ[tid]; tr.accept = accepted; tr.z = z; tr.e = sE[tid]; tr.newp = newp; tr.diff = diff;
+                        a.trace[slot] = tr;
+                    }
+                }
+            }
+            sAcc[tid] = accepted;
+            const unsigned ballot = __ballot_sync(0xffffffffu, accepted);
+            if (lane == 0) ctaAccepted += __popc(ballot);     /* warps 0 and 1 each keep their own count (tid 0, 32) */
+        }
+        __syncthreads();
+        /* (e) commit accepted rows (and the chain row of every walker on stored steps) */
+        for (int r = warp; r < DenseTileRows; r += DenseThreads / 32) {
+            const int i = row0 + r;
+            if (i >= a.slot_count) continue;
+            const int w = a.half * a.K + a.slot_begin + i;
+            const double* xr = Xs + (size_t)r * stride;
+            double* own = a.pos + (size_t)w * D;
+            const bool accepted = sAcc[r] != 0;
+            if (a.chain_row) {
+                double* chainRow = a.chain_row + (size_t)w * D;
+                for (int d = lane; d < D; d += 32) chainRow[d] = accepted ? xr[d] : own[d];
+            }
+            if (accepted) for (int d = lane; d < D; d += 32) own[d] = xr[d];
+        }
+    }
+    if ((tid == 0 || tid == 32) && ctaAccepted) atomicAdd(a.accept_slots + blockIdx.x, ctaAccepted);
+}
+
+struct DenseCalc
+{
+    const double* P;
+    int D;
+    int smCount;
+};
+
+template <int NB>
+int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_t stream)
+{
+    const int Dp = 8 * NB, stride = denseStride(Dp);
+    const size_t smem = sizeof(double) * ((size_t)Dp * stride + (size_t)DenseTileRows * stride + 3 * DenseTileRows) + sizeof(int) * 2 * DenseTileRows;
+    const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
+    int grid = numTiles < c.smCount ? numTiles : c.smCount;
+    if (grid > a.max_grid) grid = a.max_grid;
+    static bool attr[2] = {false, false};
+    if (a.trace) {
+        if (!attr[1]) { cudaFuncSetAttribute(denseGaussHalfStep<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr[1] = true; }
+        denseGaussHalfStep<NB, true><<<grid, DenseThreads, smem, stream>>>(a, c.P);
+    } else {
+        if (!attr[0]) { cudaFuncSetAttribute(denseGaussHalfStep<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr[0] = true; }
+        denseGaussHalfStep<NB, false><<<grid, DenseThreads, smem, stream>>>(a, c.P);
+    }
+    return launchStatus();
+}
+
+int denseLaunch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)
+{
+    const mcmcpp_halfstep_args& a = *args;
+    const DenseCalc& c = *static_cast<const DenseCalc*>(calculator);
+    cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
+    if (a.slot_count <= 0) return MCMCPP_OK;
+    const int nb = (a.D + 7) / 8;
+    if (nb <= 2) return launchDenseNB<2>(a, c, stream);
+    if (nb <= 4) return launchDenseNB<4>(a, c, stream);
+    if (nb <= 8) return launchDenseNB<8>(a, c, stream);
+    if (nb <= 13) return launchDenseNB<13>(a, c, stream);
+    if (nb <= 16) return launchDenseNB<16>(a, c, stream);
+    return MCMCPP_ERR_UNSUPPORTED;
+}
+
+}  // namespace
+
+/* Tensor-core path for 8 < D <= 128 (unless MCMCPP_B200_DENSE_GENERIC=1 asks for the reference-order generic path). */
+bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator)
+{
+    const char* e = getenv("MCMCPP_B200_DENSE_GENERIC");
+    if (D <= 8 || D > 128 || (e && e[0] == '1')) return false;
+    DenseCalc c;
+    c.P = devP; c.D = D; c.smCount = 148;
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&c.smCount, cudaDevAttrMultiProcessorCount, dev);
+    calculator->resize(sizeof c);
+    std::memcpy(calculator->data(), &c, sizeof c);
+    *launcher = &denseLaunch;
+    return true;
+}
+
+/* ---- measured FP64 tensor-core peak (roofline denominator for the dense-likelihood kernels; MEASURED_PEAKS.json
+ * has no FP64 entry): register-resident DMMA chains, 8 independent accumulator pairs per warp ---------------------- */
+namespace
+{
+__global__ void __launch_bounds__(256) dmmaPeakKernel(double* out, int iters)
+{
+    double c[8][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { c[i][0] = 0.0; c[i][1] = 0.0; }
+    const double a = 1.0 + 1e-9 * threadIdx.x, b = 1.0 - 1e-9 * threadIdx.x;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dmma884(c[i][0], c[i][1], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += c[i][0] + c[i][1];
+    if (s == 12345.678) out[0] = s;   /* keep the chain alive */
+}
+}
+
+extern "C" int mcmcpp_fp64_tensor_peak(int device, double* tflops)
+{
+    if (!tflops) return MCMCPP_ERR_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return MCMCPP_ERR_CUDA;
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    double* out = nullptr;
+    if (cudaMalloc(&out, sizeof(double)) != cudaSuccess) return MCMCPP_ERR_CUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int iters = 20000, grid = sms * 8;
+    dmmaPeakKernel<<<grid, 256>>>(out, 200);
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0);
+        dmmaPeakKernel<<<grid, 256>>>(out, iters);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(out); return MCMCPP_ERR_CUDA; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flops = (double)grid * 8.0 /*warps*/ * (double)iters * 8.0 * 512.0;   /* m8n8k4 = 2*8*8*4 */
+        const double tf = flops / (ms * 1e-3) / 1e12;
+        if (tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(out);
+    *tflops = best;
+    return MCMCPP_OK;
+}

@@ -113,8 +113,9 @@ def test_diag_gauss_every_kernel_shape(port, W, D, steps):
     s.close()
 
 
-def test_generic_calculator_in_warp_kernel(port):
+def test_generic_calculator_in_warp_kernel(port, monkeypatch):
     """non-separable Calculator, D > 8: proposal staged in shared memory, evaluated in the reference's order."""
+    monkeypatch.setenv("MCMCPP_B200_DENSE_GENERIC", "1")       # not the tensor-core specialisation
     D, W = 24, 128
     idx = np.arange(D)
     P = np.linalg.inv(0.9 ** np.abs(idx[:, None] - idx[None, :]))
@@ -159,4 +160,47 @@ def test_successive_runs_continue_the_stream(port):
         assert s.runMCMC(n)
     o = port.run(g["kind"], g["params"], g["init"], g["logp"], 100)
     assert np.array_equal(s.getChain()[1:], o["chain"])
+    s.close()
+
+
+def corr_precision(D, rho=0.9):
+    idx = np.arange(D)
+    return np.linalg.inv(rho ** np.abs(idx[:, None] - idx[None, :]))
+
+
+@pytest.mark.parametrize("W,D,steps", [(4096, 100, 12), (64, 12, 30), (256, 24, 20), (512, 101, 8), (1024, 128, 6), (130, 64, 10)])
+def test_dense_gauss_tensor_core_tier_b(port, W, D, steps):
+    """BASELINE config 3 path (FP64 DMMA quadratic form).  Draws, partners, proposals: bit-exact.  log-posterior:
+    tensor-core summation order -> tolerance 1e-12 relative (north_star); decisions and therefore positions must
+    still agree exactly over these runs (a flip needs a decision within ~1e-13 of its threshold)."""
+    P = corr_precision(D).reshape(-1)
+    init, lp = seeded_init(port, "dense_gauss", P, W, D, 40 + D)
+    s = make_sampler("dense_gauss", P, W, D, seed=6, traceUpdates=W * 2)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run("dense_gauss", P, init, lp, steps, seed=6, want_trace=True)
+    tr, otr = s.getTrace(W * 2), o["trace"][:W * 2]
+    assert np.array_equal(tr["j"], otr["j"]) and np.array_equal(tr["z"], otr["z"])
+    assert np.allclose(tr["newp"], otr["newp"], rtol=1e-12, atol=0)
+    assert np.array_equal(tr["accept"], otr["accept"])
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(pos, o["pos"])
+    assert np.allclose(aux, o["logp"], rtol=1e-12, atol=0)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum())
+    s.close()
+
+
+def test_c3_full_size_dense_gauss(port):
+    """BASELINE config 3 at full size: D=100, 65,536 walkers, 2 steps against the oracle."""
+    W, D = 1 << 16, 100
+    P = corr_precision(D).reshape(-1)
+    init, lp = seeded_init(port, "dense_gauss", P, W, D, 3)
+    s = make_sampler("dense_gauss", P, W, D, seed=0, maxChainSizeBytes=0)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(2)
+    o = port.run("dense_gauss", P, init, lp, 2, seed=0, want_chain=False)
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(pos, o["pos"]) and np.allclose(aux, o["logp"], rtol=1e-12, atol=0)
+    assert s.getAcceptedSteps() == int(o["acc"].sum())
     s.close()
