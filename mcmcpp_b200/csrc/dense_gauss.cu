@@ -84,19 +84,39 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
             }
         }
         __syncthreads();
-        /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic */
-        for (int r = warp; r < DenseTileRows; r += DenseThreads / 32) {
-            const int i = row0 + r;
-            double* xr = Xs + (size_t)r * stride;
-            if (i < a.slot_count) {
-                const int w = a.half * a.K + a.slot_begin + i;
+        /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  All loads of the warp's 8 rows
+         * are issued before the first use so one L2/HBM latency covers the whole tile, not one per row. */
+        {
+            constexpr int RowsPerWarp = DenseTileRows / (DenseThreads / 32);
+            constexpr int KCH = (Dp + 31) / 32;
+            double cur[RowsPerWarp][KCH], sl[RowsPerWarp][KCH];
+#pragma unroll
+            for (int rr = 0; rr < RowsPerWarp; ++rr) {
+                const int r = warp + rr * (DenseThreads / 32);
+                const int i = row0 + r;
+                const bool valid = i < a.slot_count;
+                const int w = a.half * a.K + a.slot_begin + (valid ? i : 0);
                 const int j = sJ[r];
-                const double z = sZ[r];
                 const double* own = a.pos + (size_t)w * D;
                 const double* sel = partnerBase(a, j) + (size_t)(other0 + j) * D;
-                for (int d = lane; d < Dp; d += 32) xr[d] = (d < D) ? stretchPoint(__ldg(sel + d), own[d], z) : 0.0;
-            } else {
-                for (int d = lane; d < Dp; d += 32) xr[d] = 0.0;
+#pragma unroll
+                for (int k = 0; k < KCH; ++k) {
+                    const int d = lane + 32 * k;
+                    const bool ok = valid && d < D;
+                    cur[rr][k] = ok ? own[d] : 0.0;
+                    sl[rr][k] = ok ? __ldg(sel + d) : 0.0;
+                }
+            }
+#pragma unroll
+            for (int rr = 0; rr < RowsPerWarp; ++rr) {
+                const int r = warp + rr * (DenseThreads / 32);
+                const double z = sZ[r];
+                double* xr = Xs + (size_t)r * stride;
+#pragma unroll
+                for (int k = 0; k < KCH; ++k) {
+                    const int d = lane + 32 * k;
+                    if (d < Dp) xr[d] = stretchPoint(sl[rr][k], cur[rr][k], z);   /* padding: 0 + z*(0-0) = 0 */
+                }
             }
         }
         __syncthreads();
