@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- walker-updates/s of the ensemble-update hot path on N B200s (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c1] [--shard allgather|peer]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c5|c1] [--shard allgather|peer]
   python bench.py --impl reference ...       the reference's own CPU implementation on the host cores
 
 A "step" is one ensemble step (EnsembleSampler::performStep, MCMCpp/EnsembleSampler.h:341-360): every one of
@@ -31,11 +31,30 @@ WORKLOADS = {
     "c2": ("BASELINE configs[1]: Rosenbrock 2-D banana, 2^20 walkers, stretch move a=2", "rosenbrock_2d", 1 << 20, 2, 65536, 300),
     "c3": ("BASELINE configs[2]: 100-D correlated Gaussian (dense precision, rho=0.9), 65,536 walkers, FP64 tensor-core quadratic form",
            "dense_gauss", 1 << 16, 100, 4096, 60),
+    "c5": ("BASELINE configs[4]: Bayesian linear regression, 50 params over 1e6 synthetic data points, 16,384 walkers, "
+           "likelihood of each colour as one FP64 tensor-core GEMM; data rows sharded over the GPUs", "linreg", 1 << 14, 50, 128, 1),
     "c1": ("BASELINE configs[0]: 2-D skewed Gaussian, 32 walkers", "skewed_gauss_2d", 32, 2, 32, 20000),
 }
 
 
+C5_M = int(os.environ.get("MCMCPP_BENCH_C5_ROWS", "1000000"))     # data points of configs[4]
+_LINREG = {}
+
+
+def linreg_data(D):
+    """X ~ N(0,1), theta* ~ N(0,1), y = X theta* + N(0,1), prior N(0, 10^2 I); seed 1234."""
+    if D not in _LINREG:
+        rng = np.random.default_rng(1234)
+        X = rng.standard_normal((C5_M, D))
+        y = X @ rng.standard_normal(D) + rng.standard_normal(C5_M)
+        _LINREG[D] = (X, y, np.linalg.lstsq(X, y, rcond=None)[0])
+    return _LINREG[D]
+
+
 def target_params(kind, D):
+    if kind == "linreg":
+        X, y, _ = linreg_data(D)
+        return np.concatenate([[float(X.shape[0]), 100.0], X.reshape(-1), y])
     if kind == "diag_gauss":
         return 1.0 / (1.0 + (np.arange(D) % 10))        # SURVEY.md s.8(d) C4
     if kind == "skewed_gauss_2d":
@@ -107,6 +126,8 @@ def cpu_reference_run(workload, steps, warmup, seed=0):
     params = target_params(kind, D)
     rng = np.random.default_rng(1)
     init = rng.standard_normal((Wc, D))
+    if kind == "linreg":
+        init = linreg_data(D)[2] + 0.1 * init
     port = Port()
     lp = port.logp(kind, params, init)
     cores = os.cpu_count() or 1
@@ -177,12 +198,27 @@ def device_inputs(torch, kind, W, D, params, device):
     elif kind == "skewed_gauss_2d":
         t1, t2 = pos[:, 0] / 2 - pos[:, 1], pos[:, 0] / 2 + pos[:, 1]
         aux = -((t1 * t1) / float(params[0]) + t2 * t2) / 2.0
+    elif kind == "linreg":
+        X, y, ols = linreg_data(D)
+        pos = torch.tensor(ols, dtype=torch.float64, device=device) + 0.1 * pos        # theta ~ OLS + 0.1 N(0, I)
+        ss = torch.zeros(W, dtype=torch.float64, device=device)
+        for b in range(0, X.shape[0], 1 << 17):
+            Xb = torch.tensor(X[b:b + (1 << 17)], device=device)
+            r = torch.tensor(y[b:b + (1 << 17)], device=device)[:, None] - Xb @ pos.T
+            ss += (r * r).sum(dim=0)
+        aux = -0.5 * ss - 0.5 * (pos * pos).sum(dim=1) / 100.0
     else:
         raise ValueError(kind)
-    return pos, aux.contiguous()
+    return pos.contiguous(), aux.contiguous()
 
 
-def make_calc(m, kind, params):
+def make_calc(m, kind, params, rank=0, world=1):
+    if kind == "linreg":
+        from mcmcpp_b200 import parallel
+        D = int(round((params.size - 2) / params[0])) - 1
+        X, y, _ = linreg_data(D)
+        b, e = parallel.shard_data_rows(X.shape[0], rank, world)       # DATA sharding: this rank's rows
+        return m.LinearRegression(X[b:e], y[b:e], 100.0)
     return {"diag_gauss": lambda: m.DiagGaussian(params), "dense_gauss": lambda: m.DenseGaussian(params.reshape(int(round(params.size ** 0.5)), -1)),
             "rosenbrock_2d": lambda: m.RosenbrockTwoDim(),
             "skewed_gauss_2d": lambda: m.SkewedGaussianTwoDim(params[0])}[kind]()
@@ -204,7 +240,7 @@ def gpu_arm(args):
         print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
     desc, kind, W, D, Wc, cpu_steps = WORKLOADS[args.workload]
     params = target_params(kind, D)
-    shard = "none" if world == 1 else args.shard
+    shard = "none" if world == 1 else ("data" if kind == "linreg" else args.shard)
     rng_mode = args.rng
 
     def barrier():
@@ -214,7 +250,7 @@ def gpu_arm(args):
             torch.cuda.synchronize()
 
     def new_sampler():
-        s = m.EnsembleSampler(0, W, D, m.StretchMove(D, 0, make_calc(m, kind, params)), maxChainSizeBytes=0,
+        s = m.EnsembleSampler(0, W, D, m.StretchMove(D, 0, make_calc(m, kind, params, rank, world)), maxChainSizeBytes=0,
                               rngMode=rng_mode, device=local, rank=rank, world=world, shardMode=shard)
         parallel.connect(s)
         return s
@@ -275,8 +311,8 @@ def gpu_arm(args):
         return 0
 
     peak, peak_src = measured_peaks()
-    per_launch_updates = (W // 2) // world
-    launch_ms = ms / max(1, launches)
+    per_launch_updates = (W // 2) if shard == "data" else (W // 2) // world
+    launch_ms = ms / (2.0 * args.steps)         # one colour = one half-step (1 launch; 4 for the GEMM-form linreg target)
     alg_bytes = per_launch_updates * algorithmic_bytes_per_update(D, False)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
@@ -301,6 +337,20 @@ def gpu_arm(args):
                     "kernel": "denseGaussHalfStep (mma.sync.m8n8k4.f64)", "peak_source": "measured here: mcmcpp_fp64_tensor_peak (register-resident DMMA chains); MEASURED_PEAKS.json has no FP64 entry",
                     "flops_per_update": 2 * D * D + 5 * D, "updates_per_launch": per_launch_updates, "launch_ms": launch_ms,
                     "hbm_view": {"achieved_gbs": achieved, "frac_of_hbm_peak": achieved / peak}}
+    if kind == "linreg":
+        import ctypes
+        from mcmcpp_b200 import _capi
+        tf = ctypes.c_double()
+        _capi.check(_capi.lib().mcmcpp_fp64_tensor_peak(local, ctypes.byref(tf)))
+        rows = parallel.shard_data_rows(C5_M, rank, world)
+        rows = rows[1] - rows[0]
+        fl = 2.0 * rows * D + 3.0 * rows                                  # 2 M P + 3 M per update
+        ach = per_launch_updates * fl / (launch_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value, "traffic": traffic,
+                    "kernel": "linregSse (mma.sync.m8n8k4.f64 GEMM [M x 52] x [52 x K], square-and-sum epilogue)",
+                    "peak_source": "measured here: mcmcpp_fp64_tensor_peak (register-resident DMMA chains); MEASURED_PEAKS.json has no FP64 entry",
+                    "flops_per_update": fl, "updates_per_launch": per_launch_updates, "launch_ms": launch_ms, "data_rows_this_rank": rows,
+                    "note": "launch_ms = half-step time (propose + GEMM + reduce + accept" + ("" if world == 1 else " + all-reduce of K partial sums") + "); the GEMM is > 99 % of it"}
     cpu = None
     if world == 1 and not args.no_cpu:
         cpu = cpu_reference_run(args.workload, cpu_steps, 1)

@@ -47,8 +47,13 @@ enum { MCMCPP_RNG_SEQUENTIAL = 0, MCMCPP_RNG_PER_WALKER = 1 };
  *              NCCL so every rank holds the full ensemble (BASELINE.json north_star)
  *   PEER       walker-index shards; partner rows are read straight from the owning GPU's HBM
  *              over NVLink (peer-mapped memory) inside the update kernel, one device-side
- *              barrier per half-step, no bulk exchange */
-enum { MCMCPP_SHARD_NONE = 0, MCMCPP_SHARD_ALLGATHER = 1, MCMCPP_SHARD_PEER = 2 };
+ *              barrier per half-step, no bulk exchange
+ *   DATA       the Calculator's DATA is sharded, the ensemble is replicated: every rank makes the same draws
+ *              and proposals for all W walkers, evaluates its partial log-likelihoods (its rows of the data
+ *              matrix, or its slice of a separable sum), the K partials of a colour are summed over ranks with
+ *              one ncclAllReduce (8 K bytes) and every rank takes the same decisions.  The
+ *              launcher calls args->allreduce_sum between its partial and decision kernels. */
+enum { MCMCPP_SHARD_NONE = 0, MCMCPP_SHARD_ALLGATHER = 1, MCMCPP_SHARD_PEER = 2, MCMCPP_SHARD_DATA = 3 };
 
 /* built-in Calculators (include/mcmcpp_b200/targets.h); params layout as in oracle/oracle.c */
 enum {
@@ -92,6 +97,10 @@ typedef struct {
  * (EnsembleSampler.h:225-226) -- the reference's own chain-row layout (ChainBlock.h:125-131),
  * so a stored step is a plain copy of the state.
  */
+/* DATA sharding: sums dev_buf[0..count) over all ranks in place, ordered on cuda_stream; every rank receives the
+ * same bits. */
+typedef int (*mcmcpp_allreduce_fn)(void* ctx, double* dev_buf, size_t count, void* cuda_stream);
+
 typedef struct {
     double* pos;               /* [W*D] local full-ensemble array (own rows always valid; all rows valid unless PEER) */
     double* logp;              /* [W]   auxData of owned walkers */
@@ -115,6 +124,9 @@ typedef struct {
     double gw_inv_sqrt_alpha;
     int32_t max_grid;          /* size of accept_slots */
     int32_t trace_rows;        /* rows available at `trace` (slots >= trace_rows are not recorded) */
+    mcmcpp_allreduce_fn allreduce_sum; /* DATA sharding with world > 1, else NULL */
+    void* allreduce_ctx;
+    unsigned long long* launch_count;  /* host counter: a launcher that enqueues n kernels adds n-1 (the runtime adds 1) */
 } mcmcpp_halfstep_args;
 
 typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);

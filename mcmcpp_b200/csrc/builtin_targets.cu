@@ -23,7 +23,6 @@ int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t
                         mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux)
 {
     using namespace MCMC::Targets;
-    (void)W;
     *aux = nullptr;
     switch (kind) {
     case MCMCPP_TARGET_SKEWED_GAUSS_2D: {
@@ -56,6 +55,8 @@ int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t
         const long M = (long)hostParams[0];
         if (M <= 0 || nValues != 2 + (size_t)M * (size_t)D + (size_t)M) return MCMCPP_ERR_ARG;
         const double* X = devParams + 2;
+        if (mcmcpp_linreg_bind(W, D, M, hostParams[1], X, X + (size_t)M * D, launcher, calculator, aux)) return MCMCPP_OK;
+        if (*aux) { mcmcpp_linreg_release(*aux); *aux = nullptr; }
         storeCalc(LinearRegression<double>(X, X + (size_t)M * D, M, D, hostParams[1]), calculator);
         *launcher = &MCMC::Device::HalfStepLauncher<LinearRegression<double> >::launch;
         return MCMCPP_OK;
@@ -64,4 +65,4 @@ int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t
     }
 }
 
-void mcmcpp_builtin_release(void* aux) { (void)aux; }
+void mcmcpp_builtin_release(void* aux) { mcmcpp_linreg_release(aux); }   /* the only target with scratch */

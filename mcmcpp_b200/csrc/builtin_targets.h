@@ -15,4 +15,8 @@ int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t
 void mcmcpp_builtin_release(void* aux);
 /* dense_gauss.cu: FP64 tensor-core half-step for the dense Gaussian; false = use the generic launcher */
 bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);
+/* linreg.cu: FP64 tensor-core GEMM half-step for the linear-regression target; false = use the generic launcher */
+bool mcmcpp_linreg_bind(int W, int D, long M, double priorVar, const double* devX, const double* devY, mcmcpp_halfstep_fn* launcher,
+                        std::vector<char>* calculator, void** aux);
+void mcmcpp_linreg_release(void* aux);
 #endif

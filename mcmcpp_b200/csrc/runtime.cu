@@ -235,6 +235,14 @@ int halfStep(mcmcpp_sampler* s, int half, double* chainRow)
     return MCMCPP_OK;
 }
 
+/* mcmcpp_allreduce_fn of DATA sharding: in-place ncclAllReduce(sum) on the launcher's stream */
+int allreduceSum(void* ctx, double* devBuf, size_t count, void* cudaStream)
+{
+    mcmcpp_sampler* s = static_cast<mcmcpp_sampler*>(ctx);
+    NCCL_TRY(nccl().AllReduce(devBuf, devBuf, count, ncclDouble, ncclSum, s->comm, static_cast<cudaStream_t>(cudaStream)));
+    return MCMCPP_OK;
+}
+
 int appendRowFromDeviceSlot(mcmcpp_sampler* s, int slot)
 {
     /* side stream: wait for the black half-step, copy the row to its place in the pinned host chain */
@@ -255,7 +263,8 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     if (W <= 0 || D <= 0 || (W % 2) != 0 || W <= 2 * D) return fail(MCMCPP_ERR_ARG, "numWalkers must be even and exceed 2*numParams");
     if (cfg->alpha_num <= 0 || cfg->alpha_denom <= 0) return fail(MCMCPP_ERR_ARG, "alpha must be positive");
     if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world) return fail(MCMCPP_ERR_ARG, "bad rank/world");
-    if ((W / 2) % cfg->world != 0) return fail(MCMCPP_ERR_ARG, "walkers per colour must divide evenly over the GPUs");
+    if (cfg->shard_mode != MCMCPP_SHARD_DATA && (W / 2) % cfg->world != 0)
+        return fail(MCMCPP_ERR_ARG, "walkers per colour must divide evenly over the GPUs");
     if (cfg->world > 1 && cfg->shard_mode == MCMCPP_SHARD_NONE) return fail(MCMCPP_ERR_ARG, "world > 1 needs a shard mode");
 
     int count = 0;
@@ -267,8 +276,13 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     mcmcpp_sampler* s = new mcmcpp_sampler();
     s->cfg = *cfg;
     s->W = W; s->D = D; s->K = W / 2;
-    s->slotCount = s->K / cfg->world;
-    s->slotBegin = cfg->rank * s->slotCount;
+    if (cfg->shard_mode == MCMCPP_SHARD_DATA) {      /* replicated ensemble: every rank updates every walker */
+        s->slotCount = s->K;
+        s->slotBegin = 0;
+    } else {
+        s->slotCount = s->K / cfg->world;
+        s->slotBegin = cfg->rank * s->slotCount;
+    }
     s->capRows = (long long)(cfg->max_chain_bytes / (sizeof(double) * (unsigned long long)W * (unsigned long long)D));
     *out = s;   /* destroy() cleans up on later failure */
 
@@ -315,6 +329,7 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     MCMC::Device::GwConstants gw = MCMC::Device::makeGwConstants(cfg->alpha_num, cfg->alpha_denom);
     a.gw_term1 = gw.term1; a.gw_inv_sqrt_alpha = gw.invSqrtAlpha;
     a.max_grid = s->maxGrid;
+    a.launch_count = &s->launches;
     return MCMCPP_OK;
 }
 
@@ -628,6 +643,10 @@ int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128)
     ncclUniqueId id;
     std::memcpy(&id, id128, sizeof id);
     NCCL_TRY(nccl().CommInitRank(&s->comm, s->cfg.world, id, s->cfg.rank));
+    if (s->cfg.shard_mode == MCMCPP_SHARD_DATA) {
+        s->base.allreduce_sum = &allreduceSum;
+        s->base.allreduce_ctx = s;
+    }
     return MCMCPP_OK;
 }
 

@@ -28,6 +28,14 @@ def owned_walkers(num_walkers, rank, world):
     return list(range(b, e)) + list(range(K + b, K + e))
 
 
+def shard_data_rows(num_rows, rank, world):
+    """DATA sharding: contiguous row range [begin, end) of the Calculator's data matrix held by `rank`
+    (remainder rows go to the first ranks)."""
+    base, rem = divmod(num_rows, world)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
 def sequential_draw_index(step, half, slot, num_walkers):
     """First (0-based) draw of the sampler's single pcg64 stream used by (step, colour, slot):
     3 draws per update in red-then-black walker order -- independent of the GPU count."""
@@ -63,7 +71,7 @@ def reduce_counts(sampler, group=None):
     import torch
     import torch.distributed as dist
     a, t = sampler._counts()
-    if sampler.world == 1:
+    if sampler.world == 1 or sampler.shardMode == "data":      # DATA sharding: the ensemble is replicated on every rank
         return a, t
     dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
     v = torch.tensor([a, t], dtype=torch.int64, device=dev)

@@ -108,7 +108,8 @@ class EnsembleSampler:
             num_walkers=self.numWalkers, num_params=self.numParams, seed=int(randSeed),
             rng_mode={"sequential": _capi.RNG_SEQUENTIAL, "per_walker": _capi.RNG_PER_WALKER}[rngMode],
             alpha_num=move.alpha[0], alpha_denom=move.alpha[1], device=int(device), rank=self.rank, world=self.world,
-            shard_mode={"none": _capi.SHARD_NONE, "allgather": _capi.SHARD_ALLGATHER, "peer": _capi.SHARD_PEER}[shardMode],
+            shard_mode={"none": _capi.SHARD_NONE, "allgather": _capi.SHARD_ALLGATHER, "peer": _capi.SHARD_PEER,
+                        "data": _capi.SHARD_DATA}[shardMode],
             trace_updates=int(traceUpdates), max_chain_bytes=int(maxChainSizeBytes))
         self.shardMode = shardMode
         params = np.ascontiguousarray(move.calc.params(), dtype=np.float64)

@@ -14,6 +14,33 @@ from mcmcpp_b200 import parallel             # noqa: E402
 from oracle.pyoracle import Port             # noqa: E402
 
 
+def data_sharded_linreg(port, rank, world, local):
+    """DATA sharding: replicated ensemble, each rank holds its rows of the data matrix, partial sums of squares
+    all-reduced per colour.  Every rank must take the oracle's decisions (log-probs within 1e-12)."""
+    W, P, M, steps = 512, 50, 6000, 5
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((M, P))
+    y = X @ rng.standard_normal(P) + rng.standard_normal(M)
+    params = np.concatenate([[float(M), 100.0], X.reshape(-1), y])
+    init = np.linalg.lstsq(X, y, rcond=None)[0] + 0.1 * rng.standard_normal((W, P))
+    lp = port.logp("linreg", params, init)
+    o = port.run("linreg", params, init, lp, steps, seed=4)
+    b, e = parallel.shard_data_rows(M, rank, world)
+    s = m.EnsembleSampler(4, W, P, m.StretchMove(P, 4, m.LinearRegression(X[b:e], y[b:e], 100.0)), device=local, rank=rank,
+                          world=world, shardMode="data")
+    parallel.connect(s)
+    s.setInitialWalkerPos(init, lp)
+    ok = s.runMCMC(steps)
+    pos, aux = s.getWalkerState()
+    acc, tot = parallel.reduce_counts(s)
+    good = ok and np.array_equal(pos, o["pos"]) and np.allclose(aux, o["logp"], rtol=1e-12, atol=0)
+    good = good and (acc, tot) == (int(o["acc"].sum()), int(o["tot"].sum())) and np.array_equal(s.getChain()[1:], o["chain"])
+    print("rank %d linreg W=%d P=%d M=%d data-sharded: %s" % (rank, W, P, M, "ok" if good else "MISMATCH"), flush=True)
+    s.close()
+    dist.barrier()
+    return 0 if good else 1
+
+
 def main():
     rank, world, local = parallel.env_rank_world()
     torch.cuda.set_device(local)
@@ -46,6 +73,7 @@ def main():
             failures += 0 if good else 1
             s.close()
             dist.barrier()
+    failures += data_sharded_linreg(port, rank, world, local)
     t = torch.tensor([failures], device="cuda")
     dist.all_reduce(t)
     dist.destroy_process_group()

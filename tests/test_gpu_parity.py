@@ -204,3 +204,65 @@ def test_c3_full_size_dense_gauss(port):
     assert np.array_equal(pos, o["pos"]) and np.allclose(aux, o["logp"], rtol=1e-12, atol=0)
     assert s.getAcceptedSteps() == int(o["acc"].sum())
     s.close()
+
+
+def linreg_problem(M, P, seed):
+    rng = np.random.default_rng(seed)
+    X = rng.standard_normal((M, P))
+    theta = rng.standard_normal(P)
+    y = X @ theta + rng.standard_normal(M)
+    ols = np.linalg.lstsq(X, y, rcond=None)[0]
+    return X, y, ols, np.concatenate([[float(M), 100.0], X.reshape(-1), y])
+
+
+@pytest.mark.parametrize("W,P,M,steps", [(64, 3, 500, 20), (256, 50, 3000, 6), (1024, 20, 10000, 4), (600, 63, 2000, 4),
+                                         (2048, 50, 20000, 2), (16, 3, 64, 30)])
+def test_linreg_tensor_core_gemm_tier_b(port, W, P, M, steps):
+    """BASELINE config 5 path (likelihood of all proposals of a colour as one FP64 DMMA GEMM).  Draws, partners and
+    proposals bit-exact; log-posterior summed in tensor-core order: 1e-12 relative (north_star); decisions, and
+    therefore positions and the chain, must still agree exactly over these runs.  Shapes cover every k-step
+    instantiation (4, 8, 13, 16), ragged data tiles (M % 64 != 0) and ragged / multiple proposal tiles."""
+    X, y, ols, params = linreg_problem(M, P, 7 + P)
+    rng = np.random.default_rng(P)
+    init = ols + 0.1 * rng.standard_normal((W, P))
+    lp = port.logp("linreg", params, init)
+    s = make_sampler("linreg", params, W, P, seed=9, traceUpdates=W * 2)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    assert s.getLaunchCount() == 8 * steps            # propose, GEMM, reduce, accept per colour
+    o = port.run("linreg", params, init, lp, steps, seed=9, want_trace=True)
+    tr, otr = s.getTrace(W * 2), o["trace"][:W * 2]
+    assert np.array_equal(tr["j"], otr["j"]) and np.array_equal(tr["z"], otr["z"])
+    assert np.allclose(tr["newp"], otr["newp"], rtol=1e-12, atol=0)
+    assert np.array_equal(tr["accept"], otr["accept"])
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(pos, o["pos"])
+    assert np.allclose(aux, o["logp"], rtol=1e-12, atol=0)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum())
+    s.close()
+
+
+def test_c5_full_size_linreg_against_sufficient_statistics():
+    """BASELINE config 5 at full size (P=50, M=1e6, W=16,384): the oracle needs 1e8 flops per update, so the check is a
+    size-independent property: after 2 steps every walker's stored log-posterior must equal the closed form
+    -1/2 (y'y - 2 th'X'y + th'X'X th) - 1/2 |th|^2/100 evaluated from the sufficient statistics (a different
+    algorithm; 1e-9 relative covers its own cancellation)."""
+    M, P, W = 1000000, 50, 16384
+    X, y, ols, params = linreg_problem(M, P, 1234)
+    XtX, Xty, yty = X.T @ X, X.T @ y, float(y @ y)
+
+    def closed(th):
+        return -0.5 * (yty - 2.0 * th @ Xty + np.einsum("wi,ij,wj->w", th, XtX, th)) - 0.5 * np.sum(th * th, axis=1) / 100.0
+
+    rng = np.random.default_rng(5)
+    init = ols + 0.1 * rng.standard_normal((W, P))
+    s = make_sampler("linreg", params, W, P, seed=0, maxChainSizeBytes=0)
+    s.setInitialWalkerPos(init, closed(init))
+    assert s.runMCMC(2)
+    pos, aux = s.getWalkerState()
+    moved = np.any(pos != init, axis=1)
+    assert 0.05 < moved.mean() < 0.95                      # acceptance of a 50-D stretch move
+    assert np.allclose(aux[moved], closed(pos[moved]), rtol=1e-9, atol=0)
+    assert W + int(moved.sum()) <= s.getAcceptedSteps() <= 3 * W
+    s.close()
