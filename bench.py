@@ -240,7 +240,9 @@ def gpu_arm(args):
         print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
     desc, kind, W, D, Wc, cpu_steps = WORKLOADS[args.workload]
     params = target_params(kind, D)
-    shard = "none" if world == 1 else ("data" if kind == "linreg" else args.shard)
+    shard = "data" if kind == "linreg" else args.shard
+    if world == 1 and shard != "dim":           # dim with one rank = the two-kernel form on one GPU (overhead measurement)
+        shard = "none"
     rng_mode = args.rng
 
     def barrier():
@@ -311,9 +313,13 @@ def gpu_arm(args):
         return 0
 
     peak, peak_src = measured_peaks()
-    per_launch_updates = (W // 2) if shard == "data" else (W // 2) // world
+    per_launch_updates = (W // 2) if shard in ("data", "dim") else (W // 2) // world
     launch_ms = ms / (2.0 * args.steps)         # one colour = one half-step (1 launch; 4 for the GEMM-form linreg target)
-    alg_bytes = per_launch_updates * algorithmic_bytes_per_update(D, False)
+    Dl = D
+    if shard == "dim":
+        b_, e_ = parallel.dim_slice(D, rank, world)
+        Dl = e_ - b_                                # this rank streams its columns of every walker
+    alg_bytes = per_launch_updates * algorithmic_bytes_per_update(Dl, False)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -321,7 +327,8 @@ def gpu_arm(args):
         with open(tpath) as f:
             traffic = json.load(f).get(args.workload)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "kernel": "stretchHalfStepWarp" if D > 8 else "stretchHalfStepThread", "peak_source": peak_src,
+                "kernel": ("dimShardPartial + dimShardCommit" if shard == "dim" else "stretchHalfStepBulk (TMA)" if (D >= 130 and D % 2 == 0)
+                           else "stretchHalfStepWarp" if D > 8 else "stretchHalfStepThread"), "peak_source": peak_src,
                 "algorithmic_bytes_per_update": algorithmic_bytes_per_update(D, False), "updates_per_launch": per_launch_updates,
                 "launch_ms": launch_ms,
                 "note": "launch_ms = CUDA-event time of the timed region / launches" + ("" if world == 1 else " (includes the per-half-step exchange)")}
@@ -377,7 +384,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
-    ap.add_argument("--shard", default="peer", choices=["allgather", "peer"])
+    ap.add_argument("--shard", default="peer", choices=["allgather", "peer", "dim"])
     ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

@@ -52,8 +52,15 @@ enum { MCMCPP_RNG_SEQUENTIAL = 0, MCMCPP_RNG_PER_WALKER = 1 };
  *              and proposals for all W walkers, evaluates its partial log-likelihoods (its rows of the data
  *              matrix, or its slice of a separable sum), the K partials of a colour are summed over ranks with
  *              one ncclAllReduce (8 K bytes) and every rank takes the same decisions.  The
- *              launcher calls args->allreduce_sum between its partial and decision kernels. */
-enum { MCMCPP_SHARD_NONE = 0, MCMCPP_SHARD_ALLGATHER = 1, MCMCPP_SHARD_PEER = 2, MCMCPP_SHARD_DATA = 3 };
+ *              launcher calls args->allreduce_sum between its partial and decision kernels.
+ *   DIM        the PARAMETER dimension is sharded, the walkers are replicated: rank r holds columns
+ *              [dim_begin, dim_begin + D_local) of every walker row (even-sized slices, see
+ *              mcmcpp_dim_slice), makes the same draws as everyone, and a separable Calculator's partial sums are
+ *              exchanged by the update kernel itself through peer-mapped tables (NVLink stores), summed in rank
+ *              order (include/mcmcpp_b200/dim_shard_kernels.cuh).  Traffic per rank is 1/world of the
+ *              single-GPU kernel's and the exchange does not grow with D.  Host-facing arrays keep the full
+ *              [W][num_params] shape; a rank reads/writes only its columns of them. */
+enum { MCMCPP_SHARD_NONE = 0, MCMCPP_SHARD_ALLGATHER = 1, MCMCPP_SHARD_PEER = 2, MCMCPP_SHARD_DATA = 3, MCMCPP_SHARD_DIM = 4 };
 
 /* built-in Calculators (include/mcmcpp_b200/targets.h); params layout as in oracle/oracle.c */
 enum {
@@ -127,6 +134,15 @@ typedef struct {
     mcmcpp_allreduce_fn allreduce_sum; /* DATA sharding with world > 1, else NULL */
     void* allreduce_ctx;
     unsigned long long* launch_count;  /* host counter: a launcher that enqueues n kernels adds n-1 (the runtime adds 1) */
+    /* DIM sharding (D above is then this rank's slice length) */
+    int32_t D_total;           /* numParams of the whole row: log(z) * (D_total - 1)  (StretchMove.h:110) */
+    int32_t dim_begin;         /* global index of local column 0 */
+    int32_t rank, world;
+    double* const* dim_partial;/* [world] every rank's partial table [2 colours][world][K] (own entry local, others peer-mapped) */
+    double* dim_z;             /* [K] draws of the colour in flight, kept between the two kernels */
+    double* dim_e;
+    int32_t* dim_j;
+    double* sync_word;         /* 1 double: operand of the stream-ordered rendezvous (allreduce_sum of 1 element) */
 } mcmcpp_halfstep_args;
 
 typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);
@@ -186,12 +202,15 @@ int mcmcpp_fp64_tensor_peak(int device, double* tflops);
 
 /* ---- multi-GPU plumbing (one process per GPU) -------------------------------------------------
  *      ALLGATHER: rank 0 makes an id, the host layer broadcasts the 128 bytes, every rank joins.
- *      PEER: every rank exports a 64-byte IPC handle of its pos array (and of a barrier word), the
+ *      PEER / DIM: every rank exports a 64-byte IPC handle (PEER: its pos array; DIM: its partial table), the
  *      host layer all-gathers them, every rank imports the others'. */
 int mcmcpp_comm_unique_id(void* id128);
 int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128);
 int mcmcpp_sampler_peer_export(mcmcpp_sampler* s, void* handle64);
 int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_ranks);
+/* DIM sharding: columns [*begin, *begin + *count) of a num_params-wide row held by `rank` (pairs of columns are dealt
+ * out so that every slice but possibly the last has even length: 16-byte aligned slices for vector loads). */
+int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,206 @@
+/*
+ * include/mcmcpp_b200/dim_shard_kernels.cuh -- MCMCPP_SHARD_DIM: the stretch-move half-step with the PARAMETER
+ * dimension sharded over the GPUs of one box (SURVEY.md s.8(e) alternative 2).
+ *
+ * Every rank holds all W walkers but only its columns [dim_begin, dim_begin + D) of each row, makes the SAME draws
+ * (j, z, log(1-u)) from the sampler's pcg64 stream, builds its slice of every proposal
+ * (MCMCpp/Movers/StretchMove.h:103-109) and the partial sum of a separable Calculator (term()/finish(), targets.h)
+ * over its columns.  The K partial sums of a colour are exchanged INSIDE the update kernel: 16 walkers per CTA, so one
+ * 128-byte line per peer is stored straight into every rank's partial table over NVLink (peer-mapped memory); a
+ * 4-byte stream-ordered rendezvous follows; the second kernel adds the `world` partials in rank order -- the same
+ * bits on every rank, so every rank takes the same Metropolis decision (StretchMove.h:112-122) -- and commits its
+ * slice of the accepted proposals by rebuilding them from the two rows (17 % of the walkers at D = 1000; cheaper
+ * than keeping every proposal).  Traffic per rank is 1/world of the single-GPU kernel's, the exchange is 8 K bytes
+ * per peer per colour whatever D is.
+ *
+ * The log-posterior is summed slice by slice (canonical 64-way order inside a slice, rank order across), so for
+ * world > 1 it carries the tolerance tier (<= 1e-12 relative); with world == 1 it is the single-GPU order, bit-exact.
+ */
+#ifndef MCMCPP_B200_DIM_SHARD_KERNELS_CUH
+#define MCMCPP_B200_DIM_SHARD_KERNELS_CUH
+
+#include "mcmcpp_b200/stretch_kernels.cuh"
+
+namespace MCMC
+{
+namespace Device
+{
+
+enum { DimWarps = 16, DimThreads = DimWarps * 32, DimBatch = 4 };
+
+/* lane l owns elements 64c + 2l, 64c + 2l + 1 of a row slice (the canonical order of targets.h) */
+template <bool VEC>
+__device__ __forceinline__ double2 dimLoad2(const double* __restrict__ row, int d, int D)
+{
+    double2 v = make_double2(0.0, 0.0);
+    if (VEC) {
+        if (d < D) v = *reinterpret_cast<const double2*>(row + d);
+    } else {
+        if (d < D) v.x = row[d];
+        if (d + 1 < D) v.y = row[d + 1];
+    }
+    return v;
+}
+
+template <bool VEC>
+__device__ __forceinline__ void dimStore2(double* __restrict__ row, int d, int D, double2 v)
+{
+    if (VEC) {
+        if (d < D) *reinterpret_cast<double2*>(row + d) = v;
+    } else {
+        if (d < D) row[d] = v.x;
+        if (d + 1 < D) row[d + 1] = v.y;
+    }
+}
+
+/* ---- phase 1: draws, proposal slice, partial sum, partial -> every rank's table ---------------------------- */
+template <class Calc, bool VEC>
+__global__ void __launch_bounds__(DimThreads) dimShardPartial(const mcmcpp_halfstep_args a, const Calc calcIn)
+{
+    __shared__ double ctaPartial[DimWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i = blockIdx.x * DimWarps + warp;           /* slot of this colour; DIM sharding owns every slot */
+    const int D = a.D;
+    double partial = 0.0;
+    if (i < a.K) {
+        Calc calc = calcIn;
+        const int w = a.half * a.K + i;
+        const int other0 = (1 - a.half) * a.K;
+        WalkerRng rng = loadRng(a, w);
+        StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+        const double* ownRow = a.pos + (size_t)w * D;
+        const double* selRow = a.pos + (size_t)(other0 + dr.j) * D;
+        double p0 = 0.0, p1 = 0.0;
+        for (int c0 = 0; c0 * 64 < D; c0 += DimBatch) {
+            double2 cur[DimBatch], sel[DimBatch];
+#pragma unroll
+            for (int b = 0; b < DimBatch; ++b) {          /* all loads of the batch in flight before the first use */
+                const int d = 64 * (c0 + b) + 2 * lane;
+                cur[b] = dimLoad2<VEC>(ownRow, d, D);
+                sel[b] = dimLoad2<VEC>(selRow, d, D);
+            }
+#pragma unroll
+            for (int b = 0; b < DimBatch; ++b) {
+                const int d = 64 * (c0 + b) + 2 * lane;
+                if (d < D) p0 = __dadd_rn(p0, calc.term(stretchPoint(sel[b].x, cur[b].x, dr.z), d));
+                if (d + 1 < D) p1 = __dadd_rn(p1, calc.term(stretchPoint(sel[b].y, cur[b].y, dr.z), d + 1));
+            }
+        }
+        double s = __dadd_rn(p0, p1);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) s = __dadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
+        partial = s;
+        if (lane == 0) {
+            storeRng(a, w, rng);
+            if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+            a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
+        }
+    }
+    if (lane == 0) ctaPartial[warp] = partial;
+    __syncthreads();
+    /* one 128-byte line per rank: thread t stores walker (t % 16)'s partial into rank (t / 16)'s table */
+    const int slot0 = blockIdx.x * DimWarps;
+    for (int t = threadIdx.x; t < a.world * DimWarps; t += DimThreads) {
+        const int q = t / DimWarps, k = t - q * DimWarps;
+        if (slot0 + k < a.K)
+            a.dim_partial[q][((size_t)a.half * a.world + a.rank) * a.K + slot0 + k] = ctaPartial[k];
+    }
+}
+
+/* ---- phase 2: rank-ordered sum, Metropolis test, commit the slice ------------------------------------------- */
+template <class Calc, bool VEC, bool TRACE>
+__global__ void __launch_bounds__(DimThreads) dimShardCommit(const mcmcpp_halfstep_args a, const Calc calcIn)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i = blockIdx.x * DimWarps + warp;
+    const int D = a.D;
+    bool accepted = false;
+    if (i < a.K) {
+        Calc calc = calcIn;
+        const int w = a.half * a.K + i;
+        const int other0 = (1 - a.half) * a.K;
+        const double* table = a.dim_partial[a.rank] + (size_t)a.half * a.world * a.K + i;
+        double sum = table[0];
+        for (int r = 1; r < a.world; ++r) sum = __dadd_rn(sum, table[(size_t)r * a.K]);
+        const double z = a.dim_z[i], e = a.dim_e[i];
+        const int j = a.dim_j[i];
+        const double scaling = __dmul_rn(log(z), (double)(a.D_total - 1));
+        const double newp = calc.finish(sum);
+        const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
+        accepted = e < diff;
+        double* ownRow = a.pos + (size_t)w * D;
+        double* chainRow = a.chain_row ? a.chain_row + (size_t)w * D : nullptr;
+        if (accepted || chainRow) {
+            const double* selRow = a.pos + (size_t)(other0 + j) * D;
+            for (int c0 = 0; c0 * 64 < D; c0 += DimBatch) {
+                double2 cur[DimBatch], sel[DimBatch];
+#pragma unroll
+                for (int b = 0; b < DimBatch; ++b) {
+                    const int d = 64 * (c0 + b) + 2 * lane;
+                    cur[b] = dimLoad2<VEC>(ownRow, d, D);
+                    sel[b] = accepted ? dimLoad2<VEC>(selRow, d, D) : cur[b];
+                }
+#pragma unroll
+                for (int b = 0; b < DimBatch; ++b) {
+                    const int d = 64 * (c0 + b) + 2 * lane;
+                    double2 v = cur[b];
+                    if (accepted) {
+                        v.x = stretchPoint(sel[b].x, cur[b].x, z);
+                        v.y = stretchPoint(sel[b].y, cur[b].y, z);
+                        dimStore2<VEC>(ownRow, d, D, v);
+                    }
+                    if (chainRow) dimStore2<VEC>(chainRow, d, D, v);
+                }
+            }
+        }
+        if (lane == 0) {
+            if (accepted) a.logp[w] = newp;
+            if (TRACE) {
+                if (i < a.trace_rows) {
+                    mcmcpp_trace t;
+                    t.j = j; t.accept = accepted ? 1 : 0; t.z = z; t.e = e; t.newp = newp; t.diff = diff;
+                    a.trace[i] = t;
+                }
+            }
+        }
+    }
+    const int blockAccepted = __syncthreads_count(accepted && lane == 0);
+    if (threadIdx.x == 0 && blockAccepted) a.accept_slots[blockIdx.x] += (unsigned long long)blockAccepted;
+}
+
+/* Launcher of a DIM-sharded colour for a separable Calculator (a VIEW of this rank's columns: term(x, d) takes the
+ * local column index).  Pass &DimShardLauncher<Calc>::launch to mcmcpp_sampler_create with shard_mode DIM. */
+template <class Calc>
+struct DimShardLauncher
+{
+    static_assert(IsSeparable<Calc>::value, "DIM sharding needs a separable Calculator: term(x, d) and finish(sum)");
+
+    template <bool VEC>
+    static int run(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream)
+    {
+        const int grid = (a.K + DimWarps - 1) / DimWarps;
+        dimShardPartial<Calc, VEC><<<grid, DimThreads, 0, stream>>>(a, calc);
+        if (a.world > 1) {
+            /* rendezvous: every rank's partials have landed in every table before anyone reads them */
+            int rc = a.allreduce_sum ? a.allreduce_sum(a.allreduce_ctx, a.sync_word, 1, stream) : MCMCPP_ERR_STATE;
+            if (rc != MCMCPP_OK) return rc;
+        }
+        if (a.trace) dimShardCommit<Calc, VEC, true><<<grid, DimThreads, 0, stream>>>(a, calc);
+        else dimShardCommit<Calc, VEC, false><<<grid, DimThreads, 0, stream>>>(a, calc);
+        if (a.launch_count) *a.launch_count += 1;
+        return launchStatus();
+    }
+
+    static int launch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)
+    {
+        const mcmcpp_halfstep_args& a = *args;
+        if (!a.dim_partial || !a.dim_z || a.K > a.max_grid * DimWarps) return MCMCPP_ERR_STATE;
+        const Calc& calc = *static_cast<const Calc*>(calculator);
+        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
+        return (a.D % 2 == 0) ? run<true>(a, calc, stream) : run<false>(a, calc, stream);
+    }
+};
+
+}
+}
+#endif

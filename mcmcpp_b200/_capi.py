@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(HERE, "libmcmcpp_b200.so")
 OK, CHAIN_FULL = 0, 1
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE, ERR_UNSUPPORTED = -1, -2, -3, -4, -5
 RNG_SEQUENTIAL, RNG_PER_WALKER = 0, 1
-SHARD_NONE, SHARD_ALLGATHER, SHARD_PEER, SHARD_DATA = 0, 1, 2, 3
+SHARD_NONE, SHARD_ALLGATHER, SHARD_PEER, SHARD_DATA, SHARD_DIM = 0, 1, 2, 3, 4
 TARGET = {"skewed_gauss_2d": 0, "rosenbrock_2d": 1, "diag_gauss": 2, "dense_gauss": 3, "linreg": 4}
 
 
@@ -58,6 +58,7 @@ SYMBOLS = {
     "mcmcpp_sampler_comm_init": (C.c_int, [_h, C.c_void_p]),
     "mcmcpp_sampler_peer_export": (C.c_int, [_h, C.c_void_p]),
     "mcmcpp_sampler_peer_import": (C.c_int, [_h, C.c_void_p]),
+    "mcmcpp_dim_slice": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 
 _lib = None

@@ -7,6 +7,7 @@
 #include <cstring>
 #include "builtin_targets.h"
 #include "mcmcpp_b200/stretch_kernels.cuh"
+#include "mcmcpp_b200/dim_shard_kernels.cuh"
 #include "mcmcpp_b200/targets.h"
 
 namespace
@@ -20,10 +21,17 @@ void storeCalc(const Calc& c, std::vector<char>* blob)
 }
 
 int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t nValues, const double* devParams,
-                        mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux)
+                        mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux, int shardMode, int dimBegin, int dimCount)
 {
     using namespace MCMC::Targets;
     *aux = nullptr;
+    if (shardMode == MCMCPP_SHARD_DIM) {
+        /* parameter-dimension sharding: separable Calculators only; the functor views this rank's columns */
+        if (kind != MCMCPP_TARGET_DIAG_GAUSS || nValues != (size_t)D) return MCMCPP_ERR_UNSUPPORTED;
+        storeCalc(DiagGaussian<double>(devParams + dimBegin, dimCount), calculator);
+        *launcher = &MCMC::Device::DimShardLauncher<DiagGaussian<double> >::launch;
+        return MCMCPP_OK;
+    }
     switch (kind) {
     case MCMCPP_TARGET_SKEWED_GAUSS_2D: {
         if (D != 2 || nValues != 1) return MCMCPP_ERR_ARG;

@@ -127,6 +127,7 @@ struct mcmcpp_sampler
 {
     mcmcpp_config cfg;
     int W = 0, D = 0, K = 0;
+    int Dl = 0, dimBegin = 0;              /* DIM sharding: local slice of the row (else Dl == D, dimBegin == 0) */
     int slotBegin = 0, slotCount = 0;      /* owned slots of each colour */
     mcmcpp_halfstep_fn launcher = nullptr;
     std::vector<char> calculator;
@@ -167,12 +168,45 @@ struct mcmcpp_sampler
     int32_t* dBarrier = nullptr;
     std::vector<void*> peerOpened;
     const double** dPeerPos = nullptr;
+    /* DIM sharding */
+    double* dDimPartial = nullptr;         /* [2][world][K] */
+    double** dDimTable = nullptr;          /* [world] device table of every rank's partial table */
+    double* dDimZ = nullptr;
+    double* dDimE = nullptr;
+    int32_t* dDimJ = nullptr;
+    double* dSyncWord = nullptr;
 };
 
 namespace
 {
 
-size_t rowDoubles(const mcmcpp_sampler* s) { return (size_t)s->W * (size_t)s->D; }
+size_t rowDoubles(const mcmcpp_sampler* s) { return (size_t)s->W * (size_t)s->D; }       /* host-facing step row */
+size_t devRowDoubles(const mcmcpp_sampler* s) { return (size_t)s->W * (size_t)s->Dl; }   /* what this rank holds of it */
+
+void dimSlice(int D, int rank, int world, int* begin, int* count)
+{
+    /* deal out PAIRS of columns: every slice but possibly the last is even (16-byte aligned rows) */
+    const int pairs = D / 2, base = pairs / world, rem = pairs % world;
+    const int b = 2 * (rank * base + std::min(rank, rem));
+    int c = 2 * (base + (rank < rem ? 1 : 0));
+    if (rank == world - 1) c = D - b;
+    *begin = b; *count = c;
+}
+
+/* device slice <-> host-facing full-width rows (plain copy when the rank holds whole rows) */
+cudaError_t copyToHostRows(mcmcpp_sampler* s, double* hostRow, const double* devRow, cudaStream_t st, cudaMemcpyKind kind = cudaMemcpyDeviceToHost)
+{
+    if (s->Dl == s->D) return cudaMemcpyAsync(hostRow, devRow, sizeof(double) * rowDoubles(s), kind, st);
+    return cudaMemcpy2DAsync(hostRow + s->dimBegin, sizeof(double) * s->D, devRow, sizeof(double) * s->Dl, sizeof(double) * s->Dl,
+                             (size_t)s->W, kind, st);
+}
+
+cudaError_t copyFromFullRows(mcmcpp_sampler* s, double* devRow, const double* fullRow, cudaStream_t st, cudaMemcpyKind kind)
+{
+    if (s->Dl == s->D) return cudaMemcpyAsync(devRow, fullRow, sizeof(double) * rowDoubles(s), kind, st);
+    return cudaMemcpy2DAsync(devRow, sizeof(double) * s->Dl, fullRow + s->dimBegin, sizeof(double) * s->D, sizeof(double) * s->Dl,
+                             (size_t)s->W, kind, st);
+}
 
 int ensureHostChain(mcmcpp_sampler* s, long long rowsNeeded)
 {
@@ -182,6 +216,7 @@ int ensureHostChain(mcmcpp_sampler* s, long long rowsNeeded)
     long long newRows = std::min(s->capRows, std::max(rowsNeeded, s->hChainRows * 2));
     double* fresh = nullptr;
     CUDA_TRY(cudaMallocHost(&fresh, sizeof(double) * rowDoubles(s) * (size_t)newRows));
+    if (s->Dl != s->D) std::memset(fresh, 0, sizeof(double) * rowDoubles(s) * (size_t)newRows);   /* columns of other ranks read 0 */
     if (s->hChain) {
         std::memcpy(fresh, s->hChain, sizeof(double) * rowDoubles(s) * (size_t)std::min(s->stored, s->hChainRows));
         cudaFreeHost(s->hChain);
@@ -195,9 +230,9 @@ int ensureDeviceChain(mcmcpp_sampler* s)
 {
     if (s->capRows == 0 || s->dChain[0]) return MCMCPP_OK;
     for (int i = 0; i < ChainSlots; ++i) {
-        CUDA_TRY(cudaMalloc(&s->dChain[i], sizeof(double) * rowDoubles(s)));
+        CUDA_TRY(cudaMalloc(&s->dChain[i], sizeof(double) * devRowDoubles(s)));
         /* rows of walkers this rank does not own stay zero so the host layer can sum shards */
-        CUDA_TRY(cudaMemsetAsync(s->dChain[i], 0, sizeof(double) * rowDoubles(s), s->stream));
+        CUDA_TRY(cudaMemsetAsync(s->dChain[i], 0, sizeof(double) * devRowDoubles(s), s->stream));
     }
     return MCMCPP_OK;
 }
@@ -248,8 +283,7 @@ int appendRowFromDeviceSlot(mcmcpp_sampler* s, int slot)
     /* side stream: wait for the black half-step, copy the row to its place in the pinned host chain */
     CUDA_TRY(cudaEventRecord(s->slotReady[slot], s->stream));
     CUDA_TRY(cudaStreamWaitEvent(s->copyStream, s->slotReady[slot], 0));
-    CUDA_TRY(cudaMemcpyAsync(s->hChain + rowDoubles(s) * (size_t)s->stored, s->dChain[slot], sizeof(double) * rowDoubles(s),
-                             cudaMemcpyDeviceToHost, s->copyStream));
+    CUDA_TRY(copyToHostRows(s, s->hChain + rowDoubles(s) * (size_t)s->stored, s->dChain[slot], s->copyStream));
     CUDA_TRY(cudaEventRecord(s->slotFree[slot], s->copyStream));
     s->slotBusy[slot] = true;
     return MCMCPP_OK;
@@ -263,7 +297,9 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     if (W <= 0 || D <= 0 || (W % 2) != 0 || W <= 2 * D) return fail(MCMCPP_ERR_ARG, "numWalkers must be even and exceed 2*numParams");
     if (cfg->alpha_num <= 0 || cfg->alpha_denom <= 0) return fail(MCMCPP_ERR_ARG, "alpha must be positive");
     if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world) return fail(MCMCPP_ERR_ARG, "bad rank/world");
-    if (cfg->shard_mode != MCMCPP_SHARD_DATA && (W / 2) % cfg->world != 0)
+    if (cfg->shard_mode == MCMCPP_SHARD_DIM && D / 2 < cfg->world)
+        return fail(MCMCPP_ERR_ARG, "DIM sharding needs at least two columns per GPU");
+    if (cfg->shard_mode != MCMCPP_SHARD_DATA && cfg->shard_mode != MCMCPP_SHARD_DIM && (W / 2) % cfg->world != 0)
         return fail(MCMCPP_ERR_ARG, "walkers per colour must divide evenly over the GPUs");
     if (cfg->world > 1 && cfg->shard_mode == MCMCPP_SHARD_NONE) return fail(MCMCPP_ERR_ARG, "world > 1 needs a shard mode");
 
@@ -276,7 +312,9 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     mcmcpp_sampler* s = new mcmcpp_sampler();
     s->cfg = *cfg;
     s->W = W; s->D = D; s->K = W / 2;
-    if (cfg->shard_mode == MCMCPP_SHARD_DATA) {      /* replicated ensemble: every rank updates every walker */
+    s->Dl = D; s->dimBegin = 0;
+    if (cfg->shard_mode == MCMCPP_SHARD_DIM) dimSlice(D, cfg->rank, cfg->world, &s->dimBegin, &s->Dl);
+    if (cfg->shard_mode == MCMCPP_SHARD_DATA || cfg->shard_mode == MCMCPP_SHARD_DIM) {   /* replicated walkers: every rank updates all */
         s->slotCount = s->K;
         s->slotBegin = 0;
     } else {
@@ -295,7 +333,7 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
         CUDA_TRY(cudaEventCreateWithFlags(&s->slotFree[i], cudaEventDisableTiming));
     }
     s->maxGrid = s->K;   /* upper bound for any launcher: one CTA per walker */
-    CUDA_TRY(cudaMalloc(&s->dPos, sizeof(double) * rowDoubles(s)));
+    CUDA_TRY(cudaMalloc(&s->dPos, sizeof(double) * devRowDoubles(s)));
     CUDA_TRY(cudaMalloc(&s->dLogp, sizeof(double) * (size_t)W));
     CUDA_TRY(cudaMalloc(&s->dRng, sizeof(uint64_t) * 2 * (size_t)W));
     CUDA_TRY(cudaMalloc(&s->dAcceptSlots, sizeof(unsigned long long) * (size_t)s->maxGrid));
@@ -305,7 +343,19 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     CUDA_TRY(cudaMemset(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid));
     CUDA_TRY(cudaMemset(s->dFlags, 0, sizeof(int32_t) * 4));
     CUDA_TRY(cudaMemset(s->dBarrier, 0, sizeof(int32_t)));
-    CUDA_TRY(cudaMemset(s->dPos, 0, sizeof(double) * rowDoubles(s)));
+    CUDA_TRY(cudaMemset(s->dPos, 0, sizeof(double) * devRowDoubles(s)));
+    if (cfg->shard_mode == MCMCPP_SHARD_DIM) {
+        const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K;
+        CUDA_TRY(cudaMalloc(&s->dDimPartial, sizeof(double) * tableDoubles));
+        CUDA_TRY(cudaMemset(s->dDimPartial, 0, sizeof(double) * tableDoubles));
+        CUDA_TRY(cudaMalloc(&s->dDimTable, sizeof(double*) * (size_t)cfg->world));
+        CUDA_TRY(cudaMalloc(&s->dDimZ, sizeof(double) * (size_t)s->K));
+        CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
+        CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * (size_t)s->K));
+        CUDA_TRY(cudaMalloc(&s->dSyncWord, sizeof(double)));
+        CUDA_TRY(cudaMemset(s->dSyncWord, 0, sizeof(double)));
+        if (cfg->world == 1) CUDA_TRY(cudaMemcpy(s->dDimTable, &s->dDimPartial, sizeof(double*), cudaMemcpyHostToDevice));
+    }
     if (cfg->trace_updates > 0) {
         CUDA_TRY(cudaMalloc(&s->dTrace, sizeof(mcmcpp_trace) * (size_t)cfg->trace_updates));
         CUDA_TRY(cudaMemset(s->dTrace, 0, sizeof(mcmcpp_trace) * (size_t)cfg->trace_updates));
@@ -316,7 +366,9 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     std::memset(&a, 0, sizeof a);
     a.pos = s->dPos; a.logp = s->dLogp; a.rng_state = s->dRng;
     a.accept_slots = s->dAcceptSlots; a.flags = s->dFlags;
-    a.W = W; a.D = D; a.K = s->K;
+    a.W = W; a.D = s->Dl; a.K = s->K;
+    a.D_total = D; a.dim_begin = s->dimBegin; a.rank = cfg->rank; a.world = cfg->world;
+    a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ; a.sync_word = s->dSyncWord;
     a.slot_begin = s->slotBegin; a.slot_count = s->slotCount; a.slots_per_rank = s->slotCount;
     a.rng_mode = cfg->rng_mode;
     const uint64_t K64 = (uint64_t)s->K;
@@ -349,8 +401,8 @@ int afterInitialState(mcmcpp_sampler* s, const double* hostRowOrNull)
         int rc = ensureHostChain(s, s->stored + 1);
         if (rc != MCMCPP_OK) return rc;
         double* dst = s->hChain + rowDoubles(s) * (size_t)s->stored;
-        if (hostRowOrNull) std::memcpy(dst, hostRowOrNull, sizeof(double) * rowDoubles(s));
-        else CUDA_TRY(cudaMemcpyAsync(dst, s->dPos, sizeof(double) * rowDoubles(s), cudaMemcpyDeviceToHost, s->stream));
+        if (hostRowOrNull && s->Dl == s->D) std::memcpy(dst, hostRowOrNull, sizeof(double) * rowDoubles(s));
+        else CUDA_TRY(copyToHostRows(s, dst, s->dPos, s->stream));
     }
     ++s->stored;
     CUDA_TRY(cudaStreamSynchronize(s->stream));
@@ -396,7 +448,7 @@ int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, con
         if (e != cudaSuccess) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(MCMCPP_ERR_CUDA, cudaGetErrorString(e)); }
     }
     rc = mcmcpp_builtin_bind(target_kind, s->W, s->D, params, num_params_values, s->dParams, &s->launcher, &s->calculator,
-                             &s->builtinAux);
+                             &s->builtinAux, cfg->shard_mode, s->dimBegin, s->Dl);
     if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "unknown built-in target or bad parameter count"); }
     return MCMCPP_OK;
 }
@@ -410,6 +462,7 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     if (s->comm && nccl().ok) nccl().CommDestroy(s->comm);
     for (void* p : s->peerOpened) cudaIpcCloseMemHandle(p);
     cudaFree(s->dPeerPos);
+    cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ); cudaFree(s->dSyncWord);
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
     cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
     mcmcpp_builtin_release(s->builtinAux);
@@ -431,7 +484,7 @@ int mcmcpp_sampler_set_initial(mcmcpp_sampler* s, const double* positions_host, 
 {
     if (!s || !positions_host || !aux_host) return fail(MCMCPP_ERR_ARG, "null argument");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
-    CUDA_TRY(cudaMemcpyAsync(s->dPos, positions_host, sizeof(double) * rowDoubles(s), cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(copyFromFullRows(s, s->dPos, positions_host, s->stream, cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpyAsync(s->dLogp, aux_host, sizeof(double) * (size_t)s->W, cudaMemcpyHostToDevice, s->stream));
     return afterInitialState(s, positions_host);
 }
@@ -440,7 +493,7 @@ int mcmcpp_sampler_set_initial_device(mcmcpp_sampler* s, const double* positions
 {
     if (!s || !positions_dev || !aux_dev) return fail(MCMCPP_ERR_ARG, "null argument");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
-    CUDA_TRY(cudaMemcpyAsync(s->dPos, positions_dev, sizeof(double) * rowDoubles(s), cudaMemcpyDeviceToDevice, s->stream));
+    CUDA_TRY(copyFromFullRows(s, s->dPos, positions_dev, s->stream, cudaMemcpyDeviceToDevice));
     CUDA_TRY(cudaMemcpyAsync(s->dLogp, aux_dev, sizeof(double) * (size_t)s->W, cudaMemcpyDeviceToDevice, s->stream));
     return afterInitialState(s, nullptr);
 }
@@ -462,6 +515,8 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     if (s->cfg.world > 1 && !s->comm) return fail(MCMCPP_ERR_STATE, "world > 1 but no communicator (mcmcpp_sampler_comm_init)");
     if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_PEER && !s->dPeerPos)
         return fail(MCMCPP_ERR_STATE, "PEER sharding needs mcmcpp_sampler_peer_import");
+    if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_DIM && s->peerOpened.empty())
+        return fail(MCMCPP_ERR_STATE, "DIM sharding needs mcmcpp_sampler_peer_import");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     const bool chainOn = s->capRows > 0;
     int rc = MCMCPP_OK;
@@ -541,8 +596,7 @@ int mcmcpp_sampler_store_current(mcmcpp_sampler* s)
     if (s->capRows > 0 && s->stored < s->capRows) {
         int rc = ensureHostChain(s, s->stored + 1);
         if (rc != MCMCPP_OK) return rc;
-        CUDA_TRY(cudaMemcpyAsync(s->hChain + rowDoubles(s) * (size_t)s->stored, s->dPos, sizeof(double) * rowDoubles(s),
-                                 cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(copyToHostRows(s, s->hChain + rowDoubles(s) * (size_t)s->stored, s->dPos, s->stream));
         CUDA_TRY(cudaStreamSynchronize(s->stream));
     }
     ++s->stored;    /* EnsembleSampler.h:240-241 */
@@ -578,8 +632,7 @@ int mcmcpp_sampler_get_state(mcmcpp_sampler* s, double* positions_host, double* 
 {
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
-    if (positions_host)
-        CUDA_TRY(cudaMemcpyAsync(positions_host, s->dPos, sizeof(double) * rowDoubles(s), cudaMemcpyDeviceToHost, s->stream));
+    if (positions_host) CUDA_TRY(copyToHostRows(s, positions_host, s->dPos, s->stream));   /* DIM: this rank's columns only */
     if (aux_host) CUDA_TRY(cudaMemcpyAsync(aux_host, s->dLogp, sizeof(double) * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     return MCMCPP_OK;
@@ -643,7 +696,7 @@ int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128)
     ncclUniqueId id;
     std::memcpy(&id, id128, sizeof id);
     NCCL_TRY(nccl().CommInitRank(&s->comm, s->cfg.world, id, s->cfg.rank));
-    if (s->cfg.shard_mode == MCMCPP_SHARD_DATA) {
+    if (s->cfg.shard_mode == MCMCPP_SHARD_DATA || s->cfg.shard_mode == MCMCPP_SHARD_DIM) {
         s->base.allreduce_sum = &allreduceSum;
         s->base.allreduce_ctx = s;
     }
@@ -656,7 +709,7 @@ int mcmcpp_sampler_peer_export(mcmcpp_sampler* s, void* handle64)
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     cudaIpcMemHandle_t h;
-    CUDA_TRY(cudaIpcGetMemHandle(&h, s->dPos));
+    CUDA_TRY(cudaIpcGetMemHandle(&h, s->cfg.shard_mode == MCMCPP_SHARD_DIM ? (void*)s->dDimPartial : (void*)s->dPos));
     std::memcpy(handle64, &h, sizeof h);
     return MCMCPP_OK;
 }
@@ -665,9 +718,10 @@ int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_rank
 {
     if (!s || !handles64_all_ranks) return fail(MCMCPP_ERR_ARG, "null argument");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
+    const bool dim = s->cfg.shard_mode == MCMCPP_SHARD_DIM;
     std::vector<const double*> ptrs((size_t)s->cfg.world, nullptr);
     for (int r = 0; r < s->cfg.world; ++r) {
-        if (r == s->cfg.rank) { ptrs[(size_t)r] = s->dPos; continue; }
+        if (r == s->cfg.rank) { ptrs[(size_t)r] = dim ? s->dDimPartial : s->dPos; continue; }
         cudaIpcMemHandle_t h;
         std::memcpy(&h, (const char*)handles64_all_ranks + 64 * (size_t)r, sizeof h);
         void* p = nullptr;
@@ -675,9 +729,20 @@ int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_rank
         s->peerOpened.push_back(p);
         ptrs[(size_t)r] = (const double*)p;
     }
+    if (dim) {
+        CUDA_TRY(cudaMemcpy(s->dDimTable, ptrs.data(), sizeof(double*) * (size_t)s->cfg.world, cudaMemcpyHostToDevice));
+        return MCMCPP_OK;
+    }
     CUDA_TRY(cudaMalloc(&s->dPeerPos, sizeof(double*) * (size_t)s->cfg.world));
     CUDA_TRY(cudaMemcpy(s->dPeerPos, ptrs.data(), sizeof(double*) * (size_t)s->cfg.world, cudaMemcpyHostToDevice));
     s->base.peer_pos = s->dPeerPos;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count)
+{
+    if (!begin || !count || world < 1 || rank < 0 || rank >= world || num_params / 2 < world) return fail(MCMCPP_ERR_ARG, "bad slice request");
+    dimSlice(num_params, rank, world, begin, count);
     return MCMCPP_OK;
 }
 

@@ -36,6 +36,18 @@ def shard_data_rows(num_rows, rank, world):
     return begin, begin + base + (1 if rank < rem else 0)
 
 
+def dim_slice(num_params, rank, world):
+    """DIM sharding: columns [begin, end) of a walker row held by `rank` -- pairs of columns dealt out so that every
+    slice but possibly the last is even (mirrors mcmcpp_dim_slice in the C-ABI)."""
+    pairs = num_params // 2
+    base, rem = divmod(pairs, world)
+    begin = 2 * (rank * base + min(rank, rem))
+    count = 2 * (base + (1 if rank < rem else 0))
+    if rank == world - 1:
+        count = num_params - begin
+    return begin, begin + count
+
+
 def sequential_draw_index(step, half, slot, num_walkers):
     """First (0-based) draw of the sampler's single pcg64 stream used by (step, colour, slot):
     3 draws per update in red-then-black walker order -- independent of the GPU count."""
@@ -59,7 +71,7 @@ def connect(sampler, group=None):
         ident[0] = buf.raw
     dist.broadcast_object_list(ident, src=0, group=group)
     sampler.commInit(ident[0])
-    if sampler.shardMode == "peer":
+    if sampler.shardMode in ("peer", "dim"):
         handles = [None] * sampler.world
         dist.all_gather_object(handles, sampler.peerExport(), group=group)
         sampler.peerImport(handles)
@@ -71,7 +83,7 @@ def reduce_counts(sampler, group=None):
     import torch
     import torch.distributed as dist
     a, t = sampler._counts()
-    if sampler.world == 1 or sampler.shardMode == "data":      # DATA sharding: the ensemble is replicated on every rank
+    if sampler.world == 1 or sampler.shardMode in ("data", "dim"):      # DATA / DIM sharding: every rank counts every walker
         return a, t
     dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
     v = torch.tensor([a, t], dtype=torch.int64, device=dev)

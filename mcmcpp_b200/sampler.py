@@ -109,7 +109,7 @@ class EnsembleSampler:
             rng_mode={"sequential": _capi.RNG_SEQUENTIAL, "per_walker": _capi.RNG_PER_WALKER}[rngMode],
             alpha_num=move.alpha[0], alpha_denom=move.alpha[1], device=int(device), rank=self.rank, world=self.world,
             shard_mode={"none": _capi.SHARD_NONE, "allgather": _capi.SHARD_ALLGATHER, "peer": _capi.SHARD_PEER,
-                        "data": _capi.SHARD_DATA}[shardMode],
+                        "data": _capi.SHARD_DATA, "dim": _capi.SHARD_DIM}[shardMode],
             trace_updates=int(traceUpdates), max_chain_bytes=int(maxChainSizeBytes))
         self.shardMode = shardMode
         params = np.ascontiguousarray(move.calc.params(), dtype=np.float64)
@@ -207,7 +207,8 @@ class EnsembleSampler:
 
     # -- walker state (Walker::getCurrState / getCurrAuxData) ---------------------------------
     def getWalkerState(self):
-        pos = np.empty((self.numWalkers, self.numParams))
+        # DIM sharding: only this rank's columns are written (parallel.dim_slice); the others read 0
+        pos = np.zeros((self.numWalkers, self.numParams))
         aux = np.empty(self.numWalkers)
         check(self._lib.mcmcpp_sampler_get_state(self._h, pos.ctypes.data, aux.ctypes.data))
         return pos, aux

@@ -90,3 +90,26 @@ def test_device_rng_header_host_form(tmp_path):
     assert out[8].split() == ["150", "0x1.3c1b2b7d9b63cp-1", "-0x1.36caf79505832p-3"]
     assert out[9].split() == ["38", "0x1.994069f20ce4fp-1", "-0x1.fc6a19cd94141p-7"]
     assert out[10] == "0"
+
+
+def test_dim_slices_match_the_c_abi_and_tile_the_row():
+    """DIM sharding: the Python shard arithmetic (parallel.dim_slice) is the C-ABI's (mcmcpp_dim_slice); slices tile
+    [0, D), and every slice but possibly the last is even (16-byte aligned rows on the device)."""
+    import ctypes as C
+    from mcmcpp_b200 import _capi, parallel
+    L = _capi.lib()
+    for D in (2, 7, 8, 50, 100, 125, 1000, 1001, 1023):
+        for world in (1, 2, 3, 4, 8):
+            if D // 2 < world:
+                b, c = C.c_int(), C.c_int()
+                assert L.mcmcpp_dim_slice(D, 0, world, C.byref(b), C.byref(c)) == _capi.ERR_ARG
+                continue
+            nxt = 0
+            for r in range(world):
+                b, c = C.c_int(), C.c_int()
+                assert L.mcmcpp_dim_slice(D, r, world, C.byref(b), C.byref(c)) == 0
+                assert (b.value, b.value + c.value) == parallel.dim_slice(D, r, world)
+                assert b.value == nxt and c.value > 0 and b.value % 2 == 0
+                assert c.value % 2 == 0 or r == world - 1
+                nxt = b.value + c.value
+            assert nxt == D

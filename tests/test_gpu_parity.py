@@ -266,3 +266,22 @@ def test_c5_full_size_linreg_against_sufficient_statistics():
     assert np.allclose(aux[moved], closed(pos[moved]), rtol=1e-9, atol=0)
     assert W + int(moved.sum()) <= s.getAcceptedSteps() <= 3 * W
     s.close()
+
+
+@pytest.mark.parametrize("W,D,steps", [(256, 9, 8), (512, 100, 6), (512, 125, 6), (2048, 500, 3), (2048, 1000, 3), (300, 1001, 2)])
+def test_dim_shard_kernels_single_rank_bit_exact(port, W, D, steps):
+    """The two-kernel DIM-sharded half-step (partial sums -> table -> rank-ordered sum -> commit) with world = 1 is the
+    single-GPU summation order: bit-exact against the oracle, chain and trace included (even and odd row lengths)."""
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    init, lp = seeded_init(port, "diag_gauss", iv, W, D, 200 + D)
+    s = make_sampler("diag_gauss", iv, W, D, seed=1, traceUpdates=W, shardMode="dim")
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    assert s.getLaunchCount() == 4 * steps
+    o = port.run("diag_gauss", iv, init, lp, steps, seed=1, want_trace=True)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum())
+    assert_trace_equal(s.getTrace(W), o["trace"][:W])
+    s.close()
