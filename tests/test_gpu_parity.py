@@ -268,7 +268,7 @@ def test_c5_full_size_linreg_against_sufficient_statistics():
     s.close()
 
 
-@pytest.mark.parametrize("W,D,steps", [(256, 9, 8), (512, 100, 6), (512, 125, 6), (2048, 500, 3), (2048, 1000, 3), (300, 1001, 2)])
+@pytest.mark.parametrize("W,D,steps", [(256, 9, 8), (512, 100, 6), (512, 125, 6), (2048, 500, 3), (2048, 1000, 3), (2100, 1001, 2)])
 def test_dim_shard_kernels_single_rank_bit_exact(port, W, D, steps):
     """The two-kernel DIM-sharded half-step (partial sums -> table -> rank-ordered sum -> commit) with world = 1 is the
     single-GPU summation order: bit-exact against the oracle, chain and trace included (even and odd row lengths)."""
