@@ -384,7 +384,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
-    ap.add_argument("--shard", default="peer", choices=["allgather", "peer", "dim"])
+    ap.add_argument("--shard", default="dim", choices=["allgather", "peer", "dim"])
     ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

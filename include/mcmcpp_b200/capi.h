@@ -142,6 +142,9 @@ typedef struct {
     double* dim_z;             /* [K] draws of the colour in flight, kept between the two kernels */
     double* dim_e;
     int32_t* dim_j;
+    int32_t* dim_list;         /* [K] walkers the commit kernel must touch (bit 31 = accepted) */
+    int32_t* dim_count;        /* [1] entries in dim_list */
+    int32_t sm_count;          /* multiprocessors of the device (persistent grids) */
     double* sync_word;         /* 1 double: operand of the stream-ordered rendezvous (allreduce_sum of 1 element) */
 } mcmcpp_halfstep_args;
 

@@ -7,10 +7,10 @@
  * (MCMCpp/Movers/StretchMove.h:103-109) and the partial sum of a separable Calculator (term()/finish(), targets.h)
  * over its columns.  The K partial sums of a colour are exchanged INSIDE the update kernel: 16 walkers per CTA, so one
  * 128-byte line per peer is stored straight into every rank's partial table over NVLink (peer-mapped memory); a
- * 4-byte stream-ordered rendezvous follows; the second kernel adds the `world` partials in rank order -- the same
- * bits on every rank, so every rank takes the same Metropolis decision (StretchMove.h:112-122) -- and commits its
- * slice of the accepted proposals by rebuilding them from the two rows (17 % of the walkers at D = 1000; cheaper
- * than keeping every proposal).  Traffic per rank is 1/world of the single-GPU kernel's, the exchange is 8 K bytes
+ * stream-ordered rendezvous follows; the decision kernel adds the `world` partials in rank order -- the same
+ * bits on every rank, so every rank takes the same Metropolis decision (StretchMove.h:112-122) -- and lists the
+ * accepted walkers; the commit kernel rebuilds the accepted proposals' slices from the two rows (17 % of the
+ * walkers at D = 1000; cheaper than keeping every proposal).  Traffic per rank is 1/world of the single-GPU kernel's, the exchange is 8 K bytes
  * per peer per colour whatever D is.
  *
  * The log-posterior is summed slice by slice (canonical 64-way order inside a slice, rank order across), so for
@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(DimThreads) dimShardPartial(const mcmcpp_halfs
         }
     }
     if (lane == 0) ctaPartial[warp] = partial;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *a.dim_count = 0;     /* the previous colour's commit is done (stream order) */
     __syncthreads();
     /* one 128-byte line per rank: thread t stores walker (t % 16)'s partial into rank (t / 16)'s table */
     const int slot0 = blockIdx.x * DimWarps;
@@ -107,65 +108,158 @@ __global__ void __launch_bounds__(DimThreads) dimShardPartial(const mcmcpp_halfs
     }
 }
 
-/* ---- phase 2: rank-ordered sum, Metropolis test, commit the slice ------------------------------------------- */
-template <class Calc, bool VEC, bool TRACE>
-__global__ void __launch_bounds__(DimThreads) dimShardCommit(const mcmcpp_halfstep_args a, const Calc calcIn)
+
+/* ---- phase 1, TMA form (even slices): 4 warps per CTA, WPW walkers per warp all in flight at once ------------
+ * Lane q < WPW makes walker q's draws (the pcg64 work is done once per walker, not once per lane) and issues that
+ * walker's two cp.async.bulk copies (own slice, partner slice) onto the walker's own mbarrier; the warp then reduces
+ * the walkers one after the other from shared memory.  WPW is chosen so that a CTA stages ~64 KB whatever the slice
+ * length is (3 CTAs per SM -> ~190 KB of loads outstanding per SM, as in stretchHalfStepBulk). */
+enum { DimBulkWarps = 4 };
+
+template <class Calc, int WPW>
+__global__ void __launch_bounds__(DimBulkWarps * 32) dimShardPartialBulk(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride)
 {
+    extern __shared__ __align__(128) unsigned char dimSmem[];
+    constexpr int NW = DimBulkWarps * WPW;                 /* walkers per CTA */
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int i = blockIdx.x * DimWarps + warp;
     const int D = a.D;
-    bool accepted = false;
+    const uint32_t rowBytes = (uint32_t)D * 8u;
+    unsigned char* rows = dimSmem + (size_t)warp * WPW * 2u * rowStride;
+    unsigned char* barBase = dimSmem + (size_t)NW * 2u * rowStride;
+    double* ctaPartial = reinterpret_cast<double*>(barBase + 8u * NW);
+    const int slot0 = blockIdx.x * NW;
+    const int group0 = slot0 + warp * WPW;
+    Calc calc = calcIn;
+
+    double z = 1.0;
+    if (lane < WPW && group0 + lane < a.K) {
+        const int i = group0 + lane;
+        const int w = a.half * a.K + i;
+        const int other0 = (1 - a.half) * a.K;
+        WalkerRng rng = loadRng(a, w);
+        StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+        const uint32_t bar = smemAddr(barBase + 8u * (warp * WPW + lane));
+        mbarInit(bar, 1);
+        mbarExpectTx(bar, 2u * rowBytes);
+        bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride), a.pos + (size_t)w * D, rowBytes, bar);
+        bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride + rowStride), a.pos + (size_t)(other0 + dr.j) * D, rowBytes, bar);
+        storeRng(a, w, rng);
+        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+        a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
+        z = dr.z;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < WPW; ++q) {
+        const double zq = __shfl_sync(0xffffffffu, z, q);
+        double s = 0.0;
+        if (group0 + q < a.K) {                                  /* warp-uniform */
+            mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
+            const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
+            const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
+            double p0 = 0.0, p1 = 0.0;
+            for (int d = 2 * lane; d < D; d += 64) {
+                const double2 c = *reinterpret_cast<const double2*>(ownS + d);
+                const double2 t = *reinterpret_cast<const double2*>(selS + d);
+                p0 = __dadd_rn(p0, calc.term(stretchPoint(t.x, c.x, zq), d));
+                p1 = __dadd_rn(p1, calc.term(stretchPoint(t.y, c.y, zq), d + 1));
+            }
+            s = __dadd_rn(p0, p1);
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) s = __dadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
+        }
+        if (lane == 0) ctaPartial[warp * WPW + q] = s;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) *a.dim_count = 0;     /* the previous colour's commit is done (stream order) */
+    __syncthreads();
+    /* NW consecutive partials (64..256 bytes) to every rank's table */
+    for (int t = threadIdx.x; t < a.world * NW; t += DimBulkWarps * 32) {
+        const int r = t / NW, k = t - r * NW;
+        if (slot0 + k < a.K)
+            a.dim_partial[r][((size_t)a.half * a.world + a.rank) * a.K + slot0 + k] = ctaPartial[k];
+    }
+}
+
+/* ---- phase 2a: rank-ordered sum and Metropolis test, one THREAD per walker; work list for the commit ---------
+ * Accepted walkers are a minority (17 % at D = 1000), so the commit runs over a compacted list (warp-aggregated
+ * append; the order of the list does not matter) instead of leaving 5 warps in 6 idle.  On stored steps every
+ * walker is listed (its chain row must be written either way); bit 31 of an entry = accepted. */
+template <class Calc, bool TRACE>
+__global__ void __launch_bounds__(256) dimShardDecide(const mcmcpp_halfstep_args a, const Calc calcIn)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    bool accepted = false, listed = false;
     if (i < a.K) {
         Calc calc = calcIn;
         const int w = a.half * a.K + i;
-        const int other0 = (1 - a.half) * a.K;
         const double* table = a.dim_partial[a.rank] + (size_t)a.half * a.world * a.K + i;
         double sum = table[0];
         for (int r = 1; r < a.world; ++r) sum = __dadd_rn(sum, table[(size_t)r * a.K]);
         const double z = a.dim_z[i], e = a.dim_e[i];
-        const int j = a.dim_j[i];
         const double scaling = __dmul_rn(log(z), (double)(a.D_total - 1));
         const double newp = calc.finish(sum);
         const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
         accepted = e < diff;
-        double* ownRow = a.pos + (size_t)w * D;
-        double* chainRow = a.chain_row ? a.chain_row + (size_t)w * D : nullptr;
-        if (accepted || chainRow) {
-            const double* selRow = a.pos + (size_t)(other0 + j) * D;
-            for (int c0 = 0; c0 * 64 < D; c0 += DimBatch) {
-                double2 cur[DimBatch], sel[DimBatch];
-#pragma unroll
-                for (int b = 0; b < DimBatch; ++b) {
-                    const int d = 64 * (c0 + b) + 2 * lane;
-                    cur[b] = dimLoad2<VEC>(ownRow, d, D);
-                    sel[b] = accepted ? dimLoad2<VEC>(selRow, d, D) : cur[b];
-                }
-#pragma unroll
-                for (int b = 0; b < DimBatch; ++b) {
-                    const int d = 64 * (c0 + b) + 2 * lane;
-                    double2 v = cur[b];
-                    if (accepted) {
-                        v.x = stretchPoint(sel[b].x, cur[b].x, z);
-                        v.y = stretchPoint(sel[b].y, cur[b].y, z);
-                        dimStore2<VEC>(ownRow, d, D, v);
-                    }
-                    if (chainRow) dimStore2<VEC>(chainRow, d, D, v);
-                }
-            }
-        }
-        if (lane == 0) {
-            if (accepted) a.logp[w] = newp;
-            if (TRACE) {
-                if (i < a.trace_rows) {
-                    mcmcpp_trace t;
-                    t.j = j; t.accept = accepted ? 1 : 0; t.z = z; t.e = e; t.newp = newp; t.diff = diff;
-                    a.trace[i] = t;
-                }
+        listed = accepted || a.chain_row != nullptr;
+        if (accepted) a.logp[w] = newp;
+        if (TRACE) {
+            if (i < a.trace_rows) {
+                mcmcpp_trace t;
+                t.j = a.dim_j[i]; t.accept = accepted ? 1 : 0; t.z = z; t.e = e; t.newp = newp; t.diff = diff;
+                a.trace[i] = t;
             }
         }
     }
-    const int blockAccepted = __syncthreads_count(accepted && lane == 0);
+    const unsigned ballot = __ballot_sync(0xffffffffu, listed);
+    if (ballot) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(a.dim_count, __popc(ballot));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (listed) a.dim_list[base + __popc(ballot & ((1u << lane) - 1u))] = i | (accepted ? (int)0x80000000 : 0);
+    }
+    const int blockAccepted = __syncthreads_count(accepted);
     if (threadIdx.x == 0 && blockAccepted) a.accept_slots[blockIdx.x] += (unsigned long long)blockAccepted;
+}
+
+/* ---- phase 2b: commit the listed walkers' slices (persistent CTAs; vector loads, all of a warp's loads first) -- */
+template <bool VEC>
+__global__ void __launch_bounds__(DimThreads) dimShardCommit(const mcmcpp_halfstep_args a)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int D = a.D;
+    const int count = *a.dim_count;
+    const int other0 = (1 - a.half) * a.K;
+    for (int idx = blockIdx.x * DimWarps + warp; idx < count; idx += gridDim.x * DimWarps) {
+        const int entry = a.dim_list[idx];
+        const bool accepted = entry < 0;
+        const int i = entry & 0x7fffffff;
+        const int w = a.half * a.K + i;
+        const double z = a.dim_z[i];
+        double* ownRow = a.pos + (size_t)w * D;
+        double* chainRow = a.chain_row ? a.chain_row + (size_t)w * D : nullptr;
+        const double* selRow = a.pos + (size_t)(other0 + a.dim_j[i]) * D;
+        for (int c0 = 0; c0 * 64 < D; c0 += 2 * DimBatch) {
+            double2 cur[2 * DimBatch], sel[2 * DimBatch];
+#pragma unroll
+            for (int b = 0; b < 2 * DimBatch; ++b) {
+                const int d = 64 * (c0 + b) + 2 * lane;
+                cur[b] = dimLoad2<VEC>(ownRow, d, D);
+                sel[b] = accepted ? dimLoad2<VEC>(selRow, d, D) : cur[b];
+            }
+#pragma unroll
+            for (int b = 0; b < 2 * DimBatch; ++b) {
+                const int d = 64 * (c0 + b) + 2 * lane;
+                double2 v = cur[b];
+                if (accepted) {
+                    v.x = stretchPoint(sel[b].x, cur[b].x, z);
+                    v.y = stretchPoint(sel[b].y, cur[b].y, z);
+                    dimStore2<VEC>(ownRow, d, D, v);
+                }
+                if (chainRow) dimStore2<VEC>(chainRow, d, D, v);
+            }
+        }
+    }
 }
 
 /* Launcher of a DIM-sharded colour for a separable Calculator (a VIEW of this rank's columns: term(x, d) takes the
@@ -175,26 +269,53 @@ struct DimShardLauncher
 {
     static_assert(IsSeparable<Calc>::value, "DIM sharding needs a separable Calculator: term(x, d) and finish(sum)");
 
+    template <int WPW>
+    static void partialBulk(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
+    {
+        constexpr int NW = DimBulkWarps * WPW;
+        static bool attr = false;
+        if (!attr) { cudaFuncSetAttribute(dimShardPartialBulk<Calc, WPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr = true; }
+        const size_t smem = (size_t)NW * 2u * rowStride + 16u * NW;
+        dimShardPartialBulk<Calc, WPW><<<(a.K + NW - 1) / NW, DimBulkWarps * 32, smem, stream>>>(a, calc, rowStride);
+    }
+
     template <bool VEC>
     static int run(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream)
     {
         const int grid = (a.K + DimWarps - 1) / DimWarps;
-        dimShardPartial<Calc, VEC><<<grid, DimThreads, 0, stream>>>(a, calc);
+        const uint32_t rowStride = ((uint32_t)a.D * 8u + 127u) & ~127u;
+        const size_t perWalker = 2u * (size_t)rowStride;
+        if (VEC && !bulkKernelDisabled() && DimBulkWarps * perWalker <= 226 * 1024) {
+            if (DimBulkWarps * 8 * perWalker <= 72 * 1024) partialBulk<8>(a, calc, stream, rowStride);
+            else if (DimBulkWarps * 4 * perWalker <= 72 * 1024) partialBulk<4>(a, calc, stream, rowStride);
+            else if (DimBulkWarps * 2 * perWalker <= 72 * 1024) partialBulk<2>(a, calc, stream, rowStride);
+            else partialBulk<1>(a, calc, stream, rowStride);
+        } else {
+            dimShardPartial<Calc, VEC><<<grid, DimThreads, 0, stream>>>(a, calc);
+        }
         if (a.world > 1) {
             /* rendezvous: every rank's partials have landed in every table before anyone reads them */
             int rc = a.allreduce_sum ? a.allreduce_sum(a.allreduce_ctx, a.sync_word, 1, stream) : MCMCPP_ERR_STATE;
             if (rc != MCMCPP_OK) return rc;
         }
-        if (a.trace) dimShardCommit<Calc, VEC, true><<<grid, DimThreads, 0, stream>>>(a, calc);
-        else dimShardCommit<Calc, VEC, false><<<grid, DimThreads, 0, stream>>>(a, calc);
-        if (a.launch_count) *a.launch_count += 1;
+        const int dgrid = (a.K + 255) / 256;
+        if (a.trace) dimShardDecide<Calc, true><<<dgrid, 256, 0, stream>>>(a, calc);
+        else dimShardDecide<Calc, false><<<dgrid, 256, 0, stream>>>(a, calc);
+        static int perSm = 0;                                       /* persistent grid: what is resident at once */
+        if (perSm == 0) {
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardCommit<VEC>, DimThreads, 0) != cudaSuccess || perSm < 1) perSm = 1;
+        }
+        int cgrid = (a.sm_count > 0 ? a.sm_count : 148) * perSm;
+        if (cgrid > grid) cgrid = grid;
+        dimShardCommit<VEC><<<cgrid, DimThreads, 0, stream>>>(a);
+        if (a.launch_count) *a.launch_count += 2;
         return launchStatus();
     }
 
     static int launch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)
     {
         const mcmcpp_halfstep_args& a = *args;
-        if (!a.dim_partial || !a.dim_z || a.K > a.max_grid * DimWarps) return MCMCPP_ERR_STATE;
+        if (!a.dim_partial || !a.dim_z || !a.dim_list || !a.dim_count) return MCMCPP_ERR_STATE;
         const Calc& calc = *static_cast<const Calc*>(calculator);
         cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
         return (a.D % 2 == 0) ? run<true>(a, calc, stream) : run<false>(a, calc, stream);

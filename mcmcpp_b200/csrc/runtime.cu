@@ -174,6 +174,7 @@ struct mcmcpp_sampler
     double* dDimZ = nullptr;
     double* dDimE = nullptr;
     int32_t* dDimJ = nullptr;
+    int32_t* dDimList = nullptr;           /* [K] + [1] count */
     double* dSyncWord = nullptr;
 };
 
@@ -352,6 +353,8 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
         CUDA_TRY(cudaMalloc(&s->dDimZ, sizeof(double) * (size_t)s->K));
         CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
         CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * (size_t)s->K));
+        CUDA_TRY(cudaMalloc(&s->dDimList, sizeof(int32_t) * ((size_t)s->K + 1)));
+        CUDA_TRY(cudaMemset(s->dDimList, 0, sizeof(int32_t) * ((size_t)s->K + 1)));
         CUDA_TRY(cudaMalloc(&s->dSyncWord, sizeof(double)));
         CUDA_TRY(cudaMemset(s->dSyncWord, 0, sizeof(double)));
         if (cfg->world == 1) CUDA_TRY(cudaMemcpy(s->dDimTable, &s->dDimPartial, sizeof(double*), cudaMemcpyHostToDevice));
@@ -369,6 +372,8 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     a.W = W; a.D = s->Dl; a.K = s->K;
     a.D_total = D; a.dim_begin = s->dimBegin; a.rank = cfg->rank; a.world = cfg->world;
     a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ; a.sync_word = s->dSyncWord;
+    a.dim_list = s->dDimList; a.dim_count = s->dDimList ? s->dDimList + s->K : nullptr;
+    { int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device); a.sm_count = sms; }
     a.slot_begin = s->slotBegin; a.slot_count = s->slotCount; a.slots_per_rank = s->slotCount;
     a.rng_mode = cfg->rng_mode;
     const uint64_t K64 = (uint64_t)s->K;
@@ -462,7 +467,7 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     if (s->comm && nccl().ok) nccl().CommDestroy(s->comm);
     for (void* p : s->peerOpened) cudaIpcCloseMemHandle(p);
     cudaFree(s->dPeerPos);
-    cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ); cudaFree(s->dSyncWord);
+    cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ); cudaFree(s->dDimList); cudaFree(s->dSyncWord);
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
     cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
     mcmcpp_builtin_release(s->builtinAux);

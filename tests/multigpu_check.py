@@ -45,7 +45,7 @@ def dim_sharded_diag_gauss(port, rank, world, local):
     """DIM sharding: every rank holds its columns of all walkers; partial sums exchanged through peer-mapped tables.
     Decisions must be the oracle's; this rank's columns of positions and chain bit-exact; log-probs within 1e-12."""
     bad = 0
-    for W, D, steps in ((512, 100, 6), (1024, 1000, 4), (256, 37, 5)):
+    for W, D, steps in ((512, 100, 6), (2048, 1000, 4), (256, 37, 5), (2048, 500, 3), (1024, 250, 3)):
         iv = 1.0 / (1.0 + (np.arange(D) % 10))
         rng = np.random.default_rng(23)
         init = rng.standard_normal((W, D))
