@@ -240,8 +240,11 @@ def gpu_arm(args):
         print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
     desc, kind, W, D, Wc, cpu_steps = WORKLOADS[args.workload]
     params = target_params(kind, D)
-    shard = "data" if kind == "linreg" else args.shard
-    if world == 1 and shard != "dim":           # dim with one rank = the two-kernel form on one GPU (overhead measurement)
+    # default sharding per workload: C5 shards its data rows, C4 (separable) its parameter dimension, the rest walkers
+    shard = args.shard or ("data" if kind == "linreg" else "dim" if kind == "diag_gauss" else "peer")
+    if kind == "linreg":
+        shard = "data"
+    if world == 1 and args.shard != "dim":      # explicit dim with one rank = the three-kernel form on one GPU (overhead measurement)
         shard = "none"
     rng_mode = args.rng
 
@@ -384,7 +387,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
-    ap.add_argument("--shard", default="dim", choices=["allgather", "peer", "dim"])
+    ap.add_argument("--shard", default=None, choices=["allgather", "peer", "dim"])
     ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

@@ -11,8 +11,9 @@
  * reference; the log-posterior is summed in tensor-core order, so it carries the tolerance tier (<= 1e-12 relative,
  * SURVEY.md s.8(c) tier B) and decisions agree unless one lands within that distance of its threshold.
  *
- * Persistent CTAs (one per SM, P loaded once), 8 warps: warp w owns rows 8w..8w+7 of the tile and all D/8 column
- * blocks (accumulators in registers).  Shared-memory row stride = 4 mod 16 doubles -> conflict-free fragment loads.
+ * Persistent CTAs (one per SM, P loaded once) of two 8-warp groups; each group takes 32-walker tiles from a dynamic
+ * counter; in the MMA phase warp (rg, ch) owns rows 8rg..8rg+7 and one half of the D/8 column blocks (accumulators
+ * in registers).  Shared-memory row stride = 4 mod 16 doubles -> conflict-free fragment loads.
  */
 #include <cuda_runtime.h>
 #include <cstring>
@@ -24,7 +25,10 @@ namespace
 {
 using namespace MCMC::Device;
 
-enum { DenseTileRows = 64, DenseThreads = 256 };
+/* Two independent 8-warp groups per CTA, each walking its own stream of 32-walker tiles (dynamic tile counter) and
+ * synchronising on its own named barrier: while one group is in its scalar phases (draws, row loads, decision,
+ * commit) the other keeps the FP64 tensor pipe busy.  P is shared. */
+enum { DenseTileRows = 32, DenseGroupThreads = 256, DenseGroups = 2, DenseThreads = DenseGroupThreads * DenseGroups };
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
 {
@@ -32,165 +36,200 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-__host__ __device__ inline int denseStride(int Dp)
+__device__ __forceinline__ void groupSync(int group)
 {
-    int s = Dp;
-    while ((s & 15) != 4) ++s;
-    return s;
+    asm volatile("bar.sync %0, 256;" ::"r"(group + 1) : "memory");       /* 256 = DenseGroupThreads */
+    static_assert(DenseGroupThreads == 256, "named-barrier thread count is spelled out in the asm above");
 }
 
-/* NB = number of 8-wide column blocks (padded dimension Dp = 8*NB) */
+__host__ __device__ constexpr int denseStrideC(int Dp)
+{
+    return Dp + ((4 - (Dp & 15)) & 15);                       /* smallest stride >= Dp with stride = 4 mod 16 */
+}
+__host__ __device__ inline int denseStride(int Dp) { return denseStrideC(Dp); }
+
+/* NB = number of 8-wide column blocks (padded dimension Dp = 8*NB).
+ * Static tile assignment: group gid takes tiles gid, gid + G, ...; the draws of up to DenseBatch tiles (one walker per
+ * thread of the group) are made up front, in parallel, while P streams into shared memory with cp.async.bulk. */
+enum { DenseBatch = DenseGroupThreads / DenseTileRows };      /* 8 tiles = 256 walkers per draw phase */
+
 template <int NB, bool TRACE>
 __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P)
 {
     constexpr int Dp = 8 * NB;
+    constexpr int NBH = (NB + 1) / 2;                         /* column blocks per warp: warps 0-3 take [0,NBH), 4-7 the rest */
+    constexpr int GroupWarps = DenseGroupThreads / 32;
+    constexpr int PerGroupDoubles = DenseTileRows * denseStrideC(Dp) + 3 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
     extern __shared__ __align__(16) double denseSmem[];
-    const int stride = denseStride(Dp);
-    double* Ps = denseSmem;                                   /* [Dp][stride] */
-    double* Xs = Ps + (size_t)Dp * stride;                    /* [TM][stride] proposals */
-    double* sZ = Xs + (size_t)DenseTileRows * stride;         /* per-row scalars */
-    double* sE = sZ + DenseTileRows;
-    double* sQ = sE + DenseTileRows;
-    int* sJ = reinterpret_cast<int*>(sQ + DenseTileRows);
-    int* sAcc = sJ + DenseTileRows;
+    constexpr int stride = denseStrideC(Dp);
+    const int group = threadIdx.x / DenseGroupThreads;
+    const int tid = threadIdx.x - group * DenseGroupThreads, lane = tid & 31, warp = tid >> 5;
+    double* Ps = denseSmem;                                   /* [Dp][stride], shared by both groups */
+    double* Xs = Ps + (size_t)Dp * stride + (size_t)group * PerGroupDoubles;   /* [TM][stride] proposals */
+    double* bZ = Xs + (size_t)DenseTileRows * stride;         /* draws of the batch: z, log(1-u), log(z)(D-1) */
+    double* bE = bZ + DenseGroupThreads;
+    double* bS = bE + DenseGroupThreads;
+    int* bJ = reinterpret_cast<int*>(bS + DenseGroupThreads); /* [256] ints = 128 doubles */
+    double* sQ = bS + DenseGroupThreads + DenseGroupThreads / 2;   /* [2][TM] column halves */
+    double* sOld = sQ + 2 * DenseTileRows;                    /* [TM] current log-probs */
+    __shared__ __align__(8) unsigned long long pBar;
 
     const int D = a.D;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int other0 = (1 - a.half) * a.K;
-
-    /* P -> shared, zero padded (rows/cols >= D contribute nothing) */
-    for (int idx = tid; idx < Dp * stride; idx += DenseThreads) {
-        const int r = idx / stride, c = idx - r * stride;
-        Ps[idx] = (r < D && c < D) ? P[(size_t)r * D + c] : 0.0;
-    }
-    unsigned long long ctaAccepted = 0;
     const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
+    const int gid = blockIdx.x * DenseGroups + group, gstep = gridDim.x * DenseGroups;
 
-    for (int tile = blockIdx.x; tile < numTiles; tile += gridDim.x) {
-        const int row0 = tile * DenseTileRows;
-        __syncthreads();                                      /* previous tile fully committed; Ps visible */
-        /* (a) draws: one thread per walker of the tile */
-        if (tid < DenseTileRows) {
-            const int i = row0 + tid;
-            if (i < a.slot_count) {
+    /* P -> shared, zero padded (rows/cols >= D contribute nothing).  Even D: one bulk copy per row, in flight during
+     * the first draw phase; odd D (rows not 16-byte multiples): plain loads. */
+    const bool bulkP = (D % 2) == 0;
+    for (int idx = threadIdx.x; idx < Dp * stride; idx += DenseThreads) {
+        const int r = idx / stride, c = idx - r * stride;
+        if (bulkP) { if (r >= D || c >= D) Ps[idx] = 0.0; }
+        else Ps[idx] = (r < D && c < D) ? P[(size_t)r * D + c] : 0.0;
+    }
+    if (threadIdx.x == 0) mbarInit(smemAddr(&pBar), 1);
+    __syncthreads();
+    if (bulkP) {
+        if (threadIdx.x == 0) mbarExpectTx(smemAddr(&pBar), (uint32_t)(D * D * 8));
+        __syncthreads();
+        if (threadIdx.x < D)
+            bulkLoad(smemAddr(Ps + (size_t)threadIdx.x * stride), P + (size_t)threadIdx.x * D, (uint32_t)(D * 8), smemAddr(&pBar));
+    }
+    bool pReady = !bulkP;
+    unsigned long long myAccepted = 0;                        /* lane 0 of every warp counts its own rows */
+
+    for (int tileBase = gid; tileBase < numTiles; tileBase += gstep * DenseBatch) {
+        /* (a) draws of the whole batch: thread tid <-> (tile tileBase + (tid/32)*gstep, row tid%32) */
+        groupSync(group);                                     /* previous batch done with bZ.. */
+        {
+            const int tile = tileBase + (tid >> 5) * gstep;
+            const int i = tile * DenseTileRows + lane;
+            if (tile < numTiles && i < a.slot_count) {
                 const int w = a.half * a.K + a.slot_begin + i;
                 WalkerRng rng = loadRng(a, w);
                 StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
                 storeRng(a, w, rng);
                 if (dr.redraws) atomicAdd(a.flags, dr.redraws);
-                sJ[tid] = dr.j; sZ[tid] = dr.z; sE[tid] = dr.logOneMinusU;
+                bJ[tid] = dr.j; bZ[tid] = dr.z; bE[tid] = dr.logOneMinusU;
+                bS[tid] = __dmul_rn(log(dr.z), (double)(D - 1));
             } else {
-                sJ[tid] = 0; sZ[tid] = 1.0; sE[tid] = 0.0;
+                bJ[tid] = 0; bZ[tid] = 1.0; bE[tid] = 0.0; bS[tid] = 0.0;
             }
         }
-        __syncthreads();
-        /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  All loads of the warp's 8 rows
-         * are issued before the first use so one L2/HBM latency covers the whole tile, not one per row. */
-        {
-            constexpr int RowsPerWarp = DenseTileRows / (DenseThreads / 32);
-            constexpr int KCH = (Dp + 31) / 32;
-            double cur[RowsPerWarp][KCH], sl[RowsPerWarp][KCH];
+        groupSync(group);
+        if (!pReady) { mbarWait(smemAddr(&pBar), 0); pReady = true; }
+        for (int bt = 0; bt < DenseBatch; ++bt) {
+            const int tile = tileBase + bt * gstep;
+            if (tile >= numTiles) break;                      /* group-uniform */
+            const int row0 = tile * DenseTileRows;
+            const int b0 = bt * DenseTileRows;                /* this tile's draws in the batch arrays */
+            /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  All loads of the warp's rows
+             * are issued before the first use so one L2/HBM latency covers the whole tile, not one per row. */
+            {
+                constexpr int RowsPerWarp = DenseTileRows / GroupWarps;
+                constexpr int KCH = (Dp + 31) / 32;
+                double cur[RowsPerWarp][KCH], sl[RowsPerWarp][KCH];
+                double oldp = 0.0;
 #pragma unroll
-            for (int rr = 0; rr < RowsPerWarp; ++rr) {
-                const int r = warp + rr * (DenseThreads / 32);
-                const int i = row0 + r;
-                const bool valid = i < a.slot_count;
-                const int w = a.half * a.K + a.slot_begin + (valid ? i : 0);
-                const int j = sJ[r];
-                const double* own = a.pos + (size_t)w * D;
-                const double* sel = partnerBase(a, j) + (size_t)(other0 + j) * D;
+                for (int rr = 0; rr < RowsPerWarp; ++rr) {
+                    const int r = warp + rr * GroupWarps;
+                    const int i = row0 + r;
+                    const bool valid = i < a.slot_count;
+                    const int w = a.half * a.K + a.slot_begin + (valid ? i : 0);
+                    const int j = bJ[b0 + r];
+                    const double* own = a.pos + (size_t)w * D;
+                    const double* sel = partnerBase(a, j) + (size_t)(other0 + j) * D;
+                    if (lane == rr) oldp = a.logp[w];
 #pragma unroll
-                for (int k = 0; k < KCH; ++k) {
-                    const int d = lane + 32 * k;
-                    const bool ok = valid && d < D;
-                    cur[rr][k] = ok ? own[d] : 0.0;
-                    sl[rr][k] = ok ? __ldg(sel + d) : 0.0;
+                    for (int k = 0; k < KCH; ++k) {
+                        const int d = lane + 32 * k;
+                        const bool ok = valid && d < D;
+                        cur[rr][k] = ok ? own[d] : 0.0;
+                        sl[rr][k] = ok ? __ldg(sel + d) : 0.0;
+                    }
                 }
-            }
+                if (lane < RowsPerWarp) sOld[warp + lane * GroupWarps] = oldp;
 #pragma unroll
-            for (int rr = 0; rr < RowsPerWarp; ++rr) {
-                const int r = warp + rr * (DenseThreads / 32);
-                const double z = sZ[r];
-                double* xr = Xs + (size_t)r * stride;
+                for (int rr = 0; rr < RowsPerWarp; ++rr) {
+                    const int r = warp + rr * GroupWarps;
+                    const double z = bZ[b0 + r];
+                    double* xr = Xs + (size_t)r * stride;
 #pragma unroll
-                for (int k = 0; k < KCH; ++k) {
-                    const int d = lane + 32 * k;
-                    if (d < Dp) xr[d] = stretchPoint(sl[rr][k], cur[rr][k], z);   /* padding: 0 + z*(0-0) = 0 */
-                }
-            }
-        }
-        __syncthreads();
-        /* (c) Y = Xs * Ps on the FP64 tensor cores; warp owns 8 rows x all NB column blocks */
-        {
-            double acc[NB][2];
-#pragma unroll
-            for (int nb = 0; nb < NB; ++nb) { acc[nb][0] = 0.0; acc[nb][1] = 0.0; }
-            const int g = lane >> 2, t = lane & 3;
-            const double* arow = Xs + (size_t)(warp * 8 + g) * stride + t;
-            const double* bcol = Ps + (size_t)t * stride + g;
-#pragma unroll 2
-            for (int k = 0; k < Dp; k += 4) {
-                const double av = arow[k];
-                const double* bk = bcol + (size_t)k * stride;
-#pragma unroll
-                for (int nb = 0; nb < NB; ++nb) dmma884(acc[nb][0], acc[nb][1], av, bk[nb * 8]);
-            }
-            /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols nb*8 + 2t, +1 of row g */
-            const double* xrow = Xs + (size_t)(warp * 8 + g) * stride + 2 * t;
-            double q = 0.0;
-#pragma unroll
-            for (int nb = 0; nb < NB; ++nb) {
-                const double2 xv = *reinterpret_cast<const double2*>(xrow + nb * 8);
-                q = fma(xv.x, acc[nb][0], q);
-                q = fma(xv.y, acc[nb][1], q);
-            }
-            q += __shfl_xor_sync(0xffffffffu, q, 1);
-            q += __shfl_xor_sync(0xffffffffu, q, 2);
-            if (t == 0) sQ[warp * 8 + g] = q;
-        }
-        __syncthreads();
-        /* (d) Metropolis decision, one thread per walker */
-        if (tid < DenseTileRows) {
-            const int i = row0 + tid;
-            int accepted = 0;
-            if (i < a.slot_count) {
-                const int slot = a.slot_begin + i;
-                const int w = a.half * a.K + slot;
-                const double z = sZ[tid];
-                const double scaling = __dmul_rn(log(z), (double)(D - 1));
-                const double newp = -0.5 * sQ[tid];
-                const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
-                accepted = sE[tid] < diff ? 1 : 0;
-                if (accepted) a.logp[w] = newp;
-                if (TRACE) {
-                    if (slot < a.trace_rows) {
-                        mcmcpp_trace tr;
-                        tr.j = sJ[tid]; tr.accept = accepted; tr.z = z; tr.e = sE[tid]; tr.newp = newp; tr.diff = diff;
-                        a.trace[slot] = tr;
+                    for (int k = 0; k < KCH; ++k) {
+                        const int d = lane + 32 * k;
+                        if (d < Dp) xr[d] = stretchPoint(sl[rr][k], cur[rr][k], z);   /* padding: 0 + z*(0-0) = 0 */
                     }
                 }
             }
-            sAcc[tid] = accepted;
-            const unsigned ballot = __ballot_sync(0xffffffffu, accepted);
-            if (lane == 0) ctaAccepted += __popc(ballot);     /* warps 0 and 1 each keep their own count (tid 0, 32) */
-        }
-        __syncthreads();
-        /* (e) commit accepted rows (and the chain row of every walker on stored steps) */
-        for (int r = warp; r < DenseTileRows; r += DenseThreads / 32) {
-            const int i = row0 + r;
-            if (i >= a.slot_count) continue;
-            const int w = a.half * a.K + a.slot_begin + i;
-            const double* xr = Xs + (size_t)r * stride;
-            double* own = a.pos + (size_t)w * D;
-            const bool accepted = sAcc[r] != 0;
-            if (a.chain_row) {
-                double* chainRow = a.chain_row + (size_t)w * D;
-                for (int d = lane; d < D; d += 32) chainRow[d] = accepted ? xr[d] : own[d];
+            groupSync(group);
+            /* (c) Y = Xs * Ps on the FP64 tensor cores; warp owns 8 rows x its half of the column blocks */
+            {
+                const int rg = warp & 3, ch = warp >> 2;
+                const int nb0 = ch * NBH;
+                const int cnt = (NB - nb0) < NBH ? (NB - nb0) : NBH;
+                double acc[NBH][2];
+#pragma unroll
+                for (int nb = 0; nb < NBH; ++nb) { acc[nb][0] = 0.0; acc[nb][1] = 0.0; }
+                const int g = lane >> 2, t = lane & 3;
+                const double* arow = Xs + (size_t)(rg * 8 + g) * stride + t;
+                const double* bcol = Ps + (size_t)t * stride + g + nb0 * 8;
+#pragma unroll 2
+                for (int k = 0; k < Dp; k += 4) {
+                    const double av = arow[k];
+                    const double* bk = bcol + (size_t)k * stride;
+#pragma unroll
+                    for (int nb = 0; nb < NBH; ++nb)
+                        if (nb < cnt) dmma884(acc[nb][0], acc[nb][1], av, bk[nb * 8]);
+                }
+                /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols (nb0+nb)*8 + 2t, +1 of row g */
+                const double* xrow = Xs + (size_t)(rg * 8 + g) * stride + nb0 * 8 + 2 * t;
+                double q = 0.0;
+#pragma unroll
+                for (int nb = 0; nb < NBH; ++nb) {
+                    if (nb < cnt) {
+                        const double2 xv = *reinterpret_cast<const double2*>(xrow + nb * 8);
+                        q = fma(xv.x, acc[nb][0], q);
+                        q = fma(xv.y, acc[nb][1], q);
+                    }
+                }
+                q += __shfl_xor_sync(0xffffffffu, q, 1);
+                q += __shfl_xor_sync(0xffffffffu, q, 2);
+                if (t == 0) sQ[ch * DenseTileRows + rg * 8 + g] = q;
             }
-            if (accepted) for (int d = lane; d < D; d += 32) own[d] = xr[d];
+            groupSync(group);
+            /* (d)+(e) Metropolis decision and commit: each warp decides its own rows (every lane computes the same
+             * few adds), then writes the accepted rows (and the chain row of every walker on stored steps) */
+            for (int r = warp; r < DenseTileRows; r += GroupWarps) {
+                const int i = row0 + r;
+                if (i >= a.slot_count) continue;
+                const int slot = a.slot_begin + i;
+                const int w = a.half * a.K + slot;
+                const double newp = -0.5 * (sQ[r] + sQ[DenseTileRows + r]);
+                const double diff = __dsub_rn(__dadd_rn(bS[b0 + r], newp), sOld[r]);
+                const bool accepted = bE[b0 + r] < diff;
+                const double* xr = Xs + (size_t)r * stride;
+                double* own = a.pos + (size_t)w * D;
+                if (a.chain_row) {
+                    double* chainRow = a.chain_row + (size_t)w * D;
+                    for (int d = lane; d < D; d += 32) chainRow[d] = accepted ? xr[d] : own[d];
+                }
+                if (accepted) for (int d = lane; d < D; d += 32) own[d] = xr[d];
+                if (lane == 0) {
+                    if (accepted) { a.logp[w] = newp; ++myAccepted; }
+                    if (TRACE) {
+                        if (slot < a.trace_rows) {
+                            mcmcpp_trace tr;
+                            tr.j = bJ[b0 + r]; tr.accept = accepted ? 1 : 0; tr.z = bZ[b0 + r]; tr.e = bE[b0 + r]; tr.newp = newp; tr.diff = diff;
+                            a.trace[slot] = tr;
+                        }
+                    }
+                }
+            }
+            groupSync(group);                                 /* Xs, sQ, sOld free for the next tile */
         }
     }
-    if ((tid == 0 || tid == 32) && ctaAccepted) atomicAdd(a.accept_slots + blockIdx.x, ctaAccepted);
+    if (!pReady) mbarWait(smemAddr(&pBar), 0);                /* never exit with a bulk copy in flight */
+    if (lane == 0 && myAccepted) atomicAdd(a.accept_slots + blockIdx.x, myAccepted);
 }
 
 struct DenseCalc
@@ -204,16 +243,25 @@ template <int NB>
 int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_t stream)
 {
     const int Dp = 8 * NB, stride = denseStride(Dp);
-    const size_t smem = sizeof(double) * ((size_t)Dp * stride + (size_t)DenseTileRows * stride + 3 * DenseTileRows) + sizeof(int) * 2 * DenseTileRows;
+    const size_t perGroup = (size_t)DenseTileRows * stride + 3 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
+    const size_t smem = sizeof(double) * ((size_t)Dp * stride + (size_t)DenseGroups * perGroup);
     const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
-    int grid = numTiles < c.smCount ? numTiles : c.smCount;
+    int grid = (numTiles + DenseGroups - 1) / DenseGroups;
+    if (grid > c.smCount) grid = c.smCount;
     if (grid > a.max_grid) grid = a.max_grid;
-    static bool attr[2] = {false, false};
+    /* opt in to exactly what this shape needs (the kernel also has a few bytes of static shared memory) */
+    static size_t optedIn[2] = {0, 0};
     if (a.trace) {
-        if (!attr[1]) { cudaFuncSetAttribute(denseGaussHalfStep<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr[1] = true; }
+        if (smem > optedIn[1]) {
+            if (cudaFuncSetAttribute(denseGaussHalfStep<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
+            optedIn[1] = smem;
+        }
         denseGaussHalfStep<NB, true><<<grid, DenseThreads, smem, stream>>>(a, c.P);
     } else {
-        if (!attr[0]) { cudaFuncSetAttribute(denseGaussHalfStep<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr[0] = true; }
+        if (smem > optedIn[0]) {
+            if (cudaFuncSetAttribute(denseGaussHalfStep<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
+            optedIn[0] = smem;
+        }
         denseGaussHalfStep<NB, false><<<grid, DenseThreads, smem, stream>>>(a, c.P);
     }
     return launchStatus();
