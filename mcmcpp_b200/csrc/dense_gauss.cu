@@ -42,6 +42,18 @@ __device__ __forceinline__ void groupSync(int group)
     static_assert(DenseGroupThreads == 256, "named-barrier thread count is spelled out in the asm above");
 }
 
+/* The tensor pipe is handed from group to group like a token: barrier 3 + g is completed by the 256 waiting threads of
+ * group g plus the 256 arriving threads of the other group when it leaves its MMA phase.  Without it the two groups
+ * run in lockstep (same work, same phase lengths) and fight for the pipe, then both leave it idle. */
+__device__ __forceinline__ void tokenWait(int group)
+{
+    asm volatile("bar.sync %0, 512;" ::"r"(group + 3) : "memory");
+}
+__device__ __forceinline__ void tokenPass(int group)
+{
+    asm volatile("bar.arrive %0, 512;" ::"r"((1 - group) + 3) : "memory");
+}
+
 __host__ __device__ constexpr int denseStrideC(int Dp)
 {
     return Dp + ((4 - (Dp & 15)) & 15);                       /* smallest stride >= Dp with stride = 4 mod 16 */
@@ -77,7 +89,10 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
     const int D = a.D;
     const int other0 = (1 - a.half) * a.K;
     const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
-    const int gid = blockIdx.x * DenseGroups + group, gstep = gridDim.x * DenseGroups;
+    /* group 0 of every CTA first, then group 1: tiles spread evenly over the SMs, and group 0 never has fewer tiles */
+    const int gid = group * gridDim.x + blockIdx.x, gstep = gridDim.x * DenseGroups;
+    const int rounds = blockIdx.x < numTiles ? (numTiles - blockIdx.x + gstep - 1) / gstep : 0;   /* tiles of group 0 */
+    if (group == 1) tokenPass(1);                             /* group 0 owns the tensor pipe first */
 
     /* P -> shared, zero padded (rows/cols >= D contribute nothing).  Even D: one bulk copy per row, in flight during
      * the first draw phase; odd D (rows not 16-byte multiples): plain loads. */
@@ -98,7 +113,8 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
     bool pReady = !bulkP;
     unsigned long long myAccepted = 0;                        /* lane 0 of every warp counts its own rows */
 
-    for (int tileBase = gid; tileBase < numTiles; tileBase += gstep * DenseBatch) {
+    for (int rnd0 = 0; rnd0 < rounds; rnd0 += DenseBatch) {
+        const int tileBase = gid + rnd0 * gstep;
         /* (a) draws of the whole batch: thread tid <-> (tile tileBase + (tid/32)*gstep, row tid%32) */
         groupSync(group);                                     /* previous batch done with bZ.. */
         {
@@ -118,14 +134,15 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
         }
         groupSync(group);
         if (!pReady) { mbarWait(smemAddr(&pBar), 0); pReady = true; }
-        for (int bt = 0; bt < DenseBatch; ++bt) {
+        for (int bt = 0; bt < DenseBatch && rnd0 + bt < rounds; ++bt) {
             const int tile = tileBase + bt * gstep;
-            if (tile >= numTiles) break;                      /* group-uniform */
+            const bool has = tile < numTiles;                 /* group-uniform; group 1 may sit out the last round */
+            const bool lastRound = rnd0 + bt + 1 == rounds;
             const int row0 = tile * DenseTileRows;
             const int b0 = bt * DenseTileRows;                /* this tile's draws in the batch arrays */
             /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  All loads of the warp's rows
              * are issued before the first use so one L2/HBM latency covers the whole tile, not one per row. */
-            {
+            if (has) {
                 constexpr int RowsPerWarp = DenseTileRows / GroupWarps;
                 constexpr int KCH = (Dp + 31) / 32;
                 double cur[RowsPerWarp][KCH], sl[RowsPerWarp][KCH];
@@ -162,8 +179,9 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                 }
             }
             groupSync(group);
+            tokenWait(group);
             /* (c) Y = Xs * Ps on the FP64 tensor cores; warp owns 8 rows x its half of the column blocks */
-            {
+            if (has) {
                 const int rg = warp & 3, ch = warp >> 2;
                 const int nb0 = ch * NBH;
                 const int cnt = (NB - nb0) < NBH ? (NB - nb0) : NBH;
@@ -196,7 +214,9 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                 q += __shfl_xor_sync(0xffffffffu, q, 2);
                 if (t == 0) sQ[ch * DenseTileRows + rg * 8 + g] = q;
             }
+            if (!(group == 1 && lastRound)) tokenPass(group); /* the last pass would have nobody waiting for it */
             groupSync(group);
+            if (!has) continue;
             /* (d)+(e) Metropolis decision and commit: each warp decides its own rows (every lane computes the same
              * few adds), then writes the accepted rows (and the chain row of every walker on stored steps) */
             for (int r = warp; r < DenseTileRows; r += GroupWarps) {
