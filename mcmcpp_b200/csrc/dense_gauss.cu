@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
     constexpr int Dp = 8 * NB;
     constexpr int NBH = (NB + 1) / 2;                         /* column blocks per warp: warps 0-3 take [0,NBH), 4-7 the rest */
     constexpr int GroupWarps = DenseGroupThreads / 32;
-    constexpr int PerGroupDoubles = DenseTileRows * denseStrideC(Dp) + 3 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
+    constexpr int PerGroupDoubles = DenseTileRows * denseStrideC(Dp) + 4 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
     extern __shared__ __align__(16) double denseSmem[];
     constexpr int stride = denseStrideC(Dp);
     const int group = threadIdx.x / DenseGroupThreads;
@@ -81,8 +81,9 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
     double* bZ = Xs + (size_t)DenseTileRows * stride;         /* draws of the batch: z, log(1-u), log(z)(D-1) */
     double* bE = bZ + DenseGroupThreads;
     double* bS = bE + DenseGroupThreads;
-    int* bJ = reinterpret_cast<int*>(bS + DenseGroupThreads); /* [256] ints = 128 doubles */
-    double* sQ = bS + DenseGroupThreads + DenseGroupThreads / 2;   /* [2][TM] column halves */
+    const double** bSel = reinterpret_cast<const double**>(bS + DenseGroupThreads);   /* partner row of each walker (peer lookup done once, here) */
+    int* bJ = reinterpret_cast<int*>(bS + 2 * DenseGroupThreads); /* [256] ints = 128 doubles */
+    double* sQ = bS + 2 * DenseGroupThreads + DenseGroupThreads / 2;   /* [2][TM] column halves */
     double* sOld = sQ + 2 * DenseTileRows;                    /* [TM] current log-probs */
     __shared__ __align__(8) unsigned long long pBar;
 
@@ -127,9 +128,10 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                 storeRng(a, w, rng);
                 if (dr.redraws) atomicAdd(a.flags, dr.redraws);
                 bJ[tid] = dr.j; bZ[tid] = dr.z; bE[tid] = dr.logOneMinusU;
+                bSel[tid] = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
                 bS[tid] = __dmul_rn(log(dr.z), (double)(D - 1));
             } else {
-                bJ[tid] = 0; bZ[tid] = 1.0; bE[tid] = 0.0; bS[tid] = 0.0;
+                bJ[tid] = 0; bZ[tid] = 1.0; bE[tid] = 0.0; bS[tid] = 0.0; bSel[tid] = a.pos;
             }
         }
         groupSync(group);
@@ -153,9 +155,8 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                     const int i = row0 + r;
                     const bool valid = i < a.slot_count;
                     const int w = a.half * a.K + a.slot_begin + (valid ? i : 0);
-                    const int j = bJ[b0 + r];
                     const double* own = a.pos + (size_t)w * D;
-                    const double* sel = partnerBase(a, j) + (size_t)(other0 + j) * D;
+                    const double* sel = bSel[b0 + r];
                     if (lane == rr) oldp = a.logp[w];
 #pragma unroll
                     for (int k = 0; k < KCH; ++k) {
@@ -263,7 +264,7 @@ template <int NB>
 int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_t stream)
 {
     const int Dp = 8 * NB, stride = denseStride(Dp);
-    const size_t perGroup = (size_t)DenseTileRows * stride + 3 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
+    const size_t perGroup = (size_t)DenseTileRows * stride + 4 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
     const size_t smem = sizeof(double) * ((size_t)Dp * stride + (size_t)DenseGroups * perGroup);
     const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
     int grid = (numTiles + DenseGroups - 1) / DenseGroups;
