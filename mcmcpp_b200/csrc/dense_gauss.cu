@@ -66,7 +66,7 @@ __host__ __device__ inline int denseStride(int Dp) { return denseStrideC(Dp); }
 enum { DenseBatch = DenseGroupThreads / DenseTileRows };      /* 8 tiles = 256 walkers per draw phase */
 
 template <int NB, bool TRACE>
-__global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P)
+__global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken)
 {
     constexpr int Dp = 8 * NB;
     constexpr int NBH = (NB + 1) / 2;                         /* column blocks per warp: warps 0-3 take [0,NBH), 4-7 the rest */
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
     /* group 0 of every CTA first, then group 1: tiles spread evenly over the SMs, and group 0 never has fewer tiles */
     const int gid = group * gridDim.x + blockIdx.x, gstep = gridDim.x * DenseGroups;
     const int rounds = blockIdx.x < numTiles ? (numTiles - blockIdx.x + gstep - 1) / gstep : 0;   /* tiles of group 0 */
-    if (group == 1) tokenPass(1);                             /* group 0 owns the tensor pipe first */
+    if (useToken && group == 1) tokenPass(1);                             /* group 0 owns the tensor pipe first */
 
     /* P -> shared, zero padded (rows/cols >= D contribute nothing).  Even D: one bulk copy per row, in flight during
      * the first draw phase; odd D (rows not 16-byte multiples): plain loads. */
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                 }
             }
             groupSync(group);
-            tokenWait(group);
+            if (useToken) tokenWait(group);
             /* (c) Y = Xs * Ps on the FP64 tensor cores; warp owns 8 rows x its half of the column blocks */
             if (has) {
                 const int rg = warp & 3, ch = warp >> 2;
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                 q += __shfl_xor_sync(0xffffffffu, q, 2);
                 if (t == 0) sQ[ch * DenseTileRows + rg * 8 + g] = q;
             }
-            if (!(group == 1 && lastRound)) tokenPass(group); /* the last pass would have nobody waiting for it */
+            if (useToken && !(group == 1 && lastRound)) tokenPass(group); /* the last pass would have nobody waiting for it */
             groupSync(group);
             if (!has) continue;
             /* (d)+(e) Metropolis decision and commit: each warp decides its own rows (every lane computes the same
@@ -270,6 +270,7 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     int grid = (numTiles + DenseGroups - 1) / DenseGroups;
     if (grid > c.smCount) grid = c.smCount;
     if (grid > a.max_grid) grid = a.max_grid;
+    static const int useToken = [] { const char* e = getenv("MCMCPP_B200_DENSE_TOKEN"); return (e && e[0] == '0') ? 0 : 1; }();
     /* opt in to exactly what this shape needs (the kernel also has a few bytes of static shared memory) */
     static size_t optedIn[2] = {0, 0};
     if (a.trace) {
@@ -277,13 +278,13 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
             if (cudaFuncSetAttribute(denseGaussHalfStep<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
             optedIn[1] = smem;
         }
-        denseGaussHalfStep<NB, true><<<grid, DenseThreads, smem, stream>>>(a, c.P);
+        denseGaussHalfStep<NB, true><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken);
     } else {
         if (smem > optedIn[0]) {
             if (cudaFuncSetAttribute(denseGaussHalfStep<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
             optedIn[0] = smem;
         }
-        denseGaussHalfStep<NB, false><<<grid, DenseThreads, smem, stream>>>(a, c.P);
+        denseGaussHalfStep<NB, false><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken);
     }
     return launchStatus();
 }
