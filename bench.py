@@ -239,6 +239,9 @@ def gpu_arm(args):
     if world != args.gpus and rank == 0:
         print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
     desc, kind, W, D, Wc, cpu_steps = WORKLOADS[args.workload]
+    if os.environ.get("MCMCPP_BENCH_D"):          # analysis only (e.g. one rank's slice of C4 on one GPU); named in config
+        D = int(os.environ["MCMCPP_BENCH_D"])
+        desc += " [params overridden to %d]" % D
     params = target_params(kind, D)
     # default sharding per workload: C5 shards its data rows, C4 (separable) its parameter dimension, the rest walkers
     shard = args.shard or ("data" if kind == "linreg" else "dim" if kind == "diag_gauss" else "peer")

@@ -109,11 +109,28 @@ __global__ void __launch_bounds__(DimThreads) dimShardPartial(const mcmcpp_halfs
 }
 
 
+/* ---- phase 0 (TMA form only): the draws of a colour, one THREAD per walker --------------------------------------
+ * ~600 dependent integer/FP64 instructions per walker (three 128-bit LCG steps, the stream skip, two logs).  Made
+ * inside the copy kernel they sit in front of the bulk copies and leave its shared memory idle for ~2 us per CTA;
+ * here they run at full occupancy and the copy kernel only reads (j, z). */
+__global__ void __launch_bounds__(256) dimShardDraw(const mcmcpp_halfstep_args a)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= a.K) return;
+    const int w = a.half * a.K + i;
+    WalkerRng rng = loadRng(a, w);
+    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    storeRng(a, w, rng);
+    if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+    a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
+    if (i == 0) *a.dim_count = 0;                              /* the previous colour's commit is done (stream order) */
+}
+
 /* ---- phase 1, TMA form (even slices): 4 warps per CTA, WPW walkers per warp all in flight at once ------------
- * Lane q < WPW makes walker q's draws (the pcg64 work is done once per walker, not once per lane) and issues that
+ * Lane q < WPW reads walker q's draws (dimShardDraw) and issues that
  * walker's two cp.async.bulk copies (own slice, partner slice) onto the walker's own mbarrier; the warp then reduces
- * the walkers one after the other from shared memory.  WPW is chosen so that a CTA stages ~64 KB whatever the slice
- * length is (3 CTAs per SM -> ~190 KB of loads outstanding per SM, as in stretchHalfStepBulk). */
+ * the walkers from shared memory.  WPW is chosen so that a CTA stages ~32 KB whatever the slice length is
+ * (6-7 CTAs per SM: while some reduce, the others have their copies in flight). */
 enum { DimBulkWarps = 4 };
 
 template <class Calc, int WPW>
@@ -136,41 +153,42 @@ __global__ void __launch_bounds__(DimBulkWarps * 32) dimShardPartialBulk(const m
         const int i = group0 + lane;
         const int w = a.half * a.K + i;
         const int other0 = (1 - a.half) * a.K;
-        WalkerRng rng = loadRng(a, w);
-        StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+        const int j = a.dim_j[i];
         const uint32_t bar = smemAddr(barBase + 8u * (warp * WPW + lane));
         mbarInit(bar, 1);
         mbarExpectTx(bar, 2u * rowBytes);
         bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride), a.pos + (size_t)w * D, rowBytes, bar);
-        bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride + rowStride), a.pos + (size_t)(other0 + dr.j) * D, rowBytes, bar);
-        storeRng(a, w, rng);
-        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
-        a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
-        z = dr.z;
+        bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride + rowStride), a.pos + (size_t)(other0 + j) * D, rowBytes, bar);
+        z = a.dim_z[i];
     }
     __syncwarp();
+    /* partial sums of the warp's WPW walkers; the WPW butterflies run interleaved (independent dependency chains) */
+    double s[WPW];
 #pragma unroll
     for (int q = 0; q < WPW; ++q) {
         const double zq = __shfl_sync(0xffffffffu, z, q);
-        double s = 0.0;
+        double p0 = 0.0, p1 = 0.0;
         if (group0 + q < a.K) {                                  /* warp-uniform */
             mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
             const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
             const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
-            double p0 = 0.0, p1 = 0.0;
             for (int d = 2 * lane; d < D; d += 64) {
                 const double2 c = *reinterpret_cast<const double2*>(ownS + d);
                 const double2 t = *reinterpret_cast<const double2*>(selS + d);
                 p0 = __dadd_rn(p0, calc.term(stretchPoint(t.x, c.x, zq), d));
                 p1 = __dadd_rn(p1, calc.term(stretchPoint(t.y, c.y, zq), d + 1));
             }
-            s = __dadd_rn(p0, p1);
-#pragma unroll
-            for (int off = 16; off >= 1; off >>= 1) s = __dadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
         }
-        if (lane == 0) ctaPartial[warp * WPW + q] = s;
+        s[q] = __dadd_rn(p0, p1);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) *a.dim_count = 0;     /* the previous colour's commit is done (stream order) */
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+#pragma unroll
+        for (int q = 0; q < WPW; ++q) s[q] = __dadd_rn(s[q], __shfl_xor_sync(0xffffffffu, s[q], off));
+    }
+#pragma unroll
+    for (int q = 0; q < WPW; ++q)
+        if (lane == 0) ctaPartial[warp * WPW + q] = s[q];
     __syncthreads();
     /* NW consecutive partials (64..256 bytes) to every rank's table */
     for (int t = threadIdx.x; t < a.world * NW; t += DimBulkWarps * 32) {
@@ -262,6 +280,55 @@ __global__ void __launch_bounds__(DimThreads) dimShardCommit(const mcmcpp_halfst
     }
 }
 
+/* Short slices (<= 256 columns, even): a warp takes R = 8 / CPR listed walkers per pass so that 8 vector loads per
+ * row array are in flight per lane whatever the slice length (one walker at a time leaves only 2 KB per warp in flight
+ * at 126 columns). */
+template <int CPR>
+__global__ void __launch_bounds__(DimThreads) dimShardCommitShort(const mcmcpp_halfstep_args a)
+{
+    constexpr int R = 8 / CPR, SLOTS = R * CPR;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int D = a.D;
+    const int count = *a.dim_count;
+    const int other0 = (1 - a.half) * a.K;
+    for (int idx0 = (blockIdx.x * DimWarps + warp) * R; idx0 < count; idx0 += gridDim.x * DimWarps * R) {
+        int wRow[R];
+        bool acc[R];
+        double z[R];
+        const double* selRow[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool live = idx0 + r < count;
+            const int entry = live ? a.dim_list[idx0 + r] : 0;
+            const int i = entry & 0x7fffffff;
+            acc[r] = live && entry < 0;
+            wRow[r] = live ? a.half * a.K + i : -1;
+            z[r] = a.dim_z[i];
+            selRow[r] = a.pos + (size_t)(other0 + a.dim_j[i]) * D;
+        }
+        double2 cur[SLOTS], sel[SLOTS];
+#pragma unroll
+        for (int b = 0; b < SLOTS; ++b) {
+            const int r = b / CPR, d = 64 * (b % CPR) + 2 * lane;
+            const bool ok = wRow[r] >= 0 && d < D;
+            cur[b] = ok ? *reinterpret_cast<const double2*>(a.pos + (size_t)wRow[r] * D + d) : make_double2(0.0, 0.0);
+            sel[b] = (ok && acc[r]) ? *reinterpret_cast<const double2*>(selRow[r] + d) : cur[b];
+        }
+#pragma unroll
+        for (int b = 0; b < SLOTS; ++b) {
+            const int r = b / CPR, d = 64 * (b % CPR) + 2 * lane;
+            if (wRow[r] < 0 || d >= D) continue;
+            double2 v = cur[b];
+            if (acc[r]) {
+                v.x = stretchPoint(sel[b].x, cur[b].x, z[r]);
+                v.y = stretchPoint(sel[b].y, cur[b].y, z[r]);
+                *reinterpret_cast<double2*>(a.pos + (size_t)wRow[r] * D + d) = v;
+            }
+            if (a.chain_row) *reinterpret_cast<double2*>(a.chain_row + (size_t)wRow[r] * D + d) = v;
+        }
+    }
+}
+
 /* Launcher of a DIM-sharded colour for a separable Calculator (a VIEW of this rank's columns: term(x, d) takes the
  * local column index).  Pass &DimShardLauncher<Calc>::launch to mcmcpp_sampler_create with shard_mode DIM. */
 template <class Calc>
@@ -286,9 +353,12 @@ struct DimShardLauncher
         const uint32_t rowStride = ((uint32_t)a.D * 8u + 127u) & ~127u;
         const size_t perWalker = 2u * (size_t)rowStride;
         if (VEC && !bulkKernelDisabled() && DimBulkWarps * perWalker <= 226 * 1024) {
-            if (DimBulkWarps * 8 * perWalker <= 72 * 1024) partialBulk<8>(a, calc, stream, rowStride);
-            else if (DimBulkWarps * 4 * perWalker <= 72 * 1024) partialBulk<4>(a, calc, stream, rowStride);
-            else if (DimBulkWarps * 2 * perWalker <= 72 * 1024) partialBulk<2>(a, calc, stream, rowStride);
+            dimShardDraw<<<(a.K + 255) / 256, 256, 0, stream>>>(a);
+            if (a.launch_count) *a.launch_count += 1;
+            static const size_t stage = [] { const char* e = getenv("MCMCPP_B200_DIM_STAGE_KB"); return (size_t)(e ? atoi(e) : 36) * 1024; }();
+            if (DimBulkWarps * 8 * perWalker <= stage) partialBulk<8>(a, calc, stream, rowStride);
+            else if (DimBulkWarps * 4 * perWalker <= stage) partialBulk<4>(a, calc, stream, rowStride);
+            else if (DimBulkWarps * 2 * perWalker <= stage) partialBulk<2>(a, calc, stream, rowStride);
             else partialBulk<1>(a, calc, stream, rowStride);
         } else {
             dimShardPartial<Calc, VEC><<<grid, DimThreads, 0, stream>>>(a, calc);
@@ -307,7 +377,16 @@ struct DimShardLauncher
         }
         int cgrid = (a.sm_count > 0 ? a.sm_count : 148) * perSm;
         if (cgrid > grid) cgrid = grid;
-        dimShardCommit<VEC><<<cgrid, DimThreads, 0, stream>>>(a);
+        const int cpr = (a.D + 63) / 64;
+        if (VEC && cpr <= 4) {
+            const int sgrid = cgrid > (a.sm_count > 0 ? a.sm_count : 148) ? (a.sm_count > 0 ? a.sm_count : 148) : cgrid;
+            if (cpr == 1) dimShardCommitShort<1><<<sgrid, DimThreads, 0, stream>>>(a);
+            else if (cpr == 2) dimShardCommitShort<2><<<sgrid, DimThreads, 0, stream>>>(a);
+            else if (cpr == 3) dimShardCommitShort<3><<<sgrid, DimThreads, 0, stream>>>(a);
+            else dimShardCommitShort<4><<<sgrid, DimThreads, 0, stream>>>(a);
+        } else {
+            dimShardCommit<VEC><<<cgrid, DimThreads, 0, stream>>>(a);
+        }
         if (a.launch_count) *a.launch_count += 2;
         return launchStatus();
     }
