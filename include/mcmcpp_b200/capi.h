@@ -139,7 +139,7 @@ typedef struct {
     int32_t dim_begin;         /* global index of local column 0 */
     int32_t rank, world;
     double* const* dim_partial;/* [world] every rank's partial table [2 colours][world][K] (own entry local, others peer-mapped) */
-    double* dim_z;             /* [K] draws of the colour in flight, kept between the two kernels */
+    double* dim_z;             /* [K] draw scratch: draws of the colour in flight, kept between kernels (all shard modes) */
     double* dim_e;
     int32_t* dim_j;
     int32_t* dim_list;         /* [K] walkers the commit kernel must touch (bit 31 = accepted) */

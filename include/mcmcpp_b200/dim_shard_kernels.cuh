@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(DimThreads) dimShardPartial(const mcmcpp_halfs
  * ~600 dependent integer/FP64 instructions per walker (three 128-bit LCG steps, the stream skip, two logs).  Made
  * inside the copy kernel they sit in front of the bulk copies and leave its shared memory idle for ~2 us per CTA;
  * here they run at full occupancy and the copy kernel only reads (j, z). */
-__global__ void __launch_bounds__(256) dimShardDraw(const mcmcpp_halfstep_args a)
+static __global__ void __launch_bounds__(256) dimShardDraw(const mcmcpp_halfstep_args a)
 {
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= a.K) return;

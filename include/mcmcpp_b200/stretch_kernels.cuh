@@ -367,7 +367,23 @@ __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t phase)
 
 enum { BulkKernelMinDim = 130 };
 
-template <class Calc, int WARPS, bool TRACE>
+/* The draws of a colour, one THREAD per owned walker, for the TMA kernels.  ~600 dependent integer/FP64 instructions
+ * per walker (three 128-bit LCG steps, the stream skip, two logs): made inside a copy kernel they sit in front of its
+ * bulk copies and leave its shared memory idle for ~2 us per CTA; here they run at full occupancy and the copy
+ * kernel only reads (j, z, log(1-u)) from the draw scratch. */
+static __global__ void __launch_bounds__(256) stretchDrawKernel(const mcmcpp_halfstep_args a)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= a.slot_count) return;
+    const int w = a.half * a.K + a.slot_begin + i;
+    WalkerRng rng = loadRng(a, w);
+    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    storeRng(a, w, rng);
+    if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+    a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
+}
+
+template <class Calc, int WARPS, bool TRACE, bool PRE>
 __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride)
 {
     extern __shared__ __align__(128) unsigned char bulkSmem[];
@@ -385,8 +401,14 @@ __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_h
     const int w = a.half * a.K + slot;
     const int other0 = (1 - a.half) * a.K;
 
-    WalkerRng rng = loadRng(a, w);
-    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    WalkerRng rng;
+    StretchDraws dr;
+    if (PRE) {                               /* stretchDrawKernel made them */
+        dr.j = a.dim_j[i]; dr.z = a.dim_z[i]; dr.logOneMinusU = a.dim_e[i]; dr.redraws = 0;
+    } else {
+        rng = loadRng(a, w);
+        dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    }
     double* ownRow = a.pos + (size_t)w * D;
     const double* selRow = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
     if (lane == 0) {
@@ -438,8 +460,10 @@ __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_h
         for (int d = 2 * lane; d < D; d += 64) *reinterpret_cast<double2*>(chainRow + d) = *reinterpret_cast<const double2*>(src + d);
     }
     if (lane == 0) {
-        storeRng(a, w, rng);
-        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+        if (!PRE) {
+            storeRng(a, w, rng);
+            if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+        }
         if (accepted) {
             a.logp[w] = newp;
             atomicAdd(a.accept_slots + blockIdx.x, 1ULL);
@@ -490,21 +514,29 @@ int launchWarpKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream
     return launchStatus();
 }
 
+template <class Calc, int WARPS, bool TRACE, bool PRE>
+int launchBulkKernelWTP(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride, int grid, size_t smem)
+{
+    static bool attrDone = false;
+    if (!attrDone) { cudaFuncSetAttribute(stretchHalfStepBulk<Calc, WARPS, TRACE, PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attrDone = true; }
+    stretchHalfStepBulk<Calc, WARPS, TRACE, PRE><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
+    return launchStatus();
+}
+
 template <class Calc, int WARPS>
 int launchBulkKernelW(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
 {
     const int grid = (a.slot_count + WARPS - 1) / WARPS;
     if (grid > a.max_grid) return MCMCPP_ERR_ARG;
     const size_t smem = (size_t)WARPS * 2u * rowStride + 8u * WARPS;
-    static bool attrDone[2] = {false, false};
-    if (a.trace) {
-        if (!attrDone[1]) { cudaFuncSetAttribute(stretchHalfStepBulk<Calc, WARPS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attrDone[1] = true; }
-        stretchHalfStepBulk<Calc, WARPS, true><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
-    } else {
-        if (!attrDone[0]) { cudaFuncSetAttribute(stretchHalfStepBulk<Calc, WARPS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attrDone[0] = true; }
-        stretchHalfStepBulk<Calc, WARPS, false><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
+    if (a.dim_z && a.dim_e && a.dim_j) {     /* draw scratch available: draws in their own kernel */
+        stretchDrawKernel<<<(a.slot_count + 255) / 256, 256, 0, stream>>>(a);
+        if (a.launch_count) *a.launch_count += 1;
+        return a.trace ? launchBulkKernelWTP<Calc, WARPS, true, true>(a, calc, stream, rowStride, grid, smem)
+                       : launchBulkKernelWTP<Calc, WARPS, false, true>(a, calc, stream, rowStride, grid, smem);
     }
-    return launchStatus();
+    return a.trace ? launchBulkKernelWTP<Calc, WARPS, true, false>(a, calc, stream, rowStride, grid, smem)
+                   : launchBulkKernelWTP<Calc, WARPS, false, false>(a, calc, stream, rowStride, grid, smem);
 }
 
 /* warps per CTA chosen so that >= 3 CTAs (12 walkers, 2 rows each) fit the 227 KB of one SM when rows allow */

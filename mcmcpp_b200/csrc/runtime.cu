@@ -345,14 +345,15 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     CUDA_TRY(cudaMemset(s->dFlags, 0, sizeof(int32_t) * 4));
     CUDA_TRY(cudaMemset(s->dBarrier, 0, sizeof(int32_t)));
     CUDA_TRY(cudaMemset(s->dPos, 0, sizeof(double) * devRowDoubles(s)));
+    /* draw scratch (z, log(1-u), j of the colour in flight): kernels whose draws run in their own launch */
+    CUDA_TRY(cudaMalloc(&s->dDimZ, sizeof(double) * (size_t)s->K));
+    CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
+    CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * (size_t)s->K));
     if (cfg->shard_mode == MCMCPP_SHARD_DIM) {
         const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K;
         CUDA_TRY(cudaMalloc(&s->dDimPartial, sizeof(double) * tableDoubles));
         CUDA_TRY(cudaMemset(s->dDimPartial, 0, sizeof(double) * tableDoubles));
         CUDA_TRY(cudaMalloc(&s->dDimTable, sizeof(double*) * (size_t)cfg->world));
-        CUDA_TRY(cudaMalloc(&s->dDimZ, sizeof(double) * (size_t)s->K));
-        CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
-        CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * (size_t)s->K));
         CUDA_TRY(cudaMalloc(&s->dDimList, sizeof(int32_t) * ((size_t)s->K + 1)));
         CUDA_TRY(cudaMemset(s->dDimList, 0, sizeof(int32_t) * ((size_t)s->K + 1)));
         CUDA_TRY(cudaMalloc(&s->dSyncWord, sizeof(double)));
