@@ -215,6 +215,21 @@ int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_rank
  * out so that every slice but possibly the last has even length: 16-byte aligned slices for vector loads). */
 int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count);
 
+/* ---- Analysis::CovarianceMatrix (Analysis/CovarianceMatrix.h:120-215) on the device ------------------------
+ *      Same definitions as the reference (n = used steps x walkers, cov = E[xy] - E[x]E[y], Kahan-summed,
+ *      correlation normalised by rows then columns); the points are summed in a different order (per-CTA Kahan
+ *      pairs, CTA order), so values agree with calculateCovar to ~1e-15 relative on the sums, not bit for bit.
+ *      num_params <= 128.  Outputs (host): mean[D], cov[D*D], corr[D*D] row-major; any may be NULL.
+ *      cov_begin: zeroStorage + start adding every slice_interval-th step STORED by later mcmcpp_sampler_run calls
+ *      (the chain itself may be off); include_current != 0 counts the present walker positions as step 0, as the
+ *      chain's first row is (EnsembleSampler.h:228).  One GPU, or DATA sharding (replicated ensemble). */
+int mcmcpp_sampler_cov_begin(mcmcpp_sampler* s, int slice_interval, int include_current);
+int mcmcpp_sampler_cov_result(mcmcpp_sampler* s, double* mean, double* cov, double* corr, long long* points);
+int mcmcpp_sampler_cov_end(mcmcpp_sampler* s);
+/* calculateCovar(begin, end, sliceInterval) over a host chain [steps][num_walkers][num_params] */
+int mcmcpp_covariance(const double* chain_host, long long steps, int num_walkers, int num_params, int slice_interval, int device,
+                      double* mean, double* cov, double* corr, long long* points);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,217 @@
+/*
+ * mcmcpp_b200/csrc/analysis.cu -- MCMC::Analysis::CovarianceMatrix (MCMCpp/Analysis/CovarianceMatrix.h:120-215) on the
+ * device, so the covariance check of a 1M-walker run does not need the chain on the host.
+ *
+ * The reference adds every point to D Kahan-summed averages and D(D+1)/2 Kahan-summed products in chain order.  Here
+ * the points are spread over a fixed grid; every CTA keeps its own Kahan (sum, compensation) pair per item in HBM
+ * across calls, and finalize adds the CTAs' pairs in CTA order (Kahan again).  Same definitions (n = steps*W, cov =
+ * E[xy] - E[x]E[y], correlation normalised by rows then columns); the summation ORDER differs, so results carry the
+ * tolerance tier (<= 1e-12 relative on the sums; tests state it), not bit equality.
+ *   D <= 4   covSmallKernel: one thread per point, items in registers, CTA tree, one Kahan step per CTA per call
+ *   D <= 128 covItemKernel:  one thread per item (i, j<=i), 32-point chunks staged in shared memory
+ */
+#include <cmath>
+#include <cstdio>
+#include <vector>
+#include "analysis.h"
+#include "mcmcpp_b200/capi.h"
+
+namespace
+{
+enum { CovThreads = 512, CovChunk = 32, CovItemsPerThread = 17, CovSmallThreads = 256 };
+
+__device__ __forceinline__ void kahanAdd(double& sum, double& comp, double val)
+{
+    const double y = __dsub_rn(val, comp);
+    const double t = __dadd_rn(sum, y);
+    comp = __dsub_rn(__dsub_rn(t, sum), y);
+    sum = t;
+}
+
+/* item p: p < D -> average of x_p; else the (i, j <= i) product with q = p - D = i(i+1)/2 + j */
+__device__ __forceinline__ void itemIndices(int p, int D, int& i, int& j)
+{
+    if (p < D) { i = p; j = -1; return; }
+    const int q = p - D;
+    int r = (int)((sqrt(8.0 * (double)q + 1.0) - 1.0) * 0.5);
+    while ((r + 1) * (r + 2) / 2 <= q) ++r;
+    while (r * (r + 1) / 2 > q) --r;
+    i = r; j = q - r * (r + 1) / 2;
+}
+
+__global__ void __launch_bounds__(CovThreads) covItemKernel(const double* __restrict__ rows, long long nPoints, int D, int nItems,
+                                                            double2* __restrict__ acc)
+{
+    extern __shared__ double chunk[];                       /* [CovChunk][D] */
+    int ij[CovItemsPerThread];
+    double sum[CovItemsPerThread], comp[CovItemsPerThread];
+    double2* mine = acc + (size_t)blockIdx.x * nItems;
+#pragma unroll
+    for (int k = 0; k < CovItemsPerThread; ++k) {
+        const int p = threadIdx.x + k * CovThreads;
+        int i = 0, j = -1;
+        sum[k] = 0.0; comp[k] = 0.0;
+        if (p < nItems) {
+            itemIndices(p, D, i, j);
+            const double2 v = mine[p];
+            sum[k] = v.x; comp[k] = v.y;
+        }
+        ij[k] = (i << 8) | (j & 0xff);
+    }
+    const long long nChunks = (nPoints + CovChunk - 1) / CovChunk;
+    for (long long c = blockIdx.x; c < nChunks; c += gridDim.x) {
+        const long long p0 = c * CovChunk;
+        const int pts = (int)((nPoints - p0) < CovChunk ? (nPoints - p0) : CovChunk);
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < pts * D; idx += CovThreads) chunk[idx] = rows[(size_t)p0 * D + idx];
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < CovItemsPerThread; ++k) {
+            if (threadIdx.x + k * CovThreads >= nItems) break;
+            const int i = ij[k] >> 8, jj = ij[k] & 0xff;
+            double s = 0.0;
+            if (jj == 0xff) { for (int pt = 0; pt < pts; ++pt) s = __dadd_rn(s, chunk[pt * D + i]); }
+            else { for (int pt = 0; pt < pts; ++pt) s = __dadd_rn(s, __dmul_rn(chunk[pt * D + i], chunk[pt * D + jj])); }
+            kahanAdd(sum[k], comp[k], s);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < CovItemsPerThread; ++k) {
+        const int p = threadIdx.x + k * CovThreads;
+        if (p < nItems) mine[p] = make_double2(sum[k], comp[k]);
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(CovSmallThreads) covSmallKernel(const double* __restrict__ rows, long long nPoints, double2* __restrict__ acc)
+{
+    constexpr int NI = D + D * (D + 1) / 2;
+    __shared__ double red[CovSmallThreads / 32][NI];
+    double sum[NI], comp[NI];
+#pragma unroll
+    for (int k = 0; k < NI; ++k) { sum[k] = 0.0; comp[k] = 0.0; }
+    for (long long p = (long long)blockIdx.x * CovSmallThreads + threadIdx.x; p < nPoints; p += (long long)gridDim.x * CovSmallThreads) {
+        double x[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) x[d] = rows[(size_t)p * D + d];
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            kahanAdd(sum[i], comp[i], x[i]);
+#pragma unroll
+            for (int j = 0; j <= i; ++j) kahanAdd(sum[D + i * (i + 1) / 2 + j], comp[D + i * (i + 1) / 2 + j], __dmul_rn(x[i], x[j]));
+        }
+    }
+    /* CTA total of (sum - comp) per item: warp butterflies, then warp 0 over the warps */
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NI; ++k) {
+        double v = __dsub_rn(sum[k], comp[k]);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) v = __dadd_rn(v, __shfl_xor_sync(0xffffffffu, v, off));
+        if (lane == 0) red[warp][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < NI) {
+        double v = 0.0;
+        for (int w = 0; w < CovSmallThreads / 32; ++w) v = __dadd_rn(v, red[w][threadIdx.x]);
+        double2 a = acc[(size_t)blockIdx.x * NI + threadIdx.x];
+        kahanAdd(a.x, a.y, v);
+        acc[(size_t)blockIdx.x * NI + threadIdx.x] = a;
+    }
+}
+
+/* totals[p] = Kahan sum over CTAs of (sum, comp) pairs, CTA order */
+__global__ void covTotalsKernel(const double2* __restrict__ acc, int nBlocks, int nItems, double* __restrict__ totals)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nItems) return;
+    double s = 0.0, c = 0.0, carried = 0.0, cc = 0.0;
+    for (int b = 0; b < nBlocks; ++b) {
+        const double2 v = acc[(size_t)b * nItems + p];
+        kahanAdd(s, c, v.x);
+        kahanAdd(carried, cc, v.y);
+    }
+    totals[p] = __dsub_rn(__dsub_rn(s, c), __dsub_rn(carried, cc));
+}
+}  // namespace
+
+struct mcmcpp_cov_accum
+{
+    int D = 0, nItems = 0, nBlocks = 0;
+    double2* acc = nullptr;
+    double* totals = nullptr;
+};
+
+mcmcpp_cov_accum* mcmcpp_cov_create(int D)
+{
+    if (D < 1 || D > 128) return nullptr;
+    mcmcpp_cov_accum* c = new mcmcpp_cov_accum();
+    c->D = D;
+    c->nItems = D + D * (D + 1) / 2;
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    c->nBlocks = D <= 4 ? sms * 8 : sms * 2;
+    if (cudaMalloc(&c->acc, sizeof(double2) * (size_t)c->nBlocks * c->nItems) != cudaSuccess ||
+        cudaMalloc(&c->totals, sizeof(double) * (size_t)c->nItems) != cudaSuccess) {
+        mcmcpp_cov_destroy(c);
+        return nullptr;
+    }
+    return c;
+}
+
+void mcmcpp_cov_destroy(mcmcpp_cov_accum* c)
+{
+    if (!c) return;
+    cudaFree(c->acc); cudaFree(c->totals);
+    delete c;
+}
+
+int mcmcpp_cov_zero(mcmcpp_cov_accum* c, cudaStream_t stream)
+{
+    return cudaMemsetAsync(c->acc, 0, sizeof(double2) * (size_t)c->nBlocks * c->nItems, stream) == cudaSuccess ? MCMCPP_OK : MCMCPP_ERR_CUDA;
+}
+
+int mcmcpp_cov_accumulate(mcmcpp_cov_accum* c, const double* devRows, long long nPoints, cudaStream_t stream)
+{
+    if (nPoints <= 0) return MCMCPP_OK;
+    switch (c->D) {
+    case 1: covSmallKernel<1><<<c->nBlocks, CovSmallThreads, 0, stream>>>(devRows, nPoints, c->acc); break;
+    case 2: covSmallKernel<2><<<c->nBlocks, CovSmallThreads, 0, stream>>>(devRows, nPoints, c->acc); break;
+    case 3: covSmallKernel<3><<<c->nBlocks, CovSmallThreads, 0, stream>>>(devRows, nPoints, c->acc); break;
+    case 4: covSmallKernel<4><<<c->nBlocks, CovSmallThreads, 0, stream>>>(devRows, nPoints, c->acc); break;
+    default:
+        covItemKernel<<<c->nBlocks, CovThreads, sizeof(double) * CovChunk * c->D, stream>>>(devRows, nPoints, c->D, c->nItems, c->acc);
+    }
+    return cudaGetLastError() == cudaSuccess ? MCMCPP_OK : MCMCPP_ERR_CUDA;
+}
+
+int mcmcpp_cov_finalize(mcmcpp_cov_accum* c, long long nPoints, double* mean, double* cov, double* corr, cudaStream_t stream)
+{
+    const int D = c->D;
+    covTotalsKernel<<<(c->nItems + 255) / 256, 256, 0, stream>>>(c->acc, c->nBlocks, c->nItems, c->totals);
+    std::vector<double> t((size_t)c->nItems);
+    if (cudaMemcpyAsync(t.data(), c->totals, sizeof(double) * t.size(), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+        cudaStreamSynchronize(stream) != cudaSuccess)
+        return MCMCPP_ERR_CUDA;
+    /* finalizeMatrix, CovarianceMatrix.h:143-185 */
+    const double ptCount = (double)nPoints;
+    std::vector<double> avg((size_t)D), cv((size_t)D * D), cr((size_t)D * D);
+    for (int i = 0; i < D; ++i) avg[(size_t)i] = t[(size_t)i] / ptCount;
+    for (int i = 0; i < D; ++i)
+        for (int j = 0; j <= i; ++j) {
+            const double temp = (t[(size_t)(D + i * (i + 1) / 2 + j)] / ptCount) - (avg[(size_t)i] * avg[(size_t)j]);
+            cv[(size_t)i * D + j] = temp;
+            cv[(size_t)j * D + i] = temp;
+        }
+    for (int i = 0; i < D; ++i) {
+        const double sv = std::sqrt(cv[(size_t)i * D + i]);
+        for (int j = 0; j < D; ++j) cr[(size_t)i * D + j] = cv[(size_t)i * D + j] / sv;
+    }
+    for (int j = 0; j < D; ++j) {
+        const double sv = std::sqrt(cv[(size_t)j * D + j]);
+        for (int i = 0; i < D; ++i) cr[(size_t)i * D + j] /= sv;
+    }
+    for (int i = 0; i < D; ++i) if (mean) mean[i] = avg[(size_t)i];
+    for (size_t k = 0; k < (size_t)D * D; ++k) { if (cov) cov[k] = cv[k]; if (corr) corr[k] = cr[k]; }
+    return MCMCPP_OK;
+}

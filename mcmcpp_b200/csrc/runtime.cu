@@ -24,6 +24,7 @@
 #include "mcmcpp_b200/capi.h"
 #include "mcmcpp_b200/device_rng.cuh"
 #include "builtin_targets.h"
+#include "analysis.h"
 
 using MCMC::Device::U128;
 
@@ -168,6 +169,10 @@ struct mcmcpp_sampler
     int32_t* dBarrier = nullptr;
     std::vector<void*> peerOpened;
     const double** dPeerPos = nullptr;
+    /* on-the-fly CovarianceMatrix over the stored steps (analysis.cu) */
+    mcmcpp_cov_accum* cov = nullptr;
+    int covInterval = 1;
+    long long covIndex = 0, covSteps = 0;
     /* DIM sharding */
     double* dDimPartial = nullptr;         /* [2][world][K] */
     double** dDimTable = nullptr;          /* [world] device table of every rank's partial table */
@@ -472,6 +477,7 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
     cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
     mcmcpp_builtin_release(s->builtinAux);
+    mcmcpp_cov_destroy(s->cov);
     for (int i = 0; i < ChainSlots; ++i) {
         cudaFree(s->dChain[i]);
         if (s->slotReady[i]) cudaEventDestroy(s->slotReady[i]);
@@ -550,6 +556,13 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
         if ((rc = halfStep(s, 0, row)) != MCMCPP_OK) return rc;
         if ((rc = halfStep(s, 1, row)) != MCMCPP_OK) return rc;
         ++s->ensembleSteps;
+        if (s->cov) {                                   /* the stored row IS the state after the black half-step */
+            if ((s->covIndex % s->covInterval) == 0) {
+                if ((rc = mcmcpp_cov_accumulate(s->cov, s->dPos, s->W, s->stream)) != MCMCPP_OK) return fail(rc, "covariance accumulation failed");
+                ++s->covSteps;
+            }
+            ++s->covIndex;
+        }
         if (keepRow && (rc = appendRowFromDeviceSlot(s, slot)) != MCMCPP_OK) return rc;
         ++s->stored;
         s->totalSteps += 2ULL * (unsigned long long)s->slotCount * (unsigned long long)perStored;
@@ -743,6 +756,86 @@ int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_rank
     CUDA_TRY(cudaMemcpy(s->dPeerPos, ptrs.data(), sizeof(double*) * (size_t)s->cfg.world, cudaMemcpyHostToDevice));
     s->base.peer_pos = s->dPeerPos;
     return MCMCPP_OK;
+}
+
+/* ---- Analysis::CovarianceMatrix on the device (Analysis/CovarianceMatrix.h:120-215) -------------------------- */
+int mcmcpp_sampler_cov_begin(mcmcpp_sampler* s, int slice_interval, int include_current)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (slice_interval <= 0) return fail(MCMCPP_ERR_ARG, "slice interval must be positive");
+    if (s->Dl != s->D || (s->cfg.world > 1 && s->cfg.shard_mode != MCMCPP_SHARD_DATA))
+        return fail(MCMCPP_ERR_UNSUPPORTED, "on-the-fly covariance needs whole rows of every walker on this rank");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    if (!s->cov && !(s->cov = mcmcpp_cov_create(s->D))) return fail(MCMCPP_ERR_UNSUPPORTED, "covariance accumulator: numParams must be <= 128");
+    int rc = mcmcpp_cov_zero(s->cov, s->stream);
+    if (rc != MCMCPP_OK) return fail(rc, "covariance accumulator reset failed");
+    s->covInterval = slice_interval;
+    s->covIndex = 0;
+    s->covSteps = 0;
+    if (include_current) {
+        if (!s->initialised) return fail(MCMCPP_ERR_STATE, "no walker positions yet");
+        if ((rc = mcmcpp_cov_accumulate(s->cov, s->dPos, s->W, s->stream)) != MCMCPP_OK) return fail(rc, "covariance accumulation failed");
+        s->covIndex = 1;
+        s->covSteps = 1;
+    }
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_cov_result(mcmcpp_sampler* s, double* mean, double* cov, double* corr, long long* points)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (!s->cov) return fail(MCMCPP_ERR_STATE, "mcmcpp_sampler_cov_begin was not called");
+    if (s->covSteps == 0) return fail(MCMCPP_ERR_STATE, "no step accumulated yet");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    const long long n = s->covSteps * (long long)s->W;
+    if (points) *points = n;
+    int rc = mcmcpp_cov_finalize(s->cov, n, mean, cov, corr, s->stream);
+    return rc == MCMCPP_OK ? rc : fail(rc, "covariance finalize failed");
+}
+
+int mcmcpp_sampler_cov_end(mcmcpp_sampler* s)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    mcmcpp_cov_destroy(s->cov);
+    s->cov = nullptr;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_covariance(const double* chain_host, long long steps, int num_walkers, int num_params, int slice_interval, int device,
+                      double* mean, double* cov, double* corr, long long* points)
+{
+    if (!chain_host || steps <= 0 || num_walkers <= 0 || num_params <= 0 || slice_interval <= 0) return fail(MCMCPP_ERR_ARG, "bad argument");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return fail(MCMCPP_ERR_CUDA, "no CUDA device: mcmcpp_b200 has no CPU fallback");
+    CUDA_TRY(cudaSetDevice(device));
+    mcmcpp_cov_accum* c = mcmcpp_cov_create(num_params);
+    if (!c) return fail(MCMCPP_ERR_UNSUPPORTED, "covariance accumulator: numParams must be <= 128");
+    const size_t row = (size_t)num_walkers * (size_t)num_params;
+    /* stage up to ~256 MB of used steps per upload */
+    long long perUpload = std::max<long long>(1, (long long)((size_t)(256u << 20) / (row * sizeof(double))));
+    double* dRows = nullptr;
+    cudaStream_t st = nullptr;
+    int rc = MCMCPP_OK;
+    long long used = 0;
+    if (cudaMalloc(&dRows, sizeof(double) * row * (size_t)perUpload) != cudaSuccess || cudaStreamCreate(&st) != cudaSuccess) rc = MCMCPP_ERR_CUDA;
+    if (rc == MCMCPP_OK) rc = mcmcpp_cov_zero(c, st);
+    long long staged = 0;
+    for (long long index = 0; rc == MCMCPP_OK && index < steps; ++index) {
+        if ((index % slice_interval) != 0) continue;              /* calculateCovar's slicing (CovarianceMatrix.h:126-131) */
+        if (cudaMemcpyAsync(dRows + row * (size_t)staged, chain_host + row * (size_t)index, sizeof(double) * row, cudaMemcpyHostToDevice, st) != cudaSuccess) rc = MCMCPP_ERR_CUDA;
+        ++staged; ++used;
+        if (staged == perUpload || index + slice_interval >= steps) {
+            if (rc == MCMCPP_OK) rc = mcmcpp_cov_accumulate(c, dRows, staged * (long long)num_walkers, st);
+            if (rc == MCMCPP_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = MCMCPP_ERR_CUDA;
+            staged = 0;
+        }
+    }
+    if (rc == MCMCPP_OK) rc = mcmcpp_cov_finalize(c, used * (long long)num_walkers, mean, cov, corr, st);
+    if (points) *points = used * (long long)num_walkers;
+    if (st) cudaStreamDestroy(st);
+    cudaFree(dRows);
+    mcmcpp_cov_destroy(c);
+    return rc == MCMCPP_OK ? rc : fail(rc, "covariance computation failed");
 }
 
 int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count)

@@ -217,6 +217,20 @@ class EnsembleSampler:
         """Same, into caller-owned host buffers given as raw pointers (e.g. pinned torch tensors)."""
         check(self._lib.mcmcpp_sampler_get_state(self._h, positionsPtr, auxPtr))
 
+    # -- Analysis::CovarianceMatrix accumulated on the device while sampling (chain may be off) -----
+    def covBegin(self, sliceInterval=1, includeCurrent=True):
+        check(self._lib.mcmcpp_sampler_cov_begin(self._h, int(sliceInterval), int(bool(includeCurrent))))
+
+    def covResult(self):
+        """(mean[D], cov[D,D], corr[D,D], points) of the steps stored since covBegin."""
+        D = self.numParams
+        mean, cov, corr, n = np.empty(D), np.empty((D, D)), np.empty((D, D)), C.c_longlong()
+        check(self._lib.mcmcpp_sampler_cov_result(self._h, mean.ctypes.data, cov.ctypes.data, corr.ctypes.data, C.byref(n)))
+        return mean, cov, corr, n.value
+
+    def covEnd(self):
+        check(self._lib.mcmcpp_sampler_cov_end(self._h))
+
     # -- diagnostics -----------------------------------------------------------------------------
     def getTrace(self, maxRows):
         buf = (_capi.Trace * int(maxRows))()

@@ -381,3 +381,61 @@ void oracle_stretch_half_slots(uint64_t seed, int kind, const double* tparams, i
     }
     free(prop);
 }
+
+/*
+ * CovarianceMatrix::calculateCovar (MCMCpp/Analysis/CovarianceMatrix.h:120-141) over a contiguous chain
+ * [S][W][D]: rows with (index % sliceInterval) == 0 are used; every point adds x_i to the Kahan-summed averages
+ * (addAverage :238-245) and x_i*x_j, j <= i, to the Kahan-summed products, both triangle entries (addProduct :217-235;
+ * processPoint :201-214); finalizeMatrix (:143-185): avg /= n; cov_ij = prod_ij / n - avg_i * avg_j;
+ * corr = cov / sqrt(var_i) row by row, then / sqrt(var_j) column by column.  mean/cov/corr: D, D*D, D*D doubles.
+ * Returns the number of points used (steps used * W).
+ */
+long oracle_covariance(const double* chain, long S, int W, int D, int sliceInterval, double* mean, double* cov, double* corr)
+{
+    const size_t DD = (size_t)D * (size_t)D;
+    double* prod = (double*)calloc(DD, sizeof(double));
+    double* prodC = (double*)calloc(DD, sizeof(double));
+    double* avg = (double*)calloc((size_t)D, sizeof(double));
+    double* avgC = (double*)calloc((size_t)D, sizeof(double));
+    long numPts = 0;
+    for (long index = 0; index < S; ++index) {
+        if ((index % sliceInterval) != 0) continue;
+        for (int w = 0; w < W; ++w) {
+            const double* pt = chain + ((size_t)index * W + w) * D;
+            for (int i = 0; i < D; ++i) {
+                double y = pt[i] - avgC[i];
+                double t = avg[i] + y;
+                avgC[i] = (t - avg[i]) - y;
+                avg[i] = t;
+                for (int j = 0; j <= i; ++j) {
+                    const double val = pt[i] * pt[j];
+                    size_t o = (size_t)i * D + j;
+                    y = val - prodC[o]; t = prod[o] + y; prodC[o] = (t - prod[o]) - y; prod[o] = t;
+                    if (i != j) {
+                        o = (size_t)j * D + i;
+                        y = val - prodC[o]; t = prod[o] + y; prodC[o] = (t - prod[o]) - y; prod[o] = t;
+                    }
+                }
+            }
+        }
+        ++numPts;
+    }
+    const double ptCount = (double)(numPts * W);
+    for (int i = 0; i < D; ++i) { avg[i] /= ptCount; mean[i] = avg[i]; }
+    for (int i = 0; i < D; ++i)
+        for (int j = 0; j <= i; ++j) {
+            const double temp = (prod[(size_t)i * D + j] / ptCount) - (avg[i] * avg[j]);
+            cov[(size_t)i * D + j] = temp;
+            cov[(size_t)j * D + i] = temp;
+        }
+    for (int i = 0; i < D; ++i) {
+        const double sv = sqrt(cov[(size_t)i * D + i]);
+        for (int j = 0; j < D; ++j) corr[(size_t)i * D + j] = cov[(size_t)i * D + j] / sv;
+    }
+    for (int j = 0; j < D; ++j) {
+        const double sv = sqrt(cov[(size_t)j * D + j]);
+        for (int i = 0; i < D; ++i) corr[(size_t)i * D + j] /= sv;
+    }
+    free(prod); free(prodC); free(avg); free(avgC);
+    return numPts * W;
+}

@@ -66,6 +66,8 @@ class Port:
         L.oracle_stretch_run.argtypes = [C.c_void_p, C.c_int, c_dp, C.c_int, C.c_int, C.c_int, C.c_int,
                                          c_dp, c_dp, C.c_void_p, C.c_void_p, C.c_int, C.c_int, c_dp, C.c_void_p]
 
+        L.oracle_covariance.restype = C.c_long
+        L.oracle_covariance.argtypes = [c_dp, C.c_long, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp]
         L.oracle_stretch_run_per_walker.restype = C.c_int
         L.oracle_stretch_run_per_walker.argtypes = L.oracle_stretch_run.argtypes
         L.oracle_pcg64_seed_many.argtypes = [C.c_void_p, c_u64, C.c_int]
@@ -75,6 +77,14 @@ class Port:
                                                 C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int]
 
     # --- rng -----------------------------------------------------------
+    def covariance(self, chain, interval=1):
+        """CovarianceMatrix::calculateCovar over chain[S][W][D] -> (mean[D], cov[D,D], corr[D,D], points)."""
+        chain = np.ascontiguousarray(chain, dtype=np.float64)
+        S, W, D = chain.shape
+        mean, cov, corr = np.empty(D), np.empty((D, D)), np.empty((D, D))
+        n = self.lib.oracle_covariance(_dp(chain), S, W, D, int(interval), _dp(mean), _dp(cov), _dp(corr))
+        return mean, cov, corr, int(n)
+
     def pcg64(self, seed, stream):
         g = Pcg64()
         self.lib.oracle_pcg64_seed(C.byref(g), seed & (2**64 - 1), stream & (2**64 - 1))
@@ -174,6 +184,8 @@ class Ref:
         L.ref_draws.argtypes = [C.c_longlong, C.c_longlong, C.c_int, C.c_long, C.POINTER(C.c_int), c_dp, c_dp]
         L.ref_pcg64_raw.argtypes = [C.c_ulonglong, C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong), C.c_long]
         L.ref_pcg32_raw.argtypes = [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_uint), C.c_long]
+        L.ref_covariance.restype = C.c_int
+        L.ref_covariance.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, C.c_int, c_dp, c_dp, c_dp]
         self.block_size = L.ref_block_size()
         self.hardware_concurrency = L.ref_hardware_concurrency()
 
@@ -184,6 +196,17 @@ class Ref:
         flat = x.reshape(-1, D).copy()
         out = np.array([self.lib.ref_logp(KIND[kind], D, _dp(params), _dp(flat[i])) for i in range(flat.shape[0])])
         return out.reshape(x.shape[:-1])
+
+    def covariance(self, kind, params, pos, logp, nsteps, cov_interval=1, seed=0):
+        """Sequential reference run, then the reference's CovarianceMatrix over its chain.
+        Returns (chain[(nsteps+1),W,D], cov[D,D], corr[D,D])."""
+        pos = np.array(pos, dtype=np.float64, order="C")
+        logp = np.array(logp, dtype=np.float64)
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        chain, cov, corr = np.empty((nsteps + 1, W, D)), np.empty((D, D)), np.empty((D, D))
+        self.lib.ref_covariance(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, cov_interval, _dp(chain), _dp(cov), _dp(corr))
+        return chain, cov, corr
 
     def init_normal(self, seed, n):
         out = np.empty(n)

@@ -15,6 +15,7 @@
 #include "EnsembleSampler.h"              /* MCMCpp/EnsembleSampler.h */
 #include "ParallelEnsembleSampler.h"      /* MCMCpp/ParallelEnsembleSampler.h */
 #include "Movers/StretchMove.h"           /* MCMCpp/Movers/StretchMove.h */
+#include "Analysis/CovarianceMatrix.h"    /* MCMCpp/Analysis/CovarianceMatrix.h */
 #include "Common/SkewedGaussian.h"        /* test/sequential/SkewedGaussian/Common/SkewedGaussian.h */
 #include "mcmcpp_b200/targets.h"          /* HD functors for the synthetic configs (kinds 1-4) */
 
@@ -45,6 +46,33 @@ int runSequential(const Calc& calc, int W, int D, int seed, double* initPos, dou
         for (; it != end && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
     }
     return ok ? sampler.getStoredSteps() : -sampler.getStoredSteps();
+}
+
+/* Same run, then the reference's own CovarianceMatrix over the stored chain (Analysis/CovarianceMatrix.h:120-141). */
+template <class Calc>
+int runCovariance(const Calc& calc, int W, int D, int seed, double* initPos, double* initAux, int nsteps, int covInterval,
+                  double* chainOut, double* covOut, double* corrOut)
+{
+    typedef MCMC::Mover::StretchMove<double, Calc> Mover;
+    Mover mover(D, seed, calc);
+    unsigned long long blocks = (unsigned long long)(nsteps + 1) / MCMC::Chain::Detail::BlockSize + 2ULL;
+    unsigned long long maxBytes = blocks * sizeof(double) * D * MCMC::Chain::Detail::BlockSize * (unsigned long long)W;
+    MCMC::EnsembleSampler<double, Mover> sampler(seed, W, D, mover, maxBytes);
+    sampler.setInitialWalkerPos(initPos, initAux);
+    sampler.runMCMC(nsteps);
+    MCMC::Analysis::CovarianceMatrix<double> cm(D, W);
+    cm.calculateCovar(sampler.getStepIttBegin(), sampler.getStepIttEnd(), covInterval);
+    for (int i = 0; i < D; ++i)
+        for (int j = 0; j < D; ++j) {
+            covOut[i * D + j] = cm.getCovarianceMatrixElement(i, j);
+            corrOut[i * D + j] = cm.getCorrelationMatrixElement(i, j);
+        }
+    auto it = sampler.getStepIttBegin();
+    auto end = sampler.getStepIttEnd();
+    size_t row = (size_t)W * D;
+    int s = 0;
+    for (; it != end && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
+    return sampler.getStoredSteps();
 }
 
 /* Throughput run: steps are issued in bursts that fit one chain block, reset() in between
@@ -125,6 +153,15 @@ int ref_stretch_run(int kind, const double* p, int W, int D, int seed, double* i
 {
 #define CALL_RUN(c) runSequential(c, W, D, seed, initPos, initAux, nsteps, interval, chainOut, acc, tot)
     DISPATCH(CALL_RUN)
+    return 0;
+}
+
+/* reference CovarianceMatrix::calculateCovar over the chain of a sequential run (chainOut: nsteps+1 rows) */
+int ref_covariance(int kind, const double* p, int W, int D, int seed, double* initPos, double* initAux, int nsteps,
+                   int covInterval, double* chainOut, double* covOut, double* corrOut)
+{
+#define CALL_COV(c) runCovariance(c, W, D, seed, initPos, initAux, nsteps, covInterval, chainOut, covOut, corrOut)
+    DISPATCH(CALL_COV)
     return 0;
 }
 

@@ -53,6 +53,18 @@ def main():
     X = rng.standard_normal((M, P)); th = rng.standard_normal(P); y = X @ th + rng.standard_normal(M)
     lin = np.concatenate([[float(M), 100.0], X.reshape(-1), y])
     case("linreg_p3_w16", "linreg", lin, 16, 3, 50, scale=0.3, keep_rows=[0, 1, 50])
+    # Analysis/CovarianceMatrix.h on the chains of two short runs (reference class, unmodified)
+    def cov_case(name, kind, params, W, D, nsteps, cov_interval, init_seed=53):
+        init = R.init_normal(init_seed, W * D).reshape(W, D)
+        params = np.asarray(params, dtype=np.float64)
+        lp = R.logp(kind, params, init)
+        chain, cov, corr = R.covariance(kind, params, init, lp, nsteps, cov_interval=cov_interval)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), chain=chain, cov=cov, corr=corr, cov_interval=cov_interval)
+        print(name, cov.reshape(-1)[:3])
+
+    os.makedirs(os.path.join(HERE, "analysis"), exist_ok=True)
+    cov_case("analysis/cov_skewed_w32", "skewed_gauss_2d", [0.13], 32, 2, 300, 1)
+    cov_case("analysis/cov_diag_d5_w64_slice3", "diag_gauss", iv5, 64, 5, 60, 3)
     for k, v in out.items():
         print(k, v)
 

@@ -1,0 +1,95 @@
+"""GPU (-m gpu): device CovarianceMatrix (mcmcpp_b200/csrc/analysis.cu) through the C-ABI against the reference-made
+fixtures and the oracle.  Definitions are the reference's; the summation order is per-CTA Kahan pairs, so the bar is
+1e-12 relative on covariance entries measured against the scale of their terms (E[xy] and E[x]E[y]), stated below."""
+import os
+import numpy as np
+import pytest
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+
+def close(dev, ref, scale, rtol=1e-12):
+    return np.all(np.abs(dev - ref) <= rtol * scale)
+
+
+def scales(chain, interval):
+    pts = chain[::interval].reshape(-1, chain.shape[2])
+    m2 = (pts[:, :, None] * pts[:, None, :]).mean(axis=0)
+    return np.abs(m2) + np.abs(np.outer(pts.mean(axis=0), pts.mean(axis=0))) + 1e-300
+
+
+@pytest.mark.parametrize("name", ["cov_skewed_w32", "cov_diag_d5_w64_slice3"])
+def test_device_covariance_against_reference_fixture(name):
+    import mcmcpp_b200 as m
+    z = np.load(os.path.join(GOLDEN, "analysis", name + ".npz"))
+    chain, cov, corr, interval = z["chain"], z["cov"], z["corr"], int(z["cov_interval"])
+    S, W, D = chain.shape
+    cm = m.CovarianceMatrix(D, W)
+    cm.calculateCovar(chain, interval)
+    assert cm.points == len(range(0, S, interval)) * W
+    assert close(cm.covarMat, cov, scales(chain, interval))
+    assert np.allclose(cm.corrMat, corr, rtol=0, atol=1e-11)
+    assert cm.getCovarianceMatrixElement(D - 1, 0) == cm.covarMat[D - 1, 0]
+    assert abs(cm.getCorrelationMatrixElement(0, 0) - 1.0) < 1e-12
+
+
+@pytest.mark.parametrize("W,D,S,interval", [(64, 1, 40, 1), (4096, 2, 30, 2), (512, 3, 25, 1), (256, 4, 33, 5), (128, 7, 50, 1),
+                                            (300, 50, 12, 1), (256, 100, 9, 2), (260, 128, 5, 1)])
+def test_device_covariance_every_kernel_shape_against_oracle(port, W, D, S, interval):
+    """thread-per-point kernels (D <= 4), thread-per-item kernel (5..128, ragged chunks), slicing, multi-upload."""
+    import mcmcpp_b200 as m
+    rng = np.random.default_rng(D * 1000 + W)
+    A = rng.standard_normal((D, D)) / np.sqrt(D)
+    chain = rng.standard_normal((S, W, D)) @ A + rng.standard_normal(D) * 3.0
+    mean, cov, corr, n = port.covariance(chain, interval)
+    cm = m.CovarianceMatrix(D, W)
+    cm.calculateCovar(chain, interval)
+    assert cm.points == n
+    assert np.allclose(cm.means, mean, rtol=1e-13, atol=1e-15)
+    assert close(cm.covarMat, cov, scales(chain, interval))
+    assert np.allclose(cm.corrMat, corr, rtol=0, atol=1e-10)
+
+
+def test_on_the_fly_covariance_matches_chain_covariance(port):
+    """covBegin / runMCMC / covResult with the chain kept: the device accumulation over the stored steps equals
+    calculateCovar over the very chain the run produced (oracle restatement), slicing included."""
+    import mcmcpp_b200 as m
+    W, D, steps = 2048, 2, 60
+    rng = np.random.default_rng(4)
+    init = rng.standard_normal((W, D))
+    lp = port.logp("skewed_gauss_2d", np.array([0.13]), init)
+    s = m.EnsembleSampler(3, W, D, m.StretchMove(D, 3, m.SkewedGaussianTwoDim(0.13)))
+    s.setInitialWalkerPos(init, lp)
+    s.covBegin(sliceInterval=3, includeCurrent=True)
+    assert s.runMCMC(steps)
+    mean, cov, corr, n = s.covResult()
+    chain = s.getChain()
+    om, oc, orr, on = port.covariance(chain, 3)
+    assert n == on == len(range(0, steps + 1, 3)) * W
+    assert np.allclose(mean, om, rtol=1e-13, atol=1e-15) and close(cov, oc, scales(chain, 3))
+    assert np.allclose(corr, orr, rtol=0, atol=1e-11)
+    s.covEnd()
+    s.close()
+
+
+def test_on_the_fly_covariance_full_size_c2_without_chain():
+    """BASELINE config 2 size (2^20 walkers, chain off): burn in, then 20 accumulated steps; the banana target's
+    moments are known in closed form for x (marginal N(1, 10)): mean 1, variance 10 -- statistical check, wide bars."""
+    import mcmcpp_b200 as m
+    W, D = 1 << 20, 2
+    rng = np.random.default_rng(9)
+    x = 1.0 + np.sqrt(10.0) * rng.standard_normal(W)
+    y = x * x + np.sqrt(0.1) * rng.standard_normal(W)        # exact draws from the target: -(100 (y-x^2)^2 + (1-x)^2)/20
+    init = np.stack([x, y], axis=1)
+    lp = -(100.0 * (y - x * x) ** 2 + (1.0 - x) ** 2) / 20.0
+    s = m.EnsembleSampler(1, W, D, m.StretchMove(D, 1, m.RosenbrockTwoDim()), maxChainSizeBytes=0)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(30)
+    s.covBegin(sliceInterval=1, includeCurrent=False)
+    assert s.runMCMC(20)
+    mean, cov, corr, n = s.covResult()
+    assert n == 20 * W
+    assert abs(mean[0] - 1.0) < 0.05 and abs(cov[0, 0] - 10.0) < 0.3
+    assert abs(mean[1] - 11.0) < 0.3                           # E[y] = E[x^2] = 1 + 10
+    s.close()
