@@ -287,18 +287,21 @@ def gpu_arm(args):
     value = float(W) * args.steps / (ms * 1e-3)
 
     # ---- e2e: the call a user makes, HOST buffers in, HOST buffers out, copies inside the timed region --------
-    host_pos = torch.empty((W, D), dtype=torch.float64, pin_memory=True)
+    # DIM sharding: every process keeps its own column shard of the rows on its host side (W x D_local, contiguous)
+    lo, hi = parallel.dim_slice(D, rank, world) if shard == "dim" else (0, D)
+    Dloc = hi - lo
+    host_pos = torch.empty((W, Dloc), dtype=torch.float64, pin_memory=True)
     host_aux = torch.empty(W, dtype=torch.float64, pin_memory=True)
-    host_pos.copy_(pos)
+    host_pos.copy_(pos[:, lo:hi])
     host_aux.copy_(aux)
     del pos, aux
     torch.cuda.empty_cache()
     s = new_sampler()
     barrier()
     t0 = time.perf_counter()
-    s.setInitialWalkerPosPinned(host_pos.data_ptr(), host_aux.data_ptr())
+    s.setInitialWalkerPosLocal(host_pos.data_ptr(), host_aux.data_ptr())
     ok = s.runMCMC(args.steps)
-    s.getWalkerStateInto(host_pos.data_ptr(), host_aux.data_ptr())
+    s.getWalkerStateLocalInto(host_pos.data_ptr(), host_aux.data_ptr())
     e2e_acc, e2e_tot = s._counts()
     barrier()
     e2e_s = time.perf_counter() - t0
@@ -307,11 +310,11 @@ def gpu_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
     s.close()
-    state_bytes = W * D * 8 + W * 8
+    state_bytes = W * Dloc * 8 + W * 8
     e2e = {"value": float(W) * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": state_bytes / args.steps,
            "d2h_bytes_per_step": (state_bytes + 16) / args.steps, "seconds": e2e_s,
-           "what": "setInitialWalkerPos(pinned host) + runMCMC(%d) + walker state and counters back to pinned host, per rank"
-                   % args.steps}
+           "what": "setInitialWalkerPos(pinned host%s) + runMCMC(%d) + walker state and counters back to pinned host, per rank"
+                   % (", this rank's %d columns" % Dloc if shard == "dim" else "", args.steps)}
 
     if rank != 0:
         if world > 1:

@@ -166,6 +166,12 @@ int mcmcpp_sampler_set_initial(mcmcpp_sampler* s, const double* positions_host, 
 /* same with device-resident inputs (no host copy) */
 int mcmcpp_sampler_set_initial_device(mcmcpp_sampler* s, const double* positions_dev, const double* aux_dev);
 
+/* DIM sharding: the same with this rank's columns only, contiguous [W][D_local] (mcmcpp_dim_slice) -- each process
+ * keeps its shard of the rows on its own host side; in every other mode identical to the full-row calls.  Read side:
+ * mcmcpp_sampler_get_state_local. */
+int mcmcpp_sampler_set_initial_local(mcmcpp_sampler* s, const double* positions_local_host, const double* aux_host);
+int mcmcpp_sampler_get_state_local(mcmcpp_sampler* s, double* positions_local_host, double* aux_host);
+
 /* ---- setSlicingMode / setSamplingMode (EnsembleSampler.h:324-330, ParallelEnsembleSampler.h:322-330) */
 int mcmcpp_sampler_set_slicing(mcmcpp_sampler* s, int use_slicing, int interval);
 

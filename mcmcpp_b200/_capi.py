@@ -37,6 +37,8 @@ SYMBOLS = {
     "mcmcpp_sampler_destroy": (C.c_int, [_h]),
     "mcmcpp_sampler_set_initial": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
     "mcmcpp_sampler_set_initial_device": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
+    "mcmcpp_sampler_set_initial_local": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
+    "mcmcpp_sampler_get_state_local": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
     "mcmcpp_sampler_set_slicing": (C.c_int, [_h, C.c_int, C.c_int]),
     "mcmcpp_sampler_run": (C.c_int, [_h, C.c_int, C.POINTER(C.c_float)]),
     "mcmcpp_sampler_get_counts": (C.c_int, [_h, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),

@@ -510,6 +510,27 @@ int mcmcpp_sampler_set_initial_device(mcmcpp_sampler* s, const double* positions
     return afterInitialState(s, nullptr);
 }
 
+/* the rank's own slice of the rows, contiguous [W][D_local] (DIM sharding; otherwise the same as the full-row calls) */
+int mcmcpp_sampler_set_initial_local(mcmcpp_sampler* s, const double* positions_local_host, const double* aux_host)
+{
+    if (!s || !positions_local_host || !aux_host) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    CUDA_TRY(cudaMemcpyAsync(s->dPos, positions_local_host, sizeof(double) * devRowDoubles(s), cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->dLogp, aux_host, sizeof(double) * (size_t)s->W, cudaMemcpyHostToDevice, s->stream));
+    return afterInitialState(s, s->Dl == s->D ? positions_local_host : nullptr);
+}
+
+int mcmcpp_sampler_get_state_local(mcmcpp_sampler* s, double* positions_local_host, double* aux_host)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    if (positions_local_host)
+        CUDA_TRY(cudaMemcpyAsync(positions_local_host, s->dPos, sizeof(double) * devRowDoubles(s), cudaMemcpyDeviceToHost, s->stream));
+    if (aux_host) CUDA_TRY(cudaMemcpyAsync(aux_host, s->dLogp, sizeof(double) * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return MCMCPP_OK;
+}
+
 int mcmcpp_sampler_set_slicing(mcmcpp_sampler* s, int use_slicing, int interval)
 {
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");

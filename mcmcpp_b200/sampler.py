@@ -146,6 +146,13 @@ class EnsembleSampler:
         """Host inputs given as raw pointers (e.g. pinned torch tensors)."""
         check(self._lib.mcmcpp_sampler_set_initial(self._h, positionsPtr, auxPtr))
 
+    def setInitialWalkerPosLocal(self, positionsPtr, auxPtr):
+        """DIM sharding: this rank's columns only, contiguous [W][D_local] host buffer given as a raw pointer."""
+        check(self._lib.mcmcpp_sampler_set_initial_local(self._h, positionsPtr, auxPtr))
+
+    def getWalkerStateLocalInto(self, positionsPtr, auxPtr):
+        check(self._lib.mcmcpp_sampler_get_state_local(self._h, positionsPtr, auxPtr))
+
     # -- EnsembleSampler.h:232-242, 312-322 --------------------------------------------------
     def storeCurrentWalkerPositions(self):
         check(self._lib.mcmcpp_sampler_store_current(self._h))

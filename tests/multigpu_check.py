@@ -65,6 +65,17 @@ def dim_sharded_diag_gauss(port, rank, world, local):
         if world > 1:
             other = np.ones(D, dtype=bool); other[b:e] = False
             good = good and not np.any(chain[:, :, other])                  # other ranks' columns read 0
+        # the rank-local entry points move only this rank's columns, contiguous [W][D_local]
+        loc = np.empty((W, e - b)); laux = np.empty(W)
+        s.getWalkerStateLocalInto(loc.ctypes.data, laux.ctypes.data)
+        good = good and np.array_equal(loc, o["pos"][:, b:e]) and np.array_equal(laux, aux)
+        s2 = m.EnsembleSampler(6, W, D, m.StretchMove(D, 6, m.DiagGaussian(iv)), device=local, rank=rank, world=world, shardMode="dim")
+        parallel.connect(s2)
+        s2.setInitialWalkerPosLocal(np.ascontiguousarray(init[:, b:e]).ctypes.data, lp.ctypes.data)
+        s2.runMCMC(steps)
+        s2.getWalkerStateLocalInto(loc.ctypes.data, laux.ctypes.data)
+        good = good and np.array_equal(loc, o["pos"][:, b:e]) and np.array_equal(laux, aux)
+        s2.close()
         print("rank %d diag_gauss W=%d D=%d dim-sharded cols [%d,%d): %s" % (rank, W, D, b, e, "ok" if good else "MISMATCH"), flush=True)
         bad += 0 if good else 1
         s.close()
