@@ -71,7 +71,8 @@ def dim_sharded_diag_gauss(port, rank, world, local):
         good = good and np.array_equal(loc, o["pos"][:, b:e]) and np.array_equal(laux, aux)
         s2 = m.EnsembleSampler(6, W, D, m.StretchMove(D, 6, m.DiagGaussian(iv)), device=local, rank=rank, world=world, shardMode="dim")
         parallel.connect(s2)
-        s2.setInitialWalkerPosLocal(np.ascontiguousarray(init[:, b:e]).ctypes.data, lp.ctypes.data)
+        mine = np.ascontiguousarray(init[:, b:e])                # keep alive across the call
+        s2.setInitialWalkerPosLocal(mine.ctypes.data, lp.ctypes.data)
         s2.runMCMC(steps)
         s2.getWalkerStateLocalInto(loc.ctypes.data, laux.ctypes.data)
         good = good and np.array_equal(loc, o["pos"][:, b:e]) and np.array_equal(laux, aux)
