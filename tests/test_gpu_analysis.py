@@ -93,3 +93,37 @@ def test_on_the_fly_covariance_full_size_c2_without_chain():
     assert abs(mean[0] - 1.0) < 0.05 and abs(cov[0, 0] - 10.0) < 0.3
     assert abs(mean[1] - 11.0) < 0.3                           # E[y] = E[x^2] = 1 + 10
     s.close()
+
+
+def test_tier_c_long_run_statistics_match_oracle_and_analytic_truth(port):
+    """SURVEY s.8(c) tier C: a long run whose RNG discipline is NOT the sequential stream (one pcg64 stream per walker,
+    the reference's per-thread discipline) must be statistically indistinguishable from the sequential oracle and from
+    the analytic truth of the reference's 2-D target (eps = 0.13; covariance quoted in
+    test/sequential/SkewedGaussian/MH/src/main.cpp:74): means, covariance (device CovarianceMatrix), acceptance fraction.
+    Bars are ~6 sigma of the Monte-Carlo error of 4096 walkers x 400 kept steps at IAT ~ 3."""
+    import mcmcpp_b200 as m
+    W, D, burn, keep = 4096, 2, 100, 400
+    eps = 0.13
+    truth = np.array([[4.0 * (1 + eps) / 4.0, (1 - eps) / 2.0], [(1 - eps) / 2.0, (1 + eps) / 4.0]])   # Sigma of -(t1^2/eps + t2^2)/2
+    rng = np.random.default_rng(12)
+    init = rng.standard_normal((W, D))
+    lp = port.logp("skewed_gauss_2d", np.array([eps]), init)
+    s = m.EnsembleSampler(5, W, D, m.StretchMove(D, 5, m.SkewedGaussianTwoDim(eps)), rngMode="per_walker", maxChainSizeBytes=0)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(burn)
+    s.reset()
+    s.covBegin(1, includeCurrent=False)
+    assert s.runMCMC(keep)
+    mean, cov, corr, n = s.covResult()
+    acc_dev = s.getAcceptanceFraction()
+    s.close()
+    o = port.run("skewed_gauss_2d", np.array([eps]), init, lp, burn + keep, seed=5)
+    om, oc, _, _ = port.covariance(o["chain"][burn:], 1)
+    o1 = port.run("skewed_gauss_2d", np.array([eps]), init, lp, burn, seed=5, want_chain=False)
+    acc_orc = (o["acc"].sum() - o1["acc"].sum()) / (o["tot"].sum() - o1["tot"].sum())      # kept steps only
+    n_eff = W * keep / 3.0
+    sd = np.sqrt(np.diag(truth))
+    assert np.all(np.abs(mean) < 6 * sd / np.sqrt(n_eff)) and np.all(np.abs(mean - om) < 9 * sd / np.sqrt(n_eff))
+    tol = 6 * np.sqrt((np.outer(sd, sd) ** 2 + truth ** 2) / n_eff)
+    assert np.all(np.abs(cov - truth) < tol) and np.all(np.abs(cov - oc) < 1.5 * tol)
+    assert abs(acc_dev - acc_orc) < 0.004 and 0.6 < acc_dev < 0.8
