@@ -112,14 +112,14 @@ __global__ void sumSlotsKernel(const unsigned long long* slots, int n, unsigned 
 {
     __shared__ unsigned long long partial[256];
     unsigned long long s = 0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) s += slots[i];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) s += slots[i];
     partial[threadIdx.x] = s;
     __syncthreads();
     for (int off = 128; off > 0; off >>= 1) {
         if (threadIdx.x < off) partial[threadIdx.x] += partial[threadIdx.x + off];
         __syncthreads();
     }
-    if (threadIdx.x == 0) *out = partial[0];
+    if (threadIdx.x == 0 && partial[0]) atomicAdd(out, partial[0]);     /* integer sum: order does not matter */
 }
 
 }  // namespace
@@ -603,7 +603,8 @@ int mcmcpp_sampler_get_counts(mcmcpp_sampler* s, unsigned long long* accepted, u
 {
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
-    sumSlotsKernel<<<1, 256, 0, s->stream>>>(s->dAcceptSlots, s->maxGrid, s->dAcceptSum);
+    CUDA_TRY(cudaMemsetAsync(s->dAcceptSum, 0, sizeof(unsigned long long), s->stream));
+    sumSlotsKernel<<<std::max(1, std::min(592, (s->maxGrid + 255) / 256)), 256, 0, s->stream>>>(s->dAcceptSlots, s->maxGrid, s->dAcceptSum);
     CUDA_TRY(cudaGetLastError());
     unsigned long long sum = 0;
     CUDA_TRY(cudaMemcpyAsync(&sum, s->dAcceptSum, sizeof sum, cudaMemcpyDeviceToHost, s->stream));
