@@ -439,3 +439,116 @@ long oracle_covariance(const double* chain, long S, int W, int D, int sliceInter
     free(prod); free(prodC); free(avg); free(avgC);
     return numPts * W;
 }
+
+/* ---- AutoCorrCalc / AutoCov (MCMCpp/Analysis/AutoCorrCalc.h:150-262, Analysis/Detail/AutoCov.h:131-290) -------------
+ * Integrated autocorrelation time of every parameter from the walker-averaged, normalised, CIRCULAR autocovariance
+ * (FFT length = next power of two >= numSamples, no zero padding: AutoCov.h:285-290).
+ *   chain averages: Kahan over the steps, per (walker, param)                          AutoCorrCalc.h:234-262
+ *   per walker: centre, bit-reverse, radix-2 FFT, |X|^2 (bit-reversed), radix-2 inverse FFT (no 1/N), divide by
+ *   element 0                                                                             AutoCov.h:131-229
+ *   average over walkers with the header's compensated sum (value = acov + comp)          AutoCorrCalc.h:206-219
+ *   IAT: -rho[0] + Kahan sum of 2 rho[i] until i > windowScaling * sum; negative final sum if it never converges :180-203
+ * quirk != 0 reproduces transferWalker's accumulation into the un-cleared buffer (AutoCorrCalc.h:228-232): the series
+ * handed to the FFT is chain + (what calcNormAutoCov left there for the previous walker / parameter); the buffer is taken
+ * as zero the first time (fresh `new[]` pages).  quirk == 0 is the clean definition (series = chain) the device computes.
+ * All W walkers are used (numWalkersToUse == 0).  rho (may be NULL): D * S averaged autocovariance functions.
+ */
+static unsigned oracle_bitrev(unsigned v, int lg)
+{
+    v = ((v >> 1) & 0x55555555u) | ((v & 0x55555555u) << 1);
+    v = ((v >> 2) & 0x33333333u) | ((v & 0x33333333u) << 2);
+    v = ((v >> 4) & 0x0F0F0F0Fu) | ((v & 0x0F0F0F0Fu) << 4);
+    v = ((v >> 8) & 0x00FF00FFu) | ((v & 0x00FF00FFu) << 8);
+    v = (v >> 16) | (v << 16);
+    return v >> (32 - lg);
+}
+
+static void oracle_fft_stages(double* re, double* im, const double* wr, const double* wi, int lg, int n)
+{
+    for (int s = 1; s <= lg; ++s) {
+        const int m1 = 1 << s, m2 = m1 >> 1, stride = n >> s;
+        for (int k = 0; k < n; k += m1) {
+            int tw = 0;
+            for (int j = 0; j < m2; ++j) {
+                const double xr = re[k + j + m2], xi = im[k + j + m2];
+                const double t1r = wr[tw] * xr - wi[tw] * xi;          /* std::complex operator*: (ac - bd, ad + bc) */
+                const double t1i = wr[tw] * xi + wi[tw] * xr;
+                const double t2r = re[k + j], t2i = im[k + j];
+                re[k + j] = t2r + t1r; im[k + j] = t2i + t1i;
+                re[k + j + m2] = t2r - t1r; im[k + j + m2] = t2i - t1i;
+                tw += stride;
+            }
+        }
+    }
+}
+
+int oracle_fft_size_log2(int numSamples) { return (int)ceil(log2((double)numSamples)); }
+
+/* twiddles exactly as AutoCov::calculateRootsOfUnity (AutoCov.h:270-281): cos/sin of TwoPi*i/N, TwoPi from the rational pi */
+void oracle_autocov_twiddles(int lg, double* cosPart, double* sinPart)
+{
+    const int n = 1 << lg;
+    const double twoPi = 2.0 * ((double)3141592653589793239ULL / (double)1000000000000000000ULL);
+    for (int i = 0; i < n / 2; ++i) {
+        const double angle = twoPi * (double)i / (double)n;
+        cosPart[i] = cos(angle);
+        sinPart[i] = sin(angle);
+    }
+}
+
+void oracle_autocorr(const double* chain, int S, int W, int D, int windowScaling, int quirk, double* iat, double* rho)
+{
+    const int lg = oracle_fft_size_log2(S), n = 1 << lg;
+    double* cs = (double*)malloc(sizeof(double) * (size_t)(n / 2 + 1));
+    double* sn = (double*)malloc(sizeof(double) * (size_t)(n / 2 + 1));
+    double* nsn = (double*)malloc(sizeof(double) * (size_t)(n / 2 + 1));
+    oracle_autocov_twiddles(lg, cs, sn);
+    for (int i = 0; i < n / 2; ++i) nsn[i] = -sn[i];
+    double* re1 = (double*)malloc(sizeof(double) * (size_t)n); double* im1 = (double*)malloc(sizeof(double) * (size_t)n);
+    double* re2 = (double*)malloc(sizeof(double) * (size_t)n); double* im2 = (double*)malloc(sizeof(double) * (size_t)n);
+    double* acov = (double*)calloc((size_t)S, sizeof(double));           /* acovFuncArray */
+    double* avgA = (double*)malloc(sizeof(double) * (size_t)S); double* avgC = (double*)malloc(sizeof(double) * (size_t)S);
+    double* mean = (double*)calloc((size_t)W * D, sizeof(double)); double* meanC = (double*)calloc((size_t)W * D, sizeof(double));
+    for (int t = 0; t < S; ++t)
+        for (int j = 0; j < W * D; ++j) {
+            const double value = chain[(size_t)t * W * D + j] - meanC[j];
+            const double temp = mean[j] + value;
+            meanC[j] = (temp - mean[j]) - value;
+            mean[j] = temp;
+        }
+    for (int j = 0; j < W * D; ++j) mean[j] /= (double)S;
+    for (int p = 0; p < D; ++p) {
+        for (int i = 0; i < S; ++i) { avgA[i] = 0.0; avgC[i] = 0.0; }
+        for (int w = 0; w < W; ++w) {
+            const int off = w * D + p;
+            for (int t = 0; t < S; ++t) acov[t] = chain[(size_t)t * W * D + off] + (quirk ? acov[t] : 0.0);   /* transferWalker */
+            for (int i = 0; i < S; ++i) { const unsigned r = oracle_bitrev((unsigned)i, lg); re1[r] = acov[i] - mean[off]; im1[r] = 0.0; }
+            for (int i = S; i < n; ++i) { const unsigned r = oracle_bitrev((unsigned)i, lg); re1[r] = 0.0; im1[r] = 0.0; }
+            oracle_fft_stages(re1, im1, cs, nsn, lg, n);
+            for (int i = 0; i < n; ++i) { const unsigned r = oracle_bitrev((unsigned)i, lg); re2[r] = re1[i] * re1[i] + im1[i] * im1[i]; im2[r] = 0.0; }
+            oracle_fft_stages(re2, im2, cs, sn, lg, n);
+            const double norm = re2[0];
+            for (int i = 0; i < S; ++i) acov[i] = re2[i] / norm;
+            for (int i = 0; i < S; ++i) {                                 /* averageAutocovarianceFunctions */
+                const double value = acov[i] + avgC[i];
+                const double temp = avgA[i] + value;
+                avgC[i] = (temp - avgA[i]) - value;
+                avgA[i] = temp;
+            }
+        }
+        for (int i = 0; i < S; ++i) avgA[i] /= (double)W;
+        if (rho) memcpy(rho + (size_t)p * S, avgA, sizeof(double) * (size_t)S);
+        double sum = -avgA[0], comp = 0.0;
+        const double factor = (double)windowScaling;
+        int converged = 0;
+        for (int i = 0; i < S; ++i) {
+            const double value = (2.0 * avgA[i]) - comp;
+            const double temp = sum + value;
+            comp = (temp - sum) - value;
+            sum = temp;
+            if ((double)i > factor * sum) { converged = 1; break; }
+        }
+        iat[p] = converged ? sum : -sum;
+    }
+    free(cs); free(sn); free(nsn); free(re1); free(im1); free(re2); free(im2); free(acov); free(avgA); free(avgC); free(mean); free(meanC);
+}

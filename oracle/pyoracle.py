@@ -68,6 +68,8 @@ class Port:
 
         L.oracle_covariance.restype = C.c_long
         L.oracle_covariance.argtypes = [c_dp, C.c_long, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp]
+        L.oracle_autocorr.restype = None
+        L.oracle_autocorr.argtypes = [c_dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp]
         L.oracle_stretch_run_per_walker.restype = C.c_int
         L.oracle_stretch_run_per_walker.argtypes = L.oracle_stretch_run.argtypes
         L.oracle_pcg64_seed_many.argtypes = [C.c_void_p, c_u64, C.c_int]
@@ -77,6 +79,16 @@ class Port:
                                                 C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int]
 
     # --- rng -----------------------------------------------------------
+    def autocorr(self, chain, window_scaling=4, quirk=True, want_rho=False):
+        """AutoCorrCalc::calcAutoCorrTimes over chain[S][W][D], all walkers -> iat[D] (and rho[D,S]).  quirk=True is the
+        reference as written (transferWalker accumulates into the un-cleared buffer); False the clean definition."""
+        chain = np.ascontiguousarray(chain, dtype=np.float64)
+        S, W, D = chain.shape
+        iat = np.empty(D)
+        rho = np.empty((D, S)) if want_rho else None
+        self.lib.oracle_autocorr(_dp(chain), S, W, D, int(window_scaling), int(bool(quirk)), _dp(iat), _dp(rho) if want_rho else None)
+        return (iat, rho) if want_rho else iat
+
     def covariance(self, chain, interval=1):
         """CovarianceMatrix::calculateCovar over chain[S][W][D] -> (mean[D], cov[D,D], corr[D,D], points)."""
         chain = np.ascontiguousarray(chain, dtype=np.float64)
@@ -184,6 +196,8 @@ class Ref:
         L.ref_draws.argtypes = [C.c_longlong, C.c_longlong, C.c_int, C.c_long, C.POINTER(C.c_int), c_dp, c_dp]
         L.ref_pcg64_raw.argtypes = [C.c_ulonglong, C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong), C.c_long]
         L.ref_pcg32_raw.argtypes = [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_uint), C.c_long]
+        L.ref_autocorr.restype = C.c_int
+        L.ref_autocorr.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, c_dp, c_dp]
         L.ref_covariance.restype = C.c_int
         L.ref_covariance.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, C.c_int, c_dp, c_dp, c_dp]
         self.block_size = L.ref_block_size()
@@ -207,6 +221,16 @@ class Ref:
         chain, cov, corr = np.empty((nsteps + 1, W, D)), np.empty((D, D)), np.empty((D, D))
         self.lib.ref_covariance(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, cov_interval, _dp(chain), _dp(cov), _dp(corr))
         return chain, cov, corr
+
+    def autocorr(self, kind, params, pos, logp, nsteps, seed=0):
+        """Sequential reference run, then the reference's AutoCorrCalc (all walkers) -> (chain, iat[D])."""
+        pos = np.array(pos, dtype=np.float64, order="C")
+        logp = np.array(logp, dtype=np.float64)
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        chain, iat = np.empty((nsteps + 1, W, D)), np.empty(D)
+        self.lib.ref_autocorr(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, _dp(chain), _dp(iat))
+        return chain, iat
 
     def init_normal(self, seed, n):
         out = np.empty(n)

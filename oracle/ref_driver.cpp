@@ -16,6 +16,7 @@
 #include "ParallelEnsembleSampler.h"      /* MCMCpp/ParallelEnsembleSampler.h */
 #include "Movers/StretchMove.h"           /* MCMCpp/Movers/StretchMove.h */
 #include "Analysis/CovarianceMatrix.h"    /* MCMCpp/Analysis/CovarianceMatrix.h */
+#include "Analysis/AutoCorrCalc.h"        /* MCMCpp/Analysis/AutoCorrCalc.h */
 #include "Common/SkewedGaussian.h"        /* test/sequential/SkewedGaussian/Common/SkewedGaussian.h */
 #include "mcmcpp_b200/targets.h"          /* HD functors for the synthetic configs (kinds 1-4) */
 
@@ -72,6 +73,29 @@ int runCovariance(const Calc& calc, int W, int D, int seed, double* initPos, dou
     size_t row = (size_t)W * D;
     int s = 0;
     for (; it != end && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
+    return sampler.getStoredSteps();
+}
+
+/* Same run, then the reference's own AutoCorrCalc over the stored chain, all walkers (Analysis/AutoCorrCalc.h:150-168). */
+template <class Calc>
+int runAutoCorr(const Calc& calc, int W, int D, int seed, double* initPos, double* initAux, int nsteps, double* chainOut, double* iatOut)
+{
+    typedef MCMC::Mover::StretchMove<double, Calc> Mover;
+    Mover mover(D, seed, calc);
+    unsigned long long blocks = (unsigned long long)(nsteps + 1) / MCMC::Chain::Detail::BlockSize + 2ULL;
+    unsigned long long maxBytes = blocks * sizeof(double) * D * MCMC::Chain::Detail::BlockSize * (unsigned long long)W;
+    MCMC::EnsembleSampler<double, Mover> sampler(seed, W, D, mover, maxBytes);
+    sampler.setInitialWalkerPos(initPos, initAux);
+    sampler.runMCMC(nsteps);
+    MCMC::Analysis::AutoCorrCalc<double> ac(D, W);
+    auto b = sampler.getStepIttBegin();
+    auto e = sampler.getStepIttEnd();
+    ac.calcAutoCorrTimes(b, e, sampler.getStoredSteps());
+    for (int i = 0; i < D; ++i) iatOut[i] = ac.retrieveAutoCorrelationTime(i);
+    auto it = sampler.getStepIttBegin();
+    size_t row = (size_t)W * D;
+    int s = 0;
+    for (; it != e && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
     return sampler.getStoredSteps();
 }
 
@@ -162,6 +186,14 @@ int ref_covariance(int kind, const double* p, int W, int D, int seed, double* in
 {
 #define CALL_COV(c) runCovariance(c, W, D, seed, initPos, initAux, nsteps, covInterval, chainOut, covOut, corrOut)
     DISPATCH(CALL_COV)
+    return 0;
+}
+
+/* reference AutoCorrCalc::calcAutoCorrTimes over the chain of a sequential run (chainOut: nsteps+1 rows) */
+int ref_autocorr(int kind, const double* p, int W, int D, int seed, double* initPos, double* initAux, int nsteps, double* chainOut, double* iatOut)
+{
+#define CALL_AC(c) runAutoCorr(c, W, D, seed, initPos, initAux, nsteps, chainOut, iatOut)
+    DISPATCH(CALL_AC)
     return 0;
 }
 

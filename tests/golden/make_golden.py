@@ -65,6 +65,22 @@ def main():
     os.makedirs(os.path.join(HERE, "analysis"), exist_ok=True)
     cov_case("analysis/cov_skewed_w32", "skewed_gauss_2d", [0.13], 32, 2, 300, 1)
     cov_case("analysis/cov_diag_d5_w64_slice3", "diag_gauss", iv5, 64, 5, 60, 3)
+    # Analysis/AutoCorrCalc.h (reference class, unmodified, all walkers).  NB the reference reads uninitialised memory for
+    # (parameter 0, first walker) -- AutoCorrCalc.h:316-318 allocates acovFuncArray with new[] and :228-232 adds the chain
+    # onto it -- so iat[0] depends on heap contents (NaN has been seen); parameters >= 1 are deterministic.
+    def ac_case(name, kind, params, W, D, nsteps, init_seed=53):
+        init = R.init_normal(init_seed, W * D).reshape(W, D)
+        params = np.asarray(params, dtype=np.float64)
+        lp = R.logp(kind, params, init)
+        for attempt in range(8):            # heap garbage can be NaN and then poisons every parameter: take a clean run
+            chain, iat = R.autocorr(kind, params, init, lp, nsteps)
+            if np.all(np.isfinite(iat[1:])):
+                break
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), chain=chain, iat=iat)
+        print(name, iat)
+
+    ac_case("analysis/ac_diag_d5_w64", "diag_gauss", iv5, 64, 5, 300)
+    ac_case("analysis/ac_diag_d3_w16", "diag_gauss", iv5[:3], 16, 3, 1023)
     for k, v in out.items():
         print(k, v)
 

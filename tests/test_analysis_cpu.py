@@ -31,3 +31,34 @@ def test_skewed_gaussian_covariance_near_analytic_truth(port):
     chain, cov, corr, interval = load("cov_skewed_w32")
     _, c, _, _ = port.covariance(chain[100:], 1)
     assert abs(c[0, 0] - 1.13) < 0.35 and abs(c[0, 1] - 0.435) < 0.2 and abs(c[1, 1] - 0.2825) < 0.12
+
+
+@pytest.mark.parametrize("name", ["ac_diag_d5_w64", "ac_diag_d3_w16"])
+def test_autocorr_restatement_bit_exact_against_reference_fixture(port, name):
+    """AutoCorrCalc + AutoCov restatement (oracle_autocorr, quirk mode) against the unmodified reference class.
+    Parameter 0 is excluded: the reference adds the first walker's chain onto an uninitialised new[] buffer
+    (AutoCorrCalc.h:228-232,316-318), so its iat[0] depends on heap contents (a NaN there poisons every later parameter; the generator retries until it
+    gets a finite run); parameters >= 1 are then deterministic and
+    must match bit for bit (FFT butterflies, twiddles, averaging, window rule)."""
+    z = np.load(os.path.join(GOLDEN, "analysis", name + ".npz"))
+    chain, iat = z["chain"], z["iat"]
+    q = port.autocorr(chain, 4, quirk=True)
+    assert np.array_equal(q[1:], iat[1:])
+    clean = port.autocorr(chain, 4, quirk=False)
+    assert np.all(clean > 1.0) and np.all(np.abs(clean / q - 1.0) < 0.25)      # the quirk perturbs, it does not dominate
+
+
+def test_autocorr_recovers_ar1_autocorrelation_time(port):
+    """AR(1) series x_t = phi x_{t-1} + noise has integrated autocorrelation time (1 + phi) / (1 - phi): the golden
+    values quoted in test/sequential/AcTime/src/main.cpp:16-22 (9 for phi = 0.8, 20 for 0.904761904762) come from that
+    formula; 64 walkers x 16383 steps recover it within a few percent (clean definition and the reference's)."""
+    rng = np.random.default_rng(0)
+    S, W, phis = 16383, 64, np.array([0.8, 0.904761904762])
+    x = np.zeros((S, W, 2))
+    x[0] = rng.standard_normal((W, 2))
+    noise = rng.standard_normal((S, W, 2)) * np.sqrt(1.0 - phis ** 2)
+    for t in range(1, S):
+        x[t] = phis * x[t - 1] + noise[t]
+    for quirk in (False, True):
+        iat = port.autocorr(x, 4, quirk=quirk)
+        assert np.all(np.abs(iat / np.array([9.0, 20.0]) - 1.0) < 0.06)
