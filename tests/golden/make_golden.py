@@ -80,7 +80,7 @@ def main():
         print(name, iat)
 
     ac_case("analysis/ac_diag_d5_w64", "diag_gauss", iv5, 64, 5, 300)
-    ac_case("analysis/ac_diag_d3_w16", "diag_gauss", iv5[:3], 16, 3, 1023)
+    ac_case("analysis/ac_diag_d3_w48", "diag_gauss", iv5[:3], 48, 3, 511)
     for k, v in out.items():
         print(k, v)
 

@@ -33,7 +33,7 @@ def test_skewed_gaussian_covariance_near_analytic_truth(port):
     assert abs(c[0, 0] - 1.13) < 0.35 and abs(c[0, 1] - 0.435) < 0.2 and abs(c[1, 1] - 0.2825) < 0.12
 
 
-@pytest.mark.parametrize("name", ["ac_diag_d5_w64", "ac_diag_d3_w16"])
+@pytest.mark.parametrize("name", ["ac_diag_d5_w64", "ac_diag_d3_w48"])
 def test_autocorr_restatement_bit_exact_against_reference_fixture(port, name):
     """AutoCorrCalc + AutoCov restatement (oracle_autocorr, quirk mode) against the unmodified reference class.
     Parameter 0 is excluded: the reference adds the first walker's chain onto an uninitialised new[] buffer
