@@ -236,6 +236,17 @@ int mcmcpp_sampler_cov_end(mcmcpp_sampler* s);
 int mcmcpp_covariance(const double* chain_host, long long steps, int num_walkers, int num_params, int slice_interval, int device,
                       double* mean, double* cov, double* corr, long long* points);
 
+/* ---- Analysis::AutoCorrCalc::calcAutoCorrTimes + retrieveAutoCorrelationTime (Analysis/AutoCorrCalc.h:77,89,150-203;
+ *      Detail/AutoCov.h:131-290) over a host chain [steps][num_walkers][num_params], all walkers: iat_out[num_params].
+ *      The reference's own arithmetic in its own order (radix-2 circular FFT autocovariance, its twiddles, its
+ *      compensated sums, window = window_scaling, default 4): bit-identical to the CPU restatement.
+ *      reference_buffer_reuse != 0 also reproduces transferWalker adding each chain onto the buffer the previous
+ *      walker's autocovariance was left in (AutoCorrCalc.h:228-232) -- the reference as written, one CTA, in order;
+ *      0 = the clean definition (series = chain), one CTA per parameter.  A negative value = the window never closed,
+ *      as in the reference (AutoCorrCalc.h:200-202). */
+int mcmcpp_autocorr_times(const double* chain_host, long long steps, int num_walkers, int num_params, int window_scaling,
+                          int reference_buffer_reuse, int device, double* iat_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,7 +5,7 @@ Host-side mirror of the reference's sampler interface over the C-ABI runtime
 library; the first sampler does, and fails loudly if it was not built."""
 from .sampler import (EnsembleSampler, ParallelEnsembleSampler, StretchMove, SkewedGaussianTwoDim, RosenbrockTwoDim,
                       DiagGaussian, DenseGaussian, LinearRegression)
-from .analysis import CovarianceMatrix
+from .analysis import CovarianceMatrix, AutoCorrCalc
 
 __all__ = ["EnsembleSampler", "ParallelEnsembleSampler", "StretchMove", "SkewedGaussianTwoDim", "RosenbrockTwoDim",
-           "DiagGaussian", "DenseGaussian", "LinearRegression", "CovarianceMatrix"]
+           "DiagGaussian", "DenseGaussian", "LinearRegression", "CovarianceMatrix", "AutoCorrCalc"]

@@ -65,6 +65,7 @@ SYMBOLS = {
     "mcmcpp_sampler_cov_end": (C.c_int, [_h]),
     "mcmcpp_covariance": (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.POINTER(C.c_longlong)]),
+    "mcmcpp_autocorr_times": (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "mcmcpp_dim_slice": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 

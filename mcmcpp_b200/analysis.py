@@ -38,3 +38,36 @@ class CovarianceMatrix:
 
     def getCorrelationMatrixElement(self, row, col):
         return float(self.corrMat[row, col])
+
+
+class AutoCorrCalc:
+    """MCMC::Analysis::AutoCorrCalc (MCMCpp/Analysis/AutoCorrCalc.h:77-89): integrated autocorrelation time of every
+    parameter.  `calcAutoCorrTimes(chain, numSamples, numWalkersToUse=0)` takes the rows the reference's iterator range
+    walks; only all-walker use is offered (the reference's subset is drawn from a random_device-seeded engine,
+    AutoCorrCalc.h:134, and is not reproducible).  `referenceBufferReuse=True` (default) computes what the reference
+    computes, including its accumulation of each chain onto the previous walker's autocovariance
+    (AutoCorrCalc.h:228-232); False gives the clean definition."""
+
+    def __init__(self, numParams, numWalkers, device=0, referenceBufferReuse=True):
+        if numParams <= 0 or numWalkers <= 0:          # the reference asserts (AutoCorrCalc.h:136-137)
+            raise _capi.McmcppError(_capi.ERR_ARG, "numParams and numWalkers must be positive")
+        self.paramCount, self.walkerCount, self.device = int(numParams), int(numWalkers), int(device)
+        self.windowScaling = 4
+        self.referenceBufferReuse = bool(referenceBufferReuse)
+        self.acorrTimeList = np.zeros(self.paramCount)
+
+    def setAutoCorrScaleFactor(self, scaleFactor=5):
+        self.windowScaling = int(scaleFactor)
+
+    def calcAutoCorrTimes(self, chain, numSamples=None, numWalkersToUse=0):
+        chain = np.ascontiguousarray(chain, dtype=np.float64)
+        if chain.ndim != 3 or chain.shape[1:] != (self.walkerCount, self.paramCount):
+            raise ValueError("chain must be [steps][%d][%d]" % (self.walkerCount, self.paramCount))
+        if numWalkersToUse not in (0, self.walkerCount):
+            raise _capi.McmcppError(_capi.ERR_UNSUPPORTED, "only all-walker autocorrelation times are offered")
+        n = chain.shape[0] if numSamples is None else int(numSamples)
+        check(_capi.lib().mcmcpp_autocorr_times(chain.ctypes.data, n, self.walkerCount, self.paramCount, self.windowScaling,
+                                                int(self.referenceBufferReuse), self.device, self.acorrTimeList.ctypes.data))
+
+    def retrieveAutoCorrelationTime(self, paramIndex):
+        return float(self.acorrTimeList[paramIndex])

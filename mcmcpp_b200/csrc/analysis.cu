@@ -215,3 +215,155 @@ int mcmcpp_cov_finalize(mcmcpp_cov_accum* c, long long nPoints, double* mean, do
     for (size_t k = 0; k < (size_t)D * D; ++k) { if (cov) cov[k] = cv[k]; if (corr) corr[k] = cr[k]; }
     return MCMCPP_OK;
 }
+
+/* =====================================================================================================================
+ * MCMC::Analysis::AutoCorrCalc / Detail::AutoCov (Analysis/AutoCorrCalc.h:150-262, Analysis/Detail/AutoCov.h:131-290)
+ * on the device: integrated autocorrelation time of every parameter from the walker-averaged, normalised, circular
+ * autocovariance (radix-2 FFT of length 2^ceil(log2 S), no zero padding, as the reference).
+ *
+ * Every arithmetic step is the reference's, in the reference's order, with its twiddles (host cos/sin of the rational
+ * 2 pi, uploaded): per-(walker, parameter) Kahan means over the steps; bit-reversed load; butterflies (independent
+ * inside a stage, so running them in parallel changes nothing); |X|^2; inverse butterflies; divide by element 0; the
+ * header's compensated walker average; the windowed Kahan sum.  One CTA per parameter walks the walkers in order, so
+ * the result is bit-identical to the CPU restatement the tests check it against.  quirk != 0 reproduces transferWalker's accumulation into the
+ * un-cleared buffer (AutoCorrCalc.h:228-232), which chains every walker and parameter to the previous one: one CTA
+ * does everything, in order.  Work buffers live in HBM/L2 (one CTA owns them; __syncthreads orders the stages).
+ * ===================================================================================================================== */
+namespace
+{
+enum { AcThreads = 1024 };
+
+__device__ __forceinline__ unsigned acBitrev(unsigned v, int lg) { return __brev(v) >> (32 - lg); }
+
+/* chain averages: thread per (walker, parameter), Kahan over the steps (AutoCorrCalc.h:234-262) */
+__global__ void acMeansKernel(const double* __restrict__ chain, int S, int WD, double* __restrict__ mean)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= WD) return;
+    double s = 0.0, c = 0.0;
+    for (int t = 0; t < S; ++t) kahanAdd(s, c, chain[(size_t)t * WD + j]);
+    mean[j] = __ddiv_rn(s, (double)S);
+}
+
+__device__ void acStages(double* re, double* im, const double* __restrict__ wr, const double* __restrict__ wi, double wiSign, int lg, int n)
+{
+    for (int s = 1; s <= lg; ++s) {
+        const int m2 = 1 << (s - 1), stride = n >> s;
+        for (int b = threadIdx.x; b < n / 2; b += AcThreads) {
+            const int j = b & (m2 - 1), k = (b >> (s - 1)) << s;
+            const double c = wr[j * stride], d = wiSign * wi[j * stride];
+            const double xr = re[k + j + m2], xi = im[k + j + m2];
+            const double t1r = __dsub_rn(__dmul_rn(c, xr), __dmul_rn(d, xi));
+            const double t1i = __dadd_rn(__dmul_rn(c, xi), __dmul_rn(d, xr));
+            const double t2r = re[k + j], t2i = im[k + j];
+            re[k + j] = __dadd_rn(t2r, t1r); im[k + j] = __dadd_rn(t2i, t1i);
+            re[k + j + m2] = __dsub_rn(t2r, t1r); im[k + j + m2] = __dsub_rn(t2i, t1i);
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(AcThreads) acKernel(const double* __restrict__ chain, int S, int W, int D, int lg,
+                                                      const double* __restrict__ twCos, const double* __restrict__ twSin,
+                                                      const double* __restrict__ mean, int quirk, int windowScaling,
+                                                      double* __restrict__ scratch, double* __restrict__ iat)
+{
+    const int n = 1 << lg;
+    double* base = scratch + (size_t)blockIdx.x * (4 * (size_t)n + 3 * (size_t)S);
+    double *re1 = base, *im1 = re1 + n, *re2 = im1 + n, *im2 = re2 + n, *acov = im2 + n, *avgA = acov + S, *avgC = avgA + S;
+    const int WD = W * D;
+    for (int i = threadIdx.x; i < S; i += AcThreads) acov[i] = 0.0;                   /* fresh buffer */
+    const int pBegin = quirk ? 0 : blockIdx.x, pEnd = quirk ? D : blockIdx.x + 1;
+    for (int p = pBegin; p < pEnd; ++p) {
+        for (int i = threadIdx.x; i < S; i += AcThreads) { avgA[i] = 0.0; avgC[i] = 0.0; }
+        __syncthreads();
+        for (int w = 0; w < W; ++w) {
+            const int off = w * D + p;
+            const double mu = mean[off];
+            /* transferWalker + copyCenterAndBitReverseChain */
+            for (int i = threadIdx.x; i < n; i += AcThreads) {
+                const unsigned r = acBitrev((unsigned)i, lg);
+                double v = 0.0;
+                if (i < S) {
+                    double x = chain[(size_t)i * WD + off];
+                    if (quirk) x = __dadd_rn(x, acov[i]);
+                    v = __dsub_rn(x, mu);
+                }
+                re1[r] = v; im1[r] = 0.0;
+            }
+            __syncthreads();
+            acStages(re1, im1, twCos, twSin, -1.0, lg, n);
+            for (int i = threadIdx.x; i < n; i += AcThreads) {
+                const unsigned r = acBitrev((unsigned)i, lg);
+                re2[r] = __dadd_rn(__dmul_rn(re1[i], re1[i]), __dmul_rn(im1[i], im1[i]));
+                im2[r] = 0.0;
+            }
+            __syncthreads();
+            acStages(re2, im2, twCos, twSin, 1.0, lg, n);
+            const double norm = re2[0];
+            __syncthreads();
+            for (int i = threadIdx.x; i < S; i += AcThreads) {
+                const double a = __ddiv_rn(re2[i], norm);
+                acov[i] = a;
+                const double value = __dadd_rn(a, avgC[i]);                              /* averageAutocovarianceFunctions */
+                const double temp = __dadd_rn(avgA[i], value);
+                avgC[i] = __dsub_rn(__dsub_rn(temp, avgA[i]), value);
+                avgA[i] = temp;
+            }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) {                                                         /* finalize + windowed sum */
+            const double wcount = (double)W, factor = (double)windowScaling;
+            double sum = -__ddiv_rn(avgA[0], wcount), comp = 0.0;
+            bool converged = false;
+            for (int i = 0; i < S; ++i) {
+                const double value = __dsub_rn(__dmul_rn(2.0, __ddiv_rn(avgA[i], wcount)), comp);
+                const double temp = __dadd_rn(sum, value);
+                comp = __dsub_rn(__dsub_rn(temp, sum), value);
+                sum = temp;
+                if ((double)i > __dmul_rn(factor, sum)) { converged = true; break; }
+            }
+            iat[p] = converged ? sum : -sum;
+        }
+        __syncthreads();
+    }
+}
+}  // namespace
+
+extern "C" int mcmcpp_autocorr_times(const double* chain_host, long long steps, int num_walkers, int num_params, int window_scaling,
+                                     int reference_buffer_reuse, int device, double* iat_out)
+{
+    if (!chain_host || !iat_out || steps < 2 || steps > (1LL << 24) || num_walkers <= 0 || num_params <= 0 || window_scaling <= 0) return MCMCPP_ERR_ARG;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || cudaSetDevice(device) != cudaSuccess) return MCMCPP_ERR_CUDA;
+    const int S = (int)steps, W = num_walkers, D = num_params;
+    const int lg = (int)std::ceil(std::log2((double)S)), n = 1 << lg;          /* AutoCov::findNextPowerOfTwo, AutoCov.h:285-290 */
+    /* AutoCov::calculateRootsOfUnity (AutoCov.h:270-281) on the host: the same libm values the reference uses */
+    std::vector<double> cs((size_t)n / 2 + 1), sn((size_t)n / 2 + 1);
+    const double twoPi = 2.0 * ((double)3141592653589793239ULL / (double)1000000000000000000ULL);
+    for (int i = 0; i < n / 2; ++i) {
+        const double angle = twoPi * (double)i / (double)n;
+        cs[(size_t)i] = std::cos(angle);
+        sn[(size_t)i] = std::sin(angle);
+    }
+    const int grid = reference_buffer_reuse ? 1 : D;
+    const size_t chainBytes = sizeof(double) * (size_t)S * W * D;
+    double *dChain = nullptr, *dCos = nullptr, *dSin = nullptr, *dMean = nullptr, *dScratch = nullptr, *dIat = nullptr;
+    int rc = MCMCPP_OK;
+    if (cudaMalloc(&dChain, chainBytes) != cudaSuccess || cudaMalloc(&dCos, sizeof(double) * cs.size()) != cudaSuccess ||
+        cudaMalloc(&dSin, sizeof(double) * sn.size()) != cudaSuccess || cudaMalloc(&dMean, sizeof(double) * (size_t)W * D) != cudaSuccess ||
+        cudaMalloc(&dScratch, sizeof(double) * (size_t)grid * (4 * (size_t)n + 3 * (size_t)S)) != cudaSuccess ||
+        cudaMalloc(&dIat, sizeof(double) * (size_t)D) != cudaSuccess)
+        rc = MCMCPP_ERR_CUDA;
+    if (rc == MCMCPP_OK) {
+        cudaMemcpy(dChain, chain_host, chainBytes, cudaMemcpyHostToDevice);
+        cudaMemcpy(dCos, cs.data(), sizeof(double) * cs.size(), cudaMemcpyHostToDevice);
+        cudaMemcpy(dSin, sn.data(), sizeof(double) * sn.size(), cudaMemcpyHostToDevice);
+        acMeansKernel<<<(W * D + 255) / 256, 256>>>(dChain, S, W * D, dMean);
+        acKernel<<<grid, AcThreads>>>(dChain, S, W, D, lg, dCos, dSin, dMean, reference_buffer_reuse ? 1 : 0, window_scaling, dScratch, dIat);
+        if (cudaMemcpy(iat_out, dIat, sizeof(double) * (size_t)D, cudaMemcpyDeviceToHost) != cudaSuccess || cudaGetLastError() != cudaSuccess)
+            rc = MCMCPP_ERR_CUDA;
+    }
+    cudaFree(dChain); cudaFree(dCos); cudaFree(dSin); cudaFree(dMean); cudaFree(dScratch); cudaFree(dIat);
+    return rc;
+}

@@ -127,3 +127,66 @@ def test_tier_c_long_run_statistics_match_oracle_and_analytic_truth(port):
     tol = 6 * np.sqrt((np.outer(sd, sd) ** 2 + truth ** 2) / n_eff)
     assert np.all(np.abs(cov - truth) < tol) and np.all(np.abs(cov - oc) < 1.5 * tol)
     assert abs(acc_dev - acc_orc) < 0.004 and 0.6 < acc_dev < 0.8
+
+
+@pytest.mark.parametrize("name", ["ac_diag_d5_w64", "ac_diag_d3_w48"])
+def test_device_autocorr_against_reference_fixture(port, name):
+    """Device AutoCorrCalc: the reference's arithmetic in the reference's order -> bit-identical to the restatement in
+    both modes, and (reference mode) to the unmodified reference class on the parameters it computes reproducibly
+    (>= 1; parameter 0 reads uninitialised memory there, tests/test_analysis_cpu.py)."""
+    import mcmcpp_b200 as m
+    z = np.load(os.path.join(GOLDEN, "analysis", name + ".npz"))
+    chain, iat = z["chain"], z["iat"]
+    S, W, D = chain.shape
+    ac = m.AutoCorrCalc(D, W)
+    ac.calcAutoCorrTimes(chain, S)
+    assert np.array_equal(ac.acorrTimeList[1:], iat[1:])
+    assert np.array_equal(ac.acorrTimeList, port.autocorr(chain, 4, quirk=True))
+    assert ac.retrieveAutoCorrelationTime(1) == iat[1]
+    clean = m.AutoCorrCalc(D, W, referenceBufferReuse=False)
+    clean.calcAutoCorrTimes(chain, S)
+    assert np.array_equal(clean.acorrTimeList, port.autocorr(chain, 4, quirk=False))
+
+
+@pytest.mark.parametrize("S,W,D,scale", [(100, 8, 2, 4), (4096, 16, 3, 4), (5000, 4, 1, 5), (16383, 32, 2, 4)])
+def test_device_autocorr_shapes_and_ar1_known_answer(port, S, W, D, scale):
+    """power-of-two and ragged lengths, other window scalings, against the oracle bit for bit; the AR(1) series'
+    autocorrelation time (1 + phi) / (1 - phi) is recovered on the long case (AcTime/src/main.cpp:16-22 goldens)."""
+    import mcmcpp_b200 as m
+    rng = np.random.default_rng(S + W)
+    phis = np.array([0.8, 0.904761904762, 0.5])[:D]
+    x = np.zeros((S, W, D))
+    x[0] = rng.standard_normal((W, D))
+    noise = rng.standard_normal((S, W, D)) * np.sqrt(1.0 - phis ** 2)
+    for t in range(1, S):
+        x[t] = phis * x[t - 1] + noise[t]
+    for reuse in (True, False):
+        ac = m.AutoCorrCalc(D, W, referenceBufferReuse=reuse)
+        ac.setAutoCorrScaleFactor(scale)
+        ac.calcAutoCorrTimes(x, S)
+        assert np.array_equal(ac.acorrTimeList, port.autocorr(x, scale, quirk=reuse))
+    if S >= 16383:
+        assert np.all(np.abs(ac.acorrTimeList / ((1 + phis) / (1 - phis)) - 1.0) < 0.08)
+
+
+def test_tier_c_autocorrelation_time_of_gpu_chain_matches_oracle_chain(port):
+    """SURVEY s.8(c) tier C, IAT: a per-walker-stream GPU run and the sequential oracle run of the same target give
+    statistically indistinguishable integrated autocorrelation times (clean definition, device AutoCorrCalc)."""
+    import mcmcpp_b200 as m
+    W, D, burn, keep = 256, 2, 200, 4095
+    eps = 0.13
+    rng = np.random.default_rng(2)
+    init = rng.standard_normal((W, D))
+    lp = port.logp("skewed_gauss_2d", np.array([eps]), init)
+    s = m.EnsembleSampler(8, W, D, m.StretchMove(D, 8, m.SkewedGaussianTwoDim(eps)), rngMode="per_walker")
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(burn + keep)
+    dev_chain = s.getChain()[burn + 1:].copy()
+    s.close()
+    o = port.run("skewed_gauss_2d", np.array([eps]), init, lp, burn + keep, seed=8)
+    ac = m.AutoCorrCalc(D, W, referenceBufferReuse=False)
+    ac.calcAutoCorrTimes(dev_chain, keep)
+    dev_iat = ac.acorrTimeList.copy()
+    ac.calcAutoCorrTimes(np.ascontiguousarray(o["chain"][burn:]), keep)
+    orc_iat = ac.acorrTimeList.copy()
+    assert np.all(dev_iat > 1.0) and np.all(np.abs(dev_iat / orc_iat - 1.0) < 0.15)
