@@ -221,6 +221,13 @@ int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_rank
  * out so that every slice but possibly the last has even length: 16-byte aligned slices for vector loads). */
 int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count);
 
+/* ---- checkpoint / resume (no counterpart: the reference's IO tree is empty).  The buffer holds this rank's walker
+ *      positions, log-probs, every walker's pcg64 state, the step index and the counters; a sampler created with the
+ *      same configuration and restored from it continues bit for bit.  The host chain is not part of it. */
+int mcmcpp_sampler_checkpoint_bytes(mcmcpp_sampler* s, size_t* bytes);
+int mcmcpp_sampler_checkpoint_save(mcmcpp_sampler* s, void* buffer, size_t bytes);
+int mcmcpp_sampler_checkpoint_restore(mcmcpp_sampler* s, const void* buffer, size_t bytes);
+
 /* ---- Analysis::CovarianceMatrix (Analysis/CovarianceMatrix.h:120-215) on the device ------------------------
  *      Same definitions as the reference (n = used steps x walkers, cov = E[xy] - E[x]E[y], Kahan-summed,
  *      correlation normalised by rows then columns); the points are summed in a different order (per-CTA Kahan

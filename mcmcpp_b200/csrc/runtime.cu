@@ -860,6 +860,81 @@ int mcmcpp_covariance(const double* chain_host, long long steps, int num_walkers
     return rc == MCMCPP_OK ? rc : fail(rc, "covariance computation failed");
 }
 
+/* ---- checkpoint / resume (the reference has none) -------------------------------------
+ * Everything the next step depends on: positions (this rank's slice), log-probs, every walker's pcg64 state, the
+ * step index and the counters.  The host chain is the caller's to keep; a restored sampler starts with an empty one. */
+namespace
+{
+struct CheckpointHeader
+{
+    uint64_t magic;                 /* "MCMCPB2\0" */
+    int32_t W, D, Dl, dimBegin, rngMode, shardMode, rank, world;
+    int64_t seed, ensembleSteps;
+    uint64_t accepted, total;
+};
+const uint64_t CheckpointMagic = 0x00324250434d434dULL;
+
+size_t checkpointBytes(const mcmcpp_sampler* s)
+{
+    return sizeof(CheckpointHeader) + sizeof(double) * devRowDoubles(s) + sizeof(double) * (size_t)s->W + sizeof(uint64_t) * 2 * (size_t)s->W;
+}
+}
+
+int mcmcpp_sampler_checkpoint_bytes(mcmcpp_sampler* s, size_t* bytes)
+{
+    if (!s || !bytes) return fail(MCMCPP_ERR_ARG, "null argument");
+    *bytes = checkpointBytes(s);
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_checkpoint_save(mcmcpp_sampler* s, void* buffer, size_t bytes)
+{
+    if (!s || !buffer) return fail(MCMCPP_ERR_ARG, "null argument");
+    if (!s->initialised) return fail(MCMCPP_ERR_STATE, "no walker positions yet");
+    if (bytes < checkpointBytes(s)) return fail(MCMCPP_ERR_ARG, "checkpoint buffer too small");
+    CheckpointHeader h;
+    std::memset(&h, 0, sizeof h);
+    h.magic = CheckpointMagic;
+    h.W = s->W; h.D = s->D; h.Dl = s->Dl; h.dimBegin = s->dimBegin; h.rngMode = s->cfg.rng_mode; h.shardMode = s->cfg.shard_mode;
+    h.rank = s->cfg.rank; h.world = s->cfg.world; h.seed = s->cfg.seed; h.ensembleSteps = s->ensembleSteps;
+    unsigned long long acc = 0, tot = 0;
+    int rc = mcmcpp_sampler_get_counts(s, &acc, &tot);
+    if (rc != MCMCPP_OK) return rc;
+    h.accepted = acc; h.total = tot;
+    char* out = static_cast<char*>(buffer);
+    std::memcpy(out, &h, sizeof h); out += sizeof h;
+    CUDA_TRY(cudaMemcpyAsync(out, s->dPos, sizeof(double) * devRowDoubles(s), cudaMemcpyDeviceToHost, s->stream)); out += sizeof(double) * devRowDoubles(s);
+    CUDA_TRY(cudaMemcpyAsync(out, s->dLogp, sizeof(double) * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream)); out += sizeof(double) * (size_t)s->W;
+    CUDA_TRY(cudaMemcpyAsync(out, s->dRng, sizeof(uint64_t) * 2 * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_checkpoint_restore(mcmcpp_sampler* s, const void* buffer, size_t bytes)
+{
+    if (!s || !buffer) return fail(MCMCPP_ERR_ARG, "null argument");
+    if (bytes < checkpointBytes(s)) return fail(MCMCPP_ERR_ARG, "checkpoint buffer too small for this sampler");
+    CheckpointHeader h;
+    std::memcpy(&h, buffer, sizeof h);
+    if (h.magic != CheckpointMagic) return fail(MCMCPP_ERR_ARG, "not a mcmcpp_b200 checkpoint");
+    if (h.W != s->W || h.D != s->D || h.Dl != s->Dl || h.dimBegin != s->dimBegin || h.rngMode != s->cfg.rng_mode || h.seed != s->cfg.seed)
+        return fail(MCMCPP_ERR_ARG, "checkpoint was taken from a different sampler configuration (walkers, parameters, slice, rng mode or seed)");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    const char* in = static_cast<const char*>(buffer) + sizeof h;
+    CUDA_TRY(cudaMemcpyAsync(s->dPos, in, sizeof(double) * devRowDoubles(s), cudaMemcpyHostToDevice, s->stream)); in += sizeof(double) * devRowDoubles(s);
+    CUDA_TRY(cudaMemcpyAsync(s->dLogp, in, sizeof(double) * (size_t)s->W, cudaMemcpyHostToDevice, s->stream)); in += sizeof(double) * (size_t)s->W;
+    CUDA_TRY(cudaMemcpyAsync(s->dRng, in, sizeof(uint64_t) * 2 * (size_t)s->W, cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemsetAsync(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid, s->stream));
+    CUDA_TRY(cudaMemsetAsync(s->dFlags, 0, sizeof(int32_t) * 4, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->acceptedBase = h.accepted;
+    s->totalSteps = h.total;
+    s->ensembleSteps = h.ensembleSteps;
+    s->stored = 0;
+    s->initialised = true;
+    return MCMCPP_OK;
+}
+
 int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count)
 {
     if (!begin || !count || world < 1 || rank < 0 || rank >= world || num_params / 2 < world) return fail(MCMCPP_ERR_ARG, "bad slice request");

@@ -238,6 +238,23 @@ class EnsembleSampler:
     def covEnd(self):
         check(self._lib.mcmcpp_sampler_cov_end(self._h))
 
+    # -- checkpoint / resume and a minimal chain writer ------------------------------
+    def saveCheckpoint(self):
+        """bytes holding positions, log-probs, RNG states, step index and counters of this rank."""
+        n = C.c_size_t()
+        check(self._lib.mcmcpp_sampler_checkpoint_bytes(self._h, C.byref(n)))
+        buf = np.empty(n.value, dtype=np.uint8)
+        check(self._lib.mcmcpp_sampler_checkpoint_save(self._h, buf.ctypes.data, n.value))
+        return buf.tobytes()
+
+    def loadCheckpoint(self, blob):
+        buf = np.frombuffer(blob, dtype=np.uint8)
+        check(self._lib.mcmcpp_sampler_checkpoint_restore(self._h, buf.ctypes.data, buf.size))
+
+    def writeChain(self, path):
+        """Stored rows [stored][W][D] as a .npy file (float64, C order)."""
+        np.save(path, self.getChain())
+
     # -- diagnostics -----------------------------------------------------------------------------
     def getTrace(self, maxRows):
         buf = (_capi.Trace * int(maxRows))()

@@ -113,3 +113,39 @@ def test_c4_shape_properties_at_65536_walkers(port):
     assert np.array_equal(aux, port.logp("diag_gauss", iv, pos))
     assert s.getAcceptedSteps() == W + int(tr["accept"].sum()) and s.getTotalSteps() == 2 * W
     s.close()
+
+
+@pytest.mark.parametrize("kind,W,D,rng", [("skewed_gauss_2d", 512, 2, "sequential"), ("diag_gauss", 256, 100, "per_walker"),
+                                          ("diag_gauss", 512, 200, "sequential")])
+def test_checkpoint_resume_continues_bit_for_bit(port, tmp_path, kind, W, D, rng):
+    """save after 7 steps, restore into a fresh sampler, run 9 more: identical to an uninterrupted 16-step run
+    (positions, log-probs, counters) in both RNG disciplines and for the thread / warp / TMA kernels."""
+    import mcmcpp_b200 as m
+    params = np.array([0.13]) if kind == "skewed_gauss_2d" else 1.0 / (1.0 + (np.arange(D) % 10))
+    calc = (lambda: m.SkewedGaussianTwoDim(0.13)) if kind == "skewed_gauss_2d" else (lambda: m.DiagGaussian(params))
+    init = np.random.default_rng(D).standard_normal((W, D))
+    lp = port.logp(kind, params, init)
+    a = m.EnsembleSampler(11, W, D, m.StretchMove(D, 11, calc()), rngMode=rng)
+    a.setInitialWalkerPos(init, lp)
+    assert a.runMCMC(16)
+    b = m.EnsembleSampler(11, W, D, m.StretchMove(D, 11, calc()), rngMode=rng)
+    b.setInitialWalkerPos(init, lp)
+    assert b.runMCMC(7)
+    blob = b.saveCheckpoint()
+    b.writeChain(str(tmp_path / "chain.npy"))
+    assert np.array_equal(np.load(str(tmp_path / "chain.npy")), b.getChain())
+    b.close()
+    c = m.EnsembleSampler(11, W, D, m.StretchMove(D, 11, calc()), rngMode=rng)
+    c.loadCheckpoint(blob)
+    assert c.runMCMC(9)
+    pa, la = a.getWalkerState()
+    pc, lc = c.getWalkerState()
+    assert np.array_equal(pa, pc) and np.array_equal(la, lc)
+    assert (a.getAcceptedSteps(), a.getTotalSteps()) == (c.getAcceptedSteps(), c.getTotalSteps())
+    assert np.array_equal(a.getChain()[8:], c.getChain())          # rows of steps 8..16
+    d = m.EnsembleSampler(12, W, D, m.StretchMove(D, 12, calc()), rngMode=rng)
+    from mcmcpp_b200._capi import McmcppError
+    with pytest.raises(McmcppError):
+        d.loadCheckpoint(blob)                                        # other seed -> refused
+    for s in (a, c, d):
+        s.close()
