@@ -221,6 +221,14 @@ int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_rank
  * out so that every slice but possibly the last has even length: 16-byte aligned slices for vector loads). */
 int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count);
 
+/* ---- PostStepAction (EnsembleSampler.h:52-56,356-359; Utility/NoAction.h:34-46) with a DEVICE-resident view of the
+ *      step: after the black half-step of every stored step the runtime calls fn(ctx, dev_row, step_index, stream) on
+ *      the host, where dev_row is this rank's [W][D_local] state = the row just stored and `stream` the cudaStream_t
+ *      the update kernels run on.  Work the action enqueues on `stream` sees exactly that step and delays the next one;
+ *      the pointer must not be used after work enqueued later on the stream.  NULL removes the action. */
+typedef void (*mcmcpp_step_fn)(void* ctx, const double* dev_row, long long step_index, void* cuda_stream);
+int mcmcpp_sampler_set_step_action(mcmcpp_sampler* s, mcmcpp_step_fn fn, void* ctx);
+
 /* ---- checkpoint / resume (no counterpart: the reference's IO tree is empty).  The buffer holds this rank's walker
  *      positions, log-probs, every walker's pcg64 state, the step index and the counters; a sampler created with the
  *      same configuration and restored from it continues bit for bit.  The host chain is not part of it. */

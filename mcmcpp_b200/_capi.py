@@ -65,12 +65,15 @@ SYMBOLS = {
     "mcmcpp_sampler_cov_end": (C.c_int, [_h]),
     "mcmcpp_covariance": (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.POINTER(C.c_longlong)]),
+    "mcmcpp_sampler_set_step_action": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
     "mcmcpp_sampler_checkpoint_bytes": (C.c_int, [_h, C.POINTER(C.c_size_t)]),
     "mcmcpp_sampler_checkpoint_save": (C.c_int, [_h, C.c_void_p, C.c_size_t]),
     "mcmcpp_sampler_checkpoint_restore": (C.c_int, [_h, C.c_void_p, C.c_size_t]),
     "mcmcpp_autocorr_times": (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "mcmcpp_dim_slice": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
+
+STEP_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p)
 
 _lib = None
 

@@ -169,6 +169,9 @@ struct mcmcpp_sampler
     int32_t* dBarrier = nullptr;
     std::vector<void*> peerOpened;
     const double** dPeerPos = nullptr;
+    /* PostStepAction with a device-resident step view (EnsembleSampler.h:356-359) */
+    mcmcpp_step_fn stepFn = nullptr;
+    void* stepCtx = nullptr;
     /* on-the-fly CovarianceMatrix over the stored steps (analysis.cu) */
     mcmcpp_cov_accum* cov = nullptr;
     int covInterval = 1;
@@ -577,6 +580,7 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
         if ((rc = halfStep(s, 0, row)) != MCMCPP_OK) return rc;
         if ((rc = halfStep(s, 1, row)) != MCMCPP_OK) return rc;
         ++s->ensembleSteps;
+        if (s->stepFn) s->stepFn(s->stepCtx, s->dPos, s->stored, (void*)s->stream);   /* stream-ordered view of the step just made */
         if (s->cov) {                                   /* the stored row IS the state after the black half-step */
             if ((s->covIndex % s->covInterval) == 0) {
                 if ((rc = mcmcpp_cov_accumulate(s->cov, s->dPos, s->W, s->stream)) != MCMCPP_OK) return fail(rc, "covariance accumulation failed");
@@ -858,6 +862,14 @@ int mcmcpp_covariance(const double* chain_host, long long steps, int num_walkers
     cudaFree(dRows);
     mcmcpp_cov_destroy(c);
     return rc == MCMCPP_OK ? rc : fail(rc, "covariance computation failed");
+}
+
+int mcmcpp_sampler_set_step_action(mcmcpp_sampler* s, mcmcpp_step_fn fn, void* ctx)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    s->stepFn = fn;
+    s->stepCtx = ctx;
+    return MCMCPP_OK;
 }
 
 /* ---- checkpoint / resume (the reference has none) -------------------------------------

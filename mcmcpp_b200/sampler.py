@@ -238,6 +238,17 @@ class EnsembleSampler:
     def covEnd(self):
         check(self._lib.mcmcpp_sampler_cov_end(self._h))
 
+    # -- PostStepAction with a device-resident step view (EnsembleSampler.h:356-359) --------------------------
+    def setDeviceStepAction(self, fn):
+        """fn(devRowPtr, stepIndex, cudaStreamPtr) is called on the host after every stored step, stream-ordered with
+        the update kernels (enqueue work on the stream to look at the step in HBM); None removes it."""
+        if fn is None:
+            self._stepThunk = None
+            check(self._lib.mcmcpp_sampler_set_step_action(self._h, None, None))
+            return
+        self._stepThunk = _capi.STEP_FN(lambda ctx, row, step, stream: fn(row, step, stream))
+        check(self._lib.mcmcpp_sampler_set_step_action(self._h, C.cast(self._stepThunk, C.c_void_p), None))
+
     # -- checkpoint / resume and a minimal chain writer (SURVEY.md s.8(f) rank 4) ------------------------------
     def saveCheckpoint(self):
         """bytes holding positions, log-probs, RNG states, step index and counters of this rank."""

@@ -149,3 +149,35 @@ def test_checkpoint_resume_continues_bit_for_bit(port, tmp_path, kind, W, D, rng
         d.loadCheckpoint(blob)                                        # other seed -> refused
     for s in (a, c, d):
         s.close()
+
+
+def test_device_step_action_sees_every_stored_step(port):
+    """PostStepAction (EnsembleSampler.h:356-359) with a device view: called once per stored step, in order, with the
+    state pointer and the sampler's stream; a copy enqueued on that stream from inside the action captures exactly the
+    row the chain stores for that step."""
+    import torch
+    import mcmcpp_b200 as m
+    W, D, steps = 256, 2, 6
+    init = np.random.default_rng(3).standard_normal((W, D))
+    lp = port.logp("skewed_gauss_2d", np.array([0.13]), init)
+    s = m.EnsembleSampler(2, W, D, m.StretchMove(D, 2, m.SkewedGaussianTwoDim(0.13)))
+    s.setSlicingMode(True, 2)                       # 2 ensemble steps per stored step: the action fires on stored ones only
+    s.setInitialWalkerPos(init, lp)
+    seen, snaps = [], torch.zeros((steps, W, D), dtype=torch.float64, device="cuda")
+    import ctypes
+    cudart = ctypes.CDLL("libcudart.so.12")          # the runtime torch already loaded
+    cudart.cudaMemcpyAsync.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_void_p]
+
+    def action(row, step, stream):
+        seen.append(step)
+        dst = snaps[len(seen) - 1].data_ptr()
+        assert cudart.cudaMemcpyAsync(dst, row, W * D * 8, 3, stream) == 0        # 3 = cudaMemcpyDeviceToDevice
+
+    s.setDeviceStepAction(action)
+    assert s.runMCMC(steps)
+    torch.cuda.synchronize()
+    assert seen == list(range(1, steps + 1))
+    assert np.array_equal(snaps.cpu().numpy(), s.getChain()[1:])
+    s.setDeviceStepAction(None)
+    assert s.runMCMC(2) and len(seen) == steps
+    s.close()
