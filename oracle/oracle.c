@@ -552,3 +552,47 @@ void oracle_autocorr(const double* chain, int S, int W, int D, int windowScaling
     }
     free(cs); free(sn); free(nsn); free(re1); free(im1); free(re2); free(im2); free(acov); free(avgA); free(avgC); free(mean); free(meanC);
 }
+
+/*
+ * DifferentialEvolution::updateWalker (MCMCpp/Movers/DifferentialEvolution.h:113-142) inside the same red/black driver
+ * (EnsembleSampler.h:341-360).  Per update: ind1 = bounded(K); ind2 = bounded(K) repeated until != ind1;
+ * proposal_i = cur_i + gamma (w1_i - w2_i) + (lowEdge + u_i * width), one uniform per parameter
+ * (MultiSampler.h:74); accept iff (newp - logp) > log(1 - u).  gamma = 2.38 / sqrt(2 D) unless overridden (:58,:83);
+ * lowEdge = -1e-4, width = 2e-4 (:150-151).  per_walker == 0: ONE stream rng[0] consumed in walker order (the sequential
+ * reference sampler); != 0: walker w owns rng[w].  trace.j = ind1, trace.z = (double)ind2, trace.diff = newp - logp.
+ */
+void oracle_de_run(pcg64_t* rng, int per_walker, int kind, const double* tparams, int W, int D, double gamma, double lowEdge, double width,
+                   double* pos, double* logp, int64_t* acc, int64_t* tot, int nsteps, int interval, double* chain, oracle_trace_t* trace)
+{
+    const int K = W / 2;
+    double* prop = (double*)malloc(sizeof(double) * (size_t)D);
+    size_t tr = 0;
+    for (int s = 0; s < nsteps; ++s)
+        for (int sub = 0; sub < interval; ++sub) {
+            const int store = (sub == interval - 1);
+            for (int h = 0; h < 2; ++h) {
+                const int own0 = h * K, oth0 = (1 - h) * K;
+                for (int i = 0; i < K; ++i) {
+                    const int w = own0 + i;
+                    pcg64_t* g = per_walker ? &rng[w] : &rng[0];
+                    const int ind1 = (int)oracle_pcg64_bounded(g, (uint64_t)K, NULL);
+                    int ind2;
+                    do { ind2 = (int)oracle_pcg64_bounded(g, (uint64_t)K, NULL); } while (ind2 == ind1);
+                    double* cur = pos + (size_t)w * D;
+                    const double* w1 = pos + (size_t)(oth0 + ind1) * D;
+                    const double* w2 = pos + (size_t)(oth0 + ind2) * D;
+                    for (int d = 0; d < D; ++d)
+                        prop[d] = cur[d] + gamma * (w1[d] - w2[d]) + (lowEdge + (oracle_u64_to_unit(oracle_pcg64_next(g)) * width));
+                    const double newp = oracle_logp(kind, D, tparams, prop);
+                    const double diff = newp - logp[w];
+                    const double e = oracle_neg_exponential(oracle_u64_to_unit(oracle_pcg64_next(g)));
+                    const int a = diff > e;
+                    if (a) { memcpy(cur, prop, sizeof(double) * (size_t)D); logp[w] = newp; ++acc[w]; }
+                    ++tot[w];
+                    if (trace) { oracle_trace_t* t = &trace[tr++]; t->j = ind1; t->accept = a; t->z = (double)ind2; t->e = e; t->newp = newp; t->diff = diff; }
+                    if (store && chain) memcpy(chain + ((size_t)s * W + w) * D, cur, sizeof(double) * (size_t)D);
+                }
+            }
+        }
+    free(prop);
+}

@@ -68,6 +68,9 @@ class Port:
 
         L.oracle_covariance.restype = C.c_long
         L.oracle_covariance.argtypes = [c_dp, C.c_long, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp]
+        L.oracle_de_run.restype = None
+        L.oracle_de_run.argtypes = [C.c_void_p, C.c_int, C.c_int, c_dp, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                                    c_dp, c_dp, C.c_void_p, C.c_void_p, C.c_int, C.c_int, c_dp, C.c_void_p]
         L.oracle_autocorr.restype = None
         L.oracle_autocorr.argtypes = [c_dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp]
         L.oracle_stretch_run_per_walker.restype = C.c_int
@@ -165,6 +168,28 @@ class Port:
         return dict(pos=pos, logp=logp, acc=acc, tot=tot, chain=chain, trace=trace, rejections=rej, rng=g)
 
 
+    def run_de(self, kind, params, pos, logp, nsteps, interval=1, seed=0, per_walker=False, gamma=None, rand=1.0e-4,
+               want_chain=True, want_trace=False):
+        """DifferentialEvolution mover in the red/black driver; one stream (seed, 0) in walker order, or one stream per
+        walker.  Returns dict(pos, logp, acc, tot, chain[nsteps,W,D], trace)."""
+        pos = np.array(pos, dtype=np.float64, order="C")
+        logp = np.array(logp, dtype=np.float64)
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        if per_walker:
+            g = (Pcg64 * W)()
+            self.lib.oracle_pcg64_seed_many(g, seed & (2**64 - 1), W)
+        else:
+            g = self.pcg64(seed, 0)
+        gamma = 2.38 / np.sqrt(2 * D) if gamma is None else gamma        # DifferentialEvolution.h:58 (integer 2*paramCount)
+        acc, tot = np.ones(W, np.int64), np.ones(W, np.int64)
+        chain = np.empty((nsteps, W, D)) if want_chain else None
+        trace = np.zeros(nsteps * interval * W, dtype=TRACE_DTYPE) if want_trace else None
+        self.lib.oracle_de_run(C.byref(g), int(per_walker), KIND[kind], _dp(params), W, D, float(gamma), -float(rand), 2.0 * float(rand),
+                               _dp(pos), _dp(logp), acc.ctypes.data, tot.ctypes.data, nsteps, interval, _dp(chain),
+                               trace.ctypes.data if want_trace else None)
+        return dict(pos=pos, logp=logp, acc=acc, tot=tot, chain=chain, trace=trace)
+
     def half_slots(self, kind, params, pos, logp, acc, step, half, slot_begin, slot_count, seed=0, alpha=(2, 1)):
         """In-place update of one colour's slots [slot_begin, +slot_count) with jump-ahead draws (one rank's work)."""
         W, D = pos.shape
@@ -196,6 +221,9 @@ class Ref:
         L.ref_draws.argtypes = [C.c_longlong, C.c_longlong, C.c_int, C.c_long, C.POINTER(C.c_int), c_dp, c_dp]
         L.ref_pcg64_raw.argtypes = [C.c_ulonglong, C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong), C.c_long]
         L.ref_pcg32_raw.argtypes = [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_uint), C.c_long]
+        L.ref_de_run.restype = C.c_int
+        L.ref_de_run.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, c_dp,
+                                 C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
         L.ref_autocorr.restype = C.c_int
         L.ref_autocorr.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, c_dp, c_dp]
         L.ref_covariance.restype = C.c_int
@@ -264,6 +292,17 @@ class Ref:
         stored = self.lib.ref_stretch_run(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, interval,
                                           _dp(chain), C.byref(acc), C.byref(tot))
         return dict(chain=chain if want_chain else None, pos=chain[-1].copy(), acc=acc.value, tot=tot.value, stored=stored)
+
+    def run_de(self, kind, params, pos, logp, nsteps, seed=0):
+        """Sequential reference EnsembleSampler with the DifferentialEvolution mover -> dict(chain[(nsteps+1),W,D], acc, tot)."""
+        pos = np.array(pos, dtype=np.float64, order="C")
+        logp = np.array(logp, dtype=np.float64)
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        chain = np.empty((nsteps + 1, W, D))
+        acc, tot = C.c_ulonglong(), C.c_ulonglong()
+        self.lib.ref_de_run(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, _dp(chain), C.byref(acc), C.byref(tot))
+        return dict(chain=chain, acc=acc.value, tot=tot.value)
 
     def time(self, kind, params, pos, logp, nsteps, threads=0, seed=0):
         """Seconds spent inside runMCMC for nsteps ensemble steps (threads=0: sequential sampler)."""

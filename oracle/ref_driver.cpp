@@ -15,6 +15,7 @@
 #include "EnsembleSampler.h"              /* MCMCpp/EnsembleSampler.h */
 #include "ParallelEnsembleSampler.h"      /* MCMCpp/ParallelEnsembleSampler.h */
 #include "Movers/StretchMove.h"           /* MCMCpp/Movers/StretchMove.h */
+#include "Movers/DifferentialEvolution.h" /* MCMCpp/Movers/DifferentialEvolution.h */
 #include "Analysis/CovarianceMatrix.h"    /* MCMCpp/Analysis/CovarianceMatrix.h */
 #include "Analysis/AutoCorrCalc.h"        /* MCMCpp/Analysis/AutoCorrCalc.h */
 #include "Common/SkewedGaussian.h"        /* test/sequential/SkewedGaussian/Common/SkewedGaussian.h */
@@ -47,6 +48,28 @@ int runSequential(const Calc& calc, int W, int D, int seed, double* initPos, dou
         for (; it != end && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
     }
     return ok ? sampler.getStoredSteps() : -sampler.getStoredSteps();
+}
+
+/* Sequential reference sampler with the DifferentialEvolution mover (Movers/DifferentialEvolution.h:113-142). */
+template <class Calc>
+int runDiffEvo(const Calc& calc, int W, int D, int seed, double* initPos, double* initAux, int nsteps, double* chainOut,
+               unsigned long long* acc, unsigned long long* tot)
+{
+    typedef MCMC::Mover::DifferentialEvolution<double, Calc> Mover;
+    Mover mover(D, seed, calc);
+    unsigned long long blocks = (unsigned long long)(nsteps + 1) / MCMC::Chain::Detail::BlockSize + 2ULL;
+    unsigned long long maxBytes = blocks * sizeof(double) * D * MCMC::Chain::Detail::BlockSize * (unsigned long long)W;
+    MCMC::EnsembleSampler<double, Mover> sampler(seed, W, D, mover, maxBytes);
+    sampler.setInitialWalkerPos(initPos, initAux);
+    sampler.runMCMC(nsteps);
+    *acc = sampler.getAcceptedSteps();
+    *tot = sampler.getTotalSteps();
+    auto it = sampler.getStepIttBegin();
+    auto end = sampler.getStepIttEnd();
+    size_t row = (size_t)W * D;
+    int s = 0;
+    for (; it != end && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
+    return sampler.getStoredSteps();
 }
 
 /* Same run, then the reference's own CovarianceMatrix over the stored chain (Analysis/CovarianceMatrix.h:120-141). */
@@ -194,6 +217,15 @@ int ref_autocorr(int kind, const double* p, int W, int D, int seed, double* init
 {
 #define CALL_AC(c) runAutoCorr(c, W, D, seed, initPos, initAux, nsteps, chainOut, iatOut)
     DISPATCH(CALL_AC)
+    return 0;
+}
+
+/* sequential EnsembleSampler<DifferentialEvolution> (chainOut: nsteps+1 rows) */
+int ref_de_run(int kind, const double* p, int W, int D, int seed, double* initPos, double* initAux, int nsteps, double* chainOut,
+               unsigned long long* acc, unsigned long long* tot)
+{
+#define CALL_DE(c) runDiffEvo(c, W, D, seed, initPos, initAux, nsteps, chainOut, acc, tot)
+    DISPATCH(CALL_DE)
     return 0;
 }
 

@@ -81,6 +81,20 @@ def main():
 
     ac_case("analysis/ac_diag_d5_w64", "diag_gauss", iv5, 64, 5, 300)
     ac_case("analysis/ac_diag_d3_w48", "diag_gauss", iv5[:3], 48, 3, 511)
+    # Movers/DifferentialEvolution.h in the sequential sampler (reference mover, unmodified)
+    def de_case(name, kind, params, W, D, nsteps, keep_rows, init_seed=53):
+        init = R.init_normal(init_seed, W * D).reshape(W, D)
+        params = np.asarray(params, dtype=np.float64)
+        lp = R.logp(kind, params, init)
+        r = R.run_de(kind, params, init, lp, nsteps)
+        rows = np.asarray(keep_rows)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), kind=kind, params=params, W=W, D=D, nsteps=nsteps, init=init, logp=lp,
+                            rows=rows, chain=r["chain"][rows], acc=r["acc"], tot=r["tot"])
+        print(name, r["acc"], r["tot"])
+
+    os.makedirs(os.path.join(HERE, "movers"), exist_ok=True)
+    de_case("movers/de_skewed_w16", "skewed_gauss_2d", [0.13], 16, 2, 300, [0, 1, 2, 150, 300])
+    de_case("movers/de_diag_d5_w64", "diag_gauss", iv5, 64, 5, 100, [0, 1, 50, 100])
     for k, v in out.items():
         print(k, v)
 
