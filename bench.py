@@ -249,7 +249,11 @@ def gpu_arm(args):
         shard = "data"
     if world == 1 and args.shard != "dim":      # explicit dim with one rank = the three-kernel form on one GPU (overhead measurement)
         shard = "none"
-    rng_mode = args.rng
+    rng_mode = "per_walker" if args.mover == "de" else args.rng
+    if args.mover == "de":
+        desc += " [mover: DifferentialEvolution instead of the stretch move]"
+        if world > 1:
+            shard = "peer"
 
     def barrier():
         torch.cuda.synchronize()
@@ -258,7 +262,8 @@ def gpu_arm(args):
             torch.cuda.synchronize()
 
     def new_sampler():
-        s = m.EnsembleSampler(0, W, D, m.StretchMove(D, 0, make_calc(m, kind, params, rank, world)), maxChainSizeBytes=0,
+        mover_cls = m.DifferentialEvolution if args.mover == "de" else m.StretchMove
+        s = m.EnsembleSampler(0, W, D, mover_cls(D, 0, make_calc(m, kind, params, rank, world)), maxChainSizeBytes=0,
                               rngMode=rng_mode, device=local, rank=rank, world=world, shardMode=shard)
         parallel.connect(s)
         return s
@@ -395,6 +400,7 @@ def main():
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--shard", default=None, choices=["allgather", "peer", "dim"])
     ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
+    ap.add_argument("--mover", default="stretch", choices=["stretch", "de"], help="de: Mover::DifferentialEvolution (analysis runs; not the BASELINE metric)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.steps <= 0:

@@ -158,6 +158,13 @@ int mcmcpp_sampler_create(const mcmcpp_config* cfg, mcmcpp_halfstep_fn launcher,
 /* Built-in Calculator: `params` (host) is uploaded and viewed by the functor. */
 int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, const double* params, size_t num_params_values,
                                   mcmcpp_sampler** out);
+/* Movers.  STRETCH = Mover::StretchMove (Movers/StretchMove.h); DIFF_EVOLUTION = Mover::DifferentialEvolution
+ * (Movers/DifferentialEvolution.h:113-142), mover_params {gamma (<= 0: 2.38/sqrt(2D), :58), rand (<= 0: 1e-4, :83)};
+ * its draw count per update varies, so it needs rng_mode PER_WALKER; walker sharding only.  User Calculators:
+ * MCMC::Device::DiffEvoLauncher<Calc> (include/mcmcpp_b200/diff_evo_kernels.cuh) through mcmcpp_sampler_create. */
+enum { MCMCPP_MOVER_STRETCH = 0, MCMCPP_MOVER_DIFF_EVOLUTION = 1 };
+int mcmcpp_sampler_create_builtin_mover(const mcmcpp_config* cfg, int mover_kind, const double* mover_params, size_t num_mover_params,
+                                        int target_kind, const double* params, size_t num_params_values, mcmcpp_sampler** out);
 int mcmcpp_sampler_destroy(mcmcpp_sampler* s);
 
 /* ---- setInitialWalkerPos (EnsembleSampler.h:220-230): AoS [walker][param] + aux[walker];

@@ -34,6 +34,7 @@ _h = C.c_void_p
 SYMBOLS = {
     "mcmcpp_sampler_create": (C.c_int, [C.POINTER(Config), C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(_h)]),
     "mcmcpp_sampler_create_builtin": (C.c_int, [C.POINTER(Config), C.c_int, _dp, C.c_size_t, C.POINTER(_h)]),
+    "mcmcpp_sampler_create_builtin_mover": (C.c_int, [C.POINTER(Config), C.c_int, _dp, C.c_size_t, C.c_int, _dp, C.c_size_t, C.POINTER(_h)]),
     "mcmcpp_sampler_destroy": (C.c_int, [_h]),
     "mcmcpp_sampler_set_initial": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
     "mcmcpp_sampler_set_initial_device": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
@@ -73,6 +74,7 @@ SYMBOLS = {
     "mcmcpp_dim_slice": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 
+MOVER_STRETCH, MOVER_DIFF_EVOLUTION = 0, 1
 STEP_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p)
 
 _lib = None

@@ -8,6 +8,7 @@
 #include "builtin_targets.h"
 #include "mcmcpp_b200/stretch_kernels.cuh"
 #include "mcmcpp_b200/dim_shard_kernels.cuh"
+#include "mcmcpp_b200/diff_evo_kernels.cuh"
 #include "mcmcpp_b200/targets.h"
 
 namespace
@@ -70,6 +71,46 @@ int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t
         return MCMCPP_OK;
     }
     default: return MCMCPP_ERR_ARG;
+    }
+}
+
+namespace
+{
+template <class Calc, int FixedD>
+int bindDiffEvo(const Calc& c, int D, const MCMC::Device::DiffEvoParams& mv, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator)
+{
+    if (FixedD > 0 && D != FixedD) return MCMCPP_ERR_ARG;
+    MCMC::Device::DiffEvoBlob<Calc> blob = {c, mv};
+    calculator->resize(sizeof blob);
+    std::memcpy(calculator->data(), &blob, sizeof blob);
+    *launcher = &MCMC::Device::DiffEvoLauncher<Calc>::launch;
+    return MCMCPP_OK;
+}
+}
+
+/* DifferentialEvolution mover over a built-in Calculator: moverParams = {gamma (<= 0: 2.38/sqrt(2D)), rand (<= 0: 1e-4)} */
+int mcmcpp_builtin_bind_diff_evo(int kind, int D, const double* moverParams, size_t nMover, const double* hostParams, size_t nValues,
+                                 const double* devParams, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator)
+{
+    using namespace MCMC::Targets;
+    MCMC::Device::DiffEvoParams mv;
+    mv.gamma = (nMover > 0 && moverParams[0] > 0.0) ? moverParams[0] : 2.38 / std::sqrt((double)(2 * D));   /* DifferentialEvolution.h:58 */
+    const double rnd = (nMover > 1 && moverParams[1] > 0.0) ? moverParams[1] : 1.0e-4;                      /* :83,150-151 */
+    mv.lowEdge = -rnd;
+    mv.width = 2.0 * rnd;
+    switch (kind) {
+    case MCMCPP_TARGET_SKEWED_GAUSS_2D:
+        if (nValues != 1) return MCMCPP_ERR_ARG;
+        return bindDiffEvo<SkewedGaussianTwoDim<double>, 2>(SkewedGaussianTwoDim<double>(hostParams[0]), D, mv, launcher, calculator);
+    case MCMCPP_TARGET_ROSENBROCK_2D:
+        return bindDiffEvo<RosenbrockTwoDim<double>, 2>(RosenbrockTwoDim<double>(), D, mv, launcher, calculator);
+    case MCMCPP_TARGET_DIAG_GAUSS:
+        if (nValues != (size_t)D) return MCMCPP_ERR_ARG;
+        return bindDiffEvo<DiagGaussian<double>, 0>(DiagGaussian<double>(devParams, D), D, mv, launcher, calculator);
+    case MCMCPP_TARGET_DENSE_GAUSS:
+        if (nValues != (size_t)D * (size_t)D) return MCMCPP_ERR_ARG;
+        return bindDiffEvo<DenseGaussian<double>, 0>(DenseGaussian<double>(devParams, D), D, mv, launcher, calculator);
+    default: return MCMCPP_ERR_UNSUPPORTED;
     }
 }
 

@@ -467,6 +467,30 @@ int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, con
     return MCMCPP_OK;
 }
 
+int mcmcpp_sampler_create_builtin_mover(const mcmcpp_config* cfg, int mover_kind, const double* mover_params, size_t num_mover_params,
+                                        int target_kind, const double* params, size_t num_params_values, mcmcpp_sampler** out)
+{
+    if (mover_kind == MCMCPP_MOVER_STRETCH) return mcmcpp_sampler_create_builtin(cfg, target_kind, params, num_params_values, out);
+    if (mover_kind != MCMCPP_MOVER_DIFF_EVOLUTION) return fail(MCMCPP_ERR_UNSUPPORTED, "unknown mover");
+    if (cfg && cfg->rng_mode != MCMCPP_RNG_PER_WALKER)
+        return fail(MCMCPP_ERR_UNSUPPORTED, "DifferentialEvolution draws a variable number of values per update: per-walker streams only");
+    if (cfg && (cfg->shard_mode == MCMCPP_SHARD_DIM || cfg->shard_mode == MCMCPP_SHARD_DATA))
+        return fail(MCMCPP_ERR_UNSUPPORTED, "DifferentialEvolution: walker sharding (allgather / peer) only");
+    int rc = createCommon(cfg, out);
+    if (rc != MCMCPP_OK) { if (out && *out) { mcmcpp_sampler_destroy(*out); *out = nullptr; } return rc; }
+    mcmcpp_sampler* s = *out;
+    if (num_params_values) {
+        if (!params) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(MCMCPP_ERR_ARG, "null params"); }
+        cudaError_t e = cudaMalloc(&s->dParams, sizeof(double) * num_params_values);
+        if (e == cudaSuccess) e = cudaMemcpy(s->dParams, params, sizeof(double) * num_params_values, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(MCMCPP_ERR_CUDA, cudaGetErrorString(e)); }
+    }
+    rc = mcmcpp_builtin_bind_diff_evo(target_kind, s->D, mover_params, num_mover_params, params, num_params_values, s->dParams,
+                                      &s->launcher, &s->calculator);
+    if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "DifferentialEvolution: unsupported target or bad parameter count"); }
+    return MCMCPP_OK;
+}
+
 int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
 {
     if (!s) return MCMCPP_OK;

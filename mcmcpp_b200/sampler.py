@@ -84,6 +84,25 @@ class StretchMove:
         self.alpha = (int(alphaNum), int(alphaDenom))
 
 
+class DifferentialEvolution:
+    """MCMC::Mover::DifferentialEvolution<ParamType, Calculator> (Movers/DifferentialEvolution.h:40-156): same constructor
+    and tuning calls.  Its draw count per update varies, so the device runs it with one pcg64 stream per walker."""
+
+    def __init__(self, numParams, prngInit, calc):
+        self.numParams = int(numParams)
+        self.prngInit = int(prngInit)
+        self.calc = calc
+        self.alpha = (2, 1)
+        self.gamma = 0.0          # <= 0: 2.38 / sqrt(2 numParams)
+        self.rand = 0.0           # <= 0: 1e-4
+
+    def overrideGamma(self, newGamma):
+        self.gamma = float(newGamma)
+
+    def overrideRandBounds(self, newRand):
+        self.rand = float(newRand)
+
+
 class EnsembleSampler:
     """MCMC::EnsembleSampler<double, StretchMove<...>> on one B200 (or one shard of an ensemble
     spread over `world` GPUs, one process per GPU).
@@ -96,8 +115,10 @@ class EnsembleSampler:
 
     def __init__(self, randSeed, numWalker, numParameter, move, maxChainSizeBytes=2147483648, stepAct=None,
                  rngMode="sequential", traceUpdates=0, device=0, rank=0, world=1, shardMode="none"):
-        if not isinstance(move, StretchMove):
-            raise TypeError("the B200 path implements Mover::StretchMove only")
+        if not isinstance(move, (StretchMove, DifferentialEvolution)):
+            raise TypeError("the B200 path implements Mover::StretchMove and Mover::DifferentialEvolution")
+        if isinstance(move, DifferentialEvolution):
+            rngMode = "per_walker"                      # variable draws per update: no sequential-stream indexing
         if move.numParams != numParameter:
             raise ValueError("mover and sampler disagree on numParams")
         self._lib = _capi.lib()
@@ -115,9 +136,17 @@ class EnsembleSampler:
         params = np.ascontiguousarray(move.calc.params(), dtype=np.float64)
         self._h = C.c_void_p()
         # the reference asserts on bad walker counts (EnsembleSampler.h:207-208); here: ERR_ARG -> exception
-        check(self._lib.mcmcpp_sampler_create_builtin(C.byref(cfg), _capi.TARGET[move.calc.kind],
-                                                      params.ctypes.data_as(C.POINTER(C.c_double)), params.size,
-                                                      C.byref(self._h)))
+        if isinstance(move, DifferentialEvolution):
+            mv = np.array([move.gamma, move.rand], dtype=np.float64)
+            check(self._lib.mcmcpp_sampler_create_builtin_mover(C.byref(cfg), _capi.MOVER_DIFF_EVOLUTION,
+                                                                mv.ctypes.data_as(C.POINTER(C.c_double)), mv.size,
+                                                                _capi.TARGET[move.calc.kind],
+                                                                params.ctypes.data_as(C.POINTER(C.c_double)), params.size,
+                                                                C.byref(self._h)))
+        else:
+            check(self._lib.mcmcpp_sampler_create_builtin(C.byref(cfg), _capi.TARGET[move.calc.kind],
+                                                          params.ctypes.data_as(C.POINTER(C.c_double)), params.size,
+                                                          C.byref(self._h)))
         self.lastDeviceMs = 0.0
 
     # -- life cycle --------------------------------------------------------------------------
