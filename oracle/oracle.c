@@ -596,3 +596,87 @@ void oracle_de_run(pcg64_t* rng, int per_walker, int kind, const double* tparams
         }
     free(prop);
 }
+
+/*
+ * WalkMove::updateWalker (MCMCpp/Movers/WalkMove.h:95-186) inside the same red/black driver.  Per update:
+ *   selectWalkers (:117-136): selection sampling of S distinct indices in increasing order, one uniform per examined
+ *     walker: skip if (K - examined) * u >= (S - selected), else take it;
+ *   calculateProposal (:139-183): S normals r_j (std::normal_distribution, libstdc++ bits/random.tcc: Marsaglia polar,
+ *     the second value of a pair is kept for the next call); for every parameter i, a = sum_j r_j v_ji, c = sum_j v_ji
+ *     (in order j), b = sum_j r_j (once): proposal_i = cur_i + (a - (b * (c / S)));
+ *   accept iff log(1 - u) < newp - logp.
+ * One engine = pcg64 + the normal distribution's saved value: nstate[2*e] = saved, nstate[2*e+1] = 1.0 if available.
+ * per_walker == 0: engine 0 for everyone in walker order (the sequential reference sampler); else engine w.
+ * trace.j = first selected index, trace.z = first normal, trace.diff = newp - logp.
+ */
+static double oracle_std_normal(pcg64_t* g, double* st)
+{
+    double ret;
+    if (st[1] != 0.0) { st[1] = 0.0; ret = st[0]; }
+    else {
+        double x, y, r2;
+        do {
+            x = 2.0 * oracle_u64_to_unit(oracle_pcg64_next(g)) - 1.0;
+            y = 2.0 * oracle_u64_to_unit(oracle_pcg64_next(g)) - 1.0;
+            r2 = x * x + y * y;
+        } while (r2 > 1.0 || r2 == 0.0);
+        const double mult = sqrt(-2 * log(r2) / r2);
+        st[0] = x * mult; st[1] = 1.0;
+        ret = y * mult;
+    }
+    return ret * 1.0 + 0.0;                               /* stddev 1, mean 0 */
+}
+
+void oracle_walk_run(pcg64_t* rng, double* nstate, int per_walker, int kind, const double* tparams, int W, int D, int S,
+                     double* pos, double* logp, int64_t* acc, int64_t* tot, int nsteps, int interval, double* chain, oracle_trace_t* trace)
+{
+    const int K = W / 2;
+    const double ptCount = (double)S;
+    double* prop = (double*)malloc(sizeof(double) * (size_t)D);
+    double* rnd = (double*)malloc(sizeof(double) * (size_t)S);
+    int* idx = (int*)malloc(sizeof(int) * (size_t)S);
+    size_t tr = 0;
+    for (int s = 0; s < nsteps; ++s)
+        for (int sub = 0; sub < interval; ++sub) {
+            const int store = (sub == interval - 1);
+            for (int h = 0; h < 2; ++h) {
+                const int own0 = h * K, oth0 = (1 - h) * K;
+                for (int i = 0; i < K; ++i) {
+                    const int w = own0 + i;
+                    pcg64_t* g = per_walker ? &rng[w] : &rng[0];
+                    double* st = per_walker ? &nstate[2 * w] : &nstate[0];
+                    int numSelected = 0, examined = 0;
+                    while (numSelected < S) {
+                        const double u = oracle_u64_to_unit(oracle_pcg64_next(g));
+                        if (((K - examined) * u) >= (ptCount - numSelected)) ++examined;
+                        else { idx[numSelected] = examined; ++examined; ++numSelected; }
+                    }
+                    double* cur = pos + (size_t)w * D;
+                    double i0 = 0.0, i1 = 0.0, i2 = 0.0;
+                    for (int j = 0; j < S; ++j) {
+                        rnd[j] = oracle_std_normal(g, st);
+                        const double value = pos[(size_t)(oth0 + idx[j]) * D];
+                        i0 += rnd[j] * value; i1 += rnd[j]; i2 += value;
+                    }
+                    prop[0] = cur[0] + (i0 - (i1 * (i2 / ptCount)));
+                    for (int d = 1; d < D; ++d) {
+                        i0 = 0.0; i2 = 0.0;
+                        for (int j = 0; j < S; ++j) {
+                            const double value = pos[(size_t)(oth0 + idx[j]) * D + d];
+                            i0 += rnd[j] * value; i2 += value;
+                        }
+                        prop[d] = (cur[d] + (i0 - (i1 * (i2 / ptCount))));
+                    }
+                    const double newp = oracle_logp(kind, D, tparams, prop);
+                    const double diff = newp - logp[w];
+                    const double e = oracle_neg_exponential(oracle_u64_to_unit(oracle_pcg64_next(g)));
+                    const int a = e < diff;
+                    if (a) { memcpy(cur, prop, sizeof(double) * (size_t)D); logp[w] = newp; ++acc[w]; }
+                    ++tot[w];
+                    if (trace) { oracle_trace_t* t = &trace[tr++]; t->j = idx[0]; t->accept = a; t->z = rnd[0]; t->e = e; t->newp = newp; t->diff = diff; }
+                    if (store && chain) memcpy(chain + ((size_t)s * W + w) * D, cur, sizeof(double) * (size_t)D);
+                }
+            }
+        }
+    free(prop); free(rnd); free(idx);
+}

@@ -71,6 +71,9 @@ class Port:
         L.oracle_de_run.restype = None
         L.oracle_de_run.argtypes = [C.c_void_p, C.c_int, C.c_int, c_dp, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                     c_dp, c_dp, C.c_void_p, C.c_void_p, C.c_int, C.c_int, c_dp, C.c_void_p]
+        L.oracle_walk_run.restype = None
+        L.oracle_walk_run.argtypes = [C.c_void_p, c_dp, C.c_int, C.c_int, c_dp, C.c_int, C.c_int, C.c_int,
+                                      c_dp, c_dp, C.c_void_p, C.c_void_p, C.c_int, C.c_int, c_dp, C.c_void_p]
         L.oracle_autocorr.restype = None
         L.oracle_autocorr.argtypes = [c_dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp]
         L.oracle_stretch_run_per_walker.restype = C.c_int
@@ -190,6 +193,28 @@ class Port:
                                trace.ctypes.data if want_trace else None)
         return dict(pos=pos, logp=logp, acc=acc, tot=tot, chain=chain, trace=trace)
 
+    def run_walk(self, kind, params, pos, logp, nsteps, num_points, interval=1, seed=0, per_walker=False, want_chain=True,
+                 want_trace=False):
+        """WalkMove mover (num_points partner walkers) in the red/black driver; one engine (seed, 0) in walker order, or one
+        engine per walker (stream = walker index, each with its own normal-distribution state)."""
+        pos = np.array(pos, dtype=np.float64, order="C")
+        logp = np.array(logp, dtype=np.float64)
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        if per_walker:
+            g = (Pcg64 * W)()
+            self.lib.oracle_pcg64_seed_many(g, seed & (2**64 - 1), W)
+        else:
+            g = self.pcg64(seed, 0)
+        nstate = np.zeros(2 * W)
+        acc, tot = np.ones(W, np.int64), np.ones(W, np.int64)
+        chain = np.empty((nsteps, W, D)) if want_chain else None
+        trace = np.zeros(nsteps * interval * W, dtype=TRACE_DTYPE) if want_trace else None
+        self.lib.oracle_walk_run(C.byref(g), _dp(nstate), int(per_walker), KIND[kind], _dp(params), W, D, int(num_points),
+                                 _dp(pos), _dp(logp), acc.ctypes.data, tot.ctypes.data, nsteps, interval, _dp(chain),
+                                 trace.ctypes.data if want_trace else None)
+        return dict(pos=pos, logp=logp, acc=acc, tot=tot, chain=chain, trace=trace)
+
     def half_slots(self, kind, params, pos, logp, acc, step, half, slot_begin, slot_count, seed=0, alpha=(2, 1)):
         """In-place update of one colour's slots [slot_begin, +slot_count) with jump-ahead draws (one rank's work)."""
         W, D = pos.shape
@@ -224,6 +249,9 @@ class Ref:
         L.ref_de_run.restype = C.c_int
         L.ref_de_run.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, c_dp,
                                  C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
+        L.ref_walk_run.restype = C.c_int
+        L.ref_walk_run.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, c_dp,
+                                   C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
         L.ref_autocorr.restype = C.c_int
         L.ref_autocorr.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, c_dp, c_dp]
         L.ref_covariance.restype = C.c_int
@@ -302,6 +330,18 @@ class Ref:
         chain = np.empty((nsteps + 1, W, D))
         acc, tot = C.c_ulonglong(), C.c_ulonglong()
         self.lib.ref_de_run(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, _dp(chain), C.byref(acc), C.byref(tot))
+        return dict(chain=chain, acc=acc.value, tot=tot.value)
+
+    def run_walk(self, kind, params, pos, logp, nsteps, num_points, seed=0):
+        """Sequential reference EnsembleSampler with the WalkMove mover -> dict(chain[(nsteps+1),W,D], acc, tot)."""
+        pos = np.array(pos, dtype=np.float64, order="C")
+        logp = np.array(logp, dtype=np.float64)
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        chain = np.empty((nsteps + 1, W, D))
+        acc, tot = C.c_ulonglong(), C.c_ulonglong()
+        self.lib.ref_walk_run(KIND[kind], _dp(params), W, D, seed, int(num_points), _dp(pos), _dp(logp), nsteps, _dp(chain),
+                              C.byref(acc), C.byref(tot))
         return dict(chain=chain, acc=acc.value, tot=tot.value)
 
     def time(self, kind, params, pos, logp, nsteps, threads=0, seed=0):

@@ -16,6 +16,7 @@
 #include "ParallelEnsembleSampler.h"      /* MCMCpp/ParallelEnsembleSampler.h */
 #include "Movers/StretchMove.h"           /* MCMCpp/Movers/StretchMove.h */
 #include "Movers/DifferentialEvolution.h" /* MCMCpp/Movers/DifferentialEvolution.h */
+#include "Movers/WalkMove.h"              /* MCMCpp/Movers/WalkMove.h */
 #include "Analysis/CovarianceMatrix.h"    /* MCMCpp/Analysis/CovarianceMatrix.h */
 #include "Analysis/AutoCorrCalc.h"        /* MCMCpp/Analysis/AutoCorrCalc.h */
 #include "Common/SkewedGaussian.h"        /* test/sequential/SkewedGaussian/Common/SkewedGaussian.h */
@@ -57,6 +58,28 @@ int runDiffEvo(const Calc& calc, int W, int D, int seed, double* initPos, double
 {
     typedef MCMC::Mover::DifferentialEvolution<double, Calc> Mover;
     Mover mover(D, seed, calc);
+    unsigned long long blocks = (unsigned long long)(nsteps + 1) / MCMC::Chain::Detail::BlockSize + 2ULL;
+    unsigned long long maxBytes = blocks * sizeof(double) * D * MCMC::Chain::Detail::BlockSize * (unsigned long long)W;
+    MCMC::EnsembleSampler<double, Mover> sampler(seed, W, D, mover, maxBytes);
+    sampler.setInitialWalkerPos(initPos, initAux);
+    sampler.runMCMC(nsteps);
+    *acc = sampler.getAcceptedSteps();
+    *tot = sampler.getTotalSteps();
+    auto it = sampler.getStepIttBegin();
+    auto end = sampler.getStepIttEnd();
+    size_t row = (size_t)W * D;
+    int s = 0;
+    for (; it != end && s <= nsteps; ++it, ++s) std::memcpy(chainOut + s * row, *it, row * sizeof(double));
+    return sampler.getStoredSteps();
+}
+
+/* Sequential reference sampler with the WalkMove mover (Movers/WalkMove.h:95-186), numSamples partner points. */
+template <class Calc>
+int runWalk(const Calc& calc, int W, int D, int seed, int numSamples, double* initPos, double* initAux, int nsteps, double* chainOut,
+            unsigned long long* acc, unsigned long long* tot)
+{
+    typedef MCMC::Mover::WalkMove<double, Calc> Mover;
+    Mover mover(D, seed, calc, numSamples);
     unsigned long long blocks = (unsigned long long)(nsteps + 1) / MCMC::Chain::Detail::BlockSize + 2ULL;
     unsigned long long maxBytes = blocks * sizeof(double) * D * MCMC::Chain::Detail::BlockSize * (unsigned long long)W;
     MCMC::EnsembleSampler<double, Mover> sampler(seed, W, D, mover, maxBytes);
@@ -226,6 +249,15 @@ int ref_de_run(int kind, const double* p, int W, int D, int seed, double* initPo
 {
 #define CALL_DE(c) runDiffEvo(c, W, D, seed, initPos, initAux, nsteps, chainOut, acc, tot)
     DISPATCH(CALL_DE)
+    return 0;
+}
+
+/* sequential EnsembleSampler<WalkMove> (chainOut: nsteps+1 rows) */
+int ref_walk_run(int kind, const double* p, int W, int D, int seed, int numSamples, double* initPos, double* initAux, int nsteps,
+                 double* chainOut, unsigned long long* acc, unsigned long long* tot)
+{
+#define CALL_WALK(c) runWalk(c, W, D, seed, numSamples, initPos, initAux, nsteps, chainOut, acc, tot)
+    DISPATCH(CALL_WALK)
     return 0;
 }
 

@@ -95,6 +95,20 @@ def main():
     os.makedirs(os.path.join(HERE, "movers"), exist_ok=True)
     de_case("movers/de_skewed_w16", "skewed_gauss_2d", [0.13], 16, 2, 300, [0, 1, 2, 150, 300])
     de_case("movers/de_diag_d5_w64", "diag_gauss", iv5, 64, 5, 100, [0, 1, 50, 100])
+    # Movers/WalkMove.h in the sequential sampler (reference mover, unmodified)
+    def walk_case(name, kind, params, W, D, nsteps, num_points, keep_rows, init_seed=53):
+        init = R.init_normal(init_seed, W * D).reshape(W, D)
+        params = np.asarray(params, dtype=np.float64)
+        lp = R.logp(kind, params, init)
+        r = R.run_walk(kind, params, init, lp, nsteps, num_points)
+        rows = np.asarray(keep_rows)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), kind=kind, params=params, W=W, D=D, nsteps=nsteps, num_points=num_points,
+                            init=init, logp=lp, rows=rows, chain=r["chain"][rows], acc=r["acc"], tot=r["tot"])
+        print(name, r["acc"], r["tot"])
+
+    walk_case("movers/walk_skewed_w16_s3", "skewed_gauss_2d", [0.13], 16, 2, 300, 3, [0, 1, 2, 150, 300])
+    walk_case("movers/walk_diag_d5_w64_s6", "diag_gauss", iv5, 64, 5, 100, 6, [0, 1, 50, 100])
+    walk_case("movers/walk_skewed_w32_s16", "skewed_gauss_2d", [0.13], 32, 2, 100, 16, [0, 1, 100])
     for k, v in out.items():
         print(k, v)
 
