@@ -84,6 +84,8 @@ typedef struct {
     int32_t shard_mode;        /* MCMCPP_SHARD_* */
     int32_t trace_updates;     /* >0: record (j, accept, z, e, newp, diff) for the first n updates (tests) */
     uint64_t max_chain_bytes;  /* maxChainSizeBytes (EnsembleSampler.h:67); 0 = keep no chain */
+    int32_t mover_state_doubles; /* doubles of per-walker mover state the runtime keeps between updates (0 for the stretch move;
+                                  * 2 for WalkMove: its normal distribution's saved value + flag); zeroed by setInitialWalkerPos */
 } mcmcpp_config;
 
 /* One row of the optional trace, in the sequential update order (step, half, slot). */
@@ -145,6 +147,7 @@ typedef struct {
     int32_t* dim_list;         /* [K] walkers the commit kernel must touch (bit 31 = accepted) */
     int32_t* dim_count;        /* [1] entries in dim_list */
     int32_t sm_count;          /* multiprocessors of the device (persistent grids) */
+    double* mover_state;       /* [W * mover_state_doubles] per-walker mover state, or NULL */
     double* sync_word;         /* 1 double: operand of the stream-ordered rendezvous (allreduce_sum of 1 element) */
 } mcmcpp_halfstep_args;
 
@@ -160,9 +163,11 @@ int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, con
                                   mcmcpp_sampler** out);
 /* Movers.  STRETCH = Mover::StretchMove (Movers/StretchMove.h); DIFF_EVOLUTION = Mover::DifferentialEvolution
  * (Movers/DifferentialEvolution.h:113-142), mover_params {gamma (<= 0: 2.38/sqrt(2D), :58), rand (<= 0: 1e-4, :83)};
- * its draw count per update varies, so it needs rng_mode PER_WALKER; walker sharding only.  User Calculators:
- * MCMC::Device::DiffEvoLauncher<Calc> (include/mcmcpp_b200/diff_evo_kernels.cuh) through mcmcpp_sampler_create. */
-enum { MCMCPP_MOVER_STRETCH = 0, MCMCPP_MOVER_DIFF_EVOLUTION = 1 };
+ * WALK = Mover::WalkMove (Movers/WalkMove.h:95-186), mover_params {numSamples (1..64, <= walkers per colour)}.
+ * Their draw counts per update vary, so they need rng_mode PER_WALKER; walker sharding only.  User Calculators:
+ * MCMC::Device::DiffEvoLauncher<Calc> / WalkMoveLauncher<Calc> (include/mcmcpp_b200/diff_evo_kernels.cuh,
+ * walk_move_kernels.cuh) through mcmcpp_sampler_create (WalkMove: cfg.mover_state_doubles = 2). */
+enum { MCMCPP_MOVER_STRETCH = 0, MCMCPP_MOVER_DIFF_EVOLUTION = 1, MCMCPP_MOVER_WALK = 2 };
 int mcmcpp_sampler_create_builtin_mover(const mcmcpp_config* cfg, int mover_kind, const double* mover_params, size_t num_mover_params,
                                         int target_kind, const double* params, size_t num_params_values, mcmcpp_sampler** out);
 int mcmcpp_sampler_destroy(mcmcpp_sampler* s);

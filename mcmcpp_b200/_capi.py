@@ -20,7 +20,8 @@ class Config(C.Structure):
     _fields_ = [("num_walkers", C.c_int32), ("num_params", C.c_int32), ("seed", C.c_int64),
                 ("rng_mode", C.c_int32), ("alpha_num", C.c_int32), ("alpha_denom", C.c_int32),
                 ("device", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("shard_mode", C.c_int32), ("trace_updates", C.c_int32), ("max_chain_bytes", C.c_uint64)]
+                ("shard_mode", C.c_int32), ("trace_updates", C.c_int32), ("max_chain_bytes", C.c_uint64),
+                ("mover_state_doubles", C.c_int32)]
 
 
 class Trace(C.Structure):
@@ -74,7 +75,7 @@ SYMBOLS = {
     "mcmcpp_dim_slice": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 
-MOVER_STRETCH, MOVER_DIFF_EVOLUTION = 0, 1
+MOVER_STRETCH, MOVER_DIFF_EVOLUTION, MOVER_WALK = 0, 1, 2
 STEP_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p)
 
 _lib = None

@@ -12,8 +12,8 @@
  * Fills *launcher and the by-value calculator blob; *aux receives optional scratch owned by the target. */
 int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t nValues, const double* devParams,
                         mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux, int shardMode, int dimBegin, int dimCount);
-int mcmcpp_builtin_bind_diff_evo(int kind, int D, const double* moverParams, size_t nMover, const double* hostParams, size_t nValues,
-                                 const double* devParams, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);
+int mcmcpp_builtin_bind_mover(int moverKind, int kind, int W, int D, const double* moverParams, size_t nMover, const double* hostParams,
+                              size_t nValues, const double* devParams, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);
 void mcmcpp_builtin_release(void* aux);
 /* dense_gauss.cu: FP64 tensor-core half-step for the dense Gaussian; false = use the generic launcher */
 bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);

@@ -169,6 +169,8 @@ struct mcmcpp_sampler
     int32_t* dBarrier = nullptr;
     std::vector<void*> peerOpened;
     const double** dPeerPos = nullptr;
+    double* dMoverState = nullptr;         /* [W][moverDoubles] */
+    int moverDoubles = 0;
     /* PostStepAction with a device-resident step view (EnsembleSampler.h:356-359) */
     mcmcpp_step_fn stepFn = nullptr;
     void* stepCtx = nullptr;
@@ -353,6 +355,11 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     CUDA_TRY(cudaMemset(s->dFlags, 0, sizeof(int32_t) * 4));
     CUDA_TRY(cudaMemset(s->dBarrier, 0, sizeof(int32_t)));
     CUDA_TRY(cudaMemset(s->dPos, 0, sizeof(double) * devRowDoubles(s)));
+    s->moverDoubles = cfg->mover_state_doubles > 0 ? cfg->mover_state_doubles : 0;
+    if (s->moverDoubles) {
+        CUDA_TRY(cudaMalloc(&s->dMoverState, sizeof(double) * (size_t)W * (size_t)s->moverDoubles));
+        CUDA_TRY(cudaMemset(s->dMoverState, 0, sizeof(double) * (size_t)W * (size_t)s->moverDoubles));
+    }
     /* draw scratch (z, log(1-u), j of the colour in flight): kernels whose draws run in their own launch */
     CUDA_TRY(cudaMalloc(&s->dDimZ, sizeof(double) * (size_t)s->K));
     CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
@@ -381,6 +388,7 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     a.W = W; a.D = s->Dl; a.K = s->K;
     a.D_total = D; a.dim_begin = s->dimBegin; a.rank = cfg->rank; a.world = cfg->world;
     a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ; a.sync_word = s->dSyncWord;
+    a.mover_state = s->dMoverState;
     a.dim_list = s->dDimList; a.dim_count = s->dDimList ? s->dDimList + s->K : nullptr;
     { int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device); a.sm_count = sms; }
     a.slot_begin = s->slotBegin; a.slot_count = s->slotCount; a.slots_per_rank = s->slotCount;
@@ -406,6 +414,7 @@ int afterInitialState(mcmcpp_sampler* s, const double* hostRowOrNull)
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemsetAsync(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid, s->stream));
     CUDA_TRY(cudaMemsetAsync(s->dFlags, 0, sizeof(int32_t) * 4, s->stream));
+    if (s->dMoverState) CUDA_TRY(cudaMemsetAsync(s->dMoverState, 0, sizeof(double) * (size_t)s->W * (size_t)s->moverDoubles, s->stream));
     const unsigned long long owned = 2ULL * (unsigned long long)s->slotCount;
     s->acceptedBase += owned;
     s->totalSteps += owned;
@@ -471,11 +480,15 @@ int mcmcpp_sampler_create_builtin_mover(const mcmcpp_config* cfg, int mover_kind
                                         int target_kind, const double* params, size_t num_params_values, mcmcpp_sampler** out)
 {
     if (mover_kind == MCMCPP_MOVER_STRETCH) return mcmcpp_sampler_create_builtin(cfg, target_kind, params, num_params_values, out);
-    if (mover_kind != MCMCPP_MOVER_DIFF_EVOLUTION) return fail(MCMCPP_ERR_UNSUPPORTED, "unknown mover");
-    if (cfg && cfg->rng_mode != MCMCPP_RNG_PER_WALKER)
-        return fail(MCMCPP_ERR_UNSUPPORTED, "DifferentialEvolution draws a variable number of values per update: per-walker streams only");
-    if (cfg && (cfg->shard_mode == MCMCPP_SHARD_DIM || cfg->shard_mode == MCMCPP_SHARD_DATA))
-        return fail(MCMCPP_ERR_UNSUPPORTED, "DifferentialEvolution: walker sharding (allgather / peer) only");
+    if (mover_kind != MCMCPP_MOVER_DIFF_EVOLUTION && mover_kind != MCMCPP_MOVER_WALK) return fail(MCMCPP_ERR_UNSUPPORTED, "unknown mover");
+    if (!cfg) return fail(MCMCPP_ERR_ARG, "null argument");
+    if (cfg->rng_mode != MCMCPP_RNG_PER_WALKER)
+        return fail(MCMCPP_ERR_UNSUPPORTED, "this mover draws a variable number of values per update: per-walker streams only");
+    if (cfg->shard_mode == MCMCPP_SHARD_DIM || cfg->shard_mode == MCMCPP_SHARD_DATA)
+        return fail(MCMCPP_ERR_UNSUPPORTED, "this mover: walker sharding (allgather / peer) only");
+    mcmcpp_config withState = *cfg;
+    if (mover_kind == MCMCPP_MOVER_WALK) withState.mover_state_doubles = 2;       /* the normal distribution's saved value + flag */
+    cfg = &withState;
     int rc = createCommon(cfg, out);
     if (rc != MCMCPP_OK) { if (out && *out) { mcmcpp_sampler_destroy(*out); *out = nullptr; } return rc; }
     mcmcpp_sampler* s = *out;
@@ -485,9 +498,9 @@ int mcmcpp_sampler_create_builtin_mover(const mcmcpp_config* cfg, int mover_kind
         if (e == cudaSuccess) e = cudaMemcpy(s->dParams, params, sizeof(double) * num_params_values, cudaMemcpyHostToDevice);
         if (e != cudaSuccess) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(MCMCPP_ERR_CUDA, cudaGetErrorString(e)); }
     }
-    rc = mcmcpp_builtin_bind_diff_evo(target_kind, s->D, mover_params, num_mover_params, params, num_params_values, s->dParams,
-                                      &s->launcher, &s->calculator);
-    if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "DifferentialEvolution: unsupported target or bad parameter count"); }
+    rc = mcmcpp_builtin_bind_mover(mover_kind, target_kind, s->W, s->D, mover_params, num_mover_params, params, num_params_values, s->dParams,
+                                   &s->launcher, &s->calculator);
+    if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "mover: unsupported target or bad parameters"); }
     return MCMCPP_OK;
 }
 
@@ -500,6 +513,7 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     if (s->comm && nccl().ok) nccl().CommDestroy(s->comm);
     for (void* p : s->peerOpened) cudaIpcCloseMemHandle(p);
     cudaFree(s->dPeerPos);
+    cudaFree(s->dMoverState);
     cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ); cudaFree(s->dDimList); cudaFree(s->dSyncWord);
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
     cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
@@ -904,7 +918,7 @@ namespace
 struct CheckpointHeader
 {
     uint64_t magic;                 /* "MCMCPB2\0" */
-    int32_t W, D, Dl, dimBegin, rngMode, shardMode, rank, world;
+    int32_t W, D, Dl, dimBegin, rngMode, shardMode, rank, world, moverDoubles, pad;
     int64_t seed, ensembleSteps;
     uint64_t accepted, total;
 };
@@ -912,7 +926,8 @@ const uint64_t CheckpointMagic = 0x00324250434d434dULL;
 
 size_t checkpointBytes(const mcmcpp_sampler* s)
 {
-    return sizeof(CheckpointHeader) + sizeof(double) * devRowDoubles(s) + sizeof(double) * (size_t)s->W + sizeof(uint64_t) * 2 * (size_t)s->W;
+    return sizeof(CheckpointHeader) + sizeof(double) * devRowDoubles(s) + sizeof(double) * (size_t)s->W + sizeof(uint64_t) * 2 * (size_t)s->W +
+           sizeof(double) * (size_t)s->W * (size_t)s->moverDoubles;
 }
 }
 
@@ -932,6 +947,7 @@ int mcmcpp_sampler_checkpoint_save(mcmcpp_sampler* s, void* buffer, size_t bytes
     std::memset(&h, 0, sizeof h);
     h.magic = CheckpointMagic;
     h.W = s->W; h.D = s->D; h.Dl = s->Dl; h.dimBegin = s->dimBegin; h.rngMode = s->cfg.rng_mode; h.shardMode = s->cfg.shard_mode;
+    h.moverDoubles = s->moverDoubles;
     h.rank = s->cfg.rank; h.world = s->cfg.world; h.seed = s->cfg.seed; h.ensembleSteps = s->ensembleSteps;
     unsigned long long acc = 0, tot = 0;
     int rc = mcmcpp_sampler_get_counts(s, &acc, &tot);
@@ -941,7 +957,9 @@ int mcmcpp_sampler_checkpoint_save(mcmcpp_sampler* s, void* buffer, size_t bytes
     std::memcpy(out, &h, sizeof h); out += sizeof h;
     CUDA_TRY(cudaMemcpyAsync(out, s->dPos, sizeof(double) * devRowDoubles(s), cudaMemcpyDeviceToHost, s->stream)); out += sizeof(double) * devRowDoubles(s);
     CUDA_TRY(cudaMemcpyAsync(out, s->dLogp, sizeof(double) * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream)); out += sizeof(double) * (size_t)s->W;
-    CUDA_TRY(cudaMemcpyAsync(out, s->dRng, sizeof(uint64_t) * 2 * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(out, s->dRng, sizeof(uint64_t) * 2 * (size_t)s->W, cudaMemcpyDeviceToHost, s->stream)); out += sizeof(uint64_t) * 2 * (size_t)s->W;
+    if (s->moverDoubles)
+        CUDA_TRY(cudaMemcpyAsync(out, s->dMoverState, sizeof(double) * (size_t)s->W * (size_t)s->moverDoubles, cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     return MCMCPP_OK;
 }
@@ -953,13 +971,16 @@ int mcmcpp_sampler_checkpoint_restore(mcmcpp_sampler* s, const void* buffer, siz
     CheckpointHeader h;
     std::memcpy(&h, buffer, sizeof h);
     if (h.magic != CheckpointMagic) return fail(MCMCPP_ERR_ARG, "not a mcmcpp_b200 checkpoint");
-    if (h.W != s->W || h.D != s->D || h.Dl != s->Dl || h.dimBegin != s->dimBegin || h.rngMode != s->cfg.rng_mode || h.seed != s->cfg.seed)
+    if (h.W != s->W || h.D != s->D || h.Dl != s->Dl || h.dimBegin != s->dimBegin || h.rngMode != s->cfg.rng_mode || h.seed != s->cfg.seed ||
+        h.moverDoubles != s->moverDoubles)
         return fail(MCMCPP_ERR_ARG, "checkpoint was taken from a different sampler configuration (walkers, parameters, slice, rng mode or seed)");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     const char* in = static_cast<const char*>(buffer) + sizeof h;
     CUDA_TRY(cudaMemcpyAsync(s->dPos, in, sizeof(double) * devRowDoubles(s), cudaMemcpyHostToDevice, s->stream)); in += sizeof(double) * devRowDoubles(s);
     CUDA_TRY(cudaMemcpyAsync(s->dLogp, in, sizeof(double) * (size_t)s->W, cudaMemcpyHostToDevice, s->stream)); in += sizeof(double) * (size_t)s->W;
-    CUDA_TRY(cudaMemcpyAsync(s->dRng, in, sizeof(uint64_t) * 2 * (size_t)s->W, cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->dRng, in, sizeof(uint64_t) * 2 * (size_t)s->W, cudaMemcpyHostToDevice, s->stream)); in += sizeof(uint64_t) * 2 * (size_t)s->W;
+    if (s->moverDoubles)
+        CUDA_TRY(cudaMemcpyAsync(s->dMoverState, in, sizeof(double) * (size_t)s->W * (size_t)s->moverDoubles, cudaMemcpyHostToDevice, s->stream));
     CUDA_TRY(cudaMemsetAsync(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid, s->stream));
     CUDA_TRY(cudaMemsetAsync(s->dFlags, 0, sizeof(int32_t) * 4, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));

@@ -103,6 +103,18 @@ class DifferentialEvolution:
         self.rand = float(newRand)
 
 
+class WalkMove:
+    """MCMC::Mover::WalkMove<ParamType, Calculator>(numParams, prngInit, calc, numSamples) (Movers/WalkMove.h:40-60):
+    numSamples partner walkers of the other colour per proposal.  One pcg64 stream per walker on the device."""
+
+    def __init__(self, numParams, prngInit, calc, numSamples):
+        self.numParams = int(numParams)
+        self.prngInit = int(prngInit)
+        self.calc = calc
+        self.alpha = (2, 1)
+        self.numPoints = int(numSamples)
+
+
 class EnsembleSampler:
     """MCMC::EnsembleSampler<double, StretchMove<...>> on one B200 (or one shard of an ensemble
     spread over `world` GPUs, one process per GPU).
@@ -115,9 +127,9 @@ class EnsembleSampler:
 
     def __init__(self, randSeed, numWalker, numParameter, move, maxChainSizeBytes=2147483648, stepAct=None,
                  rngMode="sequential", traceUpdates=0, device=0, rank=0, world=1, shardMode="none"):
-        if not isinstance(move, (StretchMove, DifferentialEvolution)):
-            raise TypeError("the B200 path implements Mover::StretchMove and Mover::DifferentialEvolution")
-        if isinstance(move, DifferentialEvolution):
+        if not isinstance(move, (StretchMove, DifferentialEvolution, WalkMove)):
+            raise TypeError("the B200 path implements Mover::StretchMove, Mover::DifferentialEvolution and Mover::WalkMove")
+        if isinstance(move, (DifferentialEvolution, WalkMove)):
             rngMode = "per_walker"                      # variable draws per update: no sequential-stream indexing
         if move.numParams != numParameter:
             raise ValueError("mover and sampler disagree on numParams")
@@ -136,9 +148,10 @@ class EnsembleSampler:
         params = np.ascontiguousarray(move.calc.params(), dtype=np.float64)
         self._h = C.c_void_p()
         # the reference asserts on bad walker counts (EnsembleSampler.h:207-208); here: ERR_ARG -> exception
-        if isinstance(move, DifferentialEvolution):
-            mv = np.array([move.gamma, move.rand], dtype=np.float64)
-            check(self._lib.mcmcpp_sampler_create_builtin_mover(C.byref(cfg), _capi.MOVER_DIFF_EVOLUTION,
+        if isinstance(move, (DifferentialEvolution, WalkMove)):
+            de = isinstance(move, DifferentialEvolution)
+            mv = np.array([move.gamma, move.rand] if de else [float(move.numPoints)], dtype=np.float64)
+            check(self._lib.mcmcpp_sampler_create_builtin_mover(C.byref(cfg), _capi.MOVER_DIFF_EVOLUTION if de else _capi.MOVER_WALK,
                                                                 mv.ctypes.data_as(C.POINTER(C.c_double)), mv.size,
                                                                 _capi.TARGET[move.calc.kind],
                                                                 params.ctypes.data_as(C.POINTER(C.c_double)), params.size,

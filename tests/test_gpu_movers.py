@@ -84,3 +84,56 @@ def test_diff_evo_needs_per_walker_streams():
     rc = _capi.lib().mcmcpp_sampler_create_builtin_mover(C.byref(cfg), _capi.MOVER_DIFF_EVOLUTION, None, 0, _capi.TARGET["skewed_gauss_2d"],
                                                          p.ctypes.data_as(C.POINTER(C.c_double)), 1, C.byref(h))
     assert rc == _capi.ERR_UNSUPPORTED
+
+
+def run_walk_both(port, kind, params, W, D, S, steps, seed, trace=0):
+    import mcmcpp_b200 as m
+    params = np.asarray(params, dtype=np.float64)
+    init = np.random.default_rng(W + D + S).standard_normal((W, D))
+    lp = port.logp(kind, params if params.size else None, init)
+    s = m.EnsembleSampler(seed, W, D, m.WalkMove(D, seed, CALC[kind](m, params, D), S), traceUpdates=trace)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run_walk(kind, params if params.size else None, init, lp, steps, S, seed=seed, per_walker=True, want_trace=trace > 0)
+    return s, o
+
+
+@pytest.mark.parametrize("kind,W,D,S,steps", [("skewed_gauss_2d", 16, 2, 3, 60), ("skewed_gauss_2d", 32, 2, 16, 30),
+                                              ("rosenbrock_2d", 1024, 2, 4, 20), ("diag_gauss", 64, 5, 6, 30),
+                                              ("diag_gauss", 512, 100, 8, 6), ("diag_gauss", 2100, 1001, 5, 2),
+                                              ("dense_gauss", 128, 24, 7, 8)])
+def test_walk_move_tolerance_tier(port, kind, W, D, S, steps):
+    """Mover::WalkMove on the device against oracle_walk_run (pinned bit-exact to the unmodified reference mover), one
+    engine per walker.  Partner selection is integer work: bit-exact.  The normals go through log(): the device's and
+    glibc's differ in the last bit on some inputs, so normals / positions / log-probs carry the tolerance tier
+    (<= 1e-12 relative, north_star); decisions must agree over these runs (a flip needs one within ~1e-13 of its threshold).
+    Covers selection of ALL walkers of the other colour (S == K), odd and wide rows, separable and generic Calculators."""
+    params = {"skewed_gauss_2d": [0.13], "rosenbrock_2d": [], "diag_gauss": 1.0 / (1.0 + (np.arange(D) % 10)),
+              "dense_gauss": np.linalg.inv(0.9 ** np.abs(np.arange(D)[:, None] - np.arange(D)[None, :])).reshape(-1)}[kind]
+    s, o = run_walk_both(port, kind, params, W, D, S, steps, seed=4, trace=W)
+    tr, otr = s.getTrace(W), o["trace"][:W]
+    assert np.array_equal(tr["j"], otr["j"]) and np.array_equal(tr["accept"], otr["accept"])
+    assert np.allclose(tr["z"], otr["z"], rtol=1e-13, atol=0)                      # first normal of every update
+    pos, aux = s.getWalkerState()
+    scale = np.abs(o["pos"]) + np.abs(o["pos"]).max()
+    assert np.all(np.abs(pos - o["pos"]) <= 1e-12 * scale)
+    assert np.allclose(aux, o["logp"], rtol=1e-11, atol=1e-12)
+    assert (s.getAcceptedSteps(), s.getTotalSteps()) == (int(o["acc"].sum()), int(o["tot"].sum()))
+    s.close()
+
+
+def test_walk_move_checkpoint_carries_the_normal_distribution_state(port):
+    """the saved second normal of a pair is mover state: a restored sampler must continue bit for bit"""
+    import mcmcpp_b200 as m
+    W, D, S = 256, 3, 5                       # odd S: every update leaves or consumes a saved value
+    iv = 1.0 / (1.0 + np.arange(D))
+    init = np.random.default_rng(1).standard_normal((W, D))
+    lp = port.logp("diag_gauss", iv, init)
+    mk = lambda: m.EnsembleSampler(9, W, D, m.WalkMove(D, 9, m.DiagGaussian(iv), S))
+    a = mk(); a.setInitialWalkerPos(init, lp); assert a.runMCMC(12)
+    b = mk(); b.setInitialWalkerPos(init, lp); assert b.runMCMC(5)
+    blob = b.saveCheckpoint(); b.close()
+    c = mk(); c.loadCheckpoint(blob); assert c.runMCMC(7)
+    pa, la = a.getWalkerState(); pc, lc = c.getWalkerState()
+    assert np.array_equal(pa, pc) and np.array_equal(la, lc)
+    a.close(); c.close()
