@@ -3,6 +3,7 @@
  * (test/sequential/SkewedGaussian/StretchMove/src/main.cpp:22-80) as a user of the drop-in headers: a USER-defined
  * Calculator (not one of the library's built-ins) given a __host__ __device__ calcLogPostProb, the reference's class
  * names and call sequence, kernels instantiated in this translation unit.
+ * `--mover de|walk` plugs MCMC::Mover::DifferentialEvolution / WalkMove into the same sampler template.
  * Prints acceptance counts, means and covariance; `--dump N` prints walker 0 of the last stored step in hex floats so
  * tests can compare with the oracle bit for bit.
  */
@@ -33,16 +34,22 @@ using namespace MCMC;
 int main(int argc, char** argv)
 {
     typedef Mover::StretchMove<double, UserSkewedGaussian<double> > Walker;
+    typedef Mover::DifferentialEvolution<double, UserSkewedGaussian<double> > DeWalker;      /* --mover de */
+    typedef Mover::WalkMove<double, UserSkewedGaussian<double> > WalkWalker;                 /* --mover walk [--points S] */
     const int runNumber = 0;
     int numWalkers = 320, numSteps = 2000, slicing = 3, threads = 0;
     const int numParams = 2;
     const double eps = 0.13;
     bool dump = false;
+    const char* moverName = "stretch";
+    int points = 3;
     for (int i = 1; i < argc; ++i) {
         if (!std::strcmp(argv[i], "--walkers") && i + 1 < argc) numWalkers = std::atoi(argv[++i]);
         else if (!std::strcmp(argv[i], "--steps") && i + 1 < argc) numSteps = std::atoi(argv[++i]);
         else if (!std::strcmp(argv[i], "--slicing") && i + 1 < argc) slicing = std::atoi(argv[++i]);
         else if (!std::strcmp(argv[i], "--threads") && i + 1 < argc) threads = std::atoi(argv[++i]);
+        else if (!std::strcmp(argv[i], "--mover") && i + 1 < argc) moverName = argv[++i];
+        else if (!std::strcmp(argv[i], "--points") && i + 1 < argc) points = std::atoi(argv[++i]);
         else if (!std::strcmp(argv[i], "--dump")) dump = true;
     }
     UserSkewedGaussian<double> likelihood(eps);
@@ -80,7 +87,17 @@ int main(int argc, char** argv)
         last[0] = (*lastStep)[0]; last[1] = (*lastStep)[1];
         std::printf("fraction %.12f\n", sampler.getAcceptanceFraction());
     };
-    if (threads > 0) {
+    if (!std::strcmp(moverName, "de")) {
+        DeWalker deMover(numParams, runNumber, likelihood);
+        EnsembleSampler<double, DeWalker> sampler(runNumber, numWalkers, numParams, deMover);
+        if (slicing > 1) sampler.setSlicingMode(true, slicing);
+        analyse(sampler);
+    } else if (!std::strcmp(moverName, "walk")) {
+        WalkWalker walkMover(numParams, runNumber, likelihood, points);
+        EnsembleSampler<double, WalkWalker> sampler(runNumber, numWalkers, numParams, walkMover);
+        if (slicing > 1) sampler.setSlicingMode(true, slicing);
+        analyse(sampler);
+    } else if (threads > 0) {
         ParallelEnsembleSampler<double, Walker> sampler(runNumber, threads, numWalkers, numParams, mover);
         if (slicing > 1) sampler.setSamplingMode(slicing, 0);
         analyse(sampler);

@@ -4,6 +4,8 @@
  *   MCMC::EnsembleSampler            MCMCpp/EnsembleSampler.h:39-197
  *   MCMC::ParallelEnsembleSampler    MCMCpp/ParallelEnsembleSampler.h:78-226
  *   MCMC::Mover::StretchMove         MCMCpp/Movers/StretchMove.h:40-131
+ *   MCMC::Mover::DifferentialEvolution  MCMCpp/Movers/DifferentialEvolution.h:41-153
+ *   MCMC::Mover::WalkMove            MCMCpp/Movers/WalkMove.h:42-197
  *   MCMC::Utility::GwDistribution    MCMCpp/Utility/GwDistribution.h:33-61
  *   MCMC::Utility::NoAction          MCMCpp/Utility/NoAction.h:34-46
  *   MCMC::Chain::ChainStepIterator / ChainPsetIterator (read side, MCMCpp/Chain/ChainStepIterator.h:125,251-272)
@@ -22,6 +24,8 @@
 #include <cstdlib>
 #include "mcmcpp_b200/capi.h"
 #include "mcmcpp_b200/stretch_kernels.cuh"
+#include "mcmcpp_b200/diff_evo_kernels.cuh"
+#include "mcmcpp_b200/walk_move_kernels.cuh"
 
 namespace MCMC
 {
@@ -111,8 +115,69 @@ public:
     void setPrng(long long s, long long st) { seed = s; stream = st; }
     int getParamCount() const { return paramCount; }
     const Calculator& getCalculator() const { return calc; }
+    /* the kernels for THIS Calculator are instantiated here, in the user's translation unit */
+    int createSampler(mcmcpp_config& cfg, mcmcpp_sampler** out) const
+    {
+        Calculator c = calc;
+        return mcmcpp_sampler_create(&cfg, &Device::HalfStepLauncher<Calculator>::launch, &c, sizeof(Calculator), out);
+    }
 private:
     int paramCount;
+    long long seed, stream;
+    Calculator calc;
+};
+
+/* MCMCpp/Movers/DifferentialEvolution.h:41-153.  The number of draws per update varies (the second partner is redrawn
+ * until it differs, :117-120), so this mover always runs on one pcg64 stream per walker, whichever front-end holds it. */
+template <class ParamType, class Calculator>
+class DifferentialEvolution
+{
+public:
+    typedef Calculator CalculatorType;
+    typedef Utility::GwDistribution<ParamType, 2, 1> DistributionType;      /* unused by this mover */
+    DifferentialEvolution(int numParams, long long prngInit, const Calculator& orig)
+        : paramCount(numParams), seed(prngInit), stream(0), calc(orig),
+          gamma(2.38 / std::sqrt(2.0 * static_cast<ParamType>(numParams))), smallRandLowEdge(-1.0e-4), smallRandWidth(2.0e-4) {}
+    void overrideGamma(ParamType newGamma) { gamma = newGamma; }                                            /* :88 */
+    void overrideRandBounds(ParamType newRand) { smallRandLowEdge = -newRand; smallRandWidth = 2 * newRand; }   /* :96 */
+    void setPrng(long long s, long long st) { seed = s; stream = st; }
+    int getParamCount() const { return paramCount; }
+    const Calculator& getCalculator() const { return calc; }
+    int createSampler(mcmcpp_config& cfg, mcmcpp_sampler** out) const
+    {
+        Device::DiffEvoBlob<Calculator> blob = {calc, {gamma, smallRandLowEdge, smallRandWidth}};
+        cfg.rng_mode = MCMCPP_RNG_PER_WALKER;
+        return mcmcpp_sampler_create(&cfg, &Device::DiffEvoLauncher<Calculator>::launch, &blob, sizeof(blob), out);
+    }
+private:
+    int paramCount;
+    long long seed, stream;
+    Calculator calc;
+    ParamType gamma, smallRandLowEdge, smallRandWidth;
+};
+
+/* MCMCpp/Movers/WalkMove.h:42-197.  Per-walker streams only (selection sampling draws a variable number of uniforms);
+ * the saved second value of std::normal_distribution is per-walker state kept by the runtime (mover_state_doubles). */
+template <class ParamType, class Calculator>
+class WalkMove
+{
+public:
+    typedef Calculator CalculatorType;
+    typedef Utility::GwDistribution<ParamType, 2, 1> DistributionType;      /* unused by this mover */
+    WalkMove(int numParams, long long prngInit, const Calculator& orig, int numSamples)
+        : paramCount(numParams), numPoints(numSamples), seed(prngInit), stream(0), calc(orig) {}
+    void setPrng(long long s, long long st) { seed = s; stream = st; }
+    int getParamCount() const { return paramCount; }
+    const Calculator& getCalculator() const { return calc; }
+    int createSampler(mcmcpp_config& cfg, mcmcpp_sampler** out) const
+    {
+        Device::WalkMoveBlob<Calculator> blob = {calc, numPoints};
+        cfg.rng_mode = MCMCPP_RNG_PER_WALKER;
+        cfg.mover_state_doubles = 2;
+        return mcmcpp_sampler_create(&cfg, &Device::WalkMoveLauncher<Calculator>::launch, &blob, sizeof(blob), out);
+    }
+private:
+    int paramCount, numPoints;
     long long seed, stream;
     Calculator calc;
 };
@@ -152,10 +217,8 @@ public:
         cfg.device = 0; cfg.rank = 0; cfg.world = 1; cfg.shard_mode = MCMCPP_SHARD_NONE; cfg.trace_updates = 0;
         cfg.max_chain_bytes = maxChainSizeBytes; cfg.mover_state_doubles = 0;
         if (const char* dev = std::getenv("MCMCPP_B200_DEVICE")) cfg.device = std::atoi(dev);
-        Calculator calc = moveProposer.getCalculator();
-        /* the kernels for THIS Calculator are instantiated here, in the user's translation unit */
-        checkStatus(mcmcpp_sampler_create(&cfg, &Device::HalfStepLauncher<Calculator>::launch, &calc, sizeof(Calculator), &handle),
-                    "EnsembleSampler()");
+        /* the mover picks its launcher (and, for movers with a variable draw count, per-walker streams) */
+        checkStatus(moveProposer.createSampler(cfg, &handle), "EnsembleSampler()");
     }
     ~DeviceSamplerBase() { mcmcpp_sampler_destroy(handle); }
     DeviceSamplerBase(const DeviceSamplerBase&) = delete;

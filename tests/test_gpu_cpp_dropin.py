@@ -56,3 +56,29 @@ def test_cpp_dropin_statistics():
     # long run: covariance of the target (analytic truth quoted in test/sequential/SkewedGaussian/MH/src/main.cpp:74)
     *_, cov, out = run_example("--walkers", 320, "--steps", 4000, "--slicing", 5)
     assert abs(cov[0] - 1.13) < 0.02 and abs(cov[1] - 0.435) < 0.01 and abs(cov[2] - 0.2825) < 0.006, out
+
+
+def test_cpp_dropin_differential_evolution_is_bit_exact(port):
+    """MCMC::Mover::DifferentialEvolution<double, UserCalc> in the sampler template (DifferentialEvolution.h:57): one
+    stream per walker, every draw, decision and stored row equal to the oracle's."""
+    W, steps = 320, 150
+    acc, tot, stored, last, cov, out = run_example("--walkers", W, "--steps", steps, "--slicing", 1, "--mover", "de", "--dump")
+    init = example_init(W)
+    lp = port.logp("skewed_gauss_2d", [0.13], init)
+    o = port.run_de("skewed_gauss_2d", [0.13], init, lp, steps, seed=0, per_walker=True)
+    assert (acc, tot) == (int(o["acc"].sum()), int(o["tot"].sum()))
+    assert stored == steps + 1 - 20 and last == o["chain"][-1, 0].tolist()
+
+
+def test_cpp_dropin_walk_move(port):
+    """MCMC::Mover::WalkMove<double, UserCalc>(numParams, prngInit, calc, numSamples) (WalkMove.h:59): decisions equal
+    to the oracle's, positions within the tolerance tier (the normals go through log(); a last-bit difference there is
+    amplified by every later proposal that uses the row -- each is a sum over S partners -- so the run is kept short
+    and the bound is 1e-10)."""
+    W, steps, S = 64, 30, 3
+    acc, tot, stored, last, cov, out = run_example("--walkers", W, "--steps", steps, "--slicing", 1, "--mover", "walk", "--points", S, "--dump")
+    init = example_init(W)
+    lp = port.logp("skewed_gauss_2d", [0.13], init)
+    o = port.run_walk("skewed_gauss_2d", [0.13], init, lp, steps, S, seed=0, per_walker=True)
+    assert (acc, tot) == (int(o["acc"].sum()), int(o["tot"].sum()))
+    assert np.allclose(last, o["chain"][-1, 0], rtol=1e-10, atol=1e-10 * np.abs(o["chain"]).max())
