@@ -31,6 +31,19 @@ private:
 
 using namespace MCMC;
 
+/* a PostStepAction (concept: EnsembleSampler.h:52-56): counts its calls and remembers the range it was last shown */
+struct CountingAction
+{
+    typedef Chain::ChainStepIterator<double> StepItt;
+    long long calls = 0, lastSteps = 0;
+    double lastFirstCell = 0.0;
+    void performAction(const StepItt& start, const StepItt& end)
+    {
+        ++calls; lastSteps = 0;
+        for (StepItt itt = start; itt != end; ++itt) { ++lastSteps; lastFirstCell = (*itt)[0]; }
+    }
+};
+
 int main(int argc, char** argv)
 {
     typedef Mover::StretchMove<double, UserSkewedGaussian<double> > Walker;
@@ -40,7 +53,7 @@ int main(int argc, char** argv)
     int numWalkers = 320, numSteps = 2000, slicing = 3, threads = 0;
     const int numParams = 2;
     const double eps = 0.13;
-    bool dump = false;
+    bool dump = false, withAction = false;
     const char* moverName = "stretch";
     int points = 3;
     for (int i = 1; i < argc; ++i) {
@@ -51,6 +64,7 @@ int main(int argc, char** argv)
         else if (!std::strcmp(argv[i], "--mover") && i + 1 < argc) moverName = argv[++i];
         else if (!std::strcmp(argv[i], "--points") && i + 1 < argc) points = std::atoi(argv[++i]);
         else if (!std::strcmp(argv[i], "--dump")) dump = true;
+        else if (!std::strcmp(argv[i], "--action")) withAction = true;
     }
     UserSkewedGaussian<double> likelihood(eps);
     Walker mover(numParams, runNumber, likelihood);
@@ -87,7 +101,13 @@ int main(int argc, char** argv)
         last[0] = (*lastStep)[0]; last[1] = (*lastStep)[1];
         std::printf("fraction %.12f\n", sampler.getAcceptanceFraction());
     };
-    if (!std::strcmp(moverName, "de")) {
+    if (withAction) {
+        CountingAction action;
+        EnsembleSampler<double, Walker, CountingAction> sampler(runNumber, numWalkers, numParams, mover, 2147483648ULL, &action);
+        if (slicing > 1) sampler.setSlicingMode(true, slicing);
+        analyse(sampler);
+        std::printf("action calls %lld last_range %lld last_first %a\n", action.calls, action.lastSteps, action.lastFirstCell);
+    } else if (!std::strcmp(moverName, "de")) {
         DeWalker deMover(numParams, runNumber, likelihood);
         EnsembleSampler<double, DeWalker> sampler(runNumber, numWalkers, numParams, deMover);
         if (slicing > 1) sampler.setSlicingMode(true, slicing);

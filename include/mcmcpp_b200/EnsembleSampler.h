@@ -231,11 +231,25 @@ public:
     void storeCurrentWalkerPositions() { checkStatus(mcmcpp_sampler_store_current(handle), "storeCurrentWalkerPositions"); }
     bool runMCMC(int numSteps)
     {
-        int rc = mcmcpp_sampler_run(handle, numSteps, nullptr);
-        checkStatus(rc, "runMCMC");
-        /* end-of-call hook over the rows stored so far; the reference calls it once per step (EnsembleSampler.h:356-359) */
-        if (stepAction != nullptr) stepAction->performAction(getStepIttBegin(), getStepIttEnd());
-        return rc != MCMCPP_CHAIN_FULL;
+        if (stepAction == nullptr) {
+            int rc = mcmcpp_sampler_run(handle, numSteps, nullptr);
+            checkStatus(rc, "runMCMC");
+            return rc != MCMCPP_CHAIN_FULL;
+        }
+        /* With an action the reference calls it after EVERY performStep, saved or not, before the step just written is
+         * counted (EnsembleSampler.h:289-308,356-359): the range it sees ends at the previous stored step.  Same here,
+         * one stored step per device call so that the host rows are current when the action runs. */
+        for (int i = 0; i < numSteps; ++i) {
+            const long long before = cellsStored();
+            int rc = mcmcpp_sampler_run(handle, 1, nullptr);
+            checkStatus(rc, "runMCMC");
+            ParamType* first = rows();
+            for (int j = 0; j < (subSampling ? subSamplingInterval : 1); ++j)
+                stepAction->performAction(StepItt(first, (long long)numWalkers * numParams),
+                                          StepItt(first + before, (long long)numWalkers * numParams));
+            if (rc == MCMCPP_CHAIN_FULL) return false;
+        }
+        return true;
     }
     void reset() { checkStatus(mcmcpp_sampler_reset(handle), "reset"); }
     ParamType getAcceptanceFraction()
@@ -278,6 +292,7 @@ protected:
     void setSubSampling(bool use, int interval)
     {
         assert(interval > 0);
+        subSampling = use; subSamplingInterval = interval;
         checkStatus(mcmcpp_sampler_set_slicing(handle, use ? 1 : 0, interval), "setSlicingMode");
     }
     ParamType* rows()
@@ -295,6 +310,8 @@ protected:
     PostStepAction* stepAction;
     Mover moveProposer;
     int numParams, numWalkers;
+    bool subSampling = false;
+    int subSamplingInterval = 1;
     mcmcpp_sampler* handle;
 };
 }

@@ -82,3 +82,17 @@ def test_cpp_dropin_walk_move(port):
     o = port.run_walk("skewed_gauss_2d", [0.13], init, lp, steps, S, seed=0, per_walker=True)
     assert (acc, tot) == (int(o["acc"].sum()), int(o["tot"].sum()))
     assert np.allclose(last, o["chain"][-1, 0], rtol=1e-10, atol=1e-10 * np.abs(o["chain"]).max())
+
+
+def test_cpp_dropin_post_step_action_call_pattern(port):
+    """PostStepAction as the reference drives it (EnsembleSampler.h:289-308,356-359): performAction after every
+    performStep, saved or not, with the range of steps counted so far -- the step just written is not in it yet."""
+    W, steps, k = 320, 40, 3
+    acc, tot, stored, last, cov, out = run_example("--walkers", W, "--steps", steps, "--slicing", k, "--action", "--dump")
+    plain = run_example("--walkers", W, "--steps", steps, "--slicing", k, "--dump")
+    assert (acc, tot, stored, last) == plain[:4]                       # one device call per stored step changes nothing
+    calls, rng, first = re.search(r"action calls (\d+) last_range (\d+) last_first (\S+)", out).groups()
+    init = example_init(W)
+    o = port.run("skewed_gauss_2d", [0.13], init, port.logp("skewed_gauss_2d", [0.13], init), steps, interval=k, seed=0)
+    assert int(calls) == steps * k and int(rng) == steps               # initial row + (steps - 1) counted steps
+    assert float.fromhex(first) == o["chain"][steps - 2, 0, 0]
