@@ -66,8 +66,9 @@ __host__ __device__ inline int denseStride(int Dp) { return denseStrideC(Dp); }
 enum { DenseBatch = DenseGroupThreads / DenseTileRows };      /* 8 tiles = 256 walkers per draw phase */
 
 template <int NB, bool TRACE>
-__global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken)
+__global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken, long long* tl)
 {
+#define DENSE_TL(slot) do { if (tl && blockIdx.x == 0 && tid == 0) { long long tNow; asm volatile("mov.u64 %0, %%clock64;" : "=l"(tNow) :: "memory"); tl[((group * 16 + rnd0 + bt) * 8) + (slot)] = tNow; } } while (0)
     constexpr int Dp = 8 * NB;
     constexpr int NBH = (NB + 1) / 2;                         /* column blocks per warp: warps 0-3 take [0,NBH), 4-7 the rest */
     constexpr int GroupWarps = DenseGroupThreads / 32;
@@ -144,6 +145,7 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
             const int b0 = bt * DenseTileRows;                /* this tile's draws in the batch arrays */
             /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  All loads of the warp's rows
              * are issued before the first use so one L2/HBM latency covers the whole tile, not one per row. */
+            DENSE_TL(0);
             if (has) {
                 constexpr int RowsPerWarp = DenseTileRows / GroupWarps;
                 constexpr int KCH = (Dp + 31) / 32;
@@ -180,7 +182,9 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                 }
             }
             groupSync(group);
+            DENSE_TL(1);
             if (useToken) tokenWait(group);
+            DENSE_TL(2);
             /* (c) Y = Xs * Ps on the FP64 tensor cores; warp owns 8 rows x its half of the column blocks */
             if (has) {
                 const int rg = warp & 3, ch = warp >> 2;
@@ -191,6 +195,7 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                 for (int nb = 0; nb < NBH; ++nb) { acc[nb][0] = 0.0; acc[nb][1] = 0.0; }
                 const int g = lane >> 2, t = lane & 3;
                 const double* arow = Xs + (size_t)(rg * 8 + g) * stride + t;
+                DENSE_TL(6);
                 const double* bcol = Ps + (size_t)t * stride + g + nb0 * 8;
 #pragma unroll 2
                 for (int k = 0; k < Dp; k += 4) {
@@ -200,34 +205,49 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                     for (int nb = 0; nb < NBH; ++nb)
                         if (nb < cnt) dmma884(acc[nb][0], acc[nb][1], av, bk[nb * 8]);
                 }
+                DENSE_TL(7);
                 /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols (nb0+nb)*8 + 2t, +1 of row g */
                 const double* xrow = Xs + (size_t)(rg * 8 + g) * stride + nb0 * 8 + 2 * t;
-                double q = 0.0;
+                double q = 0.0, q1 = 0.0;                     /* two chains: the dependent FMAs queue behind the other warp's DMMAs */
 #pragma unroll
                 for (int nb = 0; nb < NBH; ++nb) {
                     if (nb < cnt) {
                         const double2 xv = *reinterpret_cast<const double2*>(xrow + nb * 8);
                         q = fma(xv.x, acc[nb][0], q);
-                        q = fma(xv.y, acc[nb][1], q);
+                        q1 = fma(xv.y, acc[nb][1], q1);
                     }
                 }
+                q += q1;
                 q += __shfl_xor_sync(0xffffffffu, q, 1);
                 q += __shfl_xor_sync(0xffffffffu, q, 2);
                 if (t == 0) sQ[ch * DenseTileRows + rg * 8 + g] = q;
             }
+            /* (d) Metropolis decisions while this group still holds the token: the few dependent FP64 adds would
+             * otherwise queue behind the other group's DMMAs (same pipe) and stretch the commit from 0.7 to 3.4 us.
+             * Lane r of warp 0 decides row r; sQ[r] <- new log-prob, accept flag over the second half. */
+            groupSync(group);
+            int* sAcc = reinterpret_cast<int*>(sQ + DenseTileRows);
+            if (has && warp == 0) {
+                const double newp = -0.5 * (sQ[lane] + sQ[DenseTileRows + lane]);
+                const double diff = __dsub_rn(__dadd_rn(bS[b0 + lane], newp), sOld[lane]);
+                const bool accepted = bE[b0 + lane] < diff;
+                __syncwarp();
+                sQ[lane] = newp;
+                sAcc[lane] = accepted ? 1 : 0;
+            }
+            DENSE_TL(3);
             if (useToken && !(group == 1 && lastRound)) tokenPass(group); /* the last pass would have nobody waiting for it */
             groupSync(group);
+            DENSE_TL(4);
             if (!has) continue;
-            /* (d)+(e) Metropolis decision and commit: each warp decides its own rows (every lane computes the same
-             * few adds), then writes the accepted rows (and the chain row of every walker on stored steps) */
+            /* (e) commit: each warp writes its accepted rows (and the chain row of every walker on stored steps) */
             for (int r = warp; r < DenseTileRows; r += GroupWarps) {
                 const int i = row0 + r;
                 if (i >= a.slot_count) continue;
                 const int slot = a.slot_begin + i;
                 const int w = a.half * a.K + slot;
-                const double newp = -0.5 * (sQ[r] + sQ[DenseTileRows + r]);
-                const double diff = __dsub_rn(__dadd_rn(bS[b0 + r], newp), sOld[r]);
-                const bool accepted = bE[b0 + r] < diff;
+                const double newp = sQ[r];
+                const bool accepted = sAcc[r] != 0;
                 const double* xr = Xs + (size_t)r * stride;
                 double* own = a.pos + (size_t)w * D;
                 if (a.chain_row) {
@@ -240,17 +260,28 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                     if (TRACE) {
                         if (slot < a.trace_rows) {
                             mcmcpp_trace tr;
-                            tr.j = bJ[b0 + r]; tr.accept = accepted ? 1 : 0; tr.z = bZ[b0 + r]; tr.e = bE[b0 + r]; tr.newp = newp; tr.diff = diff;
+                            tr.j = bJ[b0 + r]; tr.accept = accepted ? 1 : 0; tr.z = bZ[b0 + r]; tr.e = bE[b0 + r]; tr.newp = newp;
+                            tr.diff = __dsub_rn(__dadd_rn(bS[b0 + r], newp), sOld[r]);
                             a.trace[slot] = tr;
                         }
                     }
                 }
             }
             groupSync(group);                                 /* Xs, sQ, sOld free for the next tile */
+            DENSE_TL(5);
         }
     }
     if (!pReady) mbarWait(smemAddr(&pBar), 0);                /* never exit with a bulk copy in flight */
     if (lane == 0 && myAccepted) atomicAdd(a.accept_slots + blockIdx.x, myAccepted);
+}
+
+/* MCMCPP_B200_DENSE_TIMELINE=1: CTA 0 records clock64() at the phase boundaries of each of its tiles (tuning aid) */
+long long* denseTimelineBuf = nullptr;
+long long* denseTimeline()
+{
+    static const bool on = [] { const char* e = getenv("MCMCPP_B200_DENSE_TIMELINE"); return e && e[0] == '1'; }();
+    if (on && !denseTimelineBuf) { cudaMalloc(&denseTimelineBuf, 2 * 16 * 8 * sizeof(long long)); cudaMemset(denseTimelineBuf, 0, 2 * 16 * 8 * sizeof(long long)); }
+    return on ? denseTimelineBuf : nullptr;
 }
 
 struct DenseCalc
@@ -273,18 +304,19 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     static const int useToken = [] { const char* e = getenv("MCMCPP_B200_DENSE_TOKEN"); return (e && e[0] == '0') ? 0 : 1; }();
     /* opt in to exactly what this shape needs (the kernel also has a few bytes of static shared memory) */
     static size_t optedIn[2] = {0, 0};
+    long long* tl = denseTimeline();
     if (a.trace) {
         if (smem > optedIn[1]) {
             if (cudaFuncSetAttribute(denseGaussHalfStep<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
             optedIn[1] = smem;
         }
-        denseGaussHalfStep<NB, true><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken);
+        denseGaussHalfStep<NB, true><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken, tl);
     } else {
         if (smem > optedIn[0]) {
             if (cudaFuncSetAttribute(denseGaussHalfStep<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
             optedIn[0] = smem;
         }
-        denseGaussHalfStep<NB, false><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken);
+        denseGaussHalfStep<NB, false><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken, tl);
     }
     return launchStatus();
 }
@@ -305,6 +337,12 @@ int denseLaunch(const mcmcpp_halfstep_args* args, const void* calculator, void* 
 }
 
 }  // namespace
+
+extern "C" int mcmcpp_dense_timeline(long long* out256)
+{
+    if (!denseTimelineBuf) return MCMCPP_ERR_STATE;
+    return cudaMemcpy(out256, denseTimelineBuf, 2 * 16 * 8 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? MCMCPP_OK : MCMCPP_ERR_CUDA;
+}
 
 /* Tensor-core path for 8 < D <= 128 (unless MCMCPP_B200_DENSE_GENERIC=1 asks for the reference-order generic path). */
 bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator)
