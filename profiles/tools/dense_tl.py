@@ -1,6 +1,6 @@
 import os, sys, ctypes as C
 os.environ["MCMCPP_B200_DENSE_TIMELINE"] = "1"
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 import mcmcpp_b200 as m
 from mcmcpp_b200 import _capi
