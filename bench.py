@@ -66,8 +66,9 @@ def target_params(kind, D):
 
 
 def algorithmic_bytes_per_update(D, stored):
-    """own row read + partner row read + own row write (+ chain row) + logp read/write."""
-    return 8 * D * (3 + (1 if stored else 0)) + 16
+    """own row read + partner row read + own row write (+ chain row) + logp read/write.
+    `stored` = fraction of the steps whose row goes to the chain (0, 1, or 1/N with subsampling)."""
+    return 8 * D * (3 + float(stored)) + 16
 
 
 def measured_peaks():
@@ -261,11 +262,23 @@ def gpu_arm(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    every = args.store_every
+    if every > 0 and (world > 1 or args.steps % every):
+        raise SystemExit("--store-every N needs one GPU and --steps a multiple of N")
+    warm = max(3, args.warmup)
+    # runMCMC counts STORED steps: with subsampling each is N - 1 unsaved ensemble steps + 1 saved (EnsembleSampler.h:297-308)
+    calls = (lambda k: k // every) if every > 0 else (lambda k: k)
+    if every > 0:
+        warm = every * max(1, warm // every)
+    chain_bytes = (calls(warm) + calls(args.steps) + 2) * W * D * 8 if every > 0 else 0
+
     def new_sampler():
         mover_cls = m.DifferentialEvolution if args.mover == "de" else m.StretchMove
-        s = m.EnsembleSampler(0, W, D, mover_cls(D, 0, make_calc(m, kind, params, rank, world)), maxChainSizeBytes=0,
+        s = m.EnsembleSampler(0, W, D, mover_cls(D, 0, make_calc(m, kind, params, rank, world)), maxChainSizeBytes=chain_bytes,
                               rngMode=rng_mode, device=local, rank=rank, world=world, shardMode=shard)
         parallel.connect(s)
+        if every > 0:
+            s.setSlicingMode(True, every)
         return s
 
     pos, aux = device_inputs(torch, kind, W, D, params, device)
@@ -273,12 +286,12 @@ def gpu_arm(args):
     # ---- value: inputs resident in HBM, K steps timed with CUDA events on the sampler's stream ------------
     s = new_sampler()
     s.setInitialWalkerPosDevice(pos.data_ptr(), aux.data_ptr())
-    s.runMCMC(max(3, args.warmup))
+    s.runMCMC(calls(warm))
     launches0 = s.getLaunchCount()
     barrier()
     with ClockSampler(local) as clocks:
         wall0 = time.perf_counter()
-        s.runMCMC(args.steps)
+        assert s.runMCMC(calls(args.steps)), "chain byte cap reached inside the timed region"
         barrier()
         wall = time.perf_counter() - wall0
     ms = torch.tensor([s.lastDeviceMs], dtype=torch.float64, device=device)
@@ -305,7 +318,7 @@ def gpu_arm(args):
     barrier()
     t0 = time.perf_counter()
     s.setInitialWalkerPosLocal(host_pos.data_ptr(), host_aux.data_ptr())
-    ok = s.runMCMC(args.steps)
+    ok = s.runMCMC(calls(args.steps))
     s.getWalkerStateLocalInto(host_pos.data_ptr(), host_aux.data_ptr())
     e2e_acc, e2e_tot = s._counts()
     barrier()
@@ -333,7 +346,8 @@ def gpu_arm(args):
     if shard == "dim":
         b_, e_ = parallel.dim_slice(D, rank, world)
         Dl = e_ - b_                                # this rank streams its columns of every walker
-    alg_bytes = per_launch_updates * algorithmic_bytes_per_update(Dl, False)
+    stored_frac = 1.0 / every if every > 0 else 0.0
+    alg_bytes = per_launch_updates * algorithmic_bytes_per_update(Dl, stored_frac)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -343,7 +357,7 @@ def gpu_arm(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "kernel": ("dimShardPartial + dimShardCommit" if shard == "dim" else "stretchHalfStepBulk (TMA)" if (D >= 130 and D % 2 == 0)
                            else "stretchHalfStepWarp" if D > 8 else "stretchHalfStepThread"), "peak_source": peak_src,
-                "algorithmic_bytes_per_update": algorithmic_bytes_per_update(D, False), "updates_per_launch": per_launch_updates,
+                "algorithmic_bytes_per_update": algorithmic_bytes_per_update(D, stored_frac), "updates_per_launch": per_launch_updates,
                 "launch_ms": launch_ms,
                 "note": "launch_ms = CUDA-event time of the timed region / launches" + ("" if world == 1 else " (includes the per-half-step exchange)")}
     if kind == "dense_gauss":
@@ -376,10 +390,12 @@ def gpu_arm(args):
     if world == 1 and not args.no_cpu:
         cpu = cpu_reference_run(args.workload, cpu_steps, 1)
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": desc, "walkers": W, "params": D, "rng": rng_mode, "shard": shard, "chain": "off",
+            "config": {"workload": desc, "walkers": W, "params": D, "rng": rng_mode, "shard": shard,
+                       "chain": "off" if every <= 0 else "every %d-th step stored: device rows -> pinned host chain on a side stream (%d rows of %.1f MB inside the timed region)"
+                                                         % (every, calls(args.steps), W * D * 8 / 1e6),
                        "l2": "inputs (%.1f GB of walker rows) far exceed the 126 MB L2; no flush needed" % (W * D * 8 / 1e9)
                        if W * D * 8 > (1 << 29) else "state fits L2: L2-resident steady state is the workload itself"},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches) * world, "roofline": roofline,
@@ -401,6 +417,7 @@ def main():
     ap.add_argument("--shard", default=None, choices=["allgather", "peer", "dim"])
     ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
     ap.add_argument("--mover", default="stretch", choices=["stretch", "de"], help="de: Mover::DifferentialEvolution (analysis runs; not the BASELINE metric)")
+    ap.add_argument("--store-every", type=int, default=0, help="N > 0: chain on, every N-th step stored (SURVEY s.8(d): C2's second run stores every 100th); single GPU")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.steps <= 0:
