@@ -139,8 +139,12 @@ __device__ __forceinline__ GwConstants gwOf(const mcmcpp_halfstep_args& a)
 }
 
 /* ---- kernel 1: one thread per walker ---------------------------------------------------------- */
+/* D <= 2: 14 CTAs of 128 threads per SM (<= 36 registers) -- 2^19 walkers of a colour are then 1.98 waves on 148 SMs
+ * instead of 2.31 at the 12 CTAs the natural 38 registers allow (a third, mostly empty, wave).
+ * Load order: rng state, own row and log-prob first (independent of the draws); then the partner index alone, the
+ * partner-row load, and only then z and log(1-u) -- ~250 instructions that cover the gather's L2 latency. */
 template <class Calc, int D, bool TRACE>
-__global__ void __launch_bounds__(ThreadKernelThreads) stretchHalfStepThread(const mcmcpp_halfstep_args a, const Calc calcIn)
+__global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 14 : 1)) stretchHalfStepThread(const mcmcpp_halfstep_args a, const Calc calcIn)
 {
     const int i = blockIdx.x * ThreadKernelThreads + threadIdx.x;
     int accepted = 0;
@@ -151,20 +155,28 @@ __global__ void __launch_bounds__(ThreadKernelThreads) stretchHalfStepThread(con
         const int other0 = (1 - a.half) * a.K;
 
         WalkerRng rng = loadRng(a, w);
-        StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
-        storeRng(a, w, rng);
-        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
-
         double cur[D], prop[D];
         double* ownRow = a.pos + (size_t)w * D;
         loadRow<D>(ownRow, cur);
+        const double oldp = a.logp[w];
+        StretchDraws dr;
+        dr.j = drawPartner(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, dr.redraws);
+        /* Programmatic dependent launch: everything above reads what THIS colour's previous launch (two launches back,
+         * complete) wrote; only the partner rows come from the launch right before.  Wait for it here, then let the next
+         * launch start its own preamble on the SM slots this one's last, partly filled wave leaves idle (it reads what
+         * the previous launch wrote, which is complete once this wait has returned). */
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         loadRowReadOnly<D>(partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D, prop);
+        drawScaleAndTest(rng.state, rng.inc, gwOf(a), dr.z, dr.logOneMinusU);
+        storeRng(a, w, rng);
+        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
 #pragma unroll
         for (int d = 0; d < D; ++d) prop[d] = stretchPoint(prop[d], cur[d], dr.z);
 
         const double scaling = __dmul_rn(log(dr.z), (double)(D - 1));
         const double newp = calc.calcLogPostProb(prop);
-        const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
+        const double diff = __dsub_rn(__dadd_rn(scaling, newp), oldp);
         accepted = dr.logOneMinusU < diff ? 1 : 0;
         if (accepted) {
             storeRow<D>(ownRow, prop);
@@ -182,9 +194,10 @@ __global__ void __launch_bounds__(ThreadKernelThreads) stretchHalfStepThread(con
             }
         }
     }
-    /* acceptance counter: one CTA-wide popcount, one plain add per CTA into its own slot */
-    const int blockAccepted = __syncthreads_count(accepted);
-    if (threadIdx.x == 0 && blockAccepted) a.accept_slots[blockIdx.x] += (unsigned long long)blockAccepted;
+    /* acceptance counter: warp popcount, one fire-and-forget RED per warp into the CTA's slot (a CTA-wide count would
+     * park every warp at a barrier until the CTA's slowest gather has come back, then expose a load for the +=) */
+    const unsigned ballot = __ballot_sync(0xffffffffu, accepted != 0);
+    if ((threadIdx.x & 31) == 0 && ballot) atomicAdd(a.accept_slots + blockIdx.x, (unsigned long long)__popc(ballot));
 }
 
 /* ---- kernel 2: one warp per walker ------------------------------------------------------------ */
@@ -489,9 +502,18 @@ int launchThreadKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStre
 {
     const int grid = (a.slot_count + ThreadKernelThreads - 1) / ThreadKernelThreads;
     if (grid > a.max_grid) return MCMCPP_ERR_ARG;
-    if (a.trace) stretchHalfStepThread<Calc, D, true><<<grid, ThreadKernelThreads, 0, stream>>>(a, calc);
-    else stretchHalfStepThread<Calc, D, false><<<grid, ThreadKernelThreads, 0, stream>>>(a, calc);
-    return launchStatus();
+    /* launched as a programmatic dependent of the kernel before it in the stream (see griddepcontrol.wait in the kernel);
+     * MCMCPP_B200_PDL=0 falls back to plain stream order */
+    static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(ThreadKernelThreads); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t rc = a.trace ? cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, true>, a, calc)
+                             : cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, false>, a, calc);
+    return rc == cudaSuccess ? launchStatus() : MCMCPP_ERR_CUDA;
 }
 
 template <class Calc, int NCHUNK>
