@@ -136,6 +136,12 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
             }
         }
         groupSync(group);
+        if (rnd0 == 0) {
+            /* programmatic dependent launch: the P load and the first draws read nothing the launch right before this one
+             * wrote (P is constant, the rng states are this colour's own); rows and log-probs are read from here on */
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        }
         if (!pReady) { mbarWait(smemAddr(&pBar), 0); pReady = true; }
         for (int bt = 0; bt < DenseBatch && rnd0 + bt < rounds; ++bt) {
             const int tile = tileBase + bt * gstep;
@@ -305,18 +311,25 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     /* opt in to exactly what this shape needs (the kernel also has a few bytes of static shared memory) */
     static size_t optedIn[2] = {0, 0};
     long long* tl = denseTimeline();
+    static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(DenseThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
     if (a.trace) {
         if (smem > optedIn[1]) {
             if (cudaFuncSetAttribute(denseGaussHalfStep<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
             optedIn[1] = smem;
         }
-        denseGaussHalfStep<NB, true><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken, tl);
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, true>, a, c.P, useToken, tl) != cudaSuccess) return MCMCPP_ERR_CUDA;
     } else {
         if (smem > optedIn[0]) {
             if (cudaFuncSetAttribute(denseGaussHalfStep<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
             optedIn[0] = smem;
         }
-        denseGaussHalfStep<NB, false><<<grid, DenseThreads, smem, stream>>>(a, c.P, useToken, tl);
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, false>, a, c.P, useToken, tl) != cudaSuccess) return MCMCPP_ERR_CUDA;
     }
     return launchStatus();
 }
