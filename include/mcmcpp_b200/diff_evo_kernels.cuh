@@ -77,7 +77,7 @@ __device__ __forceinline__ double deProposal(double cur, double w1, double w2, d
 }
 
 template <class Calc, int D, bool TRACE>
-__global__ void __launch_bounds__(ThreadKernelThreads) diffEvoThread(const mcmcpp_halfstep_args a, const DiffEvoBlob<Calc> blob)
+__global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 12 : 1)) diffEvoThread(const mcmcpp_halfstep_args a, const DiffEvoBlob<Calc> blob)
 {
     const int i = blockIdx.x * ThreadKernelThreads + threadIdx.x;
     int accepted = 0;
@@ -87,18 +87,22 @@ __global__ void __launch_bounds__(ThreadKernelThreads) diffEvoThread(const mcmcp
         const int w = a.half * a.K + slot;
         const int other0 = (1 - a.half) * a.K;
         WalkerRng rng = loadRng(a, w);
+        double cur[D], w1[D], w2[D], prop[D];
+        double* ownRow = a.pos + (size_t)w * D;
+        loadRow<D>(ownRow, cur);                              /* own row, log-prob: independent of the draws, issued first */
+        const double oldp = a.logp[w];
         const int ind1 = deBounded(rng.state, rng.inc, a);
         int ind2;
         do { ind2 = deBounded(rng.state, rng.inc, a); } while (ind2 == ind1);
-        double cur[D], w1[D], w2[D], prop[D];
-        double* ownRow = a.pos + (size_t)w * D;
-        loadRow<D>(ownRow, cur);
+        /* programmatic dependent launch (see stretchHalfStepThread): only the partner rows come from the launch before */
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         loadRowReadOnly<D>(partnerBase(a, ind1) + (size_t)(other0 + ind1) * D, w1);
         loadRowReadOnly<D>(partnerBase(a, ind2) + (size_t)(other0 + ind2) * D, w2);
 #pragma unroll
         for (int d = 0; d < D; ++d) prop[d] = deProposal(cur[d], w1[d], w2[d], unitFromU64(pcg64Next(rng.state, rng.inc)), blob.mv);
         const double newp = calc.calcLogPostProb(prop);
-        const double diff = __dsub_rn(newp, a.logp[w]);
+        const double diff = __dsub_rn(newp, oldp);
         const double e = log(1.0 - unitFromU64(pcg64Next(rng.state, rng.inc)));
         reinterpret_cast<ulonglong2*>(a.rng_state)[w] = make_ulonglong2(rng.state.lo, rng.state.hi);
         accepted = diff > e ? 1 : 0;
@@ -115,8 +119,8 @@ __global__ void __launch_bounds__(ThreadKernelThreads) diffEvoThread(const mcmcp
             }
         }
     }
-    const int blockAccepted = __syncthreads_count(accepted);
-    if (threadIdx.x == 0 && blockAccepted) a.accept_slots[blockIdx.x] += (unsigned long long)blockAccepted;
+    const unsigned ballot = __ballot_sync(0xffffffffu, accepted != 0);
+    if ((threadIdx.x & 31) == 0 && ballot) atomicAdd(a.accept_slots + blockIdx.x, (unsigned long long)__popc(ballot));
 }
 
 enum { DiffEvoWarps = 4 };
@@ -199,9 +203,16 @@ struct DiffEvoLauncher
     static int thread(const mcmcpp_halfstep_args& a, const DiffEvoBlob<Calc>& blob, cudaStream_t stream)
     {
         const int grid = (a.slot_count + ThreadKernelThreads - 1) / ThreadKernelThreads;
-        if (a.trace) diffEvoThread<Calc, D, true><<<grid, ThreadKernelThreads, 0, stream>>>(a, blob);
-        else diffEvoThread<Calc, D, false><<<grid, ThreadKernelThreads, 0, stream>>>(a, blob);
-        return launchStatus();
+        static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(ThreadKernelThreads); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+        cudaError_t rc = a.trace ? cudaLaunchKernelEx(&cfg, diffEvoThread<Calc, D, true>, a, blob)
+                                 : cudaLaunchKernelEx(&cfg, diffEvoThread<Calc, D, false>, a, blob);
+        return rc == cudaSuccess ? launchStatus() : MCMCPP_ERR_CUDA;
     }
 
     static int launch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)
