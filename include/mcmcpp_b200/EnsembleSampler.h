@@ -119,7 +119,11 @@ public:
     int createSampler(mcmcpp_config& cfg, mcmcpp_sampler** out) const
     {
         Calculator c = calc;
-        return mcmcpp_sampler_create(&cfg, &Device::HalfStepLauncher<Calculator>::launch, &c, sizeof(Calculator), out);
+        int rc = mcmcpp_sampler_create(&cfg, &Device::HalfStepLauncher<Calculator>::launch, &c, sizeof(Calculator), out);
+        /* small ensembles (the reference's own test sizes): the whole runMCMC loop in one launch */
+        if (rc == MCMCPP_OK && cfg.num_params <= Device::ThreadKernelMaxDim)
+            rc = mcmcpp_sampler_set_fused_launcher(*out, &Device::FusedLauncher<Calculator>::launch);
+        return rc;
     }
 private:
     int paramCount;

@@ -153,11 +153,27 @@ typedef struct {
 
 typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);
 
+/* Small ensembles (at most 1024 walkers per colour, at most 8 parameters): the loop of EnsembleSampler::runMCMC
+ * (EnsembleSampler.h:284-310) -- `stored_steps` x (`interval` - 1 unsaved ensemble steps + 1 saved) -- in ONE launch of
+ * one CTA, walker state in shared memory, a CTA barrier where the reference has its colour boundary.  At 32..2048
+ * walkers a half-step is a microsecond of arithmetic behind 3 us of launch latency; same arithmetic, same results. */
+typedef struct mcmcpp_fused_args {
+    mcmcpp_halfstep_args base;  /* as for a half-step; half, chain_row and trace are not used */
+    int32_t stored_steps;       /* stored steps to make */
+    int32_t interval;           /* ensemble steps per stored step */
+    double* chain_rows;         /* [stored_steps][W][D] device rows to fill, or NULL (chain off / full) */
+} mcmcpp_fused_args;
+typedef int (*mcmcpp_fused_fn)(const mcmcpp_fused_args* args, const void* calculator, void* cuda_stream);
+
 /* ---- life cycle: EnsembleSampler ctor/dtor (EnsembleSampler.h:199-218,72) -------------------- */
 /* `calculator` is copied by value (calc_bytes); it must be trivially copyable and any pointers in
  * it must be device pointers (the Calculator "view" convention of targets.h). */
 int mcmcpp_sampler_create(const mcmcpp_config* cfg, mcmcpp_halfstep_fn launcher, const void* calculator,
                           size_t calc_bytes, mcmcpp_sampler** out);
+/* Optional: the fused small-ensemble launcher for the same mover and Calculator (NULL removes it).  The runtime uses it
+ * when the ensemble fits (see mcmcpp_fused_args), one GPU, no trace, no step action and no on-the-fly covariance;
+ * MCMCPP_B200_FUSED=0 in the environment keeps the launch-per-colour path. */
+int mcmcpp_sampler_set_fused_launcher(mcmcpp_sampler* s, mcmcpp_fused_fn launcher);
 /* Built-in Calculator: `params` (host) is uploaded and viewed by the functor. */
 int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, const double* params, size_t num_params_values,
                                   mcmcpp_sampler** out);

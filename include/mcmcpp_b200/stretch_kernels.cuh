@@ -579,6 +579,130 @@ inline bool bulkKernelDisabled()
     return off;
 }
 
+/* ---- small ensembles: the whole runMCMC loop in one launch (mcmcpp_fused_args) ------------------------------------
+ * One CTA; thread t owns red walker t and black walker K + t (their rng states in registers for the whole call); the
+ * ensemble lives in shared memory; __syncthreads() is the colour boundary.  Per update exactly the arithmetic of
+ * stretchHalfStepThread, so chains, counters and rng states are the ones the launch-per-colour path produces. */
+enum { FusedMaxThreads = 1024 };
+
+template <class Calc, int D>
+__global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedSmall(const mcmcpp_fused_args f, const Calc calcIn)
+{
+    extern __shared__ double fusedSmem[];
+    const mcmcpp_halfstep_args& a = f.base;
+    const int K = a.K, W = 2 * K, t = threadIdx.x;
+    double* sPos = fusedSmem;                                 /* [W][D] */
+    double* sLogp = fusedSmem + (size_t)W * D;                /* [W] */
+    for (int idx = t; idx < W * D; idx += blockDim.x) sPos[idx] = a.pos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) sLogp[idx] = a.logp[idx];
+    Calc calc = calcIn;
+    const bool live = t < K;
+    WalkerRng rng[2];
+    if (live) { rng[0] = loadRng(a, t); rng[1] = loadRng(a, K + t); }
+    Affine128 skip;
+    skip.mult.lo = a.skip_mult[0]; skip.mult.hi = a.skip_mult[1];
+    skip.plus.lo = a.skip_plus[0]; skip.plus.hi = a.skip_plus[1];
+    const bool sequential = a.rng_mode == MCMCPP_RNG_SEQUENTIAL;
+    const GwConstants gw = gwOf(a);
+    unsigned long long accepted = 0;
+    unsigned redraws = 0;
+    __syncthreads();
+    const long long total = (long long)f.stored_steps * f.interval;
+    int sinceStore = 0;
+    long long row = 0;
+    for (long long step = 0; step < total; ++step) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            if (live) {
+                const int w = half * K + t, other0 = (1 - half) * K;
+                StretchDraws dr = drawStretch(rng[half].state, rng[half].inc, (uint64_t)K, a.bound_threshold, a.bound_recip, gw);
+                if (sequential) rng[half].state = applyAffine(skip, rng[half].state);   /* storeRng: over the other walkers' draws */
+                redraws += (unsigned)dr.redraws;
+                double cur[D], prop[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) { cur[d] = sPos[(size_t)w * D + d]; prop[d] = sPos[(size_t)(other0 + dr.j) * D + d]; }
+#pragma unroll
+                for (int d = 0; d < D; ++d) prop[d] = stretchPoint(prop[d], cur[d], dr.z);
+                const double scaling = __dmul_rn(log(dr.z), (double)(D - 1));
+                const double newp = calc.calcLogPostProb(prop);
+                const double diff = __dsub_rn(__dadd_rn(scaling, newp), sLogp[w]);
+                if (dr.logOneMinusU < diff) {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) sPos[(size_t)w * D + d] = prop[d];
+                    sLogp[w] = newp;
+                    ++accepted;
+                }
+            }
+            __syncthreads();
+        }
+        if (++sinceStore == f.interval) {
+            sinceStore = 0;
+            if (f.chain_rows && live) {
+                double* out = f.chain_rows + (size_t)row * W * D;
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    out[(size_t)t * D + d] = sPos[(size_t)t * D + d];
+                    out[(size_t)(K + t) * D + d] = sPos[(size_t)(K + t) * D + d];
+                }
+            }
+            ++row;
+        }
+    }
+    for (int idx = t; idx < W * D; idx += blockDim.x) a.pos[idx] = sPos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) a.logp[idx] = sLogp[idx];
+    if (live) {
+        reinterpret_cast<ulonglong2*>(a.rng_state)[t] = make_ulonglong2(rng[0].state.lo, rng[0].state.hi);
+        reinterpret_cast<ulonglong2*>(a.rng_state)[K + t] = make_ulonglong2(rng[1].state.lo, rng[1].state.hi);
+        if (redraws) atomicAdd(a.flags, redraws);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) accepted += __shfl_xor_sync(0xffffffffu, accepted, off);
+    if ((t & 31) == 0 && accepted) atomicAdd(a.accept_slots, accepted);
+}
+
+/* Pass &FusedLauncher<Calc>::launch to mcmcpp_sampler_set_fused_launcher (stretch move, any Calculator). */
+template <class Calc, int FixedD = 0>
+struct FusedLauncher
+{
+    template <int D>
+    static int run(const mcmcpp_fused_args& f, const Calc& calc, cudaStream_t stream)
+    {
+        const mcmcpp_halfstep_args& a = f.base;
+        const size_t smem = sizeof(double) * ((size_t)2 * a.K * D + (size_t)2 * a.K);
+        if (smem > 48 * 1024 &&
+            cudaFuncSetAttribute(stretchFusedSmall<Calc, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return MCMCPP_ERR_CUDA;
+        const int threads = ((a.K + 31) / 32) * 32;
+        stretchFusedSmall<Calc, D><<<1, threads, smem, stream>>>(f, calc);
+        return launchStatus();
+    }
+
+    static int launch(const mcmcpp_fused_args* args, const void* calculator, void* cudaStream)
+    {
+        const mcmcpp_fused_args& f = *args;
+        const Calc& calc = *static_cast<const Calc*>(calculator);
+        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
+        if (f.base.K > FusedMaxThreads || f.base.D > ThreadKernelMaxDim || f.base.slot_count != f.base.K) return MCMCPP_ERR_UNSUPPORTED;
+        if (f.stored_steps <= 0 || f.interval <= 0) return MCMCPP_ERR_ARG;
+        if constexpr (FixedD > 0) {
+            if (f.base.D != FixedD) return MCMCPP_ERR_ARG;
+            return run<FixedD>(f, calc, stream);
+        } else {
+            switch (f.base.D) {
+            case 1: return run<1>(f, calc, stream);
+            case 2: return run<2>(f, calc, stream);
+            case 3: return run<3>(f, calc, stream);
+            case 4: return run<4>(f, calc, stream);
+            case 5: return run<5>(f, calc, stream);
+            case 6: return run<6>(f, calc, stream);
+            case 7: return run<7>(f, calc, stream);
+            case 8: return run<8>(f, calc, stream);
+            default: return MCMCPP_ERR_UNSUPPORTED;
+            }
+        }
+    }
+};
+
 /* FixedD > 0 restricts the thread kernel to one dimension (2-D test targets); 0 = any D. */
 template <class Calc, int FixedD = 0>
 struct HalfStepLauncher

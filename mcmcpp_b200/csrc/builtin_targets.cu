@@ -148,4 +148,17 @@ int mcmcpp_builtin_bind_mover(int moverKind, int kind, int W, int D, const doubl
     }
 }
 
+mcmcpp_fused_fn mcmcpp_builtin_fused(int kind, int D, int shardMode)
+{
+    using namespace MCMC::Targets;
+    if (shardMode != MCMCPP_SHARD_NONE || D > MCMC::Device::ThreadKernelMaxDim) return nullptr;
+    switch (kind) {
+    case MCMCPP_TARGET_SKEWED_GAUSS_2D: return &MCMC::Device::FusedLauncher<SkewedGaussianTwoDim<double>, 2>::launch;
+    case MCMCPP_TARGET_ROSENBROCK_2D: return &MCMC::Device::FusedLauncher<RosenbrockTwoDim<double>, 2>::launch;
+    case MCMCPP_TARGET_DIAG_GAUSS: return &MCMC::Device::FusedLauncher<DiagGaussian<double> >::launch;
+    case MCMCPP_TARGET_DENSE_GAUSS: return &MCMC::Device::FusedLauncher<DenseGaussian<double> >::launch;   /* D <= 8: generic calculator blob */
+    default: return nullptr;
+    }
+}
+
 void mcmcpp_builtin_release(void* aux) { mcmcpp_linreg_release(aux); }   /* the only target with scratch */

@@ -14,6 +14,8 @@ int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t
                         mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux, int shardMode, int dimBegin, int dimCount);
 int mcmcpp_builtin_bind_mover(int moverKind, int kind, int W, int D, const double* moverParams, size_t nMover, const double* hostParams,
                               size_t nValues, const double* devParams, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);
+/* the fused small-ensemble launcher that goes with mcmcpp_builtin_bind's generic launcher for this target, or NULL */
+mcmcpp_fused_fn mcmcpp_builtin_fused(int kind, int D, int shardMode);
 void mcmcpp_builtin_release(void* aux);
 /* dense_gauss.cu: FP64 tensor-core half-step for the dense Gaussian; false = use the generic launcher */
 bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);

@@ -173,6 +173,9 @@ struct mcmcpp_sampler
     int moverDoubles = 0;
     /* PostStepAction with a device-resident step view (EnsembleSampler.h:356-359) */
     mcmcpp_step_fn stepFn = nullptr;
+    mcmcpp_fused_fn fusedFn = nullptr;     /* small ensembles: the whole runMCMC loop in one launch */
+    double* dFusedChain = nullptr;         /* [fusedRows][W][D] rows filled by the fused kernel */
+    long long fusedRows = 0;
     void* stepCtx = nullptr;
     /* on-the-fly CovarianceMatrix over the stored steps (analysis.cu) */
     mcmcpp_cov_accum* cov = nullptr;
@@ -473,6 +476,7 @@ int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, con
     rc = mcmcpp_builtin_bind(target_kind, s->W, s->D, params, num_params_values, s->dParams, &s->launcher, &s->calculator,
                              &s->builtinAux, cfg->shard_mode, s->dimBegin, s->Dl);
     if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "unknown built-in target or bad parameter count"); }
+    s->fusedFn = mcmcpp_builtin_fused(target_kind, s->D, cfg->shard_mode);
     return MCMCPP_OK;
 }
 
@@ -514,6 +518,7 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     for (void* p : s->peerOpened) cudaIpcCloseMemHandle(p);
     cudaFree(s->dPeerPos);
     cudaFree(s->dMoverState);
+    cudaFree(s->dFusedChain);
     cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ); cudaFree(s->dDimList); cudaFree(s->dSyncWord);
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
     cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
@@ -601,7 +606,41 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     const int perStored = s->subSampling ? s->interval : 1;
     int status = MCMCPP_OK;
     CUDA_TRY(cudaEventRecord(s->evStart, s->stream));
-    for (int i = 0; i < num_steps; ++i) {
+    static const bool fusedAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED"); return !(e && e[0] == '0'); }();
+    const bool fused = fusedAllowed && s->fusedFn && s->cfg.world == 1 && s->cfg.shard_mode == MCMCPP_SHARD_NONE && !s->stepFn && !s->cov
+                       && !s->dTrace && s->K <= 1024 && s->D <= 8;
+    if (fused) {
+        /* same bookkeeping as the loop below, one launch per chunk of stored steps */
+        const size_t rowBytes = sizeof(double) * rowDoubles(s);
+        if (chainOn && !s->dFusedChain) {
+            s->fusedRows = std::max<long long>(1, std::min<long long>(16384, (long long)((32u << 20) / rowBytes)));
+            CUDA_TRY(cudaMalloc(&s->dFusedChain, rowBytes * (size_t)s->fusedRows));
+        }
+        long long remaining = num_steps;
+        while (remaining > 0) {
+            long long chunk = std::min<long long>(remaining, (1 << 18) / perStored + 1);
+            const bool keep = chainOn && s->stored < s->capRows;
+            if (chainOn) chunk = keep ? std::min(chunk, std::min(s->fusedRows, s->capRows - s->stored)) : 1;
+            mcmcpp_fused_args f;
+            f.base = s->base;
+            f.base.half = 0; f.base.chain_row = nullptr; f.base.trace = nullptr; f.base.trace_rows = 0;
+            f.stored_steps = (int32_t)chunk;
+            f.interval = perStored;
+            f.chain_rows = keep ? s->dFusedChain : nullptr;
+            rc = s->fusedFn(&f, s->calculator.data(), s->stream);
+            if (rc != MCMCPP_OK) return fail(rc, std::string("fused launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+            ++s->launches;
+            if (keep) CUDA_TRY(cudaMemcpyAsync(s->hChain + rowDoubles(s) * (size_t)s->stored, s->dFusedChain, rowBytes * (size_t)chunk,
+                                               cudaMemcpyDeviceToHost, s->stream));
+            s->stored += chunk;
+            s->ensembleSteps += chunk * perStored;
+            s->totalSteps += 2ULL * (unsigned long long)s->slotCount * (unsigned long long)perStored * (unsigned long long)chunk;
+            remaining -= chunk;
+            if (chainOn && s->stored >= s->capRows) { status = MCMCPP_CHAIN_FULL; break; }
+            if (keep) CUDA_TRY(cudaStreamSynchronize(s->stream));      /* the staging rows are reused by the next chunk */
+        }
+    }
+    for (int i = 0; !fused && i < num_steps; ++i) {
         /* the interval-1 unsaved steps come first (EnsembleSampler.h:300-303) */
         for (int j = 1; j < perStored; ++j) {
             if ((rc = halfStep(s, 0, nullptr)) != MCMCPP_OK) return rc;
@@ -639,6 +678,13 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     CUDA_TRY(cudaStreamSynchronize(s->copyStream));
     if (device_ms) CUDA_TRY(cudaEventElapsedTime(device_ms, s->evStart, s->evStop));
     return status;
+}
+
+int mcmcpp_sampler_set_fused_launcher(mcmcpp_sampler* s, mcmcpp_fused_fn launcher)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    s->fusedFn = launcher;
+    return MCMCPP_OK;
 }
 
 int mcmcpp_sampler_get_counts(mcmcpp_sampler* s, unsigned long long* accepted, unsigned long long* total)

@@ -285,3 +285,46 @@ def test_dim_shard_kernels_single_rank_bit_exact(port, W, D, steps):
     assert s.getAcceptedSteps() == int(o["acc"].sum())
     assert_trace_equal(s.getTrace(W), o["trace"][:W])
     s.close()
+
+
+@pytest.mark.parametrize("kind,W,D,steps,interval,rng", [("skewed_gauss_2d", 32, 2, 200, 1, "sequential"),
+                                                         ("rosenbrock_2d", 2048, 2, 40, 3, "per_walker"),
+                                                         ("rosenbrock_2d", 2048, 2, 30, 1, "sequential"),
+                                                         ("diag_gauss", 64, 8, 50, 2, "sequential"),
+                                                         ("dense_gauss", 40, 5, 60, 1, "sequential")])
+def test_fused_small_ensemble_kernel(port, kind, W, D, steps, interval, rng):
+    """Small ensembles run the whole runMCMC loop in one launch of one CTA (mcmcpp_fused_args).  Same chain, counters and
+    rng continuation as the oracle and as the launch-per-colour path (which a trace request selects)."""
+    params = {"skewed_gauss_2d": [0.13], "rosenbrock_2d": [], "diag_gauss": 1.0 / (1.0 + (np.arange(D) % 10)),
+              "dense_gauss": corr_precision(D).reshape(-1)}[kind]
+    init, lp = seeded_init(port, kind, params if len(params) else None, W, D, 5)
+    runs = []
+    for trace in (0, 1):
+        s = make_sampler(kind, params, W, D, seed=9, rngMode=rng, traceUpdates=trace)
+        s.setSlicingMode(interval > 1, interval)
+        s.setInitialWalkerPos(init, lp)
+        assert s.runMCMC(steps) and s.runMCMC(3)                      # the second call continues every walker's stream
+        launches = s.getLaunchCount()
+        assert launches == (2 if trace == 0 else 2 * (steps + 3) * interval)
+        runs.append((np.array(s.getChain()), s.getWalkerState(), s.getAcceptedSteps(), s.getTotalSteps()))   # the chain view dies with close()
+        s.close()
+    (c0, (p0, a0), acc0, tot0), (c1, (p1, a1), acc1, tot1) = runs
+    assert np.array_equal(c0, c1) and np.array_equal(p0, p1) and np.array_equal(a0, a1) and (acc0, tot0) == (acc1, tot1)
+    o = port.run(kind, params if len(params) else None, init, lp, steps + 3, interval=interval, seed=9, per_walker=(rng == "per_walker"))
+    assert np.array_equal(c0[1:], o["chain"]) and np.array_equal(p0, o["pos"]) and np.array_equal(a0, o["logp"])
+    assert (acc0, tot0) == (int(o["acc"].sum()), int(o["tot"].sum()))
+
+
+def test_fused_small_ensemble_chain_cap(port):
+    """runMCMC returns False at the byte cap (EnsembleSampler.h:293,308) at the same stored count on both paths."""
+    W, D = 64, 2
+    init, lp = seeded_init(port, "skewed_gauss_2d", [0.13], W, D, 6)
+    out = []
+    for trace in (0, 1):
+        s = make_sampler("skewed_gauss_2d", [0.13], W, D, seed=1, maxChainSizeBytes=25 * W * D * 8, traceUpdates=trace)
+        s.setInitialWalkerPos(init, lp)
+        assert s.runMCMC(10) is True
+        assert s.runMCMC(100) is False
+        out.append((s.getStoredSteps(), np.array(s.getChain()), s.getTotalSteps()))
+        s.close()
+    assert out[0][0] == out[1][0] == 25 and np.array_equal(out[0][1], out[1][1]) and out[0][2] == out[1][2]
