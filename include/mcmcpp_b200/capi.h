@@ -140,7 +140,7 @@ typedef struct {
     int32_t D_total;           /* numParams of the whole row: log(z) * (D_total - 1)  (StretchMove.h:110) */
     int32_t dim_begin;         /* global index of local column 0 */
     int32_t rank, world;
-    double* const* dim_partial;/* [world] every rank's partial table [2 colours][world][K] (own entry local, others peer-mapped) */
+    double* const* dim_partial;/* [world] every rank's partial table [2 colours][world][K] + flag words [2][world] (own entry local, others peer-mapped) */
     double* dim_z;             /* [K] draw scratch: draws of the colour in flight, kept between kernels (all shard modes) */
     double* dim_e;
     int32_t* dim_j;
@@ -149,6 +149,9 @@ typedef struct {
     int32_t sm_count;          /* multiprocessors of the device (persistent grids) */
     double* mover_state;       /* [W * mover_state_doubles] per-walker mover state, or NULL */
     double* sync_word;         /* 1 double: operand of the stream-ordered rendezvous (allreduce_sum of 1 element) */
+    unsigned long long dim_epoch; /* DIM: > 0 = in-kernel rendezvous -- the decide kernel stores this number into every rank's flag
+                                * words (behind the partial table, [2][world]) and waits for all ranks' numbers;
+                                * 0 = stream-ordered rendezvous through allreduce_sum */
 } mcmcpp_halfstep_args;
 
 typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);

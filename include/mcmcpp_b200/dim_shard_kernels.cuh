@@ -53,6 +53,31 @@ __device__ __forceinline__ void dimStore2(double* __restrict__ row, int d, int D
     }
 }
 
+/* ---- in-kernel rendezvous (args.dim_epoch > 0) --------------------------------------------------------------------
+ * Behind every rank's partial table sit 2 x world flag words.  The decide kernel runs after this rank's partial kernel in
+ * stream order, so when it starts this rank's partials have landed everywhere: its first CTA stores the epoch into flag
+ * [colour][this rank] of EVERY rank (NVLink stores, like the partials themselves), then every CTA waits until all `world`
+ * flags of the colour have reached the epoch.  A rank can be at most one colour ahead of another (it needs the other's
+ * flag to get further), and consecutive colours use different halves of the table and of the flags, so nothing is
+ * overwritten while it is still being read.  (A fence + arrival counter at the end of the partial kernel instead costs
+ * a system-scope fence per CTA, which waits for the CTA's NVLink stores: 2.5x slower at 2 GPUs.) */
+__device__ __forceinline__ void dimRendezvous(const mcmcpp_halfstep_args& a)
+{
+    if (a.dim_epoch == 0 || a.world == 1) return;
+    const size_t tableDoubles = 2 * (size_t)a.world * (size_t)a.K;
+    if ((int)threadIdx.x < a.world) {
+        if (blockIdx.x == 0) {
+            volatile unsigned long long* theirs = reinterpret_cast<volatile unsigned long long*>(a.dim_partial[threadIdx.x] + tableDoubles);
+            theirs[(size_t)a.half * a.world + a.rank] = a.dim_epoch;
+        }
+        const volatile unsigned long long* flag = reinterpret_cast<const volatile unsigned long long*>(a.dim_partial[a.rank] + tableDoubles)
+                                                  + (size_t)a.half * a.world + threadIdx.x;
+        while (*flag < a.dim_epoch) __nanosleep(64);
+        __threadfence_system();
+    }
+    __syncthreads();
+}
+
 /* ---- phase 1: draws, proposal slice, partial sum, partial -> every rank's table ---------------------------- */
 template <class Calc, bool VEC>
 __global__ void __launch_bounds__(DimThreads) dimShardPartial(const mcmcpp_halfstep_args a, const Calc calcIn)
@@ -208,6 +233,7 @@ __global__ void __launch_bounds__(256) dimShardDecide(const mcmcpp_halfstep_args
     const int i = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31;
     bool accepted = false, listed = false;
+    dimRendezvous(a);                                         /* every rank's partials of this colour have landed */
     if (i < a.K) {
         Calc calc = calcIn;
         const int w = a.half * a.K + i;
@@ -370,8 +396,8 @@ struct DimShardLauncher
         } else {
             dimShardPartial<Calc, VEC><<<grid, DimThreads, 0, stream>>>(a, calc);
         }
-        if (a.world > 1) {
-            /* rendezvous: every rank's partials have landed in every table before anyone reads them */
+        if (a.world > 1 && a.dim_epoch == 0) {
+            /* stream-ordered rendezvous (the in-kernel flags are off): every rank's partials have landed in every table */
             int rc = a.allreduce_sum ? a.allreduce_sum(a.allreduce_ctx, a.sync_word, 1, stream) : MCMCPP_ERR_STATE;
             if (rc != MCMCPP_OK) return rc;
         }

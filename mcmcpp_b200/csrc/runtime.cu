@@ -173,6 +173,7 @@ struct mcmcpp_sampler
     int moverDoubles = 0;
     /* PostStepAction with a device-resident step view (EnsembleSampler.h:356-359) */
     mcmcpp_step_fn stepFn = nullptr;
+    unsigned long long dimEpoch = 0;       /* DIM: colours launched so far (in-kernel rendezvous number) */
     mcmcpp_fused_fn fusedFn = nullptr;     /* small ensembles: the whole runMCMC loop in one launch */
     double* dFusedChain = nullptr;         /* [fusedRows][W][D] rows filled by the fused kernel */
     long long fusedRows = 0;
@@ -257,6 +258,10 @@ int halfStep(mcmcpp_sampler* s, int half, double* chainRow)
     mcmcpp_halfstep_args a = s->base;
     a.half = half;
     a.chain_row = chainRow;
+    if (s->cfg.shard_mode == MCMCPP_SHARD_DIM) {
+        static const bool flags = [] { const char* e = getenv("MCMCPP_B200_DIM_FLAGS"); return !(e && e[0] == '0'); }();
+        a.dim_epoch = flags ? ++s->dimEpoch : 0;      /* every rank makes the same calls, so the epochs agree */
+    }
     a.trace = nullptr;
     a.trace_rows = 0;
     if (s->dTrace) {
@@ -368,7 +373,8 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
     CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * (size_t)s->K));
     if (cfg->shard_mode == MCMCPP_SHARD_DIM) {
-        const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K;
+        /* partial table + [2][world] flag words of the in-kernel rendezvous (dim_shard_kernels.cuh) */
+        const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K + 2 * (size_t)cfg->world + 2;
         CUDA_TRY(cudaMalloc(&s->dDimPartial, sizeof(double) * tableDoubles));
         CUDA_TRY(cudaMemset(s->dDimPartial, 0, sizeof(double) * tableDoubles));
         CUDA_TRY(cudaMalloc(&s->dDimTable, sizeof(double*) * (size_t)cfg->world));
