@@ -264,6 +264,9 @@ __global__ void __launch_bounds__(WarpKernelThreads) stretchHalfStepWarp(const m
     /* every lane replays the same three draws (cheaper than a broadcast of six registers) */
     WalkerRng rng = loadRng(a, w);
     StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    /* programmatic dependent launch (see stretchHalfStepThread): the draws read only this colour's rng state */
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     double* ownRow = a.pos + (size_t)w * D;
     const double* selRow = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
@@ -524,11 +527,18 @@ int launchWarpKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream
     if (grid > a.max_grid) return MCMCPP_ERR_ARG;
     const size_t smem = IsSeparable<Calc>::value ? 0 : sizeof(double) * (size_t)a.D * warpsPerBlock;
     const bool vec = (a.D % 2) == 0;
+    static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(WarpKernelThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
 #define MCMCPP_LAUNCH_WARP(V, T)                                                                             \
     do {                                                                                                     \
         if (smem > 48 * 1024)                                                                                \
             cudaFuncSetAttribute(stretchHalfStepWarp<Calc, NCHUNK, V, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        stretchHalfStepWarp<Calc, NCHUNK, V, T><<<grid, WarpKernelThreads, smem, stream>>>(a, calc);         \
+        if (cudaLaunchKernelEx(&cfg, stretchHalfStepWarp<Calc, NCHUNK, V, T>, a, calc) != cudaSuccess) return MCMCPP_ERR_CUDA; \
     } while (0)
     if (vec) { if (a.trace) MCMCPP_LAUNCH_WARP(true, true); else MCMCPP_LAUNCH_WARP(true, false); }
     else     { if (a.trace) MCMCPP_LAUNCH_WARP(false, true); else MCMCPP_LAUNCH_WARP(false, false); }
