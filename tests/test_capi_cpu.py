@@ -113,3 +113,26 @@ def test_dim_slices_match_the_c_abi_and_tile_the_row():
                 assert c.value % 2 == 0 or r == world - 1
                 nxt = b.value + c.value
             assert nxt == D
+
+
+def test_header_is_plain_c_and_python_mirrors_its_structs(tmp_path):
+    """The boundary is a C ABI: capi.h compiles as C (no C++ or torch types in any signature), and the ctypes structures
+    have the sizes and field offsets the C compiler gives the header's structs."""
+    import ctypes as C
+    from mcmcpp_b200 import _capi
+    src = tmp_path / "abi.c"
+    fields = [name for name, _ in _capi.Config._fields_]
+    tfields = [name for name, _ in _capi.Trace._fields_]
+    prints = "".join('    printf("config.%s %%zu\\n", offsetof(mcmcpp_config, %s));\n' % (f, f) for f in fields)
+    prints += "".join('    printf("trace.%s %%zu\\n", offsetof(mcmcpp_trace, %s));\n' % (f, f) for f in tfields)
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "mcmcpp_b200/capi.h"\nint main(void) {\n'
+                   '    printf("sizeof.config %zu\\nsizeof.trace %zu\\n", sizeof(mcmcpp_config), sizeof(mcmcpp_trace));\n'
+                   + prints + "    return 0;\n}\n")
+    exe = tmp_path / "abi"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = dict(line.split() for line in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    assert int(out["sizeof.config"]) == C.sizeof(_capi.Config) and int(out["sizeof.trace"]) == C.sizeof(_capi.Trace)
+    for f in fields:
+        assert int(out["config." + f]) == getattr(_capi.Config, f).offset, f
+    for f in tfields:
+        assert int(out["trace." + f]) == getattr(_capi.Trace, f).offset, f
