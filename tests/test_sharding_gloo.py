@@ -80,3 +80,70 @@ def test_shard_arithmetic():
         assert sorted(seen) == list(range(W))
     assert parallel.sequential_draw_index(0, 0, 0, W) == 0
     assert parallel.sequential_draw_index(2, 1, 5, W) == 3 * (2 * W + W // 2 + 5)
+
+
+def _dim_worker(rank, world, port_no, W, D, steps, out_dir):
+    """One rank of the DIM (parameter-column) sharding protocol of dim_shard_kernels.cuh, restated on the host: every rank
+    holds ALL walkers x its columns, replays the same draws, builds its slice of every proposal, contributes one partial
+    sum per walker to every rank's table (all_gather), adds the partials in RANK ORDER and takes the same decisions."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port_no)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle.pyoracle import Port
+    from mcmcpp_b200 import parallel
+    port = Port()
+    K = W // 2
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    full = np.random.default_rng(7).standard_normal((W, D))
+    logp = port.logp("diag_gauss", iv, full)
+    # the draws depend on the rng alone: take (j, z, log(1-u)) of every update from the sequential restatement's trace
+    tr = port.run("diag_gauss", iv, full, logp, steps, seed=11, want_chain=False, want_trace=True)["trace"]
+    lo, hi = parallel.dim_slice(D, rank, world)
+    mine = full[:, lo:hi].copy()                                   # this rank's columns of every walker
+    accepted = 0
+    for t in range(steps):
+        for h in (0, 1):
+            d = tr[t * W + h * K:t * W + h * K + K]
+            own = mine[h * K:(h + 1) * K]
+            sel = mine[(1 - h) * K + d["j"]]
+            prop = sel + d["z"][:, None] * (own - sel)
+            partial = torch.from_numpy((prop * prop * iv[lo:hi]).sum(axis=1))
+            table = [torch.empty_like(partial) for _ in range(world)]
+            dist.all_gather(table, partial)                        # "stores into every rank's table" + rendezvous
+            total = table[0].numpy().copy()
+            for r in range(1, world):
+                total = total + table[r].numpy()                   # rank order, identical on every rank
+            newp = -0.5 * total
+            take = d["e"] < (np.log(d["z"]) * (D - 1) + newp) - logp[h * K:(h + 1) * K]
+            mine[h * K:(h + 1) * K][take] = prop[take]
+            logp[h * K:(h + 1) * K][take] = newp[take]
+            accepted += int(take.sum())
+    widths = [b - a for a, b in (parallel.dim_slice(D, r, world) for r in range(world))]
+    padded = torch.zeros((W, max(widths)), dtype=torch.float64)      # gloo gathers equal shapes; slices may differ by two columns
+    padded[:, :hi - lo] = torch.from_numpy(mine)
+    cols = [torch.empty_like(padded) for _ in range(world)]
+    dist.all_gather(cols, padded)
+    cols = [c[:, :w] for c, w in zip(cols, widths)]
+    counts = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(counts, torch.tensor([accepted]))
+    if rank == 0:
+        np.savez(os.path.join(out_dir, "dim.npz"), pos=torch.cat(cols, dim=1).numpy(), logp=logp, acc=np.array([int(c) for c in counts]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("W,D,steps", [(64, 10, 6), (48, 7, 5)])
+def test_two_rank_dim_sharded_ensemble(tmp_path, port, W, D, steps):
+    """Column slices from parallel.dim_slice (even and ragged), partial sums exchanged and added in rank order: every rank
+    takes the decisions of the sequential reference; positions are exact, log-probs within 1e-12 (summation order)."""
+    world = 2
+    port_no = 29900 + (os.getpid() % 90)
+    mp.spawn(_dim_worker, args=(world, port_no, W, D, steps, str(tmp_path)), nprocs=world, join=True)
+    z = np.load(tmp_path / "dim.npz")
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    init = np.random.default_rng(7).standard_normal((W, D))
+    o = port.run("diag_gauss", iv, init, port.logp("diag_gauss", iv, init), steps, seed=11, acc=np.zeros(W), tot=np.zeros(W))
+    assert np.array_equal(z["pos"], o["pos"])
+    assert np.allclose(z["logp"], o["logp"], rtol=1e-12, atol=0)
+    assert z["acc"][0] == z["acc"][1] == int(o["acc"].sum())          # replicated decisions: every rank counts them all
