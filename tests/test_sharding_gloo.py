@@ -147,3 +147,59 @@ def test_two_rank_dim_sharded_ensemble(tmp_path, port, W, D, steps):
     assert np.array_equal(z["pos"], o["pos"])
     assert np.allclose(z["logp"], o["logp"], rtol=1e-12, atol=0)
     assert z["acc"][0] == z["acc"][1] == int(o["acc"].sum())          # replicated decisions: every rank counts them all
+
+
+def _data_worker(rank, world, port_no, W, P, M, steps, out_dir):
+    """One rank of the DATA sharding protocol (C5, csrc/linreg.cu): the ensemble is replicated, a rank holds a contiguous
+    range of the data rows, contributes its partial sum of squared residuals of every proposal, and the partials are
+    all-reduced (the runtime's ncclAllReduce of K doubles); every rank then takes the same decisions."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port_no)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle.pyoracle import Port
+    from mcmcpp_b200 import parallel
+    port = Port()
+    K = W // 2
+    g = np.random.default_rng(3)
+    X = g.standard_normal((M, P)); y = X @ g.standard_normal(P) + g.standard_normal(M)
+    params = np.concatenate([[float(M), 100.0], X.reshape(-1), y])
+    pos = np.linalg.lstsq(X, y, rcond=None)[0] + 0.1 * g.standard_normal((W, P))
+    logp = port.logp("linreg", params, pos)
+    tr = port.run("linreg", params, pos, logp, steps, seed=2, want_chain=False, want_trace=True)["trace"]
+    b, e = parallel.shard_data_rows(M, rank, world)
+    Xr, yr = X[b:e], y[b:e]
+    accepted = 0
+    for t in range(steps):
+        for h in (0, 1):
+            d = tr[t * W + h * K:t * W + h * K + K]
+            own = pos[h * K:(h + 1) * K]
+            sel = pos[(1 - h) * K + d["j"]]
+            prop = sel + d["z"][:, None] * (own - sel)
+            res = prop @ Xr.T - yr                                   # this rank's rows of the residual matrix [K x rows]
+            sse = torch.from_numpy((res * res).sum(axis=1))
+            dist.all_reduce(sse)                                     # K doubles per colour
+            newp = -0.5 * sse.numpy() - 0.5 * (prop * prop).sum(axis=1) / 100.0
+            take = d["e"] < (np.log(d["z"]) * (P - 1) + newp) - logp[h * K:(h + 1) * K]
+            pos[h * K:(h + 1) * K][take] = prop[take]
+            logp[h * K:(h + 1) * K][take] = newp[take]
+            accepted += int(take.sum())
+    np.savez(os.path.join(out_dir, "data%d.npz" % rank), pos=pos, logp=logp, acc=accepted)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_data_sharded_ensemble(tmp_path, port):
+    W, P, M, steps = 32, 4, 301, 6                                   # 301 rows: ragged shards (151 + 150)
+    world = 2
+    port_no = 29800 + (os.getpid() % 90)
+    mp.spawn(_data_worker, args=(world, port_no, W, P, M, steps, str(tmp_path)), nprocs=world, join=True)
+    g = np.random.default_rng(3)
+    X = g.standard_normal((M, P)); y = X @ g.standard_normal(P) + g.standard_normal(M)
+    params = np.concatenate([[float(M), 100.0], X.reshape(-1), y])
+    init = np.linalg.lstsq(X, y, rcond=None)[0] + 0.1 * g.standard_normal((W, P))
+    o = port.run("linreg", params, init, port.logp("linreg", params, init), steps, seed=2, acc=np.zeros(W), tot=np.zeros(W))
+    z = [np.load(tmp_path / ("data%d.npz" % r)) for r in range(world)]
+    assert np.array_equal(z[0]["pos"], z[1]["pos"]) and np.array_equal(z[0]["logp"], z[1]["logp"])   # replicas stay identical
+    assert np.array_equal(z[0]["pos"], o["pos"]) and int(z[0]["acc"]) == int(o["acc"].sum())
+    assert np.allclose(z[0]["logp"], o["logp"], rtol=1e-12, atol=0)
