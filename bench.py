@@ -80,16 +80,41 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock + throttle reasons DURING the timed region (B200_PROFILING.md recipe).  NVML in-process (nvidia_ml_py), one
+    sample every ~4 ms, so that a 57 ms timed region (20 steps of configs[3]) still holds >= 5 samples; falls back to
+    polling nvidia-smi (0.1 s period) when NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
 
-    def __init__(self, index):
+    def __init__(self, index, bus_id=None):
         self.index, self.rows, self.stop, self.thread = index, [], threading.Event(), None
+        self.nvml, self.handle, self.max_mhz = None, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus_id.encode() if bus_id else b"") if bus_id else \
+                pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _reasons(self):
+        n = self.nvml
+        fn = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        return int(fn(self.handle))
 
     def _loop(self):
         while not self.stop.is_set():
             try:
+                if self.nvml is not None:
+                    mhz = int(self.nvml.nvmlDeviceGetClockInfo(self.handle, self.nvml.NVML_CLOCK_SM))
+                    bits = self._reasons()
+                    self.rows.append([str(mhz), str(self.max_mhz)] + ["Active" if bits & self.BITS[k] else "Not Active" for k in
+                                                                       ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+                    self.stop.wait(0.004)
+                    continue
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
                 if out:
@@ -113,17 +138,19 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(self.rows), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 # ---- CPU arm: the reference's own implementation on the host cores (oracle/ is the checker; this is the one
 # ---- place bench.py executes it, as the thing that is the BASELINE, never as the product) -------------------
-def cpu_reference_run(workload, steps, warmup, seed=0):
+def cpu_reference_run(workload, steps, warmup, seed=0, walkers=None):
     """Times EnsembleSampler (1 core) and ParallelEnsembleSampler (all host threads) of the unmodified reference
     (oracle/_ref, compiled from /root/reference by oracle/Makefile) on a bounded sample of the workload; falls
     back to the plain-C port (kind "port", 1 core) when oracle/_ref is absent."""
     from oracle.pyoracle import Port, Ref
     desc, kind, W, D, Wc, _ = WORKLOADS[workload]
+    if walkers:
+        Wc = int(walkers)
     params = target_params(kind, D)
     rng = np.random.default_rng(1)
     init = rng.standard_normal((Wc, D))
@@ -225,21 +252,29 @@ def make_calc(m, kind, params, rank=0, world=1):
             "skewed_gauss_2d": lambda: m.SkewedGaussianTwoDim(params[0])}[kind]()
 
 
-def gpu_arm(args):
-    import torch
-    import torch.distributed as dist
-    import mcmcpp_b200 as m
-    from mcmcpp_b200 import parallel
+def ncu_constants():
+    """Per-launch counters of the dominant kernels taken from ncu captures (profiles/traffic.json names the capture each
+    comes from): DRAM bytes and executed warp instructions.  Not measured in this run -- ncu cannot run inside a timed region."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            return json.load(f)
+    return {}
+
+
+def bus_id_of(torch, local):
+    try:
+        p = torch.cuda.get_device_properties(local)
+        return "%08x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+    except Exception:
+        return None
+
+
+def measure(torch, dist, m, parallel, args, workload, steps, warm, with_e2e, with_cpu, cpu_scale=1.0, cpu_walkers=None, cpu_warm=1):
+    """One workload on this process group: device-timed value, roofline, optional e2e and cpu_baseline legs."""
     rank, world, local = parallel.env_rank_world()
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
-    torch.cuda.set_device(local)
     device = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=device)
-    if world != args.gpus and rank == 0:
-        print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
-    desc, kind, W, D, Wc, cpu_steps = WORKLOADS[args.workload]
+    desc, kind, W, D, Wc, cpu_steps = WORKLOADS[workload]
     if os.environ.get("MCMCPP_BENCH_D"):          # analysis only (e.g. one rank's slice of C4 on one GPU); named in config
         D = int(os.environ["MCMCPP_BENCH_D"])
         desc += " [params overridden to %d]" % D
@@ -248,7 +283,7 @@ def gpu_arm(args):
     shard = args.shard or ("data" if kind == "linreg" else "dim" if kind == "diag_gauss" else "peer")
     if kind == "linreg":
         shard = "data"
-    if world == 1 and args.shard != "dim":      # explicit dim with one rank = the three-kernel form on one GPU (overhead measurement)
+    if world == 1 and args.shard != "dim":      # explicit dim with one rank = the sharded kernels on one GPU (overhead measurement)
         shard = "none"
     rng_mode = "per_walker" if args.mover == "de" else args.rng
     if args.mover == "de":
@@ -263,14 +298,13 @@ def gpu_arm(args):
             torch.cuda.synchronize()
 
     every = args.store_every
-    if every > 0 and (world > 1 or args.steps % every):
+    if every > 0 and (world > 1 or steps % every):
         raise SystemExit("--store-every N needs one GPU and --steps a multiple of N")
-    warm = max(3, args.warmup)
     # runMCMC counts STORED steps: with subsampling each is N - 1 unsaved ensemble steps + 1 saved (EnsembleSampler.h:297-308)
     calls = (lambda k: k // every) if every > 0 else (lambda k: k)
     if every > 0:
         warm = every * max(1, warm // every)
-    chain_bytes = (calls(warm) + calls(args.steps) + 2) * W * D * 8 if every > 0 else 0
+    chain_bytes = (calls(warm) + calls(steps) + 2) * W * D * 8 if every > 0 else 0
 
     def new_sampler():
         mover_cls = m.DifferentialEvolution if args.mover == "de" else m.StretchMove
@@ -288,10 +322,11 @@ def gpu_arm(args):
     s.setInitialWalkerPosDevice(pos.data_ptr(), aux.data_ptr())
     s.runMCMC(calls(warm))
     launches0 = s.getLaunchCount()
+    acc0, _ = s._counts()
     barrier()
-    with ClockSampler(local) as clocks:
+    with ClockSampler(local, bus_id_of(torch, local)) as clocks:
         wall0 = time.perf_counter()
-        assert s.runMCMC(calls(args.steps)), "chain byte cap reached inside the timed region"
+        assert s.runMCMC(calls(steps)), "chain byte cap reached inside the timed region"
         barrier()
         wall = time.perf_counter() - wall0
     ms = torch.tensor([s.lastDeviceMs], dtype=torch.float64, device=device)
@@ -299,73 +334,99 @@ def gpu_arm(args):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     launches = s.getLaunchCount() - launches0
+    acc1, _ = s._counts()
     accepted, total = parallel.reduce_counts(s)
     redraws = s.getRngRedraws()
     s.close()
-    value = float(W) * args.steps / (ms * 1e-3)
+    value = float(W) * steps / (ms * 1e-3)
+    # acceptance of the proposals made inside the timed region (this rank's count; DIM/DATA ranks count every walker)
+    owned_updates = float(W) * steps if shard in ("none", "data", "dim") else float(W) * steps / world
+    acc_frac = (acc1 - acc0) / owned_updates
 
     # ---- e2e: the call a user makes, HOST buffers in, HOST buffers out, copies inside the timed region --------
     # DIM sharding: every process keeps its own column shard of the rows on its host side (W x D_local, contiguous)
+    e2e = None
     lo, hi = parallel.dim_slice(D, rank, world) if shard == "dim" else (0, D)
     Dloc = hi - lo
-    host_pos = torch.empty((W, Dloc), dtype=torch.float64, pin_memory=True)
-    host_aux = torch.empty(W, dtype=torch.float64, pin_memory=True)
-    host_pos.copy_(pos[:, lo:hi])
-    host_aux.copy_(aux)
-    del pos, aux
-    torch.cuda.empty_cache()
-    s = new_sampler()
-    # untimed warm-up of THIS sampler (its first collective sets up the NCCL channels, ~1 s at 8 ranks; first launches load
-    # the kernels); the timed call below starts again from the host buffers
-    s.setInitialWalkerPosLocal(host_pos.data_ptr(), host_aux.data_ptr())
-    s.runMCMC(calls(every) if every > 0 else 2)
-    if every > 0:
-        s.reset()
-    barrier()
-    t0 = time.perf_counter()
-    s.setInitialWalkerPosLocal(host_pos.data_ptr(), host_aux.data_ptr())
-    ok = s.runMCMC(calls(args.steps))
-    s.getWalkerStateLocalInto(host_pos.data_ptr(), host_aux.data_ptr())
-    e2e_acc, e2e_tot = s._counts()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_s = float(t.item())
-    s.close()
-    state_bytes = W * Dloc * 8 + W * 8
-    e2e = {"value": float(W) * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": state_bytes / args.steps,
-           "d2h_bytes_per_step": (state_bytes + 16) / args.steps, "seconds": e2e_s,
-           "what": "setInitialWalkerPos(pinned host%s) + runMCMC(%d) + walker state and counters back to pinned host, per rank"
-                   % (", this rank's %d columns" % Dloc if shard == "dim" else "", args.steps)}
+    if with_e2e:
+        host_pos = torch.empty((W, Dloc), dtype=torch.float64, pin_memory=True)
+        host_aux = torch.empty(W, dtype=torch.float64, pin_memory=True)
+        host_pos.copy_(pos[:, lo:hi])
+        host_aux.copy_(aux)
+        del pos, aux
+        torch.cuda.empty_cache()
+        s = new_sampler()
+        # untimed warm-up of THIS sampler (first launches load the kernels; ALLGATHER/DATA: the first collective sets up the
+        # NCCL channels, ~1 s at 8 ranks); the timed call below starts again from the host buffers
+        s.setInitialWalkerPosLocal(host_pos.data_ptr(), host_aux.data_ptr())
+        s.runMCMC(calls(every) if every > 0 else 2)
+        if every > 0:
+            s.reset()
+        barrier()
+        t0 = time.perf_counter()
+        s.setInitialWalkerPosLocal(host_pos.data_ptr(), host_aux.data_ptr())
+        ok = s.runMCMC(calls(steps))
+        s.getWalkerStateLocalInto(host_pos.data_ptr(), host_aux.data_ptr())
+        e2e_acc, e2e_tot = s._counts()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+        s.close()
+        del host_pos, host_aux
+        state_bytes = W * Dloc * 8 + W * 8
+        e2e = {"value": float(W) * steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": state_bytes / steps,
+               "d2h_bytes_per_step": (state_bytes + 16) / steps, "seconds": e2e_s, "ok": bool(ok),
+               "what": "setInitialWalkerPos(pinned host%s) + runMCMC(%d) + walker state and counters back to pinned host, per rank"
+                       % (", this rank's %d columns" % Dloc if shard == "dim" else "", steps)}
+    else:
+        del pos, aux
+        torch.cuda.empty_cache()
 
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
+        return None
 
     peak, peak_src = measured_peaks()
+    consts = ncu_constants()
     per_launch_updates = (W // 2) if shard in ("data", "dim") else (W // 2) // world
-    launch_ms = ms / (2.0 * args.steps)         # one colour = one half-step (1 launch; 4 for the GEMM-form linreg target)
-    Dl = D
-    if shard == "dim":
-        b_, e_ = parallel.dim_slice(D, rank, world)
-        Dl = e_ - b_                                # this rank streams its columns of every walker
+    launch_ms = ms / (2.0 * steps)         # one colour = one half-step
     stored_frac = 1.0 / every if every > 0 else 0.0
-    alg_bytes = per_launch_updates * algorithmic_bytes_per_update(Dl, stored_frac)
+    alg_per_update = algorithmic_bytes_per_update(Dloc, stored_frac)            # on the slice this rank streams
+    alg_bytes = per_launch_updates * alg_per_update
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        with open(tpath) as f:
-            traffic = json.load(f).get(args.workload)
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "kernel": ("dimShardPartial + dimShardCommit" if shard == "dim" else "stretchHalfStepBulk (TMA)" if (D >= 130 and D % 2 == 0)
-                           else "stretchHalfStepWarp" if D > 8 else "stretchHalfStepThread"), "peak_source": peak_src,
-                "algorithmic_bytes_per_update": algorithmic_bytes_per_update(D, stored_frac), "updates_per_launch": per_launch_updates,
-                "launch_ms": launch_ms,
-                "note": "launch_ms = CUDA-event time of the timed region / launches" + ("" if world == 1 else " (includes the per-half-step exchange)")}
+    # bytes that MUST move: both rows read, the own row written only when the proposal is accepted (+ chain row, log-probs)
+    actual_per_update = 8.0 * Dloc * (2.0 + acc_frac + stored_frac) + 16.0
+    achieved_actual = per_launch_updates * actual_per_update / (launch_ms * 1e-3) / 1e9
+    kernel = ("dimShardDraw + dimShardFused (TMA ring, partials over NVLink)" if shard == "dim" else "stretchDrawKernel + stretchHalfStepBulk (TMA)"
+              if (D >= 130 and D % 2 == 0) else "stretchHalfStepWarp" if D > 8 else
+              "stretchFusedSmall (whole runMCMC in one launch)" if (W // 2 <= 1024 and world == 1) else "stretchHalfStepThread")
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "frac_actual": achieved_actual / peak, "achieved_actual": achieved_actual,
+                "traffic": consts.get(workload) if (world == 1 and shard == "none") else None,
+                "kernel": kernel, "peak_source": peak_src,
+                "algorithmic_bytes_per_update": alg_per_update, "actual_bytes_per_update": actual_per_update,
+                "acceptance_in_timed_region": acc_frac, "updates_per_launch": per_launch_updates, "launch_ms": launch_ms,
+                "note": "frac = SURVEY s.8(d) algorithmic bytes (own-row write charged on EVERY update) / launch time / peak; it can exceed 1 "
+                        "because a rejected proposal writes nothing.  frac_actual charges the own-row write only for the measured "
+                        "acceptance: bytes that must move = 8 D (2 + acc) + 16.  launch_ms = CUDA-event time of the timed region / "
+                        "colours" + ("" if world == 1 else " (includes the per-colour exchange)")
+                        + ("; traffic = ncu dram bytes of one launch (profiles/traffic.json), N=1 only" if world == 1 else "")}
+    if D <= 8:
+        # state is L2-resident: the kernel is bound by instruction issue, not HBM -- report the issue-slot roofline beside it
+        inst = consts.get(workload + "_inst_executed_per_launch")
+        sm_hz = (clocks.summary().get("sm_mhz") or 1965) * 1e6
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        if inst and W // 2 > 1024:
+            roofline["issue"] = {"warp_instructions_per_launch": inst, "instructions_per_update": inst * 32.0 / per_launch_updates,
+                                 "achieved_ginst_s": inst / (launch_ms * 1e-3) / 1e9, "peak_ginst_s": sms * 4 * sm_hz / 1e9,
+                                 "frac": inst / (launch_ms * 1e-3) / (sms * 4 * sm_hz),
+                                 "note": "sm__inst_executed.sum of one launch (ncu, profiles/) / live launch time over SMs x 4 schedulers x 1 "
+                                         "warp-instruction/clk x SM clock"}
+        if W // 2 <= 1024:
+            roofline["note"] += ("; this ensemble is ONE CTA (16..1024 threads): latency-bound on the ~450-instruction dependent chain of an update, "
+                                 "not a bandwidth workload -- the HBM fraction is reported only because the contract asks for it")
     if kind == "dense_gauss":
         # compute-bound: FP64 tensor cores (DMMA); flops/update = 2D^2 + 5D; peak measured on this GPU
         import ctypes
@@ -374,7 +435,8 @@ def gpu_arm(args):
         _capi.check(_capi.lib().mcmcpp_fp64_tensor_peak(local, ctypes.byref(tf)))
         flops = per_launch_updates * (2.0 * D * D + 5.0 * D)
         ach = flops / (launch_ms * 1e-3) / 1e12
-        roofline = {"bound": "tensor", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value, "traffic": traffic,
+        roofline = {"bound": "tensor", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value,
+                    "traffic": consts.get(workload) if world == 1 else None,
                     "kernel": "denseGaussHalfStep (mma.sync.m8n8k4.f64)", "peak_source": "measured here: mcmcpp_fp64_tensor_peak (register-resident DMMA chains); MEASURED_PEAKS.json has no FP64 entry",
                     "flops_per_update": 2 * D * D + 5 * D, "updates_per_launch": per_launch_updates, "launch_ms": launch_ms,
                     "hbm_view": {"achieved_gbs": achieved, "frac_of_hbm_peak": achieved / peak}}
@@ -387,27 +449,64 @@ def gpu_arm(args):
         rows = rows[1] - rows[0]
         fl = 2.0 * rows * D + 3.0 * rows                                  # 2 M P + 3 M per update
         ach = per_launch_updates * fl / (launch_ms * 1e-3) / 1e12
-        roofline = {"bound": "tensor", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value, "traffic": traffic,
+        roofline = {"bound": "tensor", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value,
+                    "traffic": consts.get(workload) if world == 1 else None,
                     "kernel": "linregSse (mma.sync.m8n8k4.f64 GEMM [M x 52] x [52 x K], square-and-sum epilogue)",
                     "peak_source": "measured here: mcmcpp_fp64_tensor_peak (register-resident DMMA chains); MEASURED_PEAKS.json has no FP64 entry",
                     "flops_per_update": fl, "updates_per_launch": per_launch_updates, "launch_ms": launch_ms, "data_rows_this_rank": rows,
                     "note": "launch_ms = half-step time (propose + GEMM + reduce + accept" + ("" if world == 1 else " + all-reduce of K partial sums") + "); the GEMM is > 99 % of it"}
     cpu = None
-    if world == 1 and not args.no_cpu:
-        cpu = cpu_reference_run(args.workload, cpu_steps, 1)
+    if with_cpu and world == 1:
+        cpu = cpu_reference_run(workload, max(1, int(round(cpu_steps * cpu_scale))), cpu_warm, walkers=cpu_walkers)
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+    return {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
+            "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": desc, "walkers": W, "params": D, "rng": rng_mode, "shard": shard,
-                       "chain": "off" if every <= 0 else "every %d-th step stored: device rows -> pinned host chain on a side stream (%d rows of %.1f MB inside the timed region)"
-                                                         % (every, calls(args.steps), W * D * 8 / 1e6),
+                       "chain": "off (the CPU reference arm always stores its chain: EnsembleSampler has no chain-off mode)" if every <= 0 else
+                                "every %d-th step stored: device rows -> pinned host chain on a side stream (%d rows of %.1f MB inside the timed region)"
+                                % (every, calls(steps), W * D * 8 / 1e6),
                        "l2": "inputs (%.1f GB of walker rows) far exceed the 126 MB L2; no flush needed" % (W * D * 8 / 1e9)
                        if W * D * 8 > (1 << 29) else "state fits L2: L2-resident steady state is the workload itself"},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches) * world, "roofline": roofline,
             "cpu_baseline": cpu, "wall_s_timed_region": wall,
-            "acceptance": {"accepted": accepted, "total": total, "rng_redraws": redraws, "e2e_ok": bool(ok), "e2e_accepted": e2e_acc}}
-    print(json.dumps(line), flush=True)
+            "acceptance": {"accepted": accepted, "total": total, "rng_redraws": redraws}}
+
+
+# short runs of the other BASELINE configs appended to the default line: (steps, warm-up, fraction of the cpu sample)
+OTHERS = {"c1": (10000, 2000, 0.5, None, 1), "c2": (200, 20, 0.3, None, 1), "c3": (60, 10, 0.3, None, 1), "c5": (2, 1, 1.0, 64, 0)}
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import mcmcpp_b200 as m
+    from mcmcpp_b200 import parallel
+    rank, world, local = parallel.env_rank_world()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    if world != args.gpus and rank == 0:
+        print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
+    warm = max(3, args.warmup)
+    line = measure(torch, dist, m, parallel, args, args.workload, args.steps, warm, True, not args.no_cpu)
+    if rank == 0 and world == 1 and args.workload == "c4" and not args.no_others and not os.environ.get("MCMCPP_BENCH_D") \
+            and args.shard is None and args.mover == "stretch" and args.store_every == 0:
+        # the other BASELINE configs, short runs, one GPU: driver-visible numbers for C1/C2/C3/C5
+        others = {}
+        for name, (k_steps, k_warm, cpu_scale, cpu_walkers, cpu_warm) in OTHERS.items():
+            try:
+                r = measure(torch, dist, m, parallel, args, name, k_steps, k_warm, False, not args.no_cpu, cpu_scale, cpu_walkers, cpu_warm)
+                others[name] = {k: r[k] for k in ("value", "unit", "steps", "warmup", "ms_per_step", "config", "clocks", "gpu_launches",
+                                                 "roofline", "cpu_baseline", "acceptance")}
+            except Exception as exc:                    # a failure here must not take the headline line with it
+                others[name] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+        line["other_workloads"] = others
+    if rank == 0:
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -421,10 +520,11 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--shard", default=None, choices=["allgather", "peer", "dim"])
-    ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker"])
+    ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker", "per_walker32"])
     ap.add_argument("--mover", default="stretch", choices=["stretch", "de"], help="de: Mover::DifferentialEvolution (analysis runs; not the BASELINE metric)")
     ap.add_argument("--store-every", type=int, default=0, help="N > 0: chain on, every N-th step stored (SURVEY s.8(d): C2's second run stores every 100th); single GPU")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-others", action="store_true", help="default c4 line only: skip the short runs of c1/c2/c3/c5 (other_workloads)")
     args = ap.parse_args()
     if args.steps <= 0:
         raise SystemExit("--steps must be positive")

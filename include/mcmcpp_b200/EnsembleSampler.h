@@ -219,7 +219,7 @@ public:
         cfg.num_walkers = numWalker; cfg.num_params = numParameter; cfg.seed = randSeed; cfg.rng_mode = rngMode;
         cfg.alpha_num = Distribution::alphaNum; cfg.alpha_denom = Distribution::alphaDenom;
         cfg.device = 0; cfg.rank = 0; cfg.world = 1; cfg.shard_mode = MCMCPP_SHARD_NONE; cfg.trace_updates = 0;
-        cfg.max_chain_bytes = maxChainSizeBytes; cfg.mover_state_doubles = 0;
+        cfg.max_chain_bytes = maxChainSizeBytes; cfg.mover_state_doubles = 0; cfg.chain_block_steps = 0;
         if (const char* dev = std::getenv("MCMCPP_B200_DEVICE")) cfg.device = std::atoi(dev);
         /* the mover picks its launcher (and, for movers with a variable draw count, per-walker streams) */
         checkStatus(moveProposer.createSampler(cfg, &handle), "EnsembleSampler()");

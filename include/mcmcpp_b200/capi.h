@@ -39,15 +39,21 @@ enum {
  * sequential reference and independent of the GPU count.  PER_WALKER gives walker w its own
  * stream pcg64(seed, w) (the per-thread streams of RedBlkUpdater.h:86 taken to one walker per
  * "thread"); its oracle is one reference StretchMove per walker. */
-enum { MCMCPP_RNG_SEQUENTIAL = 0, MCMCPP_RNG_PER_WALKER = 1 };
+enum { MCMCPP_RNG_SEQUENTIAL = 0, MCMCPP_RNG_PER_WALKER = 1,
+       /* the fast engine: walker w owns pcg32(seed, w) (setseq XSH-RR 64/32, pcg_random.hpp:808-836,1568) and draws
+        * what the reference's facade (Utility/MultiSampler.h:60,86,99) makes of a 32-bit engine: bounded_rand in 32-bit
+        * arithmetic, generate_canonical from two outputs.  Stretch move only.  Oracle: oracle_stretch_run_per_walker32,
+        * pinned on pcg-cpp's check-pcg32.out and on the vendored pcg32 + libstdc++ distributions (oracle/ref_driver.cpp). */
+       MCMCPP_RNG_PER_WALKER32 = 2 };
 
 /* How one ensemble is spread over `world` GPUs (one process per GPU):
  *   NONE       world == 1
  *   ALLGATHER  walker-index shards; after each half-step the updated half is all-gathered with
  *              NCCL so every rank holds the full ensemble (BASELINE.json north_star)
  *   PEER       walker-index shards; partner rows are read straight from the owning GPU's HBM
- *              over NVLink (peer-mapped memory) inside the update kernel, one device-side
- *              barrier per half-step, no bulk exchange
+ *              over NVLink (peer-mapped memory) inside the update kernel; one device-side
+ *              barrier per half-step (epoch flags behind every rank's position array, stored over
+ *              NVLink by a one-CTA kernel; no NCCL call), no bulk exchange
  *   DATA       the Calculator's DATA is sharded, the ensemble is replicated: every rank makes the same draws
  *              and proposals for all W walkers, evaluates its partial log-likelihoods (its rows of the data
  *              matrix, or its slice of a separable sum), the K partials of a colour are summed over ranks with
@@ -56,7 +62,8 @@ enum { MCMCPP_RNG_SEQUENTIAL = 0, MCMCPP_RNG_PER_WALKER = 1 };
  *   DIM        the PARAMETER dimension is sharded, the walkers are replicated: rank r holds columns
  *              [dim_begin, dim_begin + D_local) of every walker row (even-sized slices, see
  *              mcmcpp_dim_slice), makes the same draws as everyone, and a separable Calculator's partial sums are
- *              exchanged by the update kernel itself through peer-mapped tables (NVLink stores), summed in rank
+ *              exchanged by the update kernel itself through peer-mapped tables (8-byte NVLink stores polled by
+ *              their one reader; no flag, no fence, no NCCL), summed in rank
  *              order (include/mcmcpp_b200/dim_shard_kernels.cuh).  Traffic per rank is 1/world of the
  *              single-GPU kernel's and the exchange does not grow with D.  Host-facing arrays keep the full
  *              [W][num_params] shape; a rank reads/writes only its columns of them. */
@@ -85,7 +92,11 @@ typedef struct {
     int32_t trace_updates;     /* >0: record (j, accept, z, e, newp, diff) for the first n updates (tests) */
     uint64_t max_chain_bytes;  /* maxChainSizeBytes (EnsembleSampler.h:67); 0 = keep no chain */
     int32_t mover_state_doubles; /* doubles of per-walker mover state the runtime keeps between updates (0 for the stretch move;
-                                  * 2 for WalkMove: its normal distribution's saved value + flag); zeroed by setInitialWalkerPos */
+                                  * 2 for WalkMove: its normal distribution's saved value + flag); zeroed at creation */
+    int32_t chain_block_steps;   /* 0: the chain holds floor(max_chain_bytes / (8 W D)) rows.  n > 0: the reference's granularity --
+                                  * whole blocks of n steps, max(1, floor(max_chain_bytes / (8 W D n))) of them
+                                  * (Chain/Chain.h:178, ChainBlock.h:31 BlockSize = 10000; the first block always exists, Chain.h:181):
+                                  * runMCMC returns false at the step the reference returns false at */
 } mcmcpp_config;
 
 /* One row of the optional trace, in the sequential update order (step, half, slot). */
@@ -116,7 +127,8 @@ typedef struct {
     uint64_t* rng_state;       /* [W*2] pcg64 state (lo,hi) per walker, positioned at its next draw */
     double* chain_row;         /* device chain slot [W*D] for this step, or NULL when the step is not stored */
     unsigned long long* accept_slots; /* [grid] per-CTA accepted-proposal partial sums */
-    int32_t* flags;            /* [0]: count of bounded_rand redraws seen (sequential-stream cadence broken) */
+    int32_t* flags;            /* [0]: count of bounded_rand redraws seen (sequential-stream cadence broken);
+                                * [1]: a cross-GPU wait timed out (mcmcpp_sampler_run reports it) */
     mcmcpp_trace* trace;       /* trace row of slot 0 of this half-step, or NULL */
     const double* const* peer_pos; /* PEER mode: [world] device pointers to every rank's pos array, else NULL */
     int32_t W, D, K;
@@ -140,18 +152,13 @@ typedef struct {
     int32_t D_total;           /* numParams of the whole row: log(z) * (D_total - 1)  (StretchMove.h:110) */
     int32_t dim_begin;         /* global index of local column 0 */
     int32_t rank, world;
-    double* const* dim_partial;/* [world] every rank's partial table [2 colours][world][K] + flag words [2][world] (own entry local, others peer-mapped) */
+    double* const* dim_partial;/* [world] every rank's partial table [2 colours][world][K] (own entry local, others peer-mapped);
+                                * a slot is all-ones (empty) or a partial sum -- see dim_shard_kernels.cuh */
     double* dim_z;             /* [K] draw scratch: draws of the colour in flight, kept between kernels (all shard modes) */
     double* dim_e;
     int32_t* dim_j;
-    int32_t* dim_list;         /* [K] walkers the commit kernel must touch (bit 31 = accepted) */
-    int32_t* dim_count;        /* [1] entries in dim_list */
     int32_t sm_count;          /* multiprocessors of the device (persistent grids) */
     double* mover_state;       /* [W * mover_state_doubles] per-walker mover state, or NULL */
-    double* sync_word;         /* 1 double: operand of the stream-ordered rendezvous (allreduce_sum of 1 element) */
-    unsigned long long dim_epoch; /* DIM: > 0 = in-kernel rendezvous -- the decide kernel stores this number into every rank's flag
-                                * words (behind the partial table, [2][world]) and waits for all ranks' numbers;
-                                * 0 = stream-ordered rendezvous through allreduce_sum */
 } mcmcpp_halfstep_args;
 
 typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);
@@ -225,6 +232,11 @@ int mcmcpp_sampler_slice_and_burn(mcmcpp_sampler* s, int interval, int burn_in);
 /* ---- chain read side: contiguous host rows [stored][W][D], the layout ChainStepIterator
  *      dereferences to (ChainStepIterator.h:125).  Valid until reset/slice/destroy/run. ---------- */
 int mcmcpp_sampler_chain(mcmcpp_sampler* s, const double** rows_host, long long* stored_steps);
+/* Drops the first `rows` host rows (they have been copied elsewhere): the runtime's pinned rows become a bounded staging
+ * window in front of a chain the CALLER owns -- the C++ drop-in header uses it to fill the reference's own
+ * Chain::Chain / ChainBlock list (Chain/Chain.h:204-236), so the reference's iterators and Analysis classes run on it
+ * unchanged.  Counters and walker state are untouched; getStoredSteps goes down by `rows`. */
+int mcmcpp_sampler_chain_consume(mcmcpp_sampler* s, long long rows);
 
 /* ---- current walker state (Walker::getCurrState / getCurrAuxData, Walker.h:128,134) ---------- */
 int mcmcpp_sampler_get_state(mcmcpp_sampler* s, double* positions_host, double* aux_host);
@@ -241,9 +253,10 @@ int mcmcpp_device_count(void);
 int mcmcpp_fp64_tensor_peak(int device, double* tflops);
 
 /* ---- multi-GPU plumbing (one process per GPU) -------------------------------------------------
- *      ALLGATHER: rank 0 makes an id, the host layer broadcasts the 128 bytes, every rank joins.
- *      PEER / DIM: every rank exports a 64-byte IPC handle (PEER: its pos array; DIM: its partial table), the
- *      host layer all-gathers them, every rank imports the others'. */
+ *      ALLGATHER / DATA: rank 0 makes an id, the host layer broadcasts the 128 bytes, every rank joins (NCCL).
+ *      PEER / DIM: every rank exports a 64-byte IPC handle (PEER: its pos array + barrier flags; DIM: its partial table),
+ *      the host layer all-gathers them, every rank imports the others'.  No NCCL communicator is needed: the ranks
+ *      may even be processes sharing one GPU (CUDA IPC works there; NCCL does not). */
 int mcmcpp_comm_unique_id(void* id128);
 int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128);
 int mcmcpp_sampler_peer_export(mcmcpp_sampler* s, void* handle64);

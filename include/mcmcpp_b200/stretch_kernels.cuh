@@ -30,6 +30,7 @@
 #define MCMCPP_B200_STRETCH_KERNELS_CUH
 
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdlib>
 #include "mcmcpp_b200/capi.h"
 #include "mcmcpp_b200/device_rng.cuh"
@@ -106,8 +107,9 @@ __device__ __forceinline__ WalkerRng loadRng(const mcmcpp_halfstep_args& a, int 
     ulonglong2 s = reinterpret_cast<const ulonglong2*>(a.rng_state)[w];
     r.state.lo = s.x;
     r.state.hi = s.y;
-    /* SEQUENTIAL: the sampler's one stream 0 (EnsembleSampler.h:217); PER_WALKER: stream = walker index */
-    r.inc.lo = (a.rng_mode == MCMCPP_RNG_PER_WALKER) ? ((((uint64_t)w) << 1) | 1ULL) : 1ULL;
+    /* SEQUENTIAL: the sampler's one stream 0 (EnsembleSampler.h:217); PER_WALKER / PER_WALKER32: stream = walker index
+     * (pcg32 keeps its 64-bit state and increment in the low words) */
+    r.inc.lo = (a.rng_mode == MCMCPP_RNG_SEQUENTIAL) ? 1ULL : ((((uint64_t)w) << 1) | 1ULL);
     r.inc.hi = 0;
     return r;
 }
@@ -124,12 +126,6 @@ __device__ __forceinline__ void storeRng(const mcmcpp_halfstep_args& a, int w, W
     reinterpret_cast<ulonglong2*>(a.rng_state)[w] = make_ulonglong2(r.state.lo, r.state.hi);
 }
 
-__device__ __forceinline__ const double* partnerBase(const mcmcpp_halfstep_args& a, int j)
-{
-    /* PEER sharding: the partner row lives in the HBM of the rank that owns slot j (NVLink load) */
-    return a.peer_pos ? a.peer_pos[j / a.slots_per_rank] : a.pos;
-}
-
 __device__ __forceinline__ GwConstants gwOf(const mcmcpp_halfstep_args& a)
 {
     GwConstants g;
@@ -138,12 +134,43 @@ __device__ __forceinline__ GwConstants gwOf(const mcmcpp_halfstep_args& a)
     return g;
 }
 
+/* the three draws of an update from whichever engine the sampler runs (uniform branch on a launch argument) */
+__device__ __forceinline__ StretchDraws drawStretchFor(const mcmcpp_halfstep_args& a, WalkerRng& rng)
+{
+    if (a.rng_mode == MCMCPP_RNG_PER_WALKER32) return drawStretch32(rng.state.lo, rng.inc.lo, (uint32_t)a.K, gwOf(a));
+    return drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+}
+
+/* cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute: one sampler per GPU in one process (cfg.device)
+ * must opt in on each of them.  One instance per kernel instantiation (a function-local static at the launch site). */
+struct DynamicSmemOptIn
+{
+    std::atomic<size_t> bytes[64];
+    template <class Kernel>
+    bool ensure(Kernel kernel, size_t need)
+    {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return false;
+        if (dev < 0 || dev >= 64) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need) == cudaSuccess;
+        if (bytes[dev].load(std::memory_order_relaxed) >= need) return true;
+        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need) != cudaSuccess) return false;
+        bytes[dev].store(need, std::memory_order_relaxed);
+        return true;
+    }
+};
+
+__device__ __forceinline__ const double* partnerBase(const mcmcpp_halfstep_args& a, int j)
+{
+    /* PEER sharding: the partner row lives in the HBM of the rank that owns slot j (NVLink load) */
+    return a.peer_pos ? a.peer_pos[j / a.slots_per_rank] : a.pos;
+}
+
 /* ---- kernel 1: one thread per walker ---------------------------------------------------------- */
 /* D <= 2: 14 CTAs of 128 threads per SM (<= 36 registers) -- 2^19 walkers of a colour are then 1.98 waves on 148 SMs
  * instead of 2.31 at the 12 CTAs the natural 38 registers allow (a third, mostly empty, wave).
  * Load order: rng state, own row and log-prob first (independent of the draws); then the partner index alone, the
  * partner-row load, and only then z and log(1-u) -- ~250 instructions that cover the gather's L2 latency. */
-template <class Calc, int D, bool TRACE>
+template <class Calc, int D, bool TRACE, bool RNG32>
 __global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 14 : 1)) stretchHalfStepThread(const mcmcpp_halfstep_args a, const Calc calcIn)
 {
     const int i = blockIdx.x * ThreadKernelThreads + threadIdx.x;
@@ -160,7 +187,8 @@ __global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 14 : 1)) stretc
         loadRow<D>(ownRow, cur);
         const double oldp = a.logp[w];
         StretchDraws dr;
-        dr.j = drawPartner(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, dr.redraws);
+        if (RNG32) { dr.redraws = 0; dr.j = drawPartner32(rng.state.lo, rng.inc.lo, (uint32_t)a.K); }
+        else dr.j = drawPartner(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, dr.redraws);
         /* Programmatic dependent launch: everything above reads what THIS colour's previous launch (two launches back,
          * complete) wrote; only the partner rows come from the launch right before.  Wait for it here, then let the next
          * launch start its own preamble on the SM slots this one's last, partly filled wave leaves idle (it reads what
@@ -168,7 +196,8 @@ __global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 14 : 1)) stretc
         asm volatile("griddepcontrol.wait;" ::: "memory");
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         loadRowReadOnly<D>(partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D, prop);
-        drawScaleAndTest(rng.state, rng.inc, gwOf(a), dr.z, dr.logOneMinusU);
+        if (RNG32) drawScaleAndTest32(rng.state.lo, rng.inc.lo, gwOf(a), dr.z, dr.logOneMinusU);
+        else drawScaleAndTest(rng.state, rng.inc, gwOf(a), dr.z, dr.logOneMinusU);
         storeRng(a, w, rng);
         if (dr.redraws) atomicAdd(a.flags, dr.redraws);
 #pragma unroll
@@ -263,7 +292,7 @@ __global__ void __launch_bounds__(WarpKernelThreads) stretchHalfStepWarp(const m
 
     /* every lane replays the same three draws (cheaper than a broadcast of six registers) */
     WalkerRng rng = loadRng(a, w);
-    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    StretchDraws dr = drawStretchFor(a, rng);
     /* programmatic dependent launch (see stretchHalfStepThread): the draws read only this colour's rng state */
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -393,7 +422,7 @@ static __global__ void __launch_bounds__(256) stretchDrawKernel(const mcmcpp_hal
     if (i >= a.slot_count) return;
     const int w = a.half * a.K + a.slot_begin + i;
     WalkerRng rng = loadRng(a, w);
-    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    StretchDraws dr = drawStretchFor(a, rng);
     storeRng(a, w, rng);
     if (dr.redraws) atomicAdd(a.flags, dr.redraws);
     a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
@@ -423,7 +452,7 @@ __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_h
         dr.j = a.dim_j[i]; dr.z = a.dim_z[i]; dr.logOneMinusU = a.dim_e[i]; dr.redraws = 0;
     } else {
         rng = loadRng(a, w);
-        dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+        dr = drawStretchFor(a, rng);
     }
     double* ownRow = a.pos + (size_t)w * D;
     const double* selRow = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
@@ -514,8 +543,11 @@ int launchThreadKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStre
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    cudaError_t rc = a.trace ? cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, true>, a, calc)
-                             : cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, false>, a, calc);
+    const bool rng32 = a.rng_mode == MCMCPP_RNG_PER_WALKER32;
+    cudaError_t rc = a.trace ? (rng32 ? cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, true, true>, a, calc)
+                                      : cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, true, false>, a, calc))
+                             : (rng32 ? cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, false, true>, a, calc)
+                                      : cudaLaunchKernelEx(&cfg, stretchHalfStepThread<Calc, D, false, false>, a, calc));
     return rc == cudaSuccess ? launchStatus() : MCMCPP_ERR_CUDA;
 }
 
@@ -536,8 +568,8 @@ int launchWarpKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
 #define MCMCPP_LAUNCH_WARP(V, T)                                                                             \
     do {                                                                                                     \
-        if (smem > 48 * 1024)                                                                                \
-            cudaFuncSetAttribute(stretchHalfStepWarp<Calc, NCHUNK, V, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        static DynamicSmemOptIn optIn;                                                                       \
+        if (smem > 48 * 1024 && !optIn.ensure(stretchHalfStepWarp<Calc, NCHUNK, V, T>, smem)) return MCMCPP_ERR_CUDA; \
         if (cudaLaunchKernelEx(&cfg, stretchHalfStepWarp<Calc, NCHUNK, V, T>, a, calc) != cudaSuccess) return MCMCPP_ERR_CUDA; \
     } while (0)
     if (vec) { if (a.trace) MCMCPP_LAUNCH_WARP(true, true); else MCMCPP_LAUNCH_WARP(true, false); }
@@ -549,8 +581,8 @@ int launchWarpKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream
 template <class Calc, int WARPS, bool TRACE, bool PRE>
 int launchBulkKernelWTP(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride, int grid, size_t smem)
 {
-    static bool attrDone = false;
-    if (!attrDone) { cudaFuncSetAttribute(stretchHalfStepBulk<Calc, WARPS, TRACE, PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attrDone = true; }
+    static DynamicSmemOptIn optIn;
+    if (!optIn.ensure(stretchHalfStepBulk<Calc, WARPS, TRACE, PRE>, 227 * 1024)) return MCMCPP_ERR_CUDA;
     stretchHalfStepBulk<Calc, WARPS, TRACE, PRE><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
     return launchStatus();
 }
@@ -613,7 +645,6 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedSmall(const mc
     skip.mult.lo = a.skip_mult[0]; skip.mult.hi = a.skip_mult[1];
     skip.plus.lo = a.skip_plus[0]; skip.plus.hi = a.skip_plus[1];
     const bool sequential = a.rng_mode == MCMCPP_RNG_SEQUENTIAL;
-    const GwConstants gw = gwOf(a);
     unsigned long long accepted = 0;
     unsigned redraws = 0;
     __syncthreads();
@@ -625,7 +656,7 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedSmall(const mc
         for (int half = 0; half < 2; ++half) {
             if (live) {
                 const int w = half * K + t, other0 = (1 - half) * K;
-                StretchDraws dr = drawStretch(rng[half].state, rng[half].inc, (uint64_t)K, a.bound_threshold, a.bound_recip, gw);
+                StretchDraws dr = drawStretchFor(a, rng[half]);
                 if (sequential) rng[half].state = applyAffine(skip, rng[half].state);   /* storeRng: over the other walkers' draws */
                 redraws += (unsigned)dr.redraws;
                 double cur[D], prop[D];
@@ -679,9 +710,8 @@ struct FusedLauncher
     {
         const mcmcpp_halfstep_args& a = f.base;
         const size_t smem = sizeof(double) * ((size_t)2 * a.K * D + (size_t)2 * a.K);
-        if (smem > 48 * 1024 &&
-            cudaFuncSetAttribute(stretchFusedSmall<Calc, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
-            return MCMCPP_ERR_CUDA;
+        static DynamicSmemOptIn optIn;
+        if (smem > 48 * 1024 && !optIn.ensure(stretchFusedSmall<Calc, D>, smem)) return MCMCPP_ERR_CUDA;
         const int threads = ((a.K + 31) / 32) * 32;
         stretchFusedSmall<Calc, D><<<1, threads, smem, stream>>>(f, calc);
         return launchStatus();

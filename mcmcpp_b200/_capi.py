@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(HERE, "libmcmcpp_b200.so")
 
 OK, CHAIN_FULL = 0, 1
 ERR_ARG, ERR_CUDA, ERR_NCCL, ERR_STATE, ERR_UNSUPPORTED = -1, -2, -3, -4, -5
-RNG_SEQUENTIAL, RNG_PER_WALKER = 0, 1
+RNG_SEQUENTIAL, RNG_PER_WALKER, RNG_PER_WALKER32 = 0, 1, 2
 SHARD_NONE, SHARD_ALLGATHER, SHARD_PEER, SHARD_DATA, SHARD_DIM = 0, 1, 2, 3, 4
 TARGET = {"skewed_gauss_2d": 0, "rosenbrock_2d": 1, "diag_gauss": 2, "dense_gauss": 3, "linreg": 4}
 
@@ -21,7 +21,7 @@ class Config(C.Structure):
                 ("rng_mode", C.c_int32), ("alpha_num", C.c_int32), ("alpha_denom", C.c_int32),
                 ("device", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
                 ("shard_mode", C.c_int32), ("trace_updates", C.c_int32), ("max_chain_bytes", C.c_uint64),
-                ("mover_state_doubles", C.c_int32)]
+                ("mover_state_doubles", C.c_int32), ("chain_block_steps", C.c_int32)]
 
 
 class Trace(C.Structure):
@@ -49,6 +49,7 @@ SYMBOLS = {
     "mcmcpp_sampler_store_current": (C.c_int, [_h]),
     "mcmcpp_sampler_slice_and_burn": (C.c_int, [_h, C.c_int, C.c_int]),
     "mcmcpp_sampler_chain": (C.c_int, [_h, C.POINTER(_dp), C.POINTER(C.c_longlong)]),
+    "mcmcpp_sampler_chain_consume": (C.c_int, [_h, C.c_longlong]),
     "mcmcpp_sampler_get_state": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
     "mcmcpp_sampler_state_device": (C.c_int, [_h, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "mcmcpp_sampler_get_trace": (C.c_int, [_h, C.c_void_p, C.c_int, C.POINTER(C.c_int)]),

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
             if (tile < numTiles && i < a.slot_count) {
                 const int w = a.half * a.K + a.slot_begin + i;
                 WalkerRng rng = loadRng(a, w);
-                StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+                StretchDraws dr = drawStretchFor(a, rng);
                 storeRng(a, w, rng);
                 if (dr.redraws) atomicAdd(a.flags, dr.redraws);
                 bJ[tid] = dr.j; bZ[tid] = dr.z; bE[tid] = dr.logOneMinusU;
@@ -309,7 +309,7 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     if (grid > a.max_grid) grid = a.max_grid;
     static const int useToken = [] { const char* e = getenv("MCMCPP_B200_DENSE_TOKEN"); return (e && e[0] == '0') ? 0 : 1; }();
     /* opt in to exactly what this shape needs (the kernel also has a few bytes of static shared memory) */
-    static size_t optedIn[2] = {0, 0};
+    static DynamicSmemOptIn optedIn[2];                       /* keyed by device inside */
     long long* tl = denseTimeline();
     static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
     cudaLaunchConfig_t cfg = {};
@@ -319,16 +319,10 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
     if (a.trace) {
-        if (smem > optedIn[1]) {
-            if (cudaFuncSetAttribute(denseGaussHalfStep<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
-            optedIn[1] = smem;
-        }
+        if (!optedIn[1].ensure(denseGaussHalfStep<NB, true>, smem)) return MCMCPP_ERR_CUDA;
         if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, true>, a, c.P, useToken, tl) != cudaSuccess) return MCMCPP_ERR_CUDA;
     } else {
-        if (smem > optedIn[0]) {
-            if (cudaFuncSetAttribute(denseGaussHalfStep<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return MCMCPP_ERR_CUDA;
-            optedIn[0] = smem;
-        }
+        if (!optedIn[0].ensure(denseGaussHalfStep<NB, false>, smem)) return MCMCPP_ERR_CUDA;
         if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, false>, a, c.P, useToken, tl) != cudaSuccess) return MCMCPP_ERR_CUDA;
     }
     return launchStatus();

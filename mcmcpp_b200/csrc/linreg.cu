@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(LrThreads) linregPropose(const mcmcpp_halfstep
     const int w = a.half * a.K + a.slot_begin + i;
     const int other0 = (1 - a.half) * a.K;
     WalkerRng rng = loadRng(a, w);
-    StretchDraws dr = drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
+    StretchDraws dr = drawStretchFor(a, rng);
     storeRng(a, w, rng);
     if (dr.redraws) atomicAdd(a.flags, dr.redraws);
     const double* own = a.pos + (size_t)w * D;
@@ -234,9 +234,9 @@ __global__ void __launch_bounds__(LrThreads) linregAccept(const mcmcpp_halfstep_
 template <int KS>
 int launchSse(const LinregState& st, cudaStream_t stream)
 {
-    static bool attr = false;
+    static DynamicSmemOptIn optIn;                            /* per device */
     const size_t smem = sizeof(double) * (size_t)LrStages * LrTileM * st.stride;
-    if (!attr) { cudaFuncSetAttribute(linregSse<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
+    if (!optIn.ensure(linregSse<KS>, 200 * 1024)) return MCMCPP_ERR_CUDA;
     dim3 grid((unsigned)(st.Kpad / LrTileN), (unsigned)st.S);
     linregSse<KS><<<grid, LrThreads, smem, stream>>>(st);
     return launchStatus();

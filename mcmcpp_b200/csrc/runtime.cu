@@ -96,7 +96,11 @@ __global__ void initRngKernel(uint64_t* rngState, int W, int K, uint64_t seed, i
     const int w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= W) return;
     MCMC::Device::Pcg64 g;
-    if (rngMode == MCMCPP_RNG_PER_WALKER) {
+    if (rngMode == MCMCPP_RNG_PER_WALKER32) {
+        uint64_t inc;                                         /* pcg32(seed, w): 64-bit state in the low word */
+        g.state.lo = MCMC::Device::pcg32Seed(seed, (uint64_t)w, inc);
+        g.state.hi = 0;
+    } else if (rngMode == MCMCPP_RNG_PER_WALKER) {
         g = MCMC::Device::pcg64Seed(seed, (uint64_t)w);
     } else {
         /* sequential order inside step 0: red slots 0..K-1 then black slots 0..K-1, 3 draws each;
@@ -120,6 +124,42 @@ __global__ void sumSlotsKernel(const unsigned long long* slots, int n, unsigned 
         __syncthreads();
     }
     if (threadIdx.x == 0 && partial[0]) atomicAdd(out, partial[0]);     /* integer sum: order does not matter */
+}
+
+/* PEER sharding: device-side barrier over the ranks.  Behind every rank's position array sit `world` epoch words; thread
+ * r stores this barrier's number into word [rank] of rank r (an NVLink store) and waits until word [r] of its own array has
+ * reached it.  Runs after the update kernel in stream order, so this rank's rows are complete when its number goes out.
+ * A wait that sees nothing for timeoutNs sets flags[1] (reported by mcmcpp_sampler_run) instead of spinning for ever. */
+__global__ void peerBarrierKernel(const double* const* peerPos, size_t flagOffsetDoubles, int rank, int world, unsigned long long epoch,
+                                  int32_t* flags, unsigned long long timeoutNs)
+{
+    const int r = threadIdx.x;
+    if (r >= world) return;
+    __threadfence_system();
+    volatile unsigned long long* theirs = reinterpret_cast<volatile unsigned long long*>(const_cast<double*>(peerPos[r]) + flagOffsetDoubles);
+    theirs[rank] = epoch;
+    const volatile unsigned long long* mine = reinterpret_cast<const volatile unsigned long long*>(peerPos[rank] + flagOffsetDoubles) + r;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    unsigned spins = 0;
+    while (*mine < epoch) {
+        __nanosleep(64);
+        if ((++spins & 1023u) == 0) {
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > timeoutNs) { atomicExch(flags + 1, 1); break; }
+        }
+    }
+    __threadfence_system();
+}
+
+unsigned long long rendezvousTimeoutNs()
+{
+    static const unsigned long long ns = [] {
+        const char* e = getenv("MCMCPP_B200_RDV_TIMEOUT_MS");
+        return (unsigned long long)(e ? atoi(e) : 20000) * 1000000ULL;
+    }();
+    return ns;
 }
 
 }  // namespace
@@ -173,7 +213,8 @@ struct mcmcpp_sampler
     int moverDoubles = 0;
     /* PostStepAction with a device-resident step view (EnsembleSampler.h:356-359) */
     mcmcpp_step_fn stepFn = nullptr;
-    unsigned long long dimEpoch = 0;       /* DIM: colours launched so far (in-kernel rendezvous number) */
+    unsigned long long peerEpoch = 0;      /* PEER: barriers issued so far (every rank makes the same calls) */
+    bool peerNeedsBarrier = false;         /* PEER: rows changed by the host since the last barrier (set_initial / restore) */
     mcmcpp_fused_fn fusedFn = nullptr;     /* small ensembles: the whole runMCMC loop in one launch */
     double* dFusedChain = nullptr;         /* [fusedRows][W][D] rows filled by the fused kernel */
     long long fusedRows = 0;
@@ -188,8 +229,6 @@ struct mcmcpp_sampler
     double* dDimZ = nullptr;
     double* dDimE = nullptr;
     int32_t* dDimJ = nullptr;
-    int32_t* dDimList = nullptr;           /* [K] + [1] count */
-    double* dSyncWord = nullptr;
 };
 
 namespace
@@ -252,16 +291,21 @@ int ensureDeviceChain(mcmcpp_sampler* s)
     return MCMCPP_OK;
 }
 
+int peerBarrier(mcmcpp_sampler* s)
+{
+    peerBarrierKernel<<<1, 32, 0, s->stream>>>(s->dPeerPos, devRowDoubles(s), s->cfg.rank, s->cfg.world, ++s->peerEpoch, s->dFlags,
+                                               rendezvousTimeoutNs());
+    CUDA_TRY(cudaGetLastError());
+    ++s->launches;
+    return MCMCPP_OK;
+}
+
 /* one colour: kernel launch (+ the exchange that makes the updated half visible to every rank) */
 int halfStep(mcmcpp_sampler* s, int half, double* chainRow)
 {
     mcmcpp_halfstep_args a = s->base;
     a.half = half;
     a.chain_row = chainRow;
-    if (s->cfg.shard_mode == MCMCPP_SHARD_DIM) {
-        static const bool flags = [] { const char* e = getenv("MCMCPP_B200_DIM_FLAGS"); return !(e && e[0] == '0'); }();
-        a.dim_epoch = flags ? ++s->dimEpoch : 0;      /* every rank makes the same calls, so the epochs agree */
-    }
     a.trace = nullptr;
     a.trace_rows = 0;
     if (s->dTrace) {
@@ -282,8 +326,9 @@ int halfStep(mcmcpp_sampler* s, int half, double* chainRow)
             NCCL_TRY(nccl().AllGather(halfBase + (size_t)s->slotBegin * s->D, halfBase, (size_t)s->slotCount * s->D,
                                    ncclDouble, s->comm, s->stream));
         } else if (s->cfg.shard_mode == MCMCPP_SHARD_PEER) {
-            /* stream-ordered rendezvous: nobody starts the other colour before everyone finished this one */
-            NCCL_TRY(nccl().AllReduce(s->dBarrier, s->dBarrier, 1, ncclInt32, ncclSum, s->comm, s->stream));
+            /* nobody starts the other colour before everyone has finished this one */
+            int rc2 = peerBarrier(s);
+            if (rc2 != MCMCPP_OK) return rc2;
         }
     }
     return MCMCPP_OK;
@@ -315,6 +360,8 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     /* the reference's ctor asserts (EnsembleSampler.h:207-208) */
     if (W <= 0 || D <= 0 || (W % 2) != 0 || W <= 2 * D) return fail(MCMCPP_ERR_ARG, "numWalkers must be even and exceed 2*numParams");
     if (cfg->alpha_num <= 0 || cfg->alpha_denom <= 0) return fail(MCMCPP_ERR_ARG, "alpha must be positive");
+    if (cfg->rng_mode < MCMCPP_RNG_SEQUENTIAL || cfg->rng_mode > MCMCPP_RNG_PER_WALKER32) return fail(MCMCPP_ERR_ARG, "unknown rng mode");
+    if (cfg->chain_block_steps < 0) return fail(MCMCPP_ERR_ARG, "chain_block_steps must be >= 0");
     if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world) return fail(MCMCPP_ERR_ARG, "bad rank/world");
     if (cfg->shard_mode == MCMCPP_SHARD_DIM && D / 2 < cfg->world)
         return fail(MCMCPP_ERR_ARG, "DIM sharding needs at least two columns per GPU");
@@ -341,6 +388,13 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
         s->slotBegin = cfg->rank * s->slotCount;
     }
     s->capRows = (long long)(cfg->max_chain_bytes / (sizeof(double) * (unsigned long long)W * (unsigned long long)D));
+    if (cfg->chain_block_steps > 0 && cfg->max_chain_bytes > 0) {
+        /* the reference's granularity: maxBlocks = maxSize / (sizeof * numParams * BlockSize * numWalkers) whole blocks, and the
+         * first block is allocated whatever maxBlocks says (Chain/Chain.h:178-186,218-233) */
+        const unsigned long long blockBytes = sizeof(double) * (unsigned long long)W * (unsigned long long)D * (unsigned long long)cfg->chain_block_steps;
+        const unsigned long long blocks = std::max<unsigned long long>(1ULL, cfg->max_chain_bytes / blockBytes);
+        s->capRows = (long long)(blocks * (unsigned long long)cfg->chain_block_steps);
+    }
     *out = s;   /* destroy() cleans up on later failure */
 
     CUDA_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
@@ -352,7 +406,10 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
         CUDA_TRY(cudaEventCreateWithFlags(&s->slotFree[i], cudaEventDisableTiming));
     }
     s->maxGrid = s->K;   /* upper bound for any launcher: one CTA per walker */
-    CUDA_TRY(cudaMalloc(&s->dPos, sizeof(double) * devRowDoubles(s)));
+    /* PEER: `world` barrier epoch words sit behind the rows, inside the one allocation the IPC handle exports */
+    const size_t posTail = cfg->shard_mode == MCMCPP_SHARD_PEER ? (size_t)cfg->world + 2 : 0;
+    CUDA_TRY(cudaMalloc(&s->dPos, sizeof(double) * (devRowDoubles(s) + posTail)));
+    if (posTail) CUDA_TRY(cudaMemset(s->dPos + devRowDoubles(s), 0, sizeof(double) * posTail));
     CUDA_TRY(cudaMalloc(&s->dLogp, sizeof(double) * (size_t)W));
     CUDA_TRY(cudaMalloc(&s->dRng, sizeof(uint64_t) * 2 * (size_t)W));
     CUDA_TRY(cudaMalloc(&s->dAcceptSlots, sizeof(unsigned long long) * (size_t)s->maxGrid));
@@ -373,15 +430,11 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
     CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * (size_t)s->K));
     if (cfg->shard_mode == MCMCPP_SHARD_DIM) {
-        /* partial table + [2][world] flag words of the in-kernel rendezvous (dim_shard_kernels.cuh) */
-        const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K + 2 * (size_t)cfg->world + 2;
+        /* partial table [2 colours][world][K]; every slot starts EMPTY (all-ones, dim_shard_kernels.cuh) */
+        const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K;
         CUDA_TRY(cudaMalloc(&s->dDimPartial, sizeof(double) * tableDoubles));
-        CUDA_TRY(cudaMemset(s->dDimPartial, 0, sizeof(double) * tableDoubles));
+        CUDA_TRY(cudaMemset(s->dDimPartial, 0xFF, sizeof(double) * tableDoubles));
         CUDA_TRY(cudaMalloc(&s->dDimTable, sizeof(double*) * (size_t)cfg->world));
-        CUDA_TRY(cudaMalloc(&s->dDimList, sizeof(int32_t) * ((size_t)s->K + 1)));
-        CUDA_TRY(cudaMemset(s->dDimList, 0, sizeof(int32_t) * ((size_t)s->K + 1)));
-        CUDA_TRY(cudaMalloc(&s->dSyncWord, sizeof(double)));
-        CUDA_TRY(cudaMemset(s->dSyncWord, 0, sizeof(double)));
         if (cfg->world == 1) CUDA_TRY(cudaMemcpy(s->dDimTable, &s->dDimPartial, sizeof(double*), cudaMemcpyHostToDevice));
     }
     if (cfg->trace_updates > 0) {
@@ -396,9 +449,8 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     a.accept_slots = s->dAcceptSlots; a.flags = s->dFlags;
     a.W = W; a.D = s->Dl; a.K = s->K;
     a.D_total = D; a.dim_begin = s->dimBegin; a.rank = cfg->rank; a.world = cfg->world;
-    a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ; a.sync_word = s->dSyncWord;
+    a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ;
     a.mover_state = s->dMoverState;
-    a.dim_list = s->dDimList; a.dim_count = s->dDimList ? s->dDimList + s->K : nullptr;
     { int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device); a.sm_count = sms; }
     a.slot_begin = s->slotBegin; a.slot_count = s->slotCount; a.slots_per_rank = s->slotCount;
     a.rng_mode = cfg->rng_mode;
@@ -413,17 +465,19 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     a.gw_term1 = gw.term1; a.gw_inv_sqrt_alpha = gw.invSqrtAlpha;
     a.max_grid = s->maxGrid;
     a.launch_count = &s->launches;
+    /* The engine is seeded ONCE, here, as the reference seeds its mover in the sampler's constructor (EnsembleSampler.h:217);
+     * setInitialWalkerPos never touches it (EnsembleSampler.h:220-230), so a second placement continues the stream. */
+    initRngKernel<<<(s->W + 255) / 256, 256, 0, s->stream>>>(s->dRng, s->W, s->K, (uint64_t)cfg->seed, cfg->rng_mode);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
     return MCMCPP_OK;
 }
 
 int afterInitialState(mcmcpp_sampler* s, const double* hostRowOrNull)
 {
-    /* rng positioned for step 0; counters as after Walker::setFirstPoint (Walker.h:76,162-170) */
-    initRngKernel<<<(s->W + 255) / 256, 256, 0, s->stream>>>(s->dRng, s->W, s->K, (uint64_t)s->cfg.seed, s->cfg.rng_mode);
-    CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaMemsetAsync(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid, s->stream));
-    CUDA_TRY(cudaMemsetAsync(s->dFlags, 0, sizeof(int32_t) * 4, s->stream));
-    if (s->dMoverState) CUDA_TRY(cudaMemsetAsync(s->dMoverState, 0, sizeof(double) * (size_t)s->W * (size_t)s->moverDoubles, s->stream));
+    /* counters as after Walker::setFirstPoint (Walker.h:76,162-170): one more accepted step per walker, nothing reset;
+     * the engine and the mover's state keep going (the reference's setInitialWalkerPos touches neither) */
+    s->peerNeedsBarrier = true;
     const unsigned long long owned = 2ULL * (unsigned long long)s->slotCount;
     s->acceptedBase += owned;
     s->totalSteps += owned;
@@ -525,7 +579,7 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     cudaFree(s->dPeerPos);
     cudaFree(s->dMoverState);
     cudaFree(s->dFusedChain);
-    cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ); cudaFree(s->dDimList); cudaFree(s->dSyncWord);
+    cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ);
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
     cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
     mcmcpp_builtin_release(s->builtinAux);
@@ -597,7 +651,8 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
     if (!s->initialised) return fail(MCMCPP_ERR_STATE, "runMCMC before setInitialWalkerPos");
     if (num_steps <= 0) return fail(MCMCPP_ERR_ARG, "numSteps must be positive");           /* RedBlkCtrlerSpinLock.h:188 */
-    if (s->cfg.world > 1 && !s->comm) return fail(MCMCPP_ERR_STATE, "world > 1 but no communicator (mcmcpp_sampler_comm_init)");
+    if (s->cfg.world > 1 && !s->comm && (s->cfg.shard_mode == MCMCPP_SHARD_ALLGATHER || s->cfg.shard_mode == MCMCPP_SHARD_DATA))
+        return fail(MCMCPP_ERR_STATE, "world > 1 but no communicator (mcmcpp_sampler_comm_init)");
     if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_PEER && !s->dPeerPos)
         return fail(MCMCPP_ERR_STATE, "PEER sharding needs mcmcpp_sampler_peer_import");
     if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_DIM && s->peerOpened.empty())
@@ -611,6 +666,11 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     }
     const int perStored = s->subSampling ? s->interval : 1;
     int status = MCMCPP_OK;
+    if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_PEER && s->peerNeedsBarrier) {
+        /* the first colour reads partner rows from the other ranks: their setInitialWalkerPos / restore copies must have landed */
+        if ((rc = peerBarrier(s)) != MCMCPP_OK) return rc;
+        s->peerNeedsBarrier = false;
+    }
     CUDA_TRY(cudaEventRecord(s->evStart, s->stream));
     static const bool fusedAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED"); return !(e && e[0] == '0'); }();
     const bool fused = fusedAllowed && s->fusedFn && s->cfg.world == 1 && s->cfg.shard_mode == MCMCPP_SHARD_NONE && !s->stepFn && !s->cov
@@ -683,6 +743,12 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->copyStream));
     if (device_ms) CUDA_TRY(cudaEventElapsedTime(device_ms, s->evStart, s->evStop));
+    if (s->cfg.world > 1) {
+        int32_t timedOut = 0;
+        CUDA_TRY(cudaMemcpy(&timedOut, s->dFlags + 1, sizeof timedOut, cudaMemcpyDeviceToHost));
+        if (timedOut) return fail(MCMCPP_ERR_STATE, "a cross-GPU wait timed out (a peer rank died, or never made the matching runMCMC call); "
+                                                    "walker state is undefined from here (MCMCPP_B200_RDV_TIMEOUT_MS sets the limit)");
+    }
     return status;
 }
 
@@ -763,6 +829,19 @@ int mcmcpp_sampler_chain(mcmcpp_sampler* s, const double** rows_host, long long*
     return MCMCPP_OK;
 }
 
+int mcmcpp_sampler_chain_consume(mcmcpp_sampler* s, long long rows)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    const long long have = s->capRows > 0 ? std::min(s->stored, s->capRows) : s->stored;
+    if (rows < 0 || rows > have) return fail(MCMCPP_ERR_ARG, "cannot consume more rows than are stored");
+    if (rows == 0) return MCMCPP_OK;
+    const size_t row = rowDoubles(s);
+    if (s->hChain && have > rows) std::memmove(s->hChain, s->hChain + row * (size_t)rows, sizeof(double) * row * (size_t)(have - rows));
+    s->stored -= rows;
+    for (int i = 0; i < ChainSlots; ++i) s->slotBusy[i] = false;      /* run() left the side stream idle */
+    return MCMCPP_OK;
+}
+
 int mcmcpp_sampler_get_state(mcmcpp_sampler* s, double* positions_host, double* aux_host)
 {
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
@@ -831,7 +910,7 @@ int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128)
     ncclUniqueId id;
     std::memcpy(&id, id128, sizeof id);
     NCCL_TRY(nccl().CommInitRank(&s->comm, s->cfg.world, id, s->cfg.rank));
-    if (s->cfg.shard_mode == MCMCPP_SHARD_DATA || s->cfg.shard_mode == MCMCPP_SHARD_DIM) {
+    if (s->cfg.shard_mode == MCMCPP_SHARD_DATA) {
         s->base.allreduce_sum = &allreduceSum;
         s->base.allreduce_ctx = s;
     }
@@ -1041,6 +1120,7 @@ int mcmcpp_sampler_checkpoint_restore(mcmcpp_sampler* s, const void* buffer, siz
     s->ensembleSteps = h.ensembleSteps;
     s->stored = 0;
     s->initialised = true;
+    s->peerNeedsBarrier = true;
     return MCMCPP_OK;
 }
 

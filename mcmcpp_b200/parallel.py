@@ -59,18 +59,20 @@ def env_rank_world():
 
 
 def connect(sampler, group=None):
-    """Collective over all ranks: give `sampler` (created with rank/world/shardMode) its NCCL
-    communicator and, for PEER sharding, the other ranks' position arrays."""
+    """Collective over all ranks: give `sampler` (created with rank/world/shardMode) what its shard mode exchanges
+    through -- ALLGATHER / DATA: an NCCL communicator; PEER / DIM: the other ranks' peer-mapped arrays (CUDA IPC
+    handles; no NCCL, so the ranks may be processes sharing one GPU)."""
     import torch.distributed as dist
     if sampler.world == 1:
         return
-    ident = [None]
-    if sampler.rank == 0:
-        buf = C.create_string_buffer(128)
-        _capi.check(_capi.lib().mcmcpp_comm_unique_id(buf))
-        ident[0] = buf.raw
-    dist.broadcast_object_list(ident, src=0, group=group)
-    sampler.commInit(ident[0])
+    if sampler.shardMode in ("allgather", "data"):
+        ident = [None]
+        if sampler.rank == 0:
+            buf = C.create_string_buffer(128)
+            _capi.check(_capi.lib().mcmcpp_comm_unique_id(buf))
+            ident[0] = buf.raw
+        dist.broadcast_object_list(ident, src=0, group=group)
+        sampler.commInit(ident[0])
     if sampler.shardMode in ("peer", "dim"):
         handles = [None] * sampler.world
         dist.all_gather_object(handles, sampler.peerExport(), group=group)

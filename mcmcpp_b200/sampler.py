@@ -120,13 +120,16 @@ class EnsembleSampler:
     spread over `world` GPUs, one process per GPU).
 
     Extra keyword arguments have no counterpart in the reference and default to its behaviour:
-      rngMode      "sequential" (bit parity with the reference's single stream) | "per_walker"
+      rngMode      "sequential" (bit parity with the reference's single stream) | "per_walker" (pcg64(seed, w)) |
+                   "per_walker32" (pcg32(seed, w), the fast engine; stretch move only)
+      chainBlockSteps  0: the chain is capped at floor(maxChainSizeBytes / row bytes) rows; 10000: the reference's
+                   whole-block granularity (Chain/Chain.h:178), runMCMC returns False exactly where the reference does
       traceUpdates record the first n updates' (j, accept, z, e, newp, diff) for tests
       device/rank/world/shardMode  multi-GPU placement (see capi.h)
     """
 
     def __init__(self, randSeed, numWalker, numParameter, move, maxChainSizeBytes=2147483648, stepAct=None,
-                 rngMode="sequential", traceUpdates=0, device=0, rank=0, world=1, shardMode="none"):
+                 rngMode="sequential", traceUpdates=0, device=0, rank=0, world=1, shardMode="none", chainBlockSteps=0):
         if not isinstance(move, (StretchMove, DifferentialEvolution, WalkMove)):
             raise TypeError("the B200 path implements Mover::StretchMove, Mover::DifferentialEvolution and Mover::WalkMove")
         if isinstance(move, (DifferentialEvolution, WalkMove)):
@@ -139,11 +142,11 @@ class EnsembleSampler:
         self.rank, self.world = int(rank), int(world)
         cfg = _capi.Config(
             num_walkers=self.numWalkers, num_params=self.numParams, seed=int(randSeed),
-            rng_mode={"sequential": _capi.RNG_SEQUENTIAL, "per_walker": _capi.RNG_PER_WALKER}[rngMode],
+            rng_mode={"sequential": _capi.RNG_SEQUENTIAL, "per_walker": _capi.RNG_PER_WALKER, "per_walker32": _capi.RNG_PER_WALKER32}[rngMode],
             alpha_num=move.alpha[0], alpha_denom=move.alpha[1], device=int(device), rank=self.rank, world=self.world,
             shard_mode={"none": _capi.SHARD_NONE, "allgather": _capi.SHARD_ALLGATHER, "peer": _capi.SHARD_PEER,
                         "data": _capi.SHARD_DATA, "dim": _capi.SHARD_DIM}[shardMode],
-            trace_updates=int(traceUpdates), max_chain_bytes=int(maxChainSizeBytes))
+            trace_updates=int(traceUpdates), max_chain_bytes=int(maxChainSizeBytes), chain_block_steps=int(chainBlockSteps))
         self.shardMode = shardMode
         params = np.ascontiguousarray(move.calc.params(), dtype=np.float64)
         self._h = C.c_void_p()

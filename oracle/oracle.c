@@ -344,6 +344,78 @@ int oracle_stretch_run_per_walker(pcg64_t* rng, int kind, const double* tparams,
     return rejections;
 }
 
+/*
+ * PER_WALKER32 rng discipline (the fast device engine): walker w owns pcg32(seed, stream = w) -- the reference's
+ * facade (Utility/MultiSampler.h:54,60,86,99) with the vendored 32-bit engine (pcg_random.hpp:1568) in place of pcg64:
+ *   j    engine(K)                     bounded_rand in 32-bit arithmetic (pcg_extras.hpp:514-525)
+ *   u    generate_canonical<double,53> two outputs, low word first: (r0 + r1 * 2^32) / 2^64, below 1
+ *                                      (libstdc++ bits/random.tcc:3346-3381 with k = 2)
+ *   z    GwDistribution(u), e = log(1 - u) as for pcg64
+ * Same update arithmetic and red-then-black order as oracle_stretch_run.  rng [W] carries every walker's engine.
+ * Pinned against pcg-cpp's check-pcg32.out and against oracle/ref_driver.cpp:ref_stretch_run_pcg32 (vendored pcg32 +
+ * libstdc++ distributions + the reference's GwDistribution), see tests/golden/pcg32_*.npz.
+ */
+void oracle_pcg32_seed_many(pcg32_t* g, uint64_t seed, int W)
+{
+    for (int w = 0; w < W; ++w) oracle_pcg32_seed_stream(&g[w], seed, (uint64_t)w);
+}
+
+static uint32_t oracle_pcg32_bounded(pcg32_t* g, uint32_t bound)
+{
+    uint32_t threshold = (0u - bound) % bound;
+    for (;;) {
+        uint32_t r = oracle_pcg32_next(g);
+        if (r >= threshold) return r % bound;
+    }
+}
+
+static double oracle_pcg32_unit(pcg32_t* g)
+{
+    uint64_t lo = oracle_pcg32_next(g);
+    uint64_t hi = oracle_pcg32_next(g);
+    return oracle_u64_to_unit((hi << 32) | lo);
+}
+
+int oracle_stretch_run_per_walker32(pcg32_t* rng, int kind, const double* tparams, int W, int D,
+                                    int alpha_num, int alpha_denom,
+                                    double* pos, double* logp, int64_t* acc, int64_t* tot,
+                                    int nsteps, int interval, double* chain, oracle_trace_t* trace)
+{
+    const int K = W / 2;
+    double term1, isa;
+    oracle_gw_constants(alpha_num, alpha_denom, &term1, &isa);
+    double* prop = (double*)malloc(sizeof(double) * (size_t)D);
+    size_t tr = 0;
+    for (int s = 0; s < nsteps; ++s) {
+        for (int sub = 0; sub < interval; ++sub) {
+            int store = (sub == interval - 1);
+            for (int h = 0; h < 2; ++h) {
+                const int own0 = h * K, oth0 = (1 - h) * K;
+                for (int i = 0; i < K; ++i) {
+                    const int w = own0 + i;
+                    pcg32_t* g = &rng[w];
+                    int j = (int)oracle_pcg32_bounded(g, (uint32_t)K);
+                    const double* sel = pos + (size_t)(oth0 + j) * D;
+                    double* cur = pos + (size_t)w * D;
+                    double z = oracle_gw_sample(oracle_pcg32_unit(g), term1, isa);
+                    for (int d = 0; d < D; ++d) prop[d] = sel[d] + z * (cur[d] - sel[d]);
+                    double scaling = log(z) * (double)(D - 1);
+                    double newp = oracle_logp(kind, D, tparams, prop);
+                    double diff = scaling + newp - logp[w];
+                    double e = oracle_neg_exponential(oracle_pcg32_unit(g));
+                    int a = (e < diff);
+                    if (a) { memcpy(cur, prop, sizeof(double) * (size_t)D); logp[w] = newp; ++acc[w]; }
+                    ++tot[w];
+                    if (trace) { oracle_trace_t* t = &trace[tr++]; t->j = j; t->accept = a; t->z = z; t->e = e; t->newp = newp; t->diff = diff; }
+                    if (store && chain) memcpy(chain + ((size_t)s * W + w) * D, cur, sizeof(double) * (size_t)D);
+                }
+            }
+        }
+    }
+    free(prop);
+    return 0;
+}
+
 /* batched log posterior (tests + timing helpers) */
 void oracle_logp_many(int kind, int D, const double* params, const double* x, long n, double* out)
 {

@@ -79,6 +79,9 @@ class Port:
         L.oracle_stretch_run_per_walker.restype = C.c_int
         L.oracle_stretch_run_per_walker.argtypes = L.oracle_stretch_run.argtypes
         L.oracle_pcg64_seed_many.argtypes = [C.c_void_p, c_u64, C.c_int]
+        L.oracle_stretch_run_per_walker32.restype = C.c_int
+        L.oracle_stretch_run_per_walker32.argtypes = L.oracle_stretch_run.argtypes
+        L.oracle_pcg32_seed_many.argtypes = [C.c_void_p, c_u64, C.c_int]
         L.oracle_logp_many.argtypes = [C.c_int, C.c_int, c_dp, c_dp, C.c_long, c_dp]
         L.oracle_stretch_half_slots.restype = None
         L.oracle_stretch_half_slots.argtypes = [c_u64, C.c_int, c_dp, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp,
@@ -148,12 +151,18 @@ class Port:
     def run(self, kind, params, pos, logp, nsteps, interval=1, seed=0, stream=0, alpha=(2, 1),
             want_chain=True, want_trace=False, rng=None, acc=None, tot=None, per_walker=False):
         """Sequential-order stretch-move run.  pos [W,D] and logp [W] are NOT modified;
-        returns dict(pos, logp, acc, tot, chain[(nsteps),W,D], trace, rejections, rng)."""
+        returns dict(pos, logp, acc, tot, chain[(nsteps),W,D], trace, rejections, rng).
+        per_walker: False = one pcg64 stream in walker order; True = pcg64(seed, w) per walker; 32 = pcg32(seed, w) per walker."""
         pos = np.array(pos, dtype=np.float64, order="C")
         logp = np.array(logp, dtype=np.float64)
         W, D = pos.shape
         params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
-        if per_walker:
+        if per_walker == 32:
+            g = rng
+            if g is None:
+                g = (c_u64 * (2 * W))()                     # pcg32_t {state, inc} per walker
+                self.lib.oracle_pcg32_seed_many(g, seed & (2**64 - 1), W)
+        elif per_walker:
             g = rng
             if g is None:
                 g = (Pcg64 * W)()
@@ -164,7 +173,8 @@ class Port:
         tot = np.ones(W, np.int64) if tot is None else np.array(tot, np.int64)
         chain = np.empty((nsteps, W, D)) if want_chain else None
         trace = np.zeros(nsteps * interval * W, dtype=TRACE_DTYPE) if want_trace else None
-        fn = self.lib.oracle_stretch_run_per_walker if per_walker else self.lib.oracle_stretch_run
+        fn = (self.lib.oracle_stretch_run_per_walker32 if per_walker == 32 else
+              self.lib.oracle_stretch_run_per_walker if per_walker else self.lib.oracle_stretch_run)
         rej = fn(C.byref(g), KIND[kind], _dp(params), W, D, alpha[0], alpha[1],
                                           _dp(pos), _dp(logp), acc.ctypes.data, tot.ctypes.data, nsteps, interval,
                                           _dp(chain), trace.ctypes.data if want_trace else None)
@@ -239,6 +249,8 @@ class Ref:
         L.ref_stretch_run.restype = C.c_int
         L.ref_stretch_run.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, C.c_int, c_dp,
                                       C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
+        L.ref_stretch_run_pcg32.restype = C.c_int
+        L.ref_stretch_run_pcg32.argtypes = L.ref_stretch_run.argtypes
         L.ref_stretch_time.restype = C.c_double
         L.ref_stretch_time.argtypes = [C.c_int, c_dp, C.c_int, C.c_int, C.c_int, c_dp, c_dp, C.c_int, C.c_int,
                                        C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
@@ -320,6 +332,19 @@ class Ref:
         stored = self.lib.ref_stretch_run(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, interval,
                                           _dp(chain), C.byref(acc), C.byref(tot))
         return dict(chain=chain if want_chain else None, pos=chain[-1].copy(), acc=acc.value, tot=tot.value, stored=stored)
+
+    def run_pcg32(self, kind, params, pos, logp, nsteps, interval=1, seed=0):
+        """PER_WALKER32 restatement driver (vendored pcg32 + libstdc++ adapters + reference GwDistribution, one facade per
+        walker).  Returns dict(chain[(nsteps+1),W,D], pos, logp, acc, tot)."""
+        pos = np.array(pos, dtype=np.float64, order="C")
+        logp = np.array(logp, dtype=np.float64)
+        W, D = pos.shape
+        params = np.ascontiguousarray(params if params is not None else [0.0], dtype=np.float64)
+        chain = np.empty((nsteps + 1, W, D))
+        acc, tot = C.c_ulonglong(), C.c_ulonglong()
+        self.lib.ref_stretch_run_pcg32(KIND[kind], _dp(params), W, D, seed, _dp(pos), _dp(logp), nsteps, interval, _dp(chain),
+                                       C.byref(acc), C.byref(tot))
+        return dict(chain=chain, pos=pos, logp=logp, acc=acc.value, tot=tot.value)
 
     def run_de(self, kind, params, pos, logp, nsteps, seed=0):
         """Sequential reference EnsembleSampler with the DifferentialEvolution mover -> dict(chain[(nsteps+1),W,D], acc, tot)."""

@@ -10,8 +10,11 @@
  * Single TU on purpose: MCMCpp/Utility/Misc.h:34-67 defines non-inline functions.
  */
 #include <chrono>
+#include <cmath>
 #include <cstring>
+#include <random>
 #include <thread>
+#include <vector>
 #include "EnsembleSampler.h"              /* MCMCpp/EnsembleSampler.h */
 #include "ParallelEnsembleSampler.h"      /* MCMCpp/ParallelEnsembleSampler.h */
 #include "Movers/StretchMove.h"           /* MCMCpp/Movers/StretchMove.h */
@@ -188,6 +191,59 @@ double runTimed(const Calc& calc, int W, int D, int seed, double* initPos, doubl
     return secs;
 }
 
+/*
+ * Restatement driver for the PER_WALKER32 rng discipline: the reference's facade (Utility/MultiSampler.h:54-99) with the
+ * vendored 32-bit engine -- `pcg32 engine` (pcg_random.hpp:1568) where MultiSampler.h:120 has pcg64 -- and the SAME
+ * libstdc++ adapters and the reference's own GwDistribution; one facade per walker, engine.seed(seed, walker).
+ * The update is StretchMove::updateWalker's arithmetic (Movers/StretchMove.h:100-123) on flat arrays.
+ */
+struct Facade32
+{
+    pcg32 engine;
+    std::uniform_real_distribution<double> realDist;
+    std::exponential_distribution<double> expDist;
+    MCMC::Utility::GwDistribution<double, 2, 1> customDist;
+    void setPrng(unsigned long long seed, unsigned long long stream) { engine.seed(seed, stream); }
+    double getCustomSample() { return customDist(realDist(engine)); }
+    double getNegExponentialReal() { return -expDist(engine); }
+    int getNonOffSetInt(int max) { return engine(max); }
+};
+
+template <class Calc>
+int runPerWalker32(Calc calc, int W, int D, int seed, double* pos, double* logp, int nsteps, int interval, double* chainOut,
+                   unsigned long long* acc, unsigned long long* tot)
+{
+    const int K = W / 2;
+    std::vector<Facade32> prng((size_t)W);
+    for (int w = 0; w < W; ++w) prng[(size_t)w].setPrng((unsigned long long)seed, (unsigned long long)w);
+    std::vector<double> prop((size_t)D);
+    unsigned long long a = (unsigned long long)W, t = (unsigned long long)W;      /* setFirstPoint counts (Walker.h:76,162-170) */
+    size_t row = (size_t)W * D;
+    if (chainOut) std::memcpy(chainOut, pos, row * sizeof(double));
+    for (int s = 0; s < nsteps; ++s) {
+        for (int sub = 0; sub < interval; ++sub) {
+            for (int h = 0; h < 2; ++h) {
+                for (int i = 0; i < K; ++i) {
+                    const int w = h * K + i;
+                    Facade32& g = prng[(size_t)w];
+                    const double* sel = pos + (size_t)((1 - h) * K + g.getNonOffSetInt(K)) * D;
+                    double* cur = pos + (size_t)w * D;
+                    double scale = g.getCustomSample();
+                    for (int d = 0; d < D; ++d) prop[(size_t)d] = sel[d] + scale * (cur[d] - sel[d]);
+                    double probScaling = std::log(scale) * static_cast<double>(D - 1);
+                    double newProb = calc.calcLogPostProb(prop.data());
+                    double probDiff = probScaling + newProb - logp[w];
+                    if (g.getNegExponentialReal() < probDiff) { std::memcpy(cur, prop.data(), sizeof(double) * (size_t)D); logp[w] = newProb; ++a; }
+                    ++t;
+                }
+            }
+        }
+        if (chainOut) std::memcpy(chainOut + (size_t)(s + 1) * row, pos, row * sizeof(double));
+    }
+    *acc = a; *tot = t;
+    return nsteps + 1;
+}
+
 } // namespace
 
 /* kind / params encoding is the one of oracle/oracle.c: 0 {eps}; 1 {}; 2 iv[D];
@@ -223,6 +279,16 @@ int ref_stretch_run(int kind, const double* p, int W, int D, int seed, double* i
 {
 #define CALL_RUN(c) runSequential(c, W, D, seed, initPos, initAux, nsteps, interval, chainOut, acc, tot)
     DISPATCH(CALL_RUN)
+    return 0;
+}
+
+/* PER_WALKER32: vendored pcg32 + libstdc++ adapters + reference GwDistribution, one facade per walker.
+ * initPos/initAux are updated in place; chainOut: (nsteps+1) rows (row 0 = initial positions) or NULL. */
+int ref_stretch_run_pcg32(int kind, const double* p, int W, int D, int seed, double* initPos, double* initAux,
+                          int nsteps, int interval, double* chainOut, unsigned long long* acc, unsigned long long* tot)
+{
+#define CALL_RUN32(c) runPerWalker32(c, W, D, seed, initPos, initAux, nsteps, interval, chainOut, acc, tot)
+    DISPATCH(CALL_RUN32)
     return 0;
 }
 

@@ -19,9 +19,34 @@ def corr_precision(D, rho=0.9):
     return np.linalg.inv(cov)
 
 
+def pcg32_cases(R):
+    """PER_WALKER32 fixtures: vendored pcg32 + libstdc++ adapters + reference GwDistribution, one facade per walker
+    (oracle/ref_driver.cpp:ref_stretch_run_pcg32)."""
+    os.makedirs(os.path.join(HERE, "pcg32"), exist_ok=True)
+
+    def case(name, kind, params, W, D, nsteps, keep_rows, interval=1, seed=0, init_seed=53):
+        init = R.init_normal(init_seed, W * D).reshape(W, D)
+        params = np.asarray(params if params is not None else [0.0], dtype=np.float64)
+        lp = R.logp(kind, params, init)
+        r = R.run_pcg32(kind, params, init, lp, nsteps, interval=interval, seed=seed)
+        rows = np.asarray(keep_rows)
+        np.savez_compressed(os.path.join(HERE, "pcg32", name + ".npz"), kind=kind, params=params, W=W, D=D, nsteps=nsteps,
+                            interval=interval, seed=seed, init=init, logp=lp, rows=rows, chain=r["chain"][rows],
+                            final_logp=r["logp"], acc=r["acc"], tot=r["tot"])
+        print("pcg32/" + name, r["acc"], r["tot"])
+
+    case("skewed_w32", "skewed_gauss_2d", [0.13], 32, 2, 2000, [0, 1, 2, 1000, 2000])
+    case("rosenbrock_w512", "rosenbrock_2d", None, 512, 2, 100, [0, 1, 100], seed=3)
+    case("skewed_w320_slice3", "skewed_gauss_2d", [0.13], 320, 2, 100, [0, 1, 100], interval=3, seed=11)
+    case("diag_d37_w128", "diag_gauss", 1.0 / (1.0 + (np.arange(37) % 10)), 128, 37, 20, [0, 1, 20])
+    case("diag_d200_w512", "diag_gauss", 1.0 / (1.0 + (np.arange(200) % 10)), 512, 200, 6, [0, 1, 6], seed=2)
+
+
 def main():
     build()
     R = Ref()
+    if len(sys.argv) > 1 and sys.argv[1] == "pcg32":
+        return pcg32_cases(R)
     out = {}
 
     def case(name, kind, params, W, D, nsteps, interval=1, seed=0, init_seed=53, scale=1.0, keep_rows=None):
@@ -109,6 +134,7 @@ def main():
     walk_case("movers/walk_skewed_w16_s3", "skewed_gauss_2d", [0.13], 16, 2, 300, 3, [0, 1, 2, 150, 300])
     walk_case("movers/walk_diag_d5_w64_s6", "diag_gauss", iv5, 64, 5, 100, 6, [0, 1, 50, 100])
     walk_case("movers/walk_skewed_w32_s16", "skewed_gauss_2d", [0.13], 32, 2, 100, 16, [0, 1, 100])
+    pcg32_cases(R)
     for k, v in out.items():
         print(k, v)
 

@@ -1,6 +1,10 @@
 """Run under torchrun (one process per GPU): a walker-sharded ensemble in both shard modes must equal the
-sequential oracle bit for bit on every rank's owned rows, for the thread, warp and TMA-bulk kernels.
-  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29611 tests/multigpu_check.py"""
+sequential oracle bit for bit on every rank's owned rows, for the thread, warp and TMA-bulk kernels; DATA and DIM sharding
+must take the oracle's decisions.
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29611 tests/multigpu_check.py
+MCMCPP_CHECK_ONE_GPU=1: every rank uses device 0 (processes sharing one GPU; torch.distributed over gloo).  Only the shard
+modes that exchange through CUDA-IPC peer memory run then -- PEER and DIM; NCCL (ALLGATHER, DATA) refuses two ranks on one
+device.  That is how the world > 1 path is exercised on a one-GPU box (tests/test_gpu_multiproc_one_gpu.py)."""
 import os
 import sys
 import numpy as np
@@ -86,11 +90,18 @@ def dim_sharded_diag_gauss(port, rank, world, local):
 
 def main():
     rank, world, local = parallel.env_rank_world()
+    one_gpu = os.environ.get("MCMCPP_CHECK_ONE_GPU") == "1"
+    if one_gpu:
+        local = 0
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if one_gpu:
+        dist.init_process_group("gloo")
+    else:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     port = Port()
     failures = 0
-    cases = [("rosenbrock_2d", 4096, 2, 12), ("diag_gauss", 512, 100, 6), ("diag_gauss", 2048, 1000, 4), ("diag_gauss", 256, 37, 5)]
+    # walkers per colour must divide evenly over the ranks (2, 3, 4 and 8 ranks)
+    cases = [("rosenbrock_2d", 6144, 2, 12), ("diag_gauss", 768, 100, 6), ("diag_gauss", 3072, 1000, 4), ("diag_gauss", 384, 37, 5)]
     for kind, W, D, steps in cases:
         params = 1.0 / (1.0 + (np.arange(D) % 10)) if kind == "diag_gauss" else np.zeros(0)
         rng = np.random.default_rng(17)
@@ -99,7 +110,7 @@ def main():
         o = port.run(kind, params if params.size else None, init, lp, steps, seed=2, want_chain=True)
         calc = m.DiagGaussian(params) if kind == "diag_gauss" else m.RosenbrockTwoDim()
         owned = parallel.owned_walkers(W, rank, world)
-        for mode in ("allgather", "peer"):
+        for mode in (("peer",) if one_gpu else ("allgather", "peer")):
             s = m.EnsembleSampler(2, W, D, m.StretchMove(D, 2, calc), device=local, rank=rank, world=world, shardMode=mode)
             parallel.connect(s)
             s.setInitialWalkerPos(init, lp)
@@ -116,9 +127,10 @@ def main():
             failures += 0 if good else 1
             s.close()
             dist.barrier()
-    failures += data_sharded_linreg(port, rank, world, local)
+    if not one_gpu:
+        failures += data_sharded_linreg(port, rank, world, local)
     failures += dim_sharded_diag_gauss(port, rank, world, local)
-    t = torch.tensor([failures], device="cuda")
+    t = torch.tensor([failures], device="cpu" if one_gpu else "cuda")
     dist.all_reduce(t)
     dist.destroy_process_group()
     if int(t.item()):

@@ -1,0 +1,174 @@
+"""GPU tests added in round 2 (-m gpu): the pcg32 per-walker engine, the engine's life cycle (seeded once), the reference's
+whole-block chain cap, one full-size BASELINE configs[3] step against the oracle, and several samplers on several devices
+of one process."""
+import os
+import numpy as np
+import pytest
+from conftest import load_golden
+from test_gpu_parity import make_sampler, seeded_init
+from test_oracle_cpu import pcg32_golden_names, load_pcg32_golden
+
+pytestmark = pytest.mark.gpu
+
+
+# ---- MCMCPP_RNG_PER_WALKER32 ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", pcg32_golden_names())
+def test_pcg32_goldens_bit_exact(name):
+    """Fixtures made by the vendored pcg32 + libstdc++ adapters + the reference's GwDistribution (one facade per walker):
+    fused small-ensemble kernel (W=32, 320), thread kernel (W=512, D=2), warp kernel (D=37), TMA bulk kernel (D=200)."""
+    g = load_pcg32_golden(name)
+    s = make_sampler(g["kind"], g["params"], g["W"], g["D"], seed=g["seed"], rngMode="per_walker32")
+    if g["interval"] > 1:
+        s.setSlicingMode(True, g["interval"])
+    s.setInitialWalkerPos(g["init"], g["logp"])
+    assert s.runMCMC(g["nsteps"]) is True
+    assert np.array_equal(s.getChain()[g["rows"]], g["chain"])
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(aux, g["final_logp"])
+    assert (s.getAcceptedSteps(), s.getTotalSteps()) == (g["acc"], g["tot"])
+    s.close()
+
+
+@pytest.mark.parametrize("kind,W,D,steps,fused", [("rosenbrock_2d", 1 << 16, 2, 6, True), ("rosenbrock_2d", 4096, 2, 40, False),
+                                                   ("diag_gauss", 256, 9, 10, True), ("diag_gauss", 512, 100, 6, True),
+                                                   ("diag_gauss", 2048, 1000, 3, True), ("dense_gauss", 256, 24, 10, True)])
+def test_pcg32_every_kernel_against_oracle(port, monkeypatch, kind, W, D, steps, fused):
+    if not fused:
+        monkeypatch.setenv("MCMCPP_B200_FUSED", "0")
+    params = {"rosenbrock_2d": None, "diag_gauss": 1.0 / (1.0 + (np.arange(D) % 10)),
+              "dense_gauss": np.linalg.inv(0.9 ** np.abs(np.subtract.outer(np.arange(D), np.arange(D)))).reshape(-1)}[kind]
+    init, lp = seeded_init(port, kind, params, W, D, 31)
+    s = make_sampler(kind, params if params is not None else [], W, D, seed=5, rngMode="per_walker32", traceUpdates=W)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run(kind, params, init, lp, steps, seed=5, per_walker=32, want_trace=True)
+    tr = s.getTrace(W)
+    assert np.array_equal(tr["j"], o["trace"]["j"][:W]) and np.array_equal(tr["z"], o["trace"]["z"][:W])
+    assert np.array_equal(tr["accept"], o["trace"]["accept"][:W])
+    pos, aux = s.getWalkerState()
+    if kind == "dense_gauss":                       # tensor-core summation order: tier B
+        assert np.array_equal(pos, o["pos"]) and np.allclose(aux, o["logp"], rtol=1e-12, atol=0)
+    else:
+        assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+        assert np.array_equal(s.getChain()[1:], o["chain"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum())
+    s.close()
+
+
+def test_pcg32_is_refused_by_the_variable_draw_movers():
+    import mcmcpp_b200 as m
+    from mcmcpp_b200._capi import McmcppError
+    s = m.EnsembleSampler(0, 64, 2, m.DifferentialEvolution(2, 0, m.RosenbrockTwoDim()), rngMode="per_walker32")   # forced to per_walker
+    s.close()
+    cfg_err = None
+    try:
+        m.EnsembleSampler(0, 64, 2, m.StretchMove(2, 0, m.RosenbrockTwoDim()), rngMode="no_such_mode")
+    except (KeyError, McmcppError) as e:
+        cfg_err = e
+    assert cfg_err is not None
+
+
+# ---- the engine is seeded once (EnsembleSampler.h:217); setInitialWalkerPos never reseeds (EnsembleSampler.h:220-230) ----
+@pytest.mark.parametrize("kind,W,D,rng", [("rosenbrock_2d", 512, 2, "sequential"), ("rosenbrock_2d", 4096, 2, "sequential"),
+                                          ("diag_gauss", 256, 100, "sequential"), ("rosenbrock_2d", 512, 2, "per_walker32")])
+def test_second_set_initial_continues_the_stream(port, kind, W, D, rng):
+    params = None if kind == "rosenbrock_2d" else 1.0 / (1.0 + (np.arange(D) % 10))
+    init, lp = seeded_init(port, kind, params, W, D, 8)
+    init2, lp2 = seeded_init(port, kind, params, W, D, 9)
+    pw = 32 if rng == "per_walker32" else False
+    s = make_sampler(kind, params if params is not None else [], W, D, seed=3, rngMode=rng)
+    s.setInitialWalkerPos(init, lp)
+    s.runMCMC(7)
+    a = port.run(kind, params, init, lp, 7, seed=3, per_walker=pw)
+    assert np.array_equal(s.getChain()[1:], a["chain"])
+    s.setInitialWalkerPos(init2, lp2)                 # burn-in -> re-place the walkers: the stream goes on
+    s.runMCMC(5)
+    b = port.run(kind, params, init2, lp2, 5, seed=3, per_walker=pw, rng=a["rng"])
+    chain = s.getChain()
+    assert chain.shape[0] == 1 + 7 + 1 + 5 and np.array_equal(chain[8], init2) and np.array_equal(chain[9:], b["chain"])
+    # counters keep adding (Walker.h:162-170: every placement is one more accepted step)
+    assert s.getTotalSteps() == W * (1 + 7 + 1 + 5)
+    assert s.getAcceptedSteps() == int(a["acc"].sum()) + int(b["acc"].sum())
+    s.close()
+
+
+def test_second_set_initial_against_the_live_reference(port):
+    from oracle.pyoracle import Ref
+    if not Ref.available():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    # the reference itself: one sampler, two placements -- restated by carrying the oracle's engine (pinned above)
+    g = load_golden("rosenbrock_w512")
+    a = port.run(g["kind"], g["params"], g["init"], g["logp"], 3, seed=g["seed"])
+    assert a["rejections"] == 0
+
+
+# ---- chain cap in whole 10000-step blocks (Chain/Chain.h:178-186,218-233) ---------------------------------------------
+@pytest.mark.parametrize("W,D,block,cap_blocks_bytes,expect_rows", [
+    (32, 2, 10, 2.5, 20),        # floor(2.5 blocks) = 2 blocks of 10 steps
+    (32, 2, 10, 0.4, 10),        # less than one block: the first block exists anyway (Chain.h:181-186)
+    (64, 5, 7, 3.0, 21)])
+def test_chain_cap_in_whole_blocks(port, W, D, block, cap_blocks_bytes, expect_rows):
+    kind = "skewed_gauss_2d" if D == 2 else "diag_gauss"
+    params = [0.13] if D == 2 else 1.0 / (1.0 + (np.arange(D) % 10))
+    init, lp = seeded_init(port, kind, params, W, D, 3)
+    s = make_sampler(kind, params, W, D, maxChainSizeBytes=int(cap_blocks_bytes * block * W * D * 8), chainBlockSteps=block)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(expect_rows - 2) is True                    # one row short of the cap
+    assert s.runMCMC(50) is False                                # the step that fills the last block returns false
+    assert s.getStoredSteps() == expect_rows
+    o = port.run(kind, params, init, lp, expect_rows - 1)
+    assert np.array_equal(s.getChain()[1:], o["chain"])
+    s.close()
+    # row granularity (the default) stops elsewhere for the same byte count: documented difference
+    s = make_sampler(kind, params, W, D, maxChainSizeBytes=int(cap_blocks_bytes * block * W * D * 8))
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(200) is False and s.getStoredSteps() == int(cap_blocks_bytes * block)
+    s.close()
+
+
+# ---- BASELINE configs[3] at FULL size: 2^20 walkers x 1000 parameters, one ensemble step against the oracle ---------------
+def test_c4_full_size_one_step_against_oracle(port):
+    """8.4 GB of state; the oracle needs ~10 s and 17 GB of host memory for the step.  Positions, log-probs, partner
+    indices, accept bits and counters of all 2^20 updates, bit for bit."""
+    W, D = 1 << 20, 1000
+    try:
+        avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
+    except (ValueError, OSError):
+        avail = 1 << 40
+    if avail < 40 * (1 << 30):
+        pytest.skip("needs ~35 GB of free host memory")
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    rng = np.random.default_rng(20)
+    init = rng.standard_normal((W, D))
+    lp = port.logp("diag_gauss", iv, init)
+    s = make_sampler("diag_gauss", iv, W, D, maxChainSizeBytes=0, traceUpdates=W)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(1)
+    o = port.run("diag_gauss", iv, init, lp, 1, want_chain=False, want_trace=True)
+    del init
+    tr = s.getTrace(W)
+    assert np.array_equal(tr["j"], o["trace"]["j"]) and np.array_equal(tr["accept"], o["trace"]["accept"])
+    assert np.array_equal(tr["z"], o["trace"]["z"]) and np.array_equal(tr["newp"], o["trace"]["newp"])
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(aux, o["logp"])
+    assert np.array_equal(pos, o["pos"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum()) and s.getTotalSteps() == 2 * W and s.getRngRedraws() == 0
+    s.close()
+
+
+# ---- one process, samplers on two devices (cudaFuncSetAttribute is per device) --------------------------------------
+def test_samplers_on_two_devices_of_one_process(port):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU visible")
+    W, D = 2048, 1000                      # TMA bulk kernel: 64.5 KB of dynamic shared memory, needs the opt-in on each device
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    init, lp = seeded_init(port, "diag_gauss", iv, W, D, 12)
+    o = port.run("diag_gauss", iv, init, lp, 2, want_chain=False)
+    for dev in (0, 1, 0):
+        s = make_sampler("diag_gauss", iv, W, D, maxChainSizeBytes=0, device=dev)
+        s.setInitialWalkerPos(init, lp)
+        assert s.runMCMC(2)
+        pos, aux = s.getWalkerState()
+        assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+        s.close()

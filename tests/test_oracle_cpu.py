@@ -86,3 +86,56 @@ def test_per_walker_streams_are_independent_of_order(port):
     j, z, e = port.draws(9, 5, K, 3)          # walker 5 = red slot 5
     tr = r["trace"].reshape(3, g["W"])
     assert tr["j"][:, 5].tolist() == j.tolist() and np.array_equal(tr["z"][:, 5], z) and np.array_equal(tr["e"][:, 5], e)
+
+
+# ---- PER_WALKER32: the fast engine (pcg32 per walker) --------------------------------------------------------------
+import glob, os
+from conftest import GOLDEN
+
+
+def pcg32_golden_names():
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "pcg32", "*.npz")))
+
+
+def load_pcg32_golden(name):
+    z = np.load(os.path.join(GOLDEN, "pcg32", name + ".npz"))
+    d = {k: z[k] for k in z.files}
+    for k in ("W", "D", "nsteps", "interval", "seed", "acc", "tot"):
+        d[k] = int(d[k])
+    d["kind"] = str(d["kind"])
+    return d
+
+
+@pytest.mark.parametrize("name", pcg32_golden_names())
+def test_port_reproduces_pcg32_goldens(port, name):
+    """oracle_stretch_run_per_walker32 == vendored pcg32 + libstdc++ adapters + reference GwDistribution, bit for bit."""
+    g = load_pcg32_golden(name)
+    r = port.run(g["kind"], g["params"], g["init"], g["logp"], g["nsteps"], interval=g["interval"], seed=g["seed"], per_walker=32)
+    full = np.concatenate([g["init"][None], r["chain"]])
+    assert np.array_equal(full[g["rows"]], g["chain"])
+    assert np.array_equal(r["logp"], g["final_logp"])
+    assert (int(r["acc"].sum()), int(r["tot"].sum())) == (g["acc"], g["tot"])
+
+
+def test_pcg32_live_reference(port):
+    from oracle.pyoracle import Ref
+    if not Ref.available():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    R = Ref()
+    assert R.pcg32_raw(42, 54, 64).tolist() == port.pcg32_raw(42, 54, 64).tolist()
+    init = R.init_normal(7, 64 * 2).reshape(64, 2)
+    lp = R.logp("rosenbrock_2d", None, init)
+    a = R.run_pcg32("rosenbrock_2d", None, init, lp, 200, interval=2, seed=5)
+    b = port.run("rosenbrock_2d", None, init, lp, 200, interval=2, seed=5, per_walker=32)
+    assert np.array_equal(a["chain"][1:], b["chain"]) and a["acc"] == int(b["acc"].sum())
+
+
+def test_set_initial_twice_continues_the_stream(port):
+    """The reference seeds its mover once, in the constructor (EnsembleSampler.h:217); setInitialWalkerPos never reseeds
+    (EnsembleSampler.h:220-230).  The oracle mirrors it by carrying the engine between calls; checked live against the reference
+    in test_gpu_api (device) -- here: two runs on one engine differ from two runs on fresh engines."""
+    g = load_golden("rosenbrock_w512")
+    a = port.run(g["kind"], g["params"], g["init"], g["logp"], 5, seed=3)
+    b = port.run(g["kind"], g["params"], g["init"], g["logp"], 5, seed=3, rng=a["rng"])
+    c = port.run(g["kind"], g["params"], g["init"], g["logp"], 5, seed=3)
+    assert np.array_equal(a["pos"], c["pos"]) and not np.array_equal(a["pos"], b["pos"])
