@@ -260,7 +260,7 @@ public:
         cfg.num_walkers = numWalker; cfg.num_params = numParameter; cfg.seed = randSeed; cfg.rng_mode = rngMode;
         cfg.alpha_num = GwAlpha<Distribution>::num; cfg.alpha_denom = GwAlpha<Distribution>::denom;
         cfg.device = 0; cfg.rank = 0; cfg.world = 1; cfg.shard_mode = MCMCPP_SHARD_NONE; cfg.trace_updates = 0;
-        cfg.max_chain_bytes = maxChainSizeBytes; cfg.mover_state_doubles = 0; cfg.chain_block_steps = 0;
+        cfg.max_chain_bytes = maxChainSizeBytes; cfg.mover_state_doubles = 0; cfg.chain_block_steps = 0; cfg.device_chain_bytes = 0;
 #ifdef MCMCPP_B200_REFERENCE_CHAIN
         /* the runtime's pinned rows are a staging window in front of the reference chain: ~64 MB of rows, at least 2 */
         const unsigned long long rowBytes = sizeof(ParamType) * (unsigned long long)numWalker * (unsigned long long)numParameter;

@@ -97,6 +97,12 @@ typedef struct {
                                   * whole blocks of n steps, max(1, floor(max_chain_bytes / (8 W D n))) of them
                                   * (Chain/Chain.h:178, ChainBlock.h:31 BlockSize = 10000; the first block always exists, Chain.h:181):
                                   * runMCMC returns false at the step the reference returns false at */
+    uint64_t device_chain_bytes; /* > 0: stored steps stay in HBM (up to this many bytes of rows) and cross PCIe only when the host
+                                  * asks for them (mcmcpp_sampler_chain) or the device block is full (then they spill to the pinned
+                                  * host chain); sliceAndBurnChain compacts them on the device; covariance and autocorrelation times
+                                  * can be taken from them in place (mcmcpp_sampler_chain_covariance / _autocorr_times).  With
+                                  * max_chain_bytes == 0 the device block IS the chain (runMCMC returns false when it is full).
+                                  * 0: every stored row is streamed to the host as it is made (2-row device ring). */
 } mcmcpp_config;
 
 /* One row of the optional trace, in the sequential update order (step, half, slot). */
@@ -154,9 +160,10 @@ typedef struct {
     int32_t rank, world;
     double* const* dim_partial;/* [world] every rank's partial table [2 colours][world][K] (own entry local, others peer-mapped);
                                 * a slot is all-ones (empty) or a partial sum -- see dim_shard_kernels.cuh */
-    double* dim_z;             /* [K] draw scratch: draws of the colour in flight, kept between kernels (all shard modes) */
+    double* dim_z;             /* [2K] draw scratch (a launcher may double-buffer by colour): draws of the colour in flight, kept between kernels (all shard modes) */
     double* dim_e;
     int32_t* dim_j;
+    double* dim_s;             /* [2K] log(z) (D_total - 1) of the draws (DIM), second half free for a launcher's own use */
     int32_t sm_count;          /* multiprocessors of the device (persistent grids) */
     double* mover_state;       /* [W * mover_state_doubles] per-walker mover state, or NULL */
 } mcmcpp_halfstep_args;
@@ -237,6 +244,17 @@ int mcmcpp_sampler_chain(mcmcpp_sampler* s, const double** rows_host, long long*
  * Chain::Chain / ChainBlock list (Chain/Chain.h:204-236), so the reference's iterators and Analysis classes run on it
  * unchanged.  Counters and walker state are untouched; getStoredSteps goes down by `rows`. */
 int mcmcpp_sampler_chain_consume(mcmcpp_sampler* s, long long rows);
+
+/* Device-resident chain (cfg.device_chain_bytes > 0): the rows currently held in HBM -- the LAST *rows stored steps, [rows][W][D_local]
+ * contiguous; *first_step is the chain index of the first of them (0 unless older rows have spilled to the host). */
+int mcmcpp_sampler_chain_device(mcmcpp_sampler* s, const double** rows_dev, long long* first_step, long long* rows);
+/* Analysis over the device-resident chain, nothing crosses PCIe but the results (one GPU or DATA sharding; the whole chain
+ * must still be in HBM).  Definitions and argument meaning as mcmcpp_covariance / mcmcpp_autocorr_times below.  With
+ * reference_buffer_reuse == 0 and many walkers the autocovariances are averaged in walker groups (one CTA per parameter and
+ * group; compensated sums inside a group and across groups): same definition, summation order differs from the sequential
+ * walker loop (~1e-13 relative). */
+int mcmcpp_sampler_chain_covariance(mcmcpp_sampler* s, int slice_interval, double* mean, double* cov, double* corr, long long* points);
+int mcmcpp_sampler_chain_autocorr_times(mcmcpp_sampler* s, int window_scaling, int reference_buffer_reuse, double* iat_out);
 
 /* ---- current walker state (Walker::getCurrState / getCurrAuxData, Walker.h:128,134) ---------- */
 int mcmcpp_sampler_get_state(mcmcpp_sampler* s, double* positions_host, double* aux_host);

@@ -7,7 +7,7 @@
  * (MCMCpp/Movers/StretchMove.h:103-109) and the partial sum of a separable Calculator (term()/finish(), targets.h)
  * over its columns.  One colour = two launches:
  *
- *   dimShardDraw    one thread per walker: the three draws of the update (j, z, log(1-u)) into the draw scratch.
+ *   dimShardDraw    one thread per walker: the three draws of the update (j, z, log(1-u)) and log(z)(D-1) into the draw scratch.
  *   dimShardFused   persistent CTAs, each a software pipeline over its tiles of NW walkers with a ring of S
  *                   shared-memory stages:
  *                     issue(n+P)   lane q of a warp issues walker q's two cp.async.bulk copies (own slice, partner
@@ -60,6 +60,7 @@ static __global__ void __launch_bounds__(256) dimShardDraw(const mcmcpp_halfstep
     storeRng(a, w, rng);
     if (dr.redraws) atomicAdd(a.flags, dr.redraws);
     a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
+    a.dim_s[i] = __dmul_rn(log(dr.z), (double)(a.D_total - 1));          /* log(z) (D - 1)  (StretchMove.h:110) */
 }
 
 __device__ __forceinline__ unsigned long long globalTimerNs()
@@ -69,11 +70,11 @@ __device__ __forceinline__ unsigned long long globalTimerNs()
     return t;
 }
 
-/* wait until the slot holds a partial sum, take it, leave the slot empty for the colour after next */
-__device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long long timeoutNs, int32_t* flags)
+/* wait until the slot holds a partial sum, take it, leave the slot empty for the colour after next.  `v` is what an
+ * earlier (prefetched) look at the slot saw. */
+__device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long long v, unsigned long long timeoutNs, int32_t* flags)
 {
     volatile unsigned long long* slot = reinterpret_cast<volatile unsigned long long*>(slotPtr);
-    unsigned long long v = *slot;
     if (v == DimEmpty) {
         const unsigned long long t0 = globalTimerNs();
         unsigned spins = 0;
@@ -92,7 +93,11 @@ __device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long 
 /* ---- phase 1 + 2, one persistent kernel (see the header comment) ------------------------------------------------
  * TMA = rows are 16-byte multiples (even slice): staged with cp.async.bulk; otherwise the warp copies its walkers'
  * rows into the stage itself (odd slices: tests and the last rank of an odd row).
- * Shared memory: S stages x [NW walkers][own row | partner row] (rowStride bytes each), S x NW mbarriers, 2 x NW partials. */
+ * Shared memory: S stages x [NW walkers][own row | partner row] (rowStride bytes each), S x NW mbarriers, S x NW x 4 doubles of
+ * per-walker scalars {z, log(1-u), log(z)(D-1), current log-prob}, 2 x NW partials.
+ * Nothing on the per-tile critical path waits for global memory except the staged rows themselves: the scalars of tile
+ * n+P+1 are loaded (lane q <-> walker q of the warp) while tile n is worked on, and the first look at the partial slots
+ * of tile n-L is taken before the partial sums of tile n are computed. */
 template <class Calc, int WPW, bool TMA, bool TRACE>
 __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
                                                                   const int S, const int P, const int L, const unsigned long long timeoutNs)
@@ -104,10 +109,13 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
     const uint32_t rowBytes = (uint32_t)D * 8u;
     const size_t stageBytes = (size_t)NW * 2u * rowStride;
     unsigned char* barBase = dimSmem + (size_t)S * stageBytes;
-    double* ctaPartial = reinterpret_cast<double*>(barBase + 8u * (size_t)S * NW);      /* [2][NW] */
+    double* meta = reinterpret_cast<double*>(barBase + 8u * (size_t)S * NW);            /* [S][NW][4] */
+    double* ctaPartial = meta + (size_t)S * NW * 4;                                      /* [2][NW] */
     const int numTiles = (K + NW - 1) / NW;
     const int myTiles = (int)blockIdx.x < numTiles ? (numTiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     const int own0 = a.half * K, other0 = (1 - a.half) * K;
+    double* const table = a.dim_partial[a.rank] + (size_t)a.half * a.world * K;          /* this rank's slots of the colour */
+    const int qpp = 32 / a.world;                            /* walkers whose partials one poll pass of the warp takes */
     Calc calc = calcIn;
     unsigned long long myAccepted = 0;
 
@@ -116,40 +124,63 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
         __syncthreads();
     }
 
-    /* walker slot (warp, q) of local tile n lives in stage n % S */
+    /* scalars of the tile this lane will issue next (lane q < WPW <-> walker q of the warp), loaded one iteration ahead */
+    int jN = 0; double zN = 1.0, eN = 0.0, sN = 0.0, pN = 0.0;
+    auto prefetch = [&](int n) {
+        const int i = ((int)blockIdx.x + n * (int)gridDim.x) * NW + warp * WPW + lane;
+        if (n < myTiles && lane < WPW && i < K) {
+            jN = __ldg(a.dim_j + i); zN = __ldg(a.dim_z + i); eN = __ldg(a.dim_e + i); sN = __ldg(a.dim_s + i);
+            pN = a.logp[own0 + i];
+        }
+    };
+    /* walker slot (warp, q) of local tile n lives in stage n % S; uses the scalars prefetch(n) loaded */
     auto issue = [&](int n) {
         const int tile = (int)blockIdx.x + n * (int)gridDim.x;
         const int st = n % S;
         unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
-        if (TMA) {
-            const int i = tile * NW + warp * WPW + lane;
-            if (lane < WPW && i < K) {
-                const int j = a.dim_j[i];
+        const int i = tile * NW + warp * WPW + lane;
+        if (lane < WPW && i < K) {
+            double* mrow = meta + ((size_t)st * NW + warp * WPW + lane) * 4;
+            mrow[0] = zN; mrow[1] = eN; mrow[2] = sN; mrow[3] = pN;
+            if (TMA) {
                 const uint32_t bar = smemAddr(barBase + 8u * (st * NW + warp * WPW + lane));
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     /* the stage's last readers were this warp's own lanes */
                 mbarExpectTx(bar, 2u * rowBytes);
                 bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride), a.pos + (size_t)(own0 + i) * D, rowBytes, bar);
-                bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride + rowStride), a.pos + (size_t)(other0 + j) * D, rowBytes, bar);
+                bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride + rowStride), a.pos + (size_t)(other0 + jN) * D, rowBytes, bar);
             }
-        } else {
+        }
+        if (!TMA) {
 #pragma unroll
             for (int q = 0; q < WPW; ++q) {
-                const int i = tile * NW + warp * WPW + q;
-                if (i >= K) break;
-                const double* ownRow = a.pos + (size_t)(own0 + i) * D;
-                const double* selRow = a.pos + (size_t)(other0 + a.dim_j[i]) * D;
+                const int iq = tile * NW + warp * WPW + q;
+                if (iq >= K) break;
+                const int jq = __shfl_sync(0xffffffffu, jN, q);
+                const double* ownRow = a.pos + (size_t)(own0 + iq) * D;
+                const double* selRow = a.pos + (size_t)(other0 + jq) * D;
                 double* ownS = reinterpret_cast<double*>(rows + (size_t)q * 2u * rowStride);
                 double* selS = reinterpret_cast<double*>(rows + (size_t)q * 2u * rowStride + rowStride);
                 for (int d = lane; d < D; d += 32) { ownS[d] = ownRow[d]; selS[d] = selRow[d]; }
             }
-            __syncwarp();
         }
+        __syncwarp();
     };
 
-    for (int n = 0; n < P && n < myTiles; ++n) issue(n);
+    prefetch(0);
+    for (int n = 0; n < P && n < myTiles; ++n) { issue(n); prefetch(n + 1); }
 
     for (int n = 0; n < myTiles + L; ++n) {
-        if (n + P < myTiles) issue(n + P);
+        if (n + P < myTiles) { issue(n + P); prefetch(n + P + 1); }
+
+        /* first look at the partial slots of tile n - L (pass 0 of the polls), taken before the arithmetic below */
+        const int m = n - L;
+        const bool finishing = m >= 0 && m < myTiles;
+        unsigned long long seen = DimEmpty;
+        if (finishing) {
+            const int ql = lane / a.world, r = lane - ql * a.world;
+            const int ip = ((int)blockIdx.x + m * (int)gridDim.x) * NW + warp * WPW + ql;
+            if (ql < qpp && ql < WPW && ip < K) seen = *reinterpret_cast<volatile unsigned long long*>(table + (size_t)r * K + ip);
+        }
 
         /* ---- partial(n): proposal slices and their partial sums, one line of NW partials to every rank ---- */
         if (n < myTiles) {
@@ -157,13 +188,14 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
             const int st = n % S;
             const uint32_t parity = (uint32_t)((n / S) & 1);
             const unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
+            const double* mrow = meta + ((size_t)st * NW + warp * WPW) * 4;
             double s[WPW];
 #pragma unroll
             for (int q = 0; q < WPW; ++q) {
                 const int i = tile * NW + warp * WPW + q;
                 double p0 = 0.0, p1 = 0.0;
                 if (i < K) {                                              /* warp-uniform */
-                    const double zq = __ldg(a.dim_z + i);
+                    const double zq = mrow[4 * q];
                     if (TMA) mbarWait(smemAddr(barBase + 8u * (st * NW + warp * WPW + q)), parity);
                     const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
                     const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
@@ -198,20 +230,18 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
         }
 
         /* ---- finish(n - L): rank-ordered sum, Metropolis test, commit from shared memory ---- */
-        const int m = n - L;
-        if (m >= 0 && m < myTiles) {
+        if (finishing) {
             const int tile = (int)blockIdx.x + m * (int)gridDim.x;
             const int st = m % S;
             const unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
-            double* table = a.dim_partial[a.rank] + (size_t)a.half * a.world * K;
+            const double* mrow = meta + ((size_t)st * NW + warp * WPW) * 4;
             /* one poll pass takes the partials of qpp walkers at once: lane (ql * world + r) reads rank r's slot of walker ql */
-            const int qpp = 32 / a.world;
             for (int q0 = 0; q0 < WPW; q0 += qpp) {
                 double part = 0.0;
                 {
                     const int ql = lane / a.world, r = lane - ql * a.world, qi = q0 + ql;
                     const int ip = tile * NW + warp * WPW + qi;
-                    if (ql < qpp && qi < WPW && ip < K) part = dimTakePartial(table + (size_t)r * K + ip, timeoutNs, a.flags);
+                    if (ql < qpp && qi < WPW && ip < K) part = dimTakePartial(table + (size_t)r * K + ip, q0 == 0 ? seen : DimEmpty, timeoutNs, a.flags);
                 }
                 for (int q = q0; q < q0 + qpp && q < WPW; ++q) {
                     const int i = tile * NW + warp * WPW + q;
@@ -220,10 +250,9 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
                     const int src = (q - q0) * a.world;
                     double sum = __shfl_sync(0xffffffffu, part, src);     /* rank order, every lane alike */
                     for (int r = 1; r < a.world; ++r) sum = __dadd_rn(sum, __shfl_sync(0xffffffffu, part, src + r));
-                    const double z = __ldg(a.dim_z + i), e = __ldg(a.dim_e + i);
-                    const double scaling = __dmul_rn(log(z), (double)(a.D_total - 1));
+                    const double z = mrow[4 * q], e = mrow[4 * q + 1], scaling = mrow[4 * q + 2], oldp = mrow[4 * q + 3];
                     const double newp = calc.finish(sum);
-                    const double diff = __dsub_rn(__dadd_rn(scaling, newp), a.logp[w]);
+                    const double diff = __dsub_rn(__dadd_rn(scaling, newp), oldp);
                     const bool accepted = e < diff;
                     const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
                     const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
@@ -292,11 +321,11 @@ struct DimShardLauncher
         static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
         int P = envP < 1 ? 1 : envP, L = envL < 1 ? 1 : envL;
         const size_t stageBytes = (size_t)NW * 2u * rowStride;
-        while (P + L + 1 > 3 && (size_t)(P + L + 1) * stageBytes + 8u * (P + L + 1) * NW + 16u * NW > 200u * 1024u) {
+        while (P + L + 1 > 3 && (size_t)(P + L + 1) * (stageBytes + 40u * NW) + 16u * NW > 200u * 1024u) {
             if (L > P) --L; else if (P > 1) --P; else --L;   /* wide slices: fewer stages */
         }
         const int S = P + L + 1;
-        const size_t smem = (size_t)S * stageBytes + 8u * (size_t)S * NW + 16u * NW;
+        const size_t smem = (size_t)S * (stageBytes + 40u * NW) + 16u * NW;      /* rows + mbarrier + 4 scalars per walker slot */
         if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
         static DynamicSmemOptIn optIn;
         if (!optIn.ensure(dimShardFused<Calc, WPW, TMA, TRACE>, smem)) return MCMCPP_ERR_CUDA;
@@ -320,7 +349,7 @@ struct DimShardLauncher
     static int launch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)
     {
         const mcmcpp_halfstep_args& a = *args;
-        if (!a.dim_partial || !a.dim_z || !a.dim_e || !a.dim_j) return MCMCPP_ERR_STATE;
+        if (!a.dim_partial || !a.dim_z || !a.dim_e || !a.dim_j || !a.dim_s) return MCMCPP_ERR_STATE;
         if (a.world > 32) return MCMCPP_ERR_UNSUPPORTED;
         const Calc& calc = *static_cast<const Calc*>(calculator);
         cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);

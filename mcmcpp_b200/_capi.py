@@ -21,7 +21,8 @@ class Config(C.Structure):
                 ("rng_mode", C.c_int32), ("alpha_num", C.c_int32), ("alpha_denom", C.c_int32),
                 ("device", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
                 ("shard_mode", C.c_int32), ("trace_updates", C.c_int32), ("max_chain_bytes", C.c_uint64),
-                ("mover_state_doubles", C.c_int32), ("chain_block_steps", C.c_int32)]
+                ("mover_state_doubles", C.c_int32), ("chain_block_steps", C.c_int32),
+                ("device_chain_bytes", C.c_uint64)]
 
 
 class Trace(C.Structure):
@@ -50,6 +51,9 @@ SYMBOLS = {
     "mcmcpp_sampler_slice_and_burn": (C.c_int, [_h, C.c_int, C.c_int]),
     "mcmcpp_sampler_chain": (C.c_int, [_h, C.POINTER(_dp), C.POINTER(C.c_longlong)]),
     "mcmcpp_sampler_chain_consume": (C.c_int, [_h, C.c_longlong]),
+    "mcmcpp_sampler_chain_device": (C.c_int, [_h, C.POINTER(C.c_void_p), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
+    "mcmcpp_sampler_chain_covariance": (C.c_int, [_h, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_longlong)]),
+    "mcmcpp_sampler_chain_autocorr_times": (C.c_int, [_h, C.c_int, C.c_int, C.c_void_p]),
     "mcmcpp_sampler_get_state": (C.c_int, [_h, C.c_void_p, C.c_void_p]),
     "mcmcpp_sampler_state_device": (C.c_int, [_h, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "mcmcpp_sampler_get_trace": (C.c_int, [_h, C.c_void_p, C.c_int, C.POINTER(C.c_int)]),

@@ -263,13 +263,17 @@ __device__ void acStages(double* re, double* im, const double* __restrict__ wr, 
     }
 }
 
+/* grid (D or 1, G): CTA (p, g) walks walkers [g * walkersPerGroup, ...) of parameter p.  G == 1 (partOut == NULL): the whole
+ * computation, bit-identical to the sequential reference order.  G > 1 (clean mode only): the group's compensated sum of the
+ * normalised autocovariances goes to partOut[p][g][S]; acCombineKernel adds the groups in order and takes the windowed sum. */
 __global__ void __launch_bounds__(AcThreads) acKernel(const double* __restrict__ chain, int S, int W, int D, int lg,
                                                       const double* __restrict__ twCos, const double* __restrict__ twSin,
                                                       const double* __restrict__ mean, int quirk, int windowScaling,
-                                                      double* __restrict__ scratch, double* __restrict__ iat)
+                                                      double* __restrict__ scratch, double* __restrict__ iat,
+                                                      int walkersPerGroup, double* __restrict__ partOut)
 {
     const int n = 1 << lg;
-    double* base = scratch + (size_t)blockIdx.x * (4 * (size_t)n + 3 * (size_t)S);
+    double* base = scratch + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * (4 * (size_t)n + 3 * (size_t)S);
     double *re1 = base, *im1 = re1 + n, *re2 = im1 + n, *im2 = re2 + n, *acov = im2 + n, *avgA = acov + S, *avgC = avgA + S;
     const int WD = W * D;
     for (int i = threadIdx.x; i < S; i += AcThreads) acov[i] = 0.0;                   /* fresh buffer */
@@ -277,7 +281,8 @@ __global__ void __launch_bounds__(AcThreads) acKernel(const double* __restrict__
     for (int p = pBegin; p < pEnd; ++p) {
         for (int i = threadIdx.x; i < S; i += AcThreads) { avgA[i] = 0.0; avgC[i] = 0.0; }
         __syncthreads();
-        for (int w = 0; w < W; ++w) {
+        const int wBegin = blockIdx.y * walkersPerGroup, wEnd = min(W, wBegin + walkersPerGroup);
+        for (int w = wBegin; w < wEnd; ++w) {
             const int off = w * D + p;
             const double mu = mean[off];
             /* transferWalker + copyCenterAndBitReverseChain */
@@ -312,6 +317,11 @@ __global__ void __launch_bounds__(AcThreads) acKernel(const double* __restrict__
             }
             __syncthreads();
         }
+        if (partOut) {                                                                  /* one group of many: hand the sums on */
+            double* out = partOut + ((size_t)p * gridDim.y + blockIdx.y) * (size_t)S;
+            for (int i = threadIdx.x; i < S; i += AcThreads) out[i] = avgA[i];
+            return;
+        }
         if (threadIdx.x == 0) {                                                         /* finalize + windowed sum */
             const double wcount = (double)W, factor = (double)windowScaling;
             double sum = -__ddiv_rn(avgA[0], wcount), comp = 0.0;
@@ -330,12 +340,41 @@ __global__ void __launch_bounds__(AcThreads) acKernel(const double* __restrict__
 }
 }  // namespace
 
-extern "C" int mcmcpp_autocorr_times(const double* chain_host, long long steps, int num_walkers, int num_params, int window_scaling,
-                                     int reference_buffer_reuse, int device, double* iat_out)
+namespace
 {
-    if (!chain_host || !iat_out || steps < 2 || steps > (1LL << 24) || num_walkers <= 0 || num_params <= 0 || window_scaling <= 0) return MCMCPP_ERR_ARG;
-    int count = 0;
-    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || cudaSetDevice(device) != cudaSuccess) return MCMCPP_ERR_CUDA;
+/* grid D: lag i of parameter p = compensated sum over the walker groups, in group order; then the reference's windowed sum
+ * (AutoCorrCalc.h:170-203) by thread 0 */
+__global__ void __launch_bounds__(AcThreads) acCombineKernel(const double* __restrict__ part, int S, int W, int G, int windowScaling,
+                                                             double* __restrict__ avg, double* __restrict__ iat)
+{
+    const int p = blockIdx.x;
+    double* a = avg + (size_t)p * S;
+    for (int i = threadIdx.x; i < S; i += AcThreads) {
+        double sum = 0.0, comp = 0.0;
+        for (int g = 0; g < G; ++g) kahanAdd(sum, comp, part[((size_t)p * G + g) * (size_t)S + i]);
+        a[i] = sum;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const double wcount = (double)W, factor = (double)windowScaling;
+        double sum = -__ddiv_rn(a[0], wcount), comp = 0.0;
+        bool converged = false;
+        for (int i = 0; i < S; ++i) {
+            const double value = __dsub_rn(__dmul_rn(2.0, __ddiv_rn(a[i], wcount)), comp);
+            const double temp = __dadd_rn(sum, value);
+            comp = __dsub_rn(__dsub_rn(temp, sum), value);
+            sum = temp;
+            if ((double)i > __dmul_rn(factor, sum)) { converged = true; break; }
+        }
+        iat[p] = converged ? sum : -sum;
+    }
+}
+}  // namespace
+
+int mcmcpp_autocorr_device(const double* dChain, long long steps, int num_walkers, int num_params, int window_scaling,
+                           int reference_buffer_reuse, double* iat_out)
+{
+    if (!dChain || !iat_out || steps < 2 || steps > (1LL << 24) || num_walkers <= 0 || num_params <= 0 || window_scaling <= 0) return MCMCPP_ERR_ARG;
     const int S = (int)steps, W = num_walkers, D = num_params;
     const int lg = (int)std::ceil(std::log2((double)S)), n = 1 << lg;          /* AutoCov::findNextPowerOfTwo, AutoCov.h:285-290 */
     /* AutoCov::calculateRootsOfUnity (AutoCov.h:270-281) on the host: the same libm values the reference uses */
@@ -346,24 +385,49 @@ extern "C" int mcmcpp_autocorr_times(const double* chain_host, long long steps, 
         cs[(size_t)i] = std::cos(angle);
         sn[(size_t)i] = std::sin(angle);
     }
-    const int grid = reference_buffer_reuse ? 1 : D;
-    const size_t chainBytes = sizeof(double) * (size_t)S * W * D;
-    double *dChain = nullptr, *dCos = nullptr, *dSin = nullptr, *dMean = nullptr, *dScratch = nullptr, *dIat = nullptr;
+    /* clean mode with many walkers: walker groups, so that the whole GPU works on it (2-3 CTAs per SM) */
+    int G = 1;
+    if (!reference_buffer_reuse && W >= 2048) {
+        int sms = 148, dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        G = std::max(1, std::min(W / 64, (2 * sms + D - 1) / D));
+    }
+    const int perGroup = (W + G - 1) / G;
+    G = (W + perGroup - 1) / perGroup;
+    const dim3 grid(reference_buffer_reuse ? 1 : D, G);
+    double *dCos = nullptr, *dSin = nullptr, *dMean = nullptr, *dScratch = nullptr, *dIat = nullptr, *dPart = nullptr;
     int rc = MCMCPP_OK;
-    if (cudaMalloc(&dChain, chainBytes) != cudaSuccess || cudaMalloc(&dCos, sizeof(double) * cs.size()) != cudaSuccess ||
+    if (cudaMalloc(&dCos, sizeof(double) * cs.size()) != cudaSuccess ||
         cudaMalloc(&dSin, sizeof(double) * sn.size()) != cudaSuccess || cudaMalloc(&dMean, sizeof(double) * (size_t)W * D) != cudaSuccess ||
-        cudaMalloc(&dScratch, sizeof(double) * (size_t)grid * (4 * (size_t)n + 3 * (size_t)S)) != cudaSuccess ||
-        cudaMalloc(&dIat, sizeof(double) * (size_t)D) != cudaSuccess)
+        cudaMalloc(&dScratch, sizeof(double) * (size_t)grid.x * grid.y * (4 * (size_t)n + 3 * (size_t)S)) != cudaSuccess ||
+        cudaMalloc(&dIat, sizeof(double) * (size_t)D) != cudaSuccess ||
+        (G > 1 && cudaMalloc(&dPart, sizeof(double) * ((size_t)D * G + D) * (size_t)S) != cudaSuccess))
         rc = MCMCPP_ERR_CUDA;
     if (rc == MCMCPP_OK) {
-        cudaMemcpy(dChain, chain_host, chainBytes, cudaMemcpyHostToDevice);
         cudaMemcpy(dCos, cs.data(), sizeof(double) * cs.size(), cudaMemcpyHostToDevice);
         cudaMemcpy(dSin, sn.data(), sizeof(double) * sn.size(), cudaMemcpyHostToDevice);
         acMeansKernel<<<(W * D + 255) / 256, 256>>>(dChain, S, W * D, dMean);
-        acKernel<<<grid, AcThreads>>>(dChain, S, W, D, lg, dCos, dSin, dMean, reference_buffer_reuse ? 1 : 0, window_scaling, dScratch, dIat);
+        acKernel<<<grid, AcThreads>>>(dChain, S, W, D, lg, dCos, dSin, dMean, reference_buffer_reuse ? 1 : 0, window_scaling, dScratch, dIat,
+                                      perGroup, G > 1 ? dPart : nullptr);
+        if (G > 1) acCombineKernel<<<D, AcThreads>>>(dPart, S, W, G, window_scaling, dPart + (size_t)D * G * S, dIat);
         if (cudaMemcpy(iat_out, dIat, sizeof(double) * (size_t)D, cudaMemcpyDeviceToHost) != cudaSuccess || cudaGetLastError() != cudaSuccess)
             rc = MCMCPP_ERR_CUDA;
     }
-    cudaFree(dChain); cudaFree(dCos); cudaFree(dSin); cudaFree(dMean); cudaFree(dScratch); cudaFree(dIat);
+    cudaFree(dCos); cudaFree(dSin); cudaFree(dMean); cudaFree(dScratch); cudaFree(dIat); cudaFree(dPart);
+    return rc;
+}
+
+extern "C" int mcmcpp_autocorr_times(const double* chain_host, long long steps, int num_walkers, int num_params, int window_scaling,
+                                     int reference_buffer_reuse, int device, double* iat_out)
+{
+    if (!chain_host || !iat_out || steps < 2 || steps > (1LL << 24) || num_walkers <= 0 || num_params <= 0 || window_scaling <= 0) return MCMCPP_ERR_ARG;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || cudaSetDevice(device) != cudaSuccess) return MCMCPP_ERR_CUDA;
+    const size_t chainBytes = sizeof(double) * (size_t)steps * num_walkers * num_params;
+    double* dChain = nullptr;
+    if (cudaMalloc(&dChain, chainBytes) != cudaSuccess) return MCMCPP_ERR_CUDA;
+    int rc = cudaMemcpy(dChain, chain_host, chainBytes, cudaMemcpyHostToDevice) == cudaSuccess ? MCMCPP_OK : MCMCPP_ERR_CUDA;
+    if (rc == MCMCPP_OK) rc = mcmcpp_autocorr_device(dChain, steps, num_walkers, num_params, window_scaling, reference_buffer_reuse, iat_out);
+    cudaFree(dChain);
     return rc;
 }

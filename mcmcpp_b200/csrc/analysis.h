@@ -17,4 +17,6 @@ int mcmcpp_cov_zero(mcmcpp_cov_accum* c, cudaStream_t stream);
 int mcmcpp_cov_accumulate(mcmcpp_cov_accum* c, const double* devRows, long long nPoints, cudaStream_t stream);
 /* finalizeMatrix (CovarianceMatrix.h:143-185); host outputs mean[D], cov[D*D], corr[D*D] (any may be NULL) */
 int mcmcpp_cov_finalize(mcmcpp_cov_accum* c, long long nPoints, double* mean, double* cov, double* corr, cudaStream_t stream);
+/* AutoCorrCalc::calcAutoCorrTimes over a DEVICE chain [steps][W][D] (all walkers) -> host iat[D]; see mcmcpp_autocorr_times */
+int mcmcpp_autocorr_device(const double* chain_dev, long long steps, int W, int D, int window_scaling, int reference_buffer_reuse, double* iat_out);
 #endif

@@ -11,9 +11,10 @@
  * reference; the log-posterior is summed in tensor-core order, so it carries the tolerance tier (<= 1e-12 relative,
  * SURVEY.md s.8(c) tier B) and decisions agree unless one lands within that distance of its threshold.
  *
- * Persistent CTAs (one per SM, P loaded once) of two 8-warp groups; each group takes 32-walker tiles from a dynamic
- * counter; in the MMA phase warp (rg, ch) owns rows 8rg..8rg+7 and one half of the D/8 column blocks (accumulators
- * in registers).  Shared-memory row stride = 4 mod 16 doubles -> conflict-free fragment loads.
+ * Persistent CTAs (one per SM, P loaded once) of up to four 4-warp groups; a CTA's tiles of 32 walkers go round the groups; in
+ * the MMA phase warp (rp, ch) owns rows 16rp..16rp+15 and one half of the D/8 column blocks (accumulators in registers, every B
+ * fragment feeds two DMMAs).  Shared-memory row stride = 4 mod 16 doubles -> conflict-free fragment loads.  The draws of a
+ * colour are made by denseDrawKernel, overlapped with the previous colour's update kernel.
  */
 #include <cuda_runtime.h>
 #include <cstring>
@@ -25,10 +26,10 @@ namespace
 {
 using namespace MCMC::Device;
 
-/* Two independent 8-warp groups per CTA, each walking its own stream of 32-walker tiles (dynamic tile counter) and
- * synchronising on its own named barrier: while one group is in its scalar phases (draws, row loads, decision,
- * commit) the other keeps the FP64 tensor pipe busy.  P is shared. */
-enum { DenseTileRows = 32, DenseGroupThreads = 256, DenseGroups = 2, DenseThreads = DenseGroupThreads * DenseGroups };
+/* GROUPS independent 4-warp groups per CTA, each walking its own sequence of 32-walker tiles and synchronising on its own named
+ * barrier: while one group holds the FP64 tensor pipe, the others are in their scalar phases (row loads, proposals, epilogue,
+ * decision, commit).  P is shared. */
+enum { DenseTileRows = 32, DenseGroupWarps = 4, DenseGroupThreads = DenseGroupWarps * 32 };
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
 {
@@ -38,20 +39,21 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 
 __device__ __forceinline__ void groupSync(int group)
 {
-    asm volatile("bar.sync %0, 256;" ::"r"(group + 1) : "memory");       /* 256 = DenseGroupThreads */
-    static_assert(DenseGroupThreads == 256, "named-barrier thread count is spelled out in the asm above");
+    asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");       /* 128 = DenseGroupThreads */
+    static_assert(DenseGroupThreads == 128, "named-barrier thread count is spelled out in the asm above");
 }
 
-/* The tensor pipe is handed from group to group like a token: barrier 3 + g is completed by the 256 waiting threads of
- * group g plus the 256 arriving threads of the other group when it leaves its MMA phase.  Without it the two groups
- * run in lockstep (same work, same phase lengths) and fight for the pipe, then both leave it idle. */
+/* The tensor pipe is handed from group to group like a token, in tile order: barrier 5 + g is completed by the 128 waiting threads
+ * of group g plus the 128 arriving threads of the group that had the tile before.  On B200 DMMA and the plain FP64 instructions
+ * share one pipe per SM sub-partition and it is a FIFO: two groups issuing DMMAs at once only interleave (both finish late), so one
+ * group at a time gets the pipe for its 2.75 us of DMMAs and the scalar phases of the other groups ride in the gaps. */
 __device__ __forceinline__ void tokenWait(int group)
 {
-    asm volatile("bar.sync %0, 512;" ::"r"(group + 3) : "memory");
+    asm volatile("bar.sync %0, 256;" ::"r"(group + 5) : "memory");
 }
-__device__ __forceinline__ void tokenPass(int group)
+__device__ __forceinline__ void tokenPass(int toGroup)
 {
-    asm volatile("bar.arrive %0, 512;" ::"r"((1 - group) + 3) : "memory");
+    asm volatile("bar.arrive %0, 256;" ::"r"(toGroup + 5) : "memory");
 }
 
 __host__ __device__ constexpr int denseStrideC(int Dp)
@@ -60,46 +62,69 @@ __host__ __device__ constexpr int denseStrideC(int Dp)
 }
 __host__ __device__ inline int denseStride(int Dp) { return denseStrideC(Dp); }
 
-/* NB = number of 8-wide column blocks (padded dimension Dp = 8*NB).
- * Static tile assignment: group gid takes tiles gid, gid + G, ...; the draws of up to DenseBatch tiles (one walker per
- * thread of the group) are made up front, in parallel, while P streams into shared memory with cp.async.bulk. */
-enum { DenseBatch = DenseGroupThreads / DenseTileRows };      /* 8 tiles = 256 walkers per draw phase */
-
-template <int NB, bool TRACE>
-__global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken, long long* tl)
+__host__ __device__ constexpr int densePerGroupDoubles(int Dp)
 {
-#define DENSE_TL(slot) do { if (tl && blockIdx.x == 0 && tid == 0) { long long tNow; asm volatile("mov.u64 %0, %%clock64;" : "=l"(tNow) :: "memory"); tl[((group * 16 + rnd0 + bt) * 8) + (slot)] = tNow; } } while (0)
+    /* proposals [32][stride] + sQ [2][32] + sOld, sZ, sE [32] each + sJ, sAcc [32] ints each */
+    return DenseTileRows * denseStrideC(Dp) + 2 * DenseTileRows + 3 * DenseTileRows + DenseTileRows;
+}
+
+/* The draws of a colour, one THREAD per owned walker, into the colour's half of the draw scratch (dim_z/dim_e/dim_j are
+ * 2K long).  Launched as a programmatic dependent of the previous colour's update kernel: it reads only THIS colour's rng
+ * states (last written two launches back), so it runs on the thread slots that kernel leaves free, entirely off the
+ * critical path; it ends with griddepcontrol.wait so that it cannot COMPLETE before the previous update kernel has --
+ * the update kernel of this colour waits for this kernel, and through it for the previous colour's rows. */
+__global__ void __launch_bounds__(256) denseDrawKernel(const mcmcpp_halfstep_args a)
+{
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < a.slot_count) {
+        const int w = a.half * a.K + a.slot_begin + i;
+        WalkerRng rng = loadRng(a, w);
+        StretchDraws dr = drawStretchFor(a, rng);
+        storeRng(a, w, rng);
+        if (dr.redraws) atomicAdd(a.flags, dr.redraws);
+        const size_t o = (size_t)a.half * a.K + i;
+        a.dim_z[o] = dr.z; a.dim_e[o] = dr.logOneMinusU; a.dim_j[o] = dr.j;
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+/* NB = number of 8-wide column blocks (padded dimension Dp = 8*NB).  CTA b takes tiles b, b + gridDim, ...; its n-th tile
+ * goes to group n % GROUPS.  In the MMA phase warp (rp, ch) of the group owns rows 16rp..16rp+15 (two 8-row fragments
+ * that share every B fragment: 9 shared-memory loads per 14 DMMAs) and one half of the D/8 column blocks. */
+template <int NB, int GROUPS, bool TRACE>
+__global__ void __launch_bounds__(DenseGroupThreads * GROUPS, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken)
+{
     constexpr int Dp = 8 * NB;
-    constexpr int NBH = (NB + 1) / 2;                         /* column blocks per warp: warps 0-3 take [0,NBH), 4-7 the rest */
-    constexpr int GroupWarps = DenseGroupThreads / 32;
-    constexpr int PerGroupDoubles = DenseTileRows * denseStrideC(Dp) + 4 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
-    extern __shared__ __align__(16) double denseSmem[];
+    constexpr int NBH = (NB + 1) / 2;                         /* column blocks per warp: warps 0-1 take [0,NBH), 2-3 the rest */
+    constexpr int Threads = DenseGroupThreads * GROUPS;
     constexpr int stride = denseStrideC(Dp);
+    constexpr int PerGroupDoubles = densePerGroupDoubles(Dp);
+    extern __shared__ __align__(16) double denseSmem[];
     const int group = threadIdx.x / DenseGroupThreads;
     const int tid = threadIdx.x - group * DenseGroupThreads, lane = tid & 31, warp = tid >> 5;
-    double* Ps = denseSmem;                                   /* [Dp][stride], shared by both groups */
-    double* Xs = Ps + (size_t)Dp * stride + (size_t)group * PerGroupDoubles;   /* [TM][stride] proposals */
-    double* bZ = Xs + (size_t)DenseTileRows * stride;         /* draws of the batch: z, log(1-u), log(z)(D-1) */
-    double* bE = bZ + DenseGroupThreads;
-    double* bS = bE + DenseGroupThreads;
-    const double** bSel = reinterpret_cast<const double**>(bS + DenseGroupThreads);   /* partner row of each walker (peer lookup done once, here) */
-    int* bJ = reinterpret_cast<int*>(bS + 2 * DenseGroupThreads); /* [256] ints = 128 doubles */
-    double* sQ = bS + 2 * DenseGroupThreads + DenseGroupThreads / 2;   /* [2][TM] column halves */
-    double* sOld = sQ + 2 * DenseTileRows;                    /* [TM] current log-probs */
+    double* Ps = denseSmem;                                   /* [Dp][stride], shared by the groups */
+    double* Xs = Ps + (size_t)Dp * stride + (size_t)group * PerGroupDoubles;   /* [32][stride] proposals */
+    double* sQ = Xs + (size_t)DenseTileRows * stride;         /* [2][32] column halves of the quadratic form */
+    double* sOld = sQ + 2 * DenseTileRows;                    /* [32] current log-probs */
+    double* sZ = sOld + DenseTileRows;                        /* [32] draws of the tile */
+    double* sE = sZ + DenseTileRows;
+    int* sJ = reinterpret_cast<int*>(sE + DenseTileRows);     /* [32] */
+    int* sAcc = sJ + DenseTileRows;                           /* [32] */
     __shared__ __align__(8) unsigned long long pBar;
 
     const int D = a.D;
     const int other0 = (1 - a.half) * a.K;
     const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
-    /* group 0 of every CTA first, then group 1: tiles spread evenly over the SMs, and group 0 never has fewer tiles */
-    const int gid = group * gridDim.x + blockIdx.x, gstep = gridDim.x * DenseGroups;
-    const int rounds = blockIdx.x < numTiles ? (numTiles - blockIdx.x + gstep - 1) / gstep : 0;   /* tiles of group 0 */
-    if (useToken && group == 1) tokenPass(1);                             /* group 0 owns the tensor pipe first */
+    const int myTiles = (int)blockIdx.x < numTiles ? (numTiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const double* dz = a.dim_z + (size_t)a.half * a.K;        /* this colour's half of the draw scratch (denseDrawKernel) */
+    const double* de = a.dim_e + (size_t)a.half * a.K;
+    const int* dj = a.dim_j + (size_t)a.half * a.K;
 
-    /* P -> shared, zero padded (rows/cols >= D contribute nothing).  Even D: one bulk copy per row, in flight during
-     * the first draw phase; odd D (rows not 16-byte multiples): plain loads. */
+    /* P -> shared, zero padded (rows/cols >= D contribute nothing).  Even D: one bulk copy per row, in flight while the
+     * kernel waits for its predecessors; odd D (rows not 16-byte multiples): plain loads. */
     const bool bulkP = (D % 2) == 0;
-    for (int idx = threadIdx.x; idx < Dp * stride; idx += DenseThreads) {
+    for (int idx = threadIdx.x; idx < Dp * stride; idx += Threads) {
         const int r = idx / stride, c = idx - r * stride;
         if (bulkP) { if (r >= D || c >= D) Ps[idx] = 0.0; }
         else Ps[idx] = (r < D && c < D) ? P[(size_t)r * D + c] : 0.0;
@@ -112,59 +137,41 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
         if (threadIdx.x < D)
             bulkLoad(smemAddr(Ps + (size_t)threadIdx.x * stride), P + (size_t)threadIdx.x * D, (uint32_t)(D * 8), smemAddr(&pBar));
     }
+    /* programmatic dependent launch: P is constant; the draws, rows and log-probs are read from here on.  The launch right
+     * before this one is the draw kernel of this colour, which itself completes only after the previous colour's update. */
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     bool pReady = !bulkP;
     unsigned long long myAccepted = 0;                        /* lane 0 of every warp counts its own rows */
 
-    for (int rnd0 = 0; rnd0 < rounds; rnd0 += DenseBatch) {
-        const int tileBase = gid + rnd0 * gstep;
-        /* (a) draws of the whole batch: thread tid <-> (tile tileBase + (tid/32)*gstep, row tid%32) */
-        groupSync(group);                                     /* previous batch done with bZ.. */
-        {
-            const int tile = tileBase + (tid >> 5) * gstep;
-            const int i = tile * DenseTileRows + lane;
-            if (tile < numTiles && i < a.slot_count) {
-                const int w = a.half * a.K + a.slot_begin + i;
-                WalkerRng rng = loadRng(a, w);
-                StretchDraws dr = drawStretchFor(a, rng);
-                storeRng(a, w, rng);
-                if (dr.redraws) atomicAdd(a.flags, dr.redraws);
-                bJ[tid] = dr.j; bZ[tid] = dr.z; bE[tid] = dr.logOneMinusU;
-                bSel[tid] = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
-                bS[tid] = __dmul_rn(log(dr.z), (double)(D - 1));
-            } else {
-                bJ[tid] = 0; bZ[tid] = 1.0; bE[tid] = 0.0; bS[tid] = 0.0; bSel[tid] = a.pos;
-            }
+    for (int n = group; n < myTiles; n += GROUPS) {
+        const int tile = (int)blockIdx.x + n * (int)gridDim.x;
+        const int row0 = tile * DenseTileRows;
+        /* (a) the tile's draws and partner rows */
+        if (tid < DenseTileRows) {
+            const int i = row0 + tid;
+            const bool valid = i < a.slot_count;
+            sZ[tid] = valid ? dz[i] : 1.0; sE[tid] = valid ? de[i] : 0.0; sJ[tid] = valid ? dj[i] : 0;
         }
         groupSync(group);
-        if (rnd0 == 0) {
-            /* programmatic dependent launch: the P load and the first draws read nothing the launch right before this one
-             * wrote (P is constant, the rng states are this colour's own); rows and log-probs are read from here on */
-            asm volatile("griddepcontrol.wait;" ::: "memory");
-            asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        }
-        if (!pReady) { mbarWait(smemAddr(&pBar), 0); pReady = true; }
-        for (int bt = 0; bt < DenseBatch && rnd0 + bt < rounds; ++bt) {
-            const int tile = tileBase + bt * gstep;
-            const bool has = tile < numTiles;                 /* group-uniform; group 1 may sit out the last round */
-            const bool lastRound = rnd0 + bt + 1 == rounds;
-            const int row0 = tile * DenseTileRows;
-            const int b0 = bt * DenseTileRows;                /* this tile's draws in the batch arrays */
-            /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  All loads of the warp's rows
-             * are issued before the first use so one L2/HBM latency covers the whole tile, not one per row. */
-            DENSE_TL(0);
-            if (has) {
-                constexpr int RowsPerWarp = DenseTileRows / GroupWarps;
-                constexpr int KCH = (Dp + 31) / 32;
-                double cur[RowsPerWarp][KCH], sl[RowsPerWarp][KCH];
+        /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  The loads of four rows are issued
+         * before their first use so one L2/HBM latency covers them all. */
+        {
+            constexpr int RowsPerWarp = DenseTileRows / DenseGroupWarps;     /* 8, in two halves of 4 */
+            constexpr int KCH = (Dp + 31) / 32;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                double cur[RowsPerWarp / 2][KCH], sl[RowsPerWarp / 2][KCH];
                 double oldp = 0.0;
 #pragma unroll
-                for (int rr = 0; rr < RowsPerWarp; ++rr) {
-                    const int r = warp + rr * GroupWarps;
+                for (int rr = 0; rr < RowsPerWarp / 2; ++rr) {
+                    const int r = warp + (h * (RowsPerWarp / 2) + rr) * DenseGroupWarps;
                     const int i = row0 + r;
                     const bool valid = i < a.slot_count;
                     const int w = a.half * a.K + a.slot_begin + (valid ? i : 0);
                     const double* own = a.pos + (size_t)w * D;
-                    const double* sel = bSel[b0 + r];
+                    const int j = sJ[r];
+                    const double* sel = partnerBase(a, j) + (size_t)(other0 + j) * D;
                     if (lane == rr) oldp = a.logp[w];
 #pragma unroll
                     for (int k = 0; k < KCH; ++k) {
@@ -174,11 +181,11 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                         sl[rr][k] = ok ? __ldg(sel + d) : 0.0;
                     }
                 }
-                if (lane < RowsPerWarp) sOld[warp + lane * GroupWarps] = oldp;
+                if (lane < RowsPerWarp / 2) sOld[warp + (h * (RowsPerWarp / 2) + lane) * DenseGroupWarps] = oldp;
 #pragma unroll
-                for (int rr = 0; rr < RowsPerWarp; ++rr) {
-                    const int r = warp + rr * GroupWarps;
-                    const double z = bZ[b0 + r];
+                for (int rr = 0; rr < RowsPerWarp / 2; ++rr) {
+                    const int r = warp + (h * (RowsPerWarp / 2) + rr) * DenseGroupWarps;
+                    const double z = sZ[r];
                     double* xr = Xs + (size_t)r * stride;
 #pragma unroll
                     for (int k = 0; k < KCH; ++k) {
@@ -187,107 +194,101 @@ __global__ void __launch_bounds__(DenseThreads, 1) denseGaussHalfStep(const mcmc
                     }
                 }
             }
-            groupSync(group);
-            DENSE_TL(1);
-            if (useToken) tokenWait(group);
-            DENSE_TL(2);
-            /* (c) Y = Xs * Ps on the FP64 tensor cores; warp owns 8 rows x its half of the column blocks */
-            if (has) {
-                const int rg = warp & 3, ch = warp >> 2;
-                const int nb0 = ch * NBH;
-                const int cnt = (NB - nb0) < NBH ? (NB - nb0) : NBH;
-                double acc[NBH][2];
+        }
+        groupSync(group);
+        if (!pReady) { mbarWait(smemAddr(&pBar), 0); pReady = true; }
+        if (useToken && n > 0) tokenWait(group);
+        /* (c) Y = Xs * Ps on the FP64 tensor cores */
+        {
+            const int rp = warp & 1, ch = warp >> 1;
+            const int nb0 = ch * NBH;
+            const int cnt = (NB - nb0) < NBH ? (NB - nb0) : NBH;
+            double acc[2][NBH][2];
 #pragma unroll
-                for (int nb = 0; nb < NBH; ++nb) { acc[nb][0] = 0.0; acc[nb][1] = 0.0; }
-                const int g = lane >> 2, t = lane & 3;
-                const double* arow = Xs + (size_t)(rg * 8 + g) * stride + t;
-                DENSE_TL(6);
-                const double* bcol = Ps + (size_t)t * stride + g + nb0 * 8;
+            for (int nb = 0; nb < NBH; ++nb) { acc[0][nb][0] = 0.0; acc[0][nb][1] = 0.0; acc[1][nb][0] = 0.0; acc[1][nb][1] = 0.0; }
+            const int g = lane >> 2, t = lane & 3;
+            const double* arow0 = Xs + (size_t)(rp * 16 + g) * stride + t;
+            const double* arow1 = arow0 + (size_t)8 * stride;
+            const double* bcol = Ps + (size_t)t * stride + g + nb0 * 8;
 #pragma unroll 2
-                for (int k = 0; k < Dp; k += 4) {
-                    const double av = arow[k];
-                    const double* bk = bcol + (size_t)k * stride;
+            for (int k = 0; k < Dp; k += 4) {
+                const double a0 = arow0[k], a1 = arow1[k];
+                const double* bk = bcol + (size_t)k * stride;
 #pragma unroll
-                    for (int nb = 0; nb < NBH; ++nb)
-                        if (nb < cnt) dmma884(acc[nb][0], acc[nb][1], av, bk[nb * 8]);
+                for (int nb = 0; nb < NBH; ++nb) {
+                    if (nb < cnt) {
+                        const double bv = bk[nb * 8];
+                        dmma884(acc[0][nb][0], acc[0][nb][1], a0, bv);
+                        dmma884(acc[1][nb][0], acc[1][nb][1], a1, bv);
+                    }
                 }
-                DENSE_TL(7);
-                /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols (nb0+nb)*8 + 2t, +1 of row g */
-                const double* xrow = Xs + (size_t)(rg * 8 + g) * stride + nb0 * 8 + 2 * t;
-                double q = 0.0, q1 = 0.0;                     /* two chains: the dependent FMAs queue behind the other warp's DMMAs */
+            }
+            /* the pipe goes to the group that has the next tile; the epilogue's few FP64 operations queue behind its DMMAs, but this
+             * group does not need the pipe again before GROUPS - 1 other tiles have gone through it */
+            if (useToken && n + 1 < myTiles) tokenPass((group + 1) % GROUPS);
+            /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols (nb0+nb)*8 + 2t, +1 of rows g and 8 + g */
+#pragma unroll
+            for (int r2 = 0; r2 < 2; ++r2) {
+                const double* xrow = Xs + (size_t)(rp * 16 + r2 * 8 + g) * stride + nb0 * 8 + 2 * t;
+                double q = 0.0, q1 = 0.0;
 #pragma unroll
                 for (int nb = 0; nb < NBH; ++nb) {
                     if (nb < cnt) {
                         const double2 xv = *reinterpret_cast<const double2*>(xrow + nb * 8);
-                        q = fma(xv.x, acc[nb][0], q);
-                        q1 = fma(xv.y, acc[nb][1], q1);
+                        q = fma(xv.x, acc[r2][nb][0], q);
+                        q1 = fma(xv.y, acc[r2][nb][1], q1);
                     }
                 }
                 q += q1;
                 q += __shfl_xor_sync(0xffffffffu, q, 1);
                 q += __shfl_xor_sync(0xffffffffu, q, 2);
-                if (t == 0) sQ[ch * DenseTileRows + rg * 8 + g] = q;
+                if (t == 0) sQ[ch * DenseTileRows + rp * 16 + r2 * 8 + g] = q;
             }
-            /* (d) Metropolis decisions while this group still holds the token: the few dependent FP64 adds would
-             * otherwise queue behind the other group's DMMAs (same pipe) and stretch the commit from 0.7 to 3.4 us.
-             * Lane r of warp 0 decides row r; sQ[r] <- new log-prob, accept flag over the second half. */
-            groupSync(group);
-            int* sAcc = reinterpret_cast<int*>(sQ + DenseTileRows);
-            if (has && warp == 0) {
-                const double newp = -0.5 * (sQ[lane] + sQ[DenseTileRows + lane]);
-                const double diff = __dsub_rn(__dadd_rn(bS[b0 + lane], newp), sOld[lane]);
-                const bool accepted = bE[b0 + lane] < diff;
-                __syncwarp();
-                sQ[lane] = newp;
-                sAcc[lane] = accepted ? 1 : 0;
+        }
+        groupSync(group);
+        /* (d) Metropolis decisions: lane r of warp 0 decides row r; sQ[r] <- new log-prob */
+        if (warp == 0) {
+            const double newp = -0.5 * (sQ[lane] + sQ[DenseTileRows + lane]);
+            const double scaling = __dmul_rn(log(sZ[lane]), (double)(D - 1));
+            const double diff = __dsub_rn(__dadd_rn(scaling, newp), sOld[lane]);
+            const bool accepted = sE[lane] < diff;
+            __syncwarp();
+            sQ[lane] = newp;
+            sQ[DenseTileRows + lane] = diff;
+            sAcc[lane] = accepted ? 1 : 0;
+        }
+        groupSync(group);
+        /* (e) commit: each warp writes its accepted rows (and the chain row of every walker on stored steps) */
+        for (int r = warp; r < DenseTileRows; r += DenseGroupWarps) {
+            const int i = row0 + r;
+            if (i >= a.slot_count) continue;
+            const int slot = a.slot_begin + i;
+            const int w = a.half * a.K + slot;
+            const double newp = sQ[r];
+            const bool accepted = sAcc[r] != 0;
+            const double* xr = Xs + (size_t)r * stride;
+            double* own = a.pos + (size_t)w * D;
+            if (a.chain_row) {
+                double* chainRow = a.chain_row + (size_t)w * D;
+                for (int d = lane; d < D; d += 32) chainRow[d] = accepted ? xr[d] : own[d];
             }
-            DENSE_TL(3);
-            if (useToken && !(group == 1 && lastRound)) tokenPass(group); /* the last pass would have nobody waiting for it */
-            groupSync(group);
-            DENSE_TL(4);
-            if (!has) continue;
-            /* (e) commit: each warp writes its accepted rows (and the chain row of every walker on stored steps) */
-            for (int r = warp; r < DenseTileRows; r += GroupWarps) {
-                const int i = row0 + r;
-                if (i >= a.slot_count) continue;
-                const int slot = a.slot_begin + i;
-                const int w = a.half * a.K + slot;
-                const double newp = sQ[r];
-                const bool accepted = sAcc[r] != 0;
-                const double* xr = Xs + (size_t)r * stride;
-                double* own = a.pos + (size_t)w * D;
-                if (a.chain_row) {
-                    double* chainRow = a.chain_row + (size_t)w * D;
-                    for (int d = lane; d < D; d += 32) chainRow[d] = accepted ? xr[d] : own[d];
-                }
-                if (accepted) for (int d = lane; d < D; d += 32) own[d] = xr[d];
-                if (lane == 0) {
-                    if (accepted) { a.logp[w] = newp; ++myAccepted; }
-                    if (TRACE) {
-                        if (slot < a.trace_rows) {
-                            mcmcpp_trace tr;
-                            tr.j = bJ[b0 + r]; tr.accept = accepted ? 1 : 0; tr.z = bZ[b0 + r]; tr.e = bE[b0 + r]; tr.newp = newp;
-                            tr.diff = __dsub_rn(__dadd_rn(bS[b0 + r], newp), sOld[r]);
-                            a.trace[slot] = tr;
-                        }
+            if (accepted) for (int d = lane; d < D; d += 32) own[d] = xr[d];
+            if (lane == 0) {
+                if (accepted) { a.logp[w] = newp; ++myAccepted; }
+                if (TRACE) {
+                    if (slot < a.trace_rows) {
+                        mcmcpp_trace tr;
+                        tr.j = sJ[r]; tr.accept = accepted ? 1 : 0; tr.z = sZ[r]; tr.e = sE[r]; tr.newp = newp;
+                        tr.diff = sQ[DenseTileRows + r];
+                        a.trace[slot] = tr;
                     }
                 }
             }
-            groupSync(group);                                 /* Xs, sQ, sOld free for the next tile */
-            DENSE_TL(5);
         }
+        groupSync(group);                                     /* Xs, sQ, sOld, draws free for the next tile */
     }
     if (!pReady) mbarWait(smemAddr(&pBar), 0);                /* never exit with a bulk copy in flight */
     if (lane == 0 && myAccepted) atomicAdd(a.accept_slots + blockIdx.x, myAccepted);
-}
-
-/* MCMCPP_B200_DENSE_TIMELINE=1: CTA 0 records clock64() at the phase boundaries of each of its tiles (tuning aid) */
-long long* denseTimelineBuf = nullptr;
-long long* denseTimeline()
-{
-    static const bool on = [] { const char* e = getenv("MCMCPP_B200_DENSE_TIMELINE"); return e && e[0] == '1'; }();
-    if (on && !denseTimelineBuf) { cudaMalloc(&denseTimelineBuf, 2 * 16 * 8 * sizeof(long long)); cudaMemset(denseTimelineBuf, 0, 2 * 16 * 8 * sizeof(long long)); }
-    return on ? denseTimelineBuf : nullptr;
 }
 
 struct DenseCalc
@@ -297,33 +298,38 @@ struct DenseCalc
     int smCount;
 };
 
-template <int NB>
+template <int NB, int GROUPS>
 int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_t stream)
 {
     const int Dp = 8 * NB, stride = denseStride(Dp);
-    const size_t perGroup = (size_t)DenseTileRows * stride + 4 * DenseGroupThreads + DenseGroupThreads / 2 + 3 * DenseTileRows;
-    const size_t smem = sizeof(double) * ((size_t)Dp * stride + (size_t)DenseGroups * perGroup);
+    const size_t smem = sizeof(double) * ((size_t)Dp * stride + (size_t)GROUPS * densePerGroupDoubles(Dp));
     const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
-    int grid = (numTiles + DenseGroups - 1) / DenseGroups;
+    int grid = numTiles;
     if (grid > c.smCount) grid = c.smCount;
     if (grid > a.max_grid) grid = a.max_grid;
     static const int useToken = [] { const char* e = getenv("MCMCPP_B200_DENSE_TOKEN"); return (e && e[0] == '0') ? 0 : 1; }();
-    /* opt in to exactly what this shape needs (the kernel also has a few bytes of static shared memory) */
     static DynamicSmemOptIn optedIn[2];                       /* keyed by device inside */
-    long long* tl = denseTimeline();
     static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(DenseThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    if (!a.dim_z || !a.dim_e || !a.dim_j) return MCMCPP_ERR_STATE;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
+    {   /* the draws of this colour: overlapped with the previous colour's update kernel */
+        cudaLaunchConfig_t dcfg = {};
+        dcfg.gridDim = dim3((a.slot_count + 255) / 256); dcfg.blockDim = dim3(256); dcfg.dynamicSmemBytes = 0; dcfg.stream = stream;
+        dcfg.attrs = attr; dcfg.numAttrs = pdl ? 1 : 0;
+        if (cudaLaunchKernelEx(&dcfg, denseDrawKernel, a) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if (a.launch_count) *a.launch_count += 1;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(DenseGroupThreads * GROUPS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
     if (a.trace) {
-        if (!optedIn[1].ensure(denseGaussHalfStep<NB, true>, smem)) return MCMCPP_ERR_CUDA;
-        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, true>, a, c.P, useToken, tl) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if (!optedIn[1].ensure(denseGaussHalfStep<NB, GROUPS, true>, smem)) return MCMCPP_ERR_CUDA;
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, true>, a, c.P, useToken) != cudaSuccess) return MCMCPP_ERR_CUDA;
     } else {
-        if (!optedIn[0].ensure(denseGaussHalfStep<NB, false>, smem)) return MCMCPP_ERR_CUDA;
-        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, false>, a, c.P, useToken, tl) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if (!optedIn[0].ensure(denseGaussHalfStep<NB, GROUPS, false>, smem)) return MCMCPP_ERR_CUDA;
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, false>, a, c.P, useToken) != cudaSuccess) return MCMCPP_ERR_CUDA;
     }
     return launchStatus();
 }
@@ -335,21 +341,16 @@ int denseLaunch(const mcmcpp_halfstep_args* args, const void* calculator, void* 
     cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
     if (a.slot_count <= 0) return MCMCPP_OK;
     const int nb = (a.D + 7) / 8;
-    if (nb <= 2) return launchDenseNB<2>(a, c, stream);
-    if (nb <= 4) return launchDenseNB<4>(a, c, stream);
-    if (nb <= 8) return launchDenseNB<8>(a, c, stream);
-    if (nb <= 13) return launchDenseNB<13>(a, c, stream);
-    if (nb <= 16) return launchDenseNB<16>(a, c, stream);
+    /* groups per CTA: as many as shared memory holds beside P (227 KB), at most 4 */
+    if (nb <= 2) return launchDenseNB<2, 4>(a, c, stream);
+    if (nb <= 4) return launchDenseNB<4, 4>(a, c, stream);
+    if (nb <= 8) return launchDenseNB<8, 4>(a, c, stream);
+    if (nb <= 13) return launchDenseNB<13, 4>(a, c, stream);
+    if (nb <= 16) return launchDenseNB<16, 2>(a, c, stream);
     return MCMCPP_ERR_UNSUPPORTED;
 }
 
 }  // namespace
-
-extern "C" int mcmcpp_dense_timeline(long long* out256)
-{
-    if (!denseTimelineBuf) return MCMCPP_ERR_STATE;
-    return cudaMemcpy(out256, denseTimelineBuf, 2 * 16 * 8 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? MCMCPP_OK : MCMCPP_ERR_CUDA;
-}
 
 /* Tensor-core path for 8 < D <= 128 (unless MCMCPP_B200_DENSE_GENERIC=1 asks for the reference-order generic path). */
 bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator)

@@ -190,6 +190,8 @@ struct mcmcpp_sampler
     double* dChain[ChainSlots] = {nullptr, nullptr};
     int maxGrid = 0;
 
+    double* dStore = nullptr;              /* device-resident chain [devCapRows][W][Dl] (cfg.device_chain_bytes > 0) */
+    long long devCapRows = 0, devRows = 0; /* rows it can hold / holds: the LAST devRows rows of the chain live here */
     double* hChain = nullptr;              /* pinned [capacityRows][W][D] */
     long long hChainRows = 0;              /* allocated rows */
     long long capRows = 0;                 /* byte cap in rows (0 = chain off) */
@@ -228,6 +230,7 @@ struct mcmcpp_sampler
     double** dDimTable = nullptr;          /* [world] device table of every rank's partial table */
     double* dDimZ = nullptr;
     double* dDimE = nullptr;
+    double* dDimS = nullptr;
     int32_t* dDimJ = nullptr;
 };
 
@@ -288,6 +291,33 @@ int ensureDeviceChain(mcmcpp_sampler* s)
         /* rows of walkers this rank does not own stay zero so the host layer can sum shards */
         CUDA_TRY(cudaMemsetAsync(s->dChain[i], 0, sizeof(double) * devRowDoubles(s), s->stream));
     }
+    return MCMCPP_OK;
+}
+
+long long keptRows(const mcmcpp_sampler* s) { return s->capRows > 0 ? std::min(s->stored, s->capRows) : 0; }
+
+/* device-resident chain: move every row held in HBM to its place in the pinned host chain */
+int spillDeviceRows(mcmcpp_sampler* s)
+{
+    if (!s->dStore || s->devRows == 0) return MCMCPP_OK;
+    const long long hostRows = keptRows(s) - s->devRows;
+    int rc = ensureHostChain(s, hostRows + s->devRows);
+    if (rc != MCMCPP_OK) return rc;
+    for (long long r = 0; r < s->devRows; ++r)
+        CUDA_TRY(copyToHostRows(s, s->hChain + rowDoubles(s) * (size_t)(hostRows + r), s->dStore + devRowDoubles(s) * (size_t)r, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->devRows = 0;
+    return MCMCPP_OK;
+}
+
+/* device-resident chain: the slot the next stored row goes to (spills first when the block is full) */
+int nextDeviceSlot(mcmcpp_sampler* s, double** slot)
+{
+    if (s->devRows == s->devCapRows) {
+        int rc = spillDeviceRows(s);
+        if (rc != MCMCPP_OK) return rc;
+    }
+    *slot = s->dStore + devRowDoubles(s) * (size_t)s->devRows;
     return MCMCPP_OK;
 }
 
@@ -395,6 +425,12 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
         const unsigned long long blocks = std::max<unsigned long long>(1ULL, cfg->max_chain_bytes / blockBytes);
         s->capRows = (long long)(blocks * (unsigned long long)cfg->chain_block_steps);
     }
+    if (cfg->device_chain_bytes > 0) {
+        const unsigned long long devRowBytes = sizeof(double) * (unsigned long long)W * (unsigned long long)s->Dl;
+        s->devCapRows = (long long)std::max<unsigned long long>(1ULL, cfg->device_chain_bytes / devRowBytes);
+        if (s->capRows == 0) s->capRows = s->devCapRows;            /* no host cap given: the device block is the chain */
+        s->devCapRows = std::min(s->devCapRows, s->capRows);
+    }
     *out = s;   /* destroy() cleans up on later failure */
 
     CUDA_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
@@ -420,15 +456,20 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     CUDA_TRY(cudaMemset(s->dFlags, 0, sizeof(int32_t) * 4));
     CUDA_TRY(cudaMemset(s->dBarrier, 0, sizeof(int32_t)));
     CUDA_TRY(cudaMemset(s->dPos, 0, sizeof(double) * devRowDoubles(s)));
+    if (s->devCapRows > 0) {
+        CUDA_TRY(cudaMalloc(&s->dStore, sizeof(double) * devRowDoubles(s) * (size_t)s->devCapRows));
+        CUDA_TRY(cudaMemset(s->dStore, 0, sizeof(double) * devRowDoubles(s) * (size_t)s->devCapRows));   /* unowned walkers' rows read 0 */
+    }
     s->moverDoubles = cfg->mover_state_doubles > 0 ? cfg->mover_state_doubles : 0;
     if (s->moverDoubles) {
         CUDA_TRY(cudaMalloc(&s->dMoverState, sizeof(double) * (size_t)W * (size_t)s->moverDoubles));
         CUDA_TRY(cudaMemset(s->dMoverState, 0, sizeof(double) * (size_t)W * (size_t)s->moverDoubles));
     }
     /* draw scratch (z, log(1-u), j of the colour in flight): kernels whose draws run in their own launch */
-    CUDA_TRY(cudaMalloc(&s->dDimZ, sizeof(double) * (size_t)s->K));
-    CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * (size_t)s->K));
-    CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * (size_t)s->K));
+    CUDA_TRY(cudaMalloc(&s->dDimZ, sizeof(double) * 2 * (size_t)s->K));      /* 2K each: room to double-buffer by colour */
+    CUDA_TRY(cudaMalloc(&s->dDimE, sizeof(double) * 2 * (size_t)s->K));
+    CUDA_TRY(cudaMalloc(&s->dDimJ, sizeof(int32_t) * 2 * (size_t)s->K));
+    CUDA_TRY(cudaMalloc(&s->dDimS, sizeof(double) * 2 * (size_t)s->K));
     if (cfg->shard_mode == MCMCPP_SHARD_DIM) {
         /* partial table [2 colours][world][K]; every slot starts EMPTY (all-ones, dim_shard_kernels.cuh) */
         const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K;
@@ -449,7 +490,7 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     a.accept_slots = s->dAcceptSlots; a.flags = s->dFlags;
     a.W = W; a.D = s->Dl; a.K = s->K;
     a.D_total = D; a.dim_begin = s->dimBegin; a.rank = cfg->rank; a.world = cfg->world;
-    a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ;
+    a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ; a.dim_s = s->dDimS;
     a.mover_state = s->dMoverState;
     { int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device); a.sm_count = sms; }
     a.slot_begin = s->slotBegin; a.slot_count = s->slotCount; a.slots_per_rank = s->slotCount;
@@ -484,11 +525,19 @@ int afterInitialState(mcmcpp_sampler* s, const double* hostRowOrNull)
     s->ensembleSteps = 0;
     /* chain row for the initial placement + incrementChainStep (EnsembleSampler.h:228-229) */
     if (s->capRows > 0 && s->stored < s->capRows) {
-        int rc = ensureHostChain(s, s->stored + 1);
-        if (rc != MCMCPP_OK) return rc;
-        double* dst = s->hChain + rowDoubles(s) * (size_t)s->stored;
-        if (hostRowOrNull && s->Dl == s->D) std::memcpy(dst, hostRowOrNull, sizeof(double) * rowDoubles(s));
-        else CUDA_TRY(copyToHostRows(s, dst, s->dPos, s->stream));
+        if (s->dStore) {
+            double* slot = nullptr;
+            int rc = nextDeviceSlot(s, &slot);
+            if (rc != MCMCPP_OK) return rc;
+            CUDA_TRY(cudaMemcpyAsync(slot, s->dPos, sizeof(double) * devRowDoubles(s), cudaMemcpyDeviceToDevice, s->stream));
+            ++s->devRows;
+        } else {
+            int rc = ensureHostChain(s, s->stored + 1);
+            if (rc != MCMCPP_OK) return rc;
+            double* dst = s->hChain + rowDoubles(s) * (size_t)s->stored;
+            if (hostRowOrNull && s->Dl == s->D) std::memcpy(dst, hostRowOrNull, sizeof(double) * rowDoubles(s));
+            else CUDA_TRY(copyToHostRows(s, dst, s->dPos, s->stream));
+        }
     }
     ++s->stored;
     CUDA_TRY(cudaStreamSynchronize(s->stream));
@@ -579,7 +628,8 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     cudaFree(s->dPeerPos);
     cudaFree(s->dMoverState);
     cudaFree(s->dFusedChain);
-    cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimJ);
+    cudaFree(s->dStore);
+    cudaFree(s->dDimPartial); cudaFree(s->dDimTable); cudaFree(s->dDimZ); cudaFree(s->dDimE); cudaFree(s->dDimS); cudaFree(s->dDimJ);
     cudaFree(s->dPos); cudaFree(s->dLogp); cudaFree(s->dRng); cudaFree(s->dAcceptSlots); cudaFree(s->dAcceptSum);
     cudaFree(s->dFlags); cudaFree(s->dTrace); cudaFree(s->dParams); cudaFree(s->dBarrier);
     mcmcpp_builtin_release(s->builtinAux);
@@ -660,7 +710,7 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     const bool chainOn = s->capRows > 0;
     int rc = MCMCPP_OK;
-    if (chainOn) {
+    if (chainOn && !s->dStore) {
         if ((rc = ensureHostChain(s, s->stored + num_steps)) != MCMCPP_OK) return rc;
         if ((rc = ensureDeviceChain(s)) != MCMCPP_OK) return rc;
     }
@@ -678,7 +728,7 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
     if (fused) {
         /* same bookkeeping as the loop below, one launch per chunk of stored steps */
         const size_t rowBytes = sizeof(double) * rowDoubles(s);
-        if (chainOn && !s->dFusedChain) {
+        if (chainOn && !s->dStore && !s->dFusedChain) {
             s->fusedRows = std::max<long long>(1, std::min<long long>(16384, (long long)((32u << 20) / rowBytes)));
             CUDA_TRY(cudaMalloc(&s->dFusedChain, rowBytes * (size_t)s->fusedRows));
         }
@@ -686,24 +736,29 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
         while (remaining > 0) {
             long long chunk = std::min<long long>(remaining, (1 << 18) / perStored + 1);
             const bool keep = chainOn && s->stored < s->capRows;
-            if (chainOn) chunk = keep ? std::min(chunk, std::min(s->fusedRows, s->capRows - s->stored)) : 1;
+            double* devSlot = nullptr;
+            if (keep && s->dStore) {                           /* device-resident chain: the kernel writes the rows where they stay */
+                if ((rc = nextDeviceSlot(s, &devSlot)) != MCMCPP_OK) return rc;
+                chunk = std::min(chunk, std::min(s->devCapRows - s->devRows, s->capRows - s->stored));
+            } else if (chainOn) chunk = keep ? std::min(chunk, std::min(s->fusedRows, s->capRows - s->stored)) : 1;
             mcmcpp_fused_args f;
             f.base = s->base;
             f.base.half = 0; f.base.chain_row = nullptr; f.base.trace = nullptr; f.base.trace_rows = 0;
             f.stored_steps = (int32_t)chunk;
             f.interval = perStored;
-            f.chain_rows = keep ? s->dFusedChain : nullptr;
+            f.chain_rows = keep ? (devSlot ? devSlot : s->dFusedChain) : nullptr;
             rc = s->fusedFn(&f, s->calculator.data(), s->stream);
             if (rc != MCMCPP_OK) return fail(rc, std::string("fused launch failed: ") + cudaGetErrorString(cudaGetLastError()));
             ++s->launches;
-            if (keep) CUDA_TRY(cudaMemcpyAsync(s->hChain + rowDoubles(s) * (size_t)s->stored, s->dFusedChain, rowBytes * (size_t)chunk,
-                                               cudaMemcpyDeviceToHost, s->stream));
+            if (keep && !devSlot) CUDA_TRY(cudaMemcpyAsync(s->hChain + rowDoubles(s) * (size_t)s->stored, s->dFusedChain, rowBytes * (size_t)chunk,
+                                                           cudaMemcpyDeviceToHost, s->stream));
+            if (devSlot) s->devRows += chunk;
             s->stored += chunk;
             s->ensembleSteps += chunk * perStored;
             s->totalSteps += 2ULL * (unsigned long long)s->slotCount * (unsigned long long)perStored * (unsigned long long)chunk;
             remaining -= chunk;
             if (chainOn && s->stored >= s->capRows) { status = MCMCPP_CHAIN_FULL; break; }
-            if (keep) CUDA_TRY(cudaStreamSynchronize(s->stream));      /* the staging rows are reused by the next chunk */
+            if (keep && !devSlot) CUDA_TRY(cudaStreamSynchronize(s->stream));      /* the staging rows are reused by the next chunk */
         }
     }
     for (int i = 0; !fused && i < num_steps; ++i) {
@@ -715,11 +770,16 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
         }
         const bool keepRow = chainOn && s->stored < s->capRows;
         const int slot = (int)(s->stored % ChainSlots);
-        if (keepRow && s->slotBusy[slot]) {
-            CUDA_TRY(cudaStreamWaitEvent(s->stream, s->slotFree[slot], 0));
-            s->slotBusy[slot] = false;
+        double* row = nullptr;
+        if (keepRow && s->dStore) {
+            if ((rc = nextDeviceSlot(s, &row)) != MCMCPP_OK) return rc;
+        } else if (keepRow) {
+            if (s->slotBusy[slot]) {
+                CUDA_TRY(cudaStreamWaitEvent(s->stream, s->slotFree[slot], 0));
+                s->slotBusy[slot] = false;
+            }
+            row = s->dChain[slot];
         }
-        double* row = keepRow ? s->dChain[slot] : nullptr;
         if ((rc = halfStep(s, 0, row)) != MCMCPP_OK) return rc;
         if ((rc = halfStep(s, 1, row)) != MCMCPP_OK) return rc;
         ++s->ensembleSteps;
@@ -731,7 +791,8 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
             }
             ++s->covIndex;
         }
-        if (keepRow && (rc = appendRowFromDeviceSlot(s, slot)) != MCMCPP_OK) return rc;
+        if (keepRow && s->dStore) ++s->devRows;
+        else if (keepRow && (rc = appendRowFromDeviceSlot(s, slot)) != MCMCPP_OK) return rc;
         ++s->stored;
         s->totalSteps += 2ULL * (unsigned long long)s->slotCount * (unsigned long long)perStored;
         if (chainOn && s->stored >= s->capRows) {   /* incrementChainStep() == EndOfChain (Chain.h:229-233) */
@@ -782,6 +843,7 @@ int mcmcpp_sampler_reset(mcmcpp_sampler* s)
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     /* storedSteps = 0, chain reset, walker counters zeroed; positions kept (EnsembleSampler.h:312-322) */
     s->stored = 0;
+    s->devRows = 0;
     s->acceptedBase = 0;
     s->totalSteps = 0;
     CUDA_TRY(cudaMemsetAsync(s->dAcceptSlots, 0, sizeof(unsigned long long) * (size_t)s->maxGrid, s->stream));
@@ -795,9 +857,17 @@ int mcmcpp_sampler_store_current(mcmcpp_sampler* s)
     if (!s->initialised) return fail(MCMCPP_ERR_STATE, "no walker positions yet");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     if (s->capRows > 0 && s->stored < s->capRows) {
-        int rc = ensureHostChain(s, s->stored + 1);
-        if (rc != MCMCPP_OK) return rc;
-        CUDA_TRY(copyToHostRows(s, s->hChain + rowDoubles(s) * (size_t)s->stored, s->dPos, s->stream));
+        if (s->dStore) {
+            double* slot = nullptr;
+            int rc = nextDeviceSlot(s, &slot);
+            if (rc != MCMCPP_OK) return rc;
+            CUDA_TRY(cudaMemcpyAsync(slot, s->dPos, sizeof(double) * devRowDoubles(s), cudaMemcpyDeviceToDevice, s->stream));
+            ++s->devRows;
+        } else {
+            int rc = ensureHostChain(s, s->stored + 1);
+            if (rc != MCMCPP_OK) return rc;
+            CUDA_TRY(copyToHostRows(s, s->hChain + rowDoubles(s) * (size_t)s->stored, s->dPos, s->stream));
+        }
         CUDA_TRY(cudaStreamSynchronize(s->stream));
     }
     ++s->stored;    /* EnsembleSampler.h:240-241 */
@@ -808,15 +878,29 @@ int mcmcpp_sampler_slice_and_burn(mcmcpp_sampler* s, int interval, int burn_in)
 {
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
     if (interval <= 0 || burn_in < 0) return fail(MCMCPP_ERR_ARG, "interval must be > 0 and burnIn >= 0");  /* EnsembleSampler.h:335-336 */
-    /* Chain::resetChainForSubSampling (Chain/Chain.h:268-305) on the contiguous host rows */
-    const long long steps = std::min(s->stored, s->hChainRows > 0 ? s->hChainRows : s->stored);
+    /* Chain::resetChainForSubSampling (Chain/Chain.h:268-305): rows burn_in, burn_in + interval, ... move to the front, in place.
+     * The chain is the host rows followed by the rows still held in HBM; each part is compacted where it lives (host: memmove,
+     * device: row copies on the sampler's stream, every destination at or before its source). */
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    const long long steps = s->capRows > 0 ? keptRows(s) : s->stored;
     if (burn_in == 0 && interval == 1) return MCMCPP_OK;
-    if ((steps - burn_in) < interval || steps <= burn_in) { s->stored = 0; return MCMCPP_OK; }
-    long long kept = 0;
-    const size_t row = rowDoubles(s);
+    if ((steps - burn_in) < interval || steps <= burn_in) { s->stored = 0; s->devRows = 0; return MCMCPP_OK; }
+    const long long hostRows = steps - s->devRows;
+    long long kept = 0, keptHost = 0;
+    const size_t row = rowDoubles(s), devRow = devRowDoubles(s);
     for (long long r = burn_in; r < steps; r += interval, ++kept) {
-        if (s->hChain && r != kept) std::memmove(s->hChain + row * (size_t)kept, s->hChain + row * (size_t)r, sizeof(double) * row);
+        if (r < hostRows) {
+            if (s->hChain && r != kept) std::memmove(s->hChain + row * (size_t)kept, s->hChain + row * (size_t)r, sizeof(double) * row);
+            keptHost = kept + 1;
+        } else {
+            const long long src = r - hostRows, dst = kept - keptHost;
+            if (src != dst)
+                CUDA_TRY(cudaMemcpyAsync(s->dStore + devRow * (size_t)dst, s->dStore + devRow * (size_t)src, sizeof(double) * devRow,
+                                         cudaMemcpyDeviceToDevice, s->stream));
+        }
     }
+    if (s->dStore) CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->devRows = kept - keptHost;
     s->stored = kept;
     return MCMCPP_OK;
 }
@@ -824,6 +908,11 @@ int mcmcpp_sampler_slice_and_burn(mcmcpp_sampler* s, int interval, int burn_in)
 int mcmcpp_sampler_chain(mcmcpp_sampler* s, const double** rows_host, long long* stored_steps)
 {
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (s->dStore && s->devRows > 0) {                     /* device-resident rows cross PCIe now, because the host asked */
+        CUDA_TRY(cudaSetDevice(s->cfg.device));
+        int rc = spillDeviceRows(s);
+        if (rc != MCMCPP_OK) return rc;
+    }
     if (rows_host) *rows_host = s->hChain;
     if (stored_steps) *stored_steps = s->capRows > 0 ? std::min(s->stored, s->capRows) : 0;
     return MCMCPP_OK;
@@ -832,6 +921,11 @@ int mcmcpp_sampler_chain(mcmcpp_sampler* s, const double** rows_host, long long*
 int mcmcpp_sampler_chain_consume(mcmcpp_sampler* s, long long rows)
 {
     if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (s->dStore && s->devRows > 0) {
+        CUDA_TRY(cudaSetDevice(s->cfg.device));
+        int rc = spillDeviceRows(s);
+        if (rc != MCMCPP_OK) return rc;
+    }
     const long long have = s->capRows > 0 ? std::min(s->stored, s->capRows) : s->stored;
     if (rows < 0 || rows > have) return fail(MCMCPP_ERR_ARG, "cannot consume more rows than are stored");
     if (rows == 0) return MCMCPP_OK;
@@ -840,6 +934,50 @@ int mcmcpp_sampler_chain_consume(mcmcpp_sampler* s, long long rows)
     s->stored -= rows;
     for (int i = 0; i < ChainSlots; ++i) s->slotBusy[i] = false;      /* run() left the side stream idle */
     return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_chain_device(mcmcpp_sampler* s, const double** rows_dev, long long* first_step, long long* rows)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (!s->dStore) return fail(MCMCPP_ERR_STATE, "no device-resident chain (cfg.device_chain_bytes == 0)");
+    if (rows_dev) *rows_dev = s->dStore;
+    if (first_step) *first_step = keptRows(s) - s->devRows;
+    if (rows) *rows = s->devRows;
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_chain_covariance(mcmcpp_sampler* s, int slice_interval, double* mean, double* cov, double* corr, long long* points)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    if (slice_interval <= 0) return fail(MCMCPP_ERR_ARG, "slice interval must be positive");
+    if (!s->dStore) return fail(MCMCPP_ERR_STATE, "no device-resident chain (cfg.device_chain_bytes == 0)");
+    if (s->Dl != s->D || (s->cfg.world > 1 && s->cfg.shard_mode != MCMCPP_SHARD_DATA))
+        return fail(MCMCPP_ERR_UNSUPPORTED, "chain analysis on the device needs whole rows of every walker on this rank");
+    if (s->devRows == 0 || s->devRows != keptRows(s)) return fail(MCMCPP_ERR_STATE, "part of the chain has spilled to the host (or it is empty)");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    mcmcpp_cov_accum* c = mcmcpp_cov_create(s->D);
+    if (!c) return fail(MCMCPP_ERR_UNSUPPORTED, "covariance accumulator: numParams must be <= 128");
+    int rc = mcmcpp_cov_zero(c, s->stream);
+    long long used = 0;
+    for (long long r = 0; rc == MCMCPP_OK && r < s->devRows; r += slice_interval, ++used)       /* calculateCovar's slicing (CovarianceMatrix.h:126-131) */
+        rc = mcmcpp_cov_accumulate(c, s->dStore + devRowDoubles(s) * (size_t)r, s->W, s->stream);
+    if (rc == MCMCPP_OK) rc = mcmcpp_cov_finalize(c, used * (long long)s->W, mean, cov, corr, s->stream);
+    if (points) *points = used * (long long)s->W;
+    mcmcpp_cov_destroy(c);
+    return rc == MCMCPP_OK ? rc : fail(rc, "covariance over the device chain failed");
+}
+
+int mcmcpp_sampler_chain_autocorr_times(mcmcpp_sampler* s, int window_scaling, int reference_buffer_reuse, double* iat_out)
+{
+    if (!s || !iat_out) return fail(MCMCPP_ERR_ARG, "null argument");
+    if (!s->dStore) return fail(MCMCPP_ERR_STATE, "no device-resident chain (cfg.device_chain_bytes == 0)");
+    if (s->Dl != s->D || (s->cfg.world > 1 && s->cfg.shard_mode != MCMCPP_SHARD_DATA))
+        return fail(MCMCPP_ERR_UNSUPPORTED, "chain analysis on the device needs whole rows of every walker on this rank");
+    if (s->devRows < 2 || s->devRows != keptRows(s)) return fail(MCMCPP_ERR_STATE, "part of the chain has spilled to the host (or it is too short)");
+    CUDA_TRY(cudaSetDevice(s->cfg.device));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    int rc = mcmcpp_autocorr_device(s->dStore, s->devRows, s->W, s->D, window_scaling, reference_buffer_reuse, iat_out);
+    return rc == MCMCPP_OK ? rc : fail(rc, "autocorrelation times over the device chain failed");
 }
 
 int mcmcpp_sampler_get_state(mcmcpp_sampler* s, double* positions_host, double* aux_host)
@@ -1119,6 +1257,7 @@ int mcmcpp_sampler_checkpoint_restore(mcmcpp_sampler* s, const void* buffer, siz
     s->totalSteps = h.total;
     s->ensembleSteps = h.ensembleSteps;
     s->stored = 0;
+    s->devRows = 0;
     s->initialised = true;
     s->peerNeedsBarrier = true;
     return MCMCPP_OK;

@@ -124,12 +124,14 @@ class EnsembleSampler:
                    "per_walker32" (pcg32(seed, w), the fast engine; stretch move only)
       chainBlockSteps  0: the chain is capped at floor(maxChainSizeBytes / row bytes) rows; 10000: the reference's
                    whole-block granularity (Chain/Chain.h:178), runMCMC returns False exactly where the reference does
+      deviceChainBytes > 0: stored steps stay in HBM (see capi.h); getChain() brings them to the host on demand,
+                   chainCovarianceDevice()/chainAutoCorrTimesDevice() analyse them in place
       traceUpdates record the first n updates' (j, accept, z, e, newp, diff) for tests
       device/rank/world/shardMode  multi-GPU placement (see capi.h)
     """
 
     def __init__(self, randSeed, numWalker, numParameter, move, maxChainSizeBytes=2147483648, stepAct=None,
-                 rngMode="sequential", traceUpdates=0, device=0, rank=0, world=1, shardMode="none", chainBlockSteps=0):
+                 rngMode="sequential", traceUpdates=0, device=0, rank=0, world=1, shardMode="none", chainBlockSteps=0, deviceChainBytes=0):
         if not isinstance(move, (StretchMove, DifferentialEvolution, WalkMove)):
             raise TypeError("the B200 path implements Mover::StretchMove, Mover::DifferentialEvolution and Mover::WalkMove")
         if isinstance(move, (DifferentialEvolution, WalkMove)):
@@ -146,7 +148,8 @@ class EnsembleSampler:
             alpha_num=move.alpha[0], alpha_denom=move.alpha[1], device=int(device), rank=self.rank, world=self.world,
             shard_mode={"none": _capi.SHARD_NONE, "allgather": _capi.SHARD_ALLGATHER, "peer": _capi.SHARD_PEER,
                         "data": _capi.SHARD_DATA, "dim": _capi.SHARD_DIM}[shardMode],
-            trace_updates=int(traceUpdates), max_chain_bytes=int(maxChainSizeBytes), chain_block_steps=int(chainBlockSteps))
+            trace_updates=int(traceUpdates), max_chain_bytes=int(maxChainSizeBytes), chain_block_steps=int(chainBlockSteps),
+            device_chain_bytes=int(deviceChainBytes))
         self.shardMode = shardMode
         params = np.ascontiguousarray(move.calc.params(), dtype=np.float64)
         self._h = C.c_void_p()
@@ -282,6 +285,26 @@ class EnsembleSampler:
 
     def covEnd(self):
         check(self._lib.mcmcpp_sampler_cov_end(self._h))
+
+    # -- analysis over the device-resident chain (deviceChainBytes > 0): nothing crosses PCIe but the results ---------------
+    def chainDeviceRows(self):
+        """(device pointer, first chain index, rows) of the stored steps currently held in HBM."""
+        ptr, first, rows = C.c_void_p(), C.c_longlong(), C.c_longlong()
+        check(self._lib.mcmcpp_sampler_chain_device(self._h, C.byref(ptr), C.byref(first), C.byref(rows)))
+        return ptr.value, first.value, rows.value
+
+    def chainCovarianceDevice(self, sliceInterval=1):
+        """Analysis::CovarianceMatrix::calculateCovar over the device-resident chain -> (mean, cov, corr, points)."""
+        D = self.numParams
+        mean, cov, corr, n = np.empty(D), np.empty((D, D)), np.empty((D, D)), C.c_longlong()
+        check(self._lib.mcmcpp_sampler_chain_covariance(self._h, int(sliceInterval), mean.ctypes.data, cov.ctypes.data, corr.ctypes.data, C.byref(n)))
+        return mean, cov, corr, n.value
+
+    def chainAutoCorrTimesDevice(self, windowScaling=4, referenceBufferReuse=False):
+        """Analysis::AutoCorrCalc::calcAutoCorrTimes (all walkers) over the device-resident chain -> iat[D]."""
+        iat = np.empty(self.numParams)
+        check(self._lib.mcmcpp_sampler_chain_autocorr_times(self._h, int(windowScaling), int(bool(referenceBufferReuse)), iat.ctypes.data))
+        return iat
 
     # -- PostStepAction with a device-resident step view (EnsembleSampler.h:356-359) --------------------------
     def setDeviceStepAction(self, fn):

@@ -172,3 +172,109 @@ def test_samplers_on_two_devices_of_one_process(port):
         pos, aux = s.getWalkerState()
         assert np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
         s.close()
+
+
+# ---- device-resident chain (cfg.device_chain_bytes): rows stay in HBM, slice/burn and analysis in place -----------------
+@pytest.mark.parametrize("kind,W,D,steps,interval,dev_rows", [
+    ("skewed_gauss_2d", 32, 2, 300, 1, 1000),      # fused small-ensemble kernel writes straight into the device block
+    ("skewed_gauss_2d", 32, 2, 300, 3, 64),        # ... with spills to the host chain in between
+    ("rosenbrock_2d", 4096, 2, 40, 1, 100),        # thread kernel, everything stays on the device
+    ("rosenbrock_2d", 4096, 2, 40, 2, 7),          # spills every 7 rows
+    ("diag_gauss", 512, 200, 9, 1, 4)])            # TMA bulk kernel
+def test_device_resident_chain_equals_the_oracle_chain(port, kind, W, D, steps, interval, dev_rows):
+    params = {"skewed_gauss_2d": [0.13], "rosenbrock_2d": None, "diag_gauss": 1.0 / (1.0 + (np.arange(D) % 10))}[kind]
+    init, lp = seeded_init(port, kind, params, W, D, 17)
+    s = make_sampler(kind, params if params is not None else [], W, D, seed=2, deviceChainBytes=dev_rows * W * D * 8)
+    if interval > 1:
+        s.setSlicingMode(True, interval)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run(kind, params, init, lp, steps, interval=interval, seed=2)
+    ptr, first, rows = s.chainDeviceRows()
+    assert rows == (steps + 1 if dev_rows > steps else rows) and first + rows == steps + 1
+    chain = s.getChain()                              # the host asks: the device rows cross PCIe now
+    assert chain.shape[0] == steps + 1 and np.array_equal(chain[0], init) and np.array_equal(chain[1:], o["chain"])
+    assert s.chainDeviceRows()[2] == 0
+    s.close()
+
+
+@pytest.mark.parametrize("interval,burn,dev_rows", [(3, 5, 1000), (1, 20, 1000), (7, 0, 25), (2, 31, 25), (50, 10, 1000), (5, 80, 25)])
+def test_slice_and_burn_on_the_device(port, interval, burn, dev_rows):
+    W, D, steps = 256, 2, 59
+    init, lp = seeded_init(port, "rosenbrock_2d", None, W, D, 5)
+    s = make_sampler("rosenbrock_2d", [], W, D, deviceChainBytes=dev_rows * W * D * 8, maxChainSizeBytes=1 << 30)
+    s.setInitialWalkerPos(init, lp)
+    s.runMCMC(steps)                                  # dev_rows = 25: rows 0..49 have spilled to the host, 50..59 are in HBM
+    o = port.run("rosenbrock_2d", None, init, lp, steps)
+    full = np.concatenate([init[None], o["chain"]])
+    n = full.shape[0]
+    s.sliceAndBurnChain(interval, burn)               # Chain::resetChainForSubSampling (Chain.h:268-305)
+    expect = full if (burn == 0 and interval == 1) else full[:0] if ((n - burn) < interval or n <= burn) else full[burn::interval]
+    assert s.getStoredSteps() == expect.shape[0]
+    assert np.array_equal(s.getChain(), expect)
+    s.runMCMC(3)                                      # and the chain goes on behind the compacted rows
+    o2 = port.run("rosenbrock_2d", None, o["pos"], o["logp"], 3, rng=o["rng"])
+    assert np.array_equal(s.getChain(), np.concatenate([expect, o2["chain"]]))
+    s.close()
+
+
+def test_device_chain_analysis_matches_the_oracle(port):
+    """CovarianceMatrix and AutoCorrCalc over the device-resident chain: the definitions of the reference classes
+    (pinned in tests/test_analysis_cpu.py), nothing but the results crossing PCIe."""
+    W, D, steps = 64, 5, 300
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    init, lp = seeded_init(port, "diag_gauss", iv, W, D, 53)
+    s = make_sampler("diag_gauss", iv, W, D, deviceChainBytes=1 << 26, maxChainSizeBytes=0)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run("diag_gauss", iv, init, lp, steps)
+    chain = np.concatenate([init[None], o["chain"]])
+    mean, cov, corr, n = s.chainCovarianceDevice(3)
+    om, oc, or_, on = port.covariance(chain, 3)
+    assert n == on and np.allclose(mean, om, rtol=1e-12, atol=1e-14) and np.allclose(cov, oc, rtol=1e-11, atol=1e-13)
+    assert np.allclose(corr, or_, rtol=1e-11, atol=1e-13)
+    assert np.array_equal(s.chainAutoCorrTimesDevice(referenceBufferReuse=True), port.autocorr(chain, quirk=True))   # one CTA, reference order
+    assert np.array_equal(s.chainAutoCorrTimesDevice(referenceBufferReuse=False), port.autocorr(chain, quirk=False))
+    assert s.chainDeviceRows()[2] == steps + 1         # still on the device
+    s.sliceAndBurnChain(2, 21)
+    assert np.array_equal(s.chainAutoCorrTimesDevice(), port.autocorr(chain[21::2], quirk=False))
+    s.close()
+
+
+def test_device_chain_autocorr_walker_groups_many_walkers(port):
+    """Clean mode, many walkers: one CTA per (parameter, walker group); same definition, compensated sums regrouped."""
+    W, D, steps = 8192, 2, 127
+    init, lp = seeded_init(port, "rosenbrock_2d", None, W, D, 6)
+    s = make_sampler("rosenbrock_2d", [], W, D, deviceChainBytes=1 << 28, maxChainSizeBytes=0)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    iat = s.chainAutoCorrTimesDevice()
+    chain = s.getChain().copy()
+    ref = port.autocorr(chain, quirk=False)
+    assert np.allclose(iat, ref, rtol=1e-10, atol=0)
+    s.close()
+
+
+def test_c2_million_walker_iat_without_the_chain_crossing_pcie(port):
+    """BASELINE configs[1] shape: 2^20 walkers, every 4th of 1024 steps kept in HBM (4.3 GB), burn-in dropped ON THE DEVICE,
+    integrated autocorrelation times and covariance taken ON THE DEVICE; compared statistically with the oracle's
+    AutoCorrCalc restatement on the first 4,096 walkers of the same chain (fetched for the test only)."""
+    W, D, kept, every = 1 << 20, 2, 256, 4
+    init, lp = seeded_init(port, "rosenbrock_2d", None, W, D, 2)
+    s = make_sampler("rosenbrock_2d", [], W, D, rngMode="per_walker32", deviceChainBytes=(kept + 2) * W * D * 8, maxChainSizeBytes=0)
+    s.setSlicingMode(True, every)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(kept)
+    s.sliceAndBurnChain(1, 65)                        # 192 rows left
+    ptr, first, rows = s.chainDeviceRows()
+    assert (first, rows) == (0, kept + 1 - 65)
+    iat = s.chainAutoCorrTimesDevice()
+    mean, cov, corr, n = s.chainCovarianceDevice(1)
+    assert n == rows * W and s.chainDeviceRows()[2] == rows           # nothing left the device
+    assert np.all(np.isfinite(iat)) and np.all(np.abs(iat) > 0.5)
+    sub = s.getChain()[:, :4096, :].copy()            # test only: now the rows cross PCIe
+    ref = port.autocorr(sub, quirk=False)
+    assert np.allclose(np.abs(iat), np.abs(ref), rtol=0.15), (iat, ref)
+    m2 = sub.reshape(-1, D).mean(axis=0)
+    assert np.allclose(mean, m2, atol=0.05)
+    s.close()
