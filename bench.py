@@ -474,7 +474,7 @@ def measure(torch, dist, m, parallel, args, workload, steps, warm, with_e2e, wit
 
 
 # short runs of the other BASELINE configs appended to the default line: (steps, warm-up, fraction of the cpu sample)
-OTHERS = {"c1": (10000, 2000, 0.5, None, 1), "c2": (200, 20, 0.3, None, 1), "c3": (60, 10, 0.3, None, 1), "c5": (2, 1, 1.0, None, 0)}
+OTHERS = {"c1": (20000, 2000, 0.5, None, 1), "c2": (2000, 50, 0.3, None, 1), "c3": (400, 20, 0.3, None, 1), "c5": (2, 1, 1.0, None, 0)}
 
 
 def gpu_arm(args):

@@ -144,7 +144,8 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
             mrow[0] = zN; mrow[1] = eN; mrow[2] = sN; mrow[3] = pN;
             if (TMA) {
                 const uint32_t bar = smemAddr(barBase + 8u * (st * NW + warp * WPW + lane));
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     /* the stage's last readers were this warp's own lanes */
+                /* the stage's last readers were this warp's own lanes, lanes whose loads have returned (their values were used):
+                 * program order is enough, and a proxy fence here would wait for the warp's copies already in flight */
                 mbarExpectTx(bar, 2u * rowBytes);
                 bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride), a.pos + (size_t)(own0 + i) * D, rowBytes, bar);
                 bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride + rowStride), a.pos + (size_t)(other0 + jN) * D, rowBytes, bar);

@@ -29,7 +29,7 @@ using namespace MCMC::Device;
 /* GROUPS independent 4-warp groups per CTA, each walking its own sequence of 32-walker tiles and synchronising on its own named
  * barrier: while one group holds the FP64 tensor pipe, the others are in their scalar phases (row loads, proposals, epilogue,
  * decision, commit).  P is shared. */
-enum { DenseTileRows = 32, DenseGroupWarps = 4, DenseGroupThreads = DenseGroupWarps * 32 };
+enum { DenseTileRows = 32 };
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
 {
@@ -37,23 +37,22 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-__device__ __forceinline__ void groupSync(int group)
+__device__ __forceinline__ void groupSync(int group, int groupThreads)
 {
-    asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");       /* 128 = DenseGroupThreads */
-    static_assert(DenseGroupThreads == 128, "named-barrier thread count is spelled out in the asm above");
+    asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "r"(groupThreads) : "memory");
 }
 
 /* The tensor pipe is handed from group to group like a token, in tile order: barrier 5 + g is completed by the 128 waiting threads
  * of group g plus the 128 arriving threads of the group that had the tile before.  On B200 DMMA and the plain FP64 instructions
  * share one pipe per SM sub-partition and it is a FIFO: two groups issuing DMMAs at once only interleave (both finish late), so one
  * group at a time gets the pipe for its 2.75 us of DMMAs and the scalar phases of the other groups ride in the gaps. */
-__device__ __forceinline__ void tokenWait(int group)
+__device__ __forceinline__ void tokenWait(int group, int groupThreads)
 {
-    asm volatile("bar.sync %0, 256;" ::"r"(group + 5) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"r"(group + 5), "r"(2 * groupThreads) : "memory");
 }
-__device__ __forceinline__ void tokenPass(int toGroup)
+__device__ __forceinline__ void tokenPass(int toGroup, int groupThreads)
 {
-    asm volatile("bar.arrive %0, 256;" ::"r"(toGroup + 5) : "memory");
+    asm volatile("bar.arrive %0, %1;" ::"r"(toGroup + 5), "r"(2 * groupThreads) : "memory");
 }
 
 __host__ __device__ constexpr int denseStrideC(int Dp)
@@ -90,11 +89,18 @@ __global__ void __launch_bounds__(256) denseDrawKernel(const mcmcpp_halfstep_arg
 }
 
 /* NB = number of 8-wide column blocks (padded dimension Dp = 8*NB).  CTA b takes tiles b, b + gridDim, ...; its n-th tile
- * goes to group n % GROUPS.  In the MMA phase warp (rp, ch) of the group owns rows 16rp..16rp+15 (two 8-row fragments
- * that share every B fragment: 9 shared-memory loads per 14 DMMAs) and one half of the D/8 column blocks. */
-template <int NB, int GROUPS, bool TRACE>
-__global__ void __launch_bounds__(DenseGroupThreads * GROUPS, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken)
+ * goes to group n % GROUPS.  A group has GW warps; in the MMA phase warp (rp, ch) owns FR = 8 / GW row fragments of 8 rows
+ * (rows 8 FR rp ...) that share every B fragment, and one half of the D/8 column blocks:
+ *   GW = 8, GROUPS = 2: one fragment per warp, 8 shared-memory loads per 7 DMMAs, two warps per SM sub-partition in the MMA phase;
+ *   GW = 4, GROUPS = 4: two fragments per warp, 9 loads per 14 DMMAs, one warp per sub-partition, three groups in scalar phases.
+ * passEarly: the token goes on right after the MMA loop (the epilogue queues behind the next group's DMMAs) instead of after
+ * the decisions. */
+template <int NB, int GROUPS, int GW, bool TRACE>
+__global__ void __launch_bounds__(32 * GW * GROUPS, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken,
+                                                                         const int passEarly)
 {
+    constexpr int DenseGroupWarps = GW, DenseGroupThreads = 32 * GW, FR = 8 / GW;
+    static_assert(GW == 4 || GW == 8, "a group is 4 or 8 warps");
     constexpr int Dp = 8 * NB;
     constexpr int NBH = (NB + 1) / 2;                         /* column blocks per warp: warps 0-1 take [0,NBH), 2-3 the rest */
     constexpr int Threads = DenseGroupThreads * GROUPS;
@@ -153,19 +159,20 @@ __global__ void __launch_bounds__(DenseGroupThreads * GROUPS, 1) denseGaussHalfS
             const bool valid = i < a.slot_count;
             sZ[tid] = valid ? dz[i] : 1.0; sE[tid] = valid ? de[i] : 0.0; sJ[tid] = valid ? dj[i] : 0;
         }
-        groupSync(group);
+        groupSync(group, DenseGroupThreads);
         /* (b) proposals: warp per row, coalesced row reads, exact reference arithmetic.  The loads of four rows are issued
          * before their first use so one L2/HBM latency covers them all. */
         {
-            constexpr int RowsPerWarp = DenseTileRows / DenseGroupWarps;     /* 8, in two halves of 4 */
+            constexpr int RowsPerWarp = DenseTileRows / DenseGroupWarps;     /* 4 or 8: four rows at a time */
+            constexpr int Halves = RowsPerWarp / 4;
             constexpr int KCH = (Dp + 31) / 32;
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                double cur[RowsPerWarp / 2][KCH], sl[RowsPerWarp / 2][KCH];
+            for (int h = 0; h < Halves; ++h) {
+                double cur[4][KCH], sl[4][KCH];
                 double oldp = 0.0;
 #pragma unroll
-                for (int rr = 0; rr < RowsPerWarp / 2; ++rr) {
-                    const int r = warp + (h * (RowsPerWarp / 2) + rr) * DenseGroupWarps;
+                for (int rr = 0; rr < 4; ++rr) {
+                    const int r = warp + (h * 4 + rr) * DenseGroupWarps;
                     const int i = row0 + r;
                     const bool valid = i < a.slot_count;
                     const int w = a.half * a.K + a.slot_begin + (valid ? i : 0);
@@ -181,10 +188,10 @@ __global__ void __launch_bounds__(DenseGroupThreads * GROUPS, 1) denseGaussHalfS
                         sl[rr][k] = ok ? __ldg(sel + d) : 0.0;
                     }
                 }
-                if (lane < RowsPerWarp / 2) sOld[warp + (h * (RowsPerWarp / 2) + lane) * DenseGroupWarps] = oldp;
+                if (lane < 4) sOld[warp + (h * 4 + lane) * DenseGroupWarps] = oldp;
 #pragma unroll
-                for (int rr = 0; rr < RowsPerWarp / 2; ++rr) {
-                    const int r = warp + (h * (RowsPerWarp / 2) + rr) * DenseGroupWarps;
+                for (int rr = 0; rr < 4; ++rr) {
+                    const int r = warp + (h * 4 + rr) * DenseGroupWarps;
                     const double z = sZ[r];
                     double* xr = Xs + (size_t)r * stride;
 #pragma unroll
@@ -195,58 +202,63 @@ __global__ void __launch_bounds__(DenseGroupThreads * GROUPS, 1) denseGaussHalfS
                 }
             }
         }
-        groupSync(group);
+        groupSync(group, DenseGroupThreads);
         if (!pReady) { mbarWait(smemAddr(&pBar), 0); pReady = true; }
-        if (useToken && n > 0) tokenWait(group);
+        if (useToken && n > 0) tokenWait(group, DenseGroupThreads);
         /* (c) Y = Xs * Ps on the FP64 tensor cores */
         {
-            const int rp = warp & 1, ch = warp >> 1;
+            constexpr int RowWarps = DenseGroupWarps / 2;                 /* warps side by side along the rows */
+            const int rp = warp % RowWarps, ch = warp / RowWarps;
             const int nb0 = ch * NBH;
             const int cnt = (NB - nb0) < NBH ? (NB - nb0) : NBH;
-            double acc[2][NBH][2];
+            double acc[FR][NBH][2];
 #pragma unroll
-            for (int nb = 0; nb < NBH; ++nb) { acc[0][nb][0] = 0.0; acc[0][nb][1] = 0.0; acc[1][nb][0] = 0.0; acc[1][nb][1] = 0.0; }
+            for (int f = 0; f < FR; ++f)
+#pragma unroll
+                for (int nb = 0; nb < NBH; ++nb) { acc[f][nb][0] = 0.0; acc[f][nb][1] = 0.0; }
             const int g = lane >> 2, t = lane & 3;
-            const double* arow0 = Xs + (size_t)(rp * 16 + g) * stride + t;
-            const double* arow1 = arow0 + (size_t)8 * stride;
+            const double* arow0 = Xs + (size_t)(rp * 8 * FR + g) * stride + t;
             const double* bcol = Ps + (size_t)t * stride + g + nb0 * 8;
 #pragma unroll 2
             for (int k = 0; k < Dp; k += 4) {
-                const double a0 = arow0[k], a1 = arow1[k];
+                double av[FR];
+#pragma unroll
+                for (int f = 0; f < FR; ++f) av[f] = arow0[(size_t)f * 8 * stride + k];
                 const double* bk = bcol + (size_t)k * stride;
 #pragma unroll
                 for (int nb = 0; nb < NBH; ++nb) {
                     if (nb < cnt) {
                         const double bv = bk[nb * 8];
-                        dmma884(acc[0][nb][0], acc[0][nb][1], a0, bv);
-                        dmma884(acc[1][nb][0], acc[1][nb][1], a1, bv);
+#pragma unroll
+                        for (int f = 0; f < FR; ++f) dmma884(acc[f][nb][0], acc[f][nb][1], av[f], bv);
                     }
                 }
             }
-            /* the pipe goes to the group that has the next tile; the epilogue's few FP64 operations queue behind its DMMAs, but this
-             * group does not need the pipe again before GROUPS - 1 other tiles have gone through it */
-            if (useToken && n + 1 < myTiles) tokenPass((group + 1) % GROUPS);
-            /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols (nb0+nb)*8 + 2t, +1 of rows g and 8 + g */
+            /* passEarly: the pipe goes to the group that has the next tile now; the epilogue's few FP64 operations queue behind its
+             * DMMAs, but this group does not need the pipe again before GROUPS - 1 other tiles have gone through it */
+            if (useToken && passEarly && n + 1 < myTiles) tokenPass((group + 1) % GROUPS, DenseGroupThreads);
+            /* epilogue: q_row = sum_col X[row][col] * Y[row][col]; this lane holds cols (nb0+nb)*8 + 2t, +1 of row g of each fragment */
 #pragma unroll
-            for (int r2 = 0; r2 < 2; ++r2) {
-                const double* xrow = Xs + (size_t)(rp * 16 + r2 * 8 + g) * stride + nb0 * 8 + 2 * t;
+            for (int f = 0; f < FR; ++f) {
+                const double* xrow = Xs + (size_t)(rp * 8 * FR + f * 8 + g) * stride + nb0 * 8 + 2 * t;
                 double q = 0.0, q1 = 0.0;
 #pragma unroll
                 for (int nb = 0; nb < NBH; ++nb) {
                     if (nb < cnt) {
                         const double2 xv = *reinterpret_cast<const double2*>(xrow + nb * 8);
-                        q = fma(xv.x, acc[r2][nb][0], q);
-                        q1 = fma(xv.y, acc[r2][nb][1], q1);
+                        q = fma(xv.x, acc[f][nb][0], q);
+                        q1 = fma(xv.y, acc[f][nb][1], q1);
                     }
                 }
                 q += q1;
                 q += __shfl_xor_sync(0xffffffffu, q, 1);
                 q += __shfl_xor_sync(0xffffffffu, q, 2);
-                if (t == 0) sQ[ch * DenseTileRows + rp * 16 + r2 * 8 + g] = q;
+                if (t == 0) sQ[ch * DenseTileRows + rp * 8 * FR + f * 8 + g] = q;
             }
         }
-        groupSync(group);
-        /* (d) Metropolis decisions: lane r of warp 0 decides row r; sQ[r] <- new log-prob */
+        groupSync(group, DenseGroupThreads);
+        /* (d) Metropolis decisions: lane r of warp 0 decides row r; sQ[r] <- new log-prob.  Unless passEarly, the group still holds
+         * the token here: the few dependent FP64 adds would otherwise queue behind the other group's DMMAs (same pipe). */
         if (warp == 0) {
             const double newp = -0.5 * (sQ[lane] + sQ[DenseTileRows + lane]);
             const double scaling = __dmul_rn(log(sZ[lane]), (double)(D - 1));
@@ -257,7 +269,8 @@ __global__ void __launch_bounds__(DenseGroupThreads * GROUPS, 1) denseGaussHalfS
             sQ[DenseTileRows + lane] = diff;
             sAcc[lane] = accepted ? 1 : 0;
         }
-        groupSync(group);
+        if (useToken && !passEarly && n + 1 < myTiles) tokenPass((group + 1) % GROUPS, DenseGroupThreads);
+        groupSync(group, DenseGroupThreads);
         /* (e) commit: each warp writes its accepted rows (and the chain row of every walker on stored steps) */
         for (int r = warp; r < DenseTileRows; r += DenseGroupWarps) {
             const int i = row0 + r;
@@ -285,7 +298,7 @@ __global__ void __launch_bounds__(DenseGroupThreads * GROUPS, 1) denseGaussHalfS
                 }
             }
         }
-        groupSync(group);                                     /* Xs, sQ, sOld, draws free for the next tile */
+        groupSync(group, DenseGroupThreads);                                     /* Xs, sQ, sOld, draws free for the next tile */
     }
     if (!pReady) mbarWait(smemAddr(&pBar), 0);                /* never exit with a bulk copy in flight */
     if (lane == 0 && myAccepted) atomicAdd(a.accept_slots + blockIdx.x, myAccepted);
@@ -298,9 +311,10 @@ struct DenseCalc
     int smCount;
 };
 
-template <int NB, int GROUPS>
+template <int NB, int GROUPS, int GW>
 int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_t stream)
 {
+    constexpr int DenseGroupThreads = 32 * GW;
     const int Dp = 8 * NB, stride = denseStride(Dp);
     const size_t smem = sizeof(double) * ((size_t)Dp * stride + (size_t)GROUPS * densePerGroupDoubles(Dp));
     const int numTiles = (a.slot_count + DenseTileRows - 1) / DenseTileRows;
@@ -308,6 +322,8 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     if (grid > c.smCount) grid = c.smCount;
     if (grid > a.max_grid) grid = a.max_grid;
     static const int useToken = [] { const char* e = getenv("MCMCPP_B200_DENSE_TOKEN"); return (e && e[0] == '0') ? 0 : 1; }();
+    static const int passEnv = [] { const char* e = getenv("MCMCPP_B200_DENSE_PASS_EARLY"); return e ? atoi(e) : -1; }();
+    const int passEarly = passEnv >= 0 ? passEnv : (GW == 4 ? 1 : 0);
     static DynamicSmemOptIn optedIn[2];                       /* keyed by device inside */
     static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
     if (!a.dim_z || !a.dim_e || !a.dim_j) return MCMCPP_ERR_STATE;
@@ -325,11 +341,11 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(DenseGroupThreads * GROUPS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
     if (a.trace) {
-        if (!optedIn[1].ensure(denseGaussHalfStep<NB, GROUPS, true>, smem)) return MCMCPP_ERR_CUDA;
-        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, true>, a, c.P, useToken) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if (!optedIn[1].ensure(denseGaussHalfStep<NB, GROUPS, GW, true>, smem)) return MCMCPP_ERR_CUDA;
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, GW, true>, a, c.P, useToken, passEarly) != cudaSuccess) return MCMCPP_ERR_CUDA;
     } else {
-        if (!optedIn[0].ensure(denseGaussHalfStep<NB, GROUPS, false>, smem)) return MCMCPP_ERR_CUDA;
-        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, false>, a, c.P, useToken) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if (!optedIn[0].ensure(denseGaussHalfStep<NB, GROUPS, GW, false>, smem)) return MCMCPP_ERR_CUDA;
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, GW, false>, a, c.P, useToken, passEarly) != cudaSuccess) return MCMCPP_ERR_CUDA;
     }
     return launchStatus();
 }
@@ -341,12 +357,19 @@ int denseLaunch(const mcmcpp_halfstep_args* args, const void* calculator, void* 
     cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
     if (a.slot_count <= 0) return MCMCPP_OK;
     const int nb = (a.D + 7) / 8;
-    /* groups per CTA: as many as shared memory holds beside P (227 KB), at most 4 */
-    if (nb <= 2) return launchDenseNB<2, 4>(a, c, stream);
-    if (nb <= 4) return launchDenseNB<4, 4>(a, c, stream);
-    if (nb <= 8) return launchDenseNB<8, 4>(a, c, stream);
-    if (nb <= 13) return launchDenseNB<13, 4>(a, c, stream);
-    if (nb <= 16) return launchDenseNB<16, 2>(a, c, stream);
+    /* CTA shape: two 8-warp groups, or (MCMCPP_B200_DENSE_SHAPE=4x4) four 4-warp groups where shared memory holds them beside P */
+    static const bool four = [] { const char* e = getenv("MCMCPP_B200_DENSE_SHAPE"); return e && e[0] == '4'; }();
+    if (four && nb <= 13) {
+        if (nb <= 2) return launchDenseNB<2, 4, 4>(a, c, stream);
+        if (nb <= 4) return launchDenseNB<4, 4, 4>(a, c, stream);
+        if (nb <= 8) return launchDenseNB<8, 4, 4>(a, c, stream);
+        return launchDenseNB<13, 4, 4>(a, c, stream);
+    }
+    if (nb <= 2) return launchDenseNB<2, 2, 8>(a, c, stream);
+    if (nb <= 4) return launchDenseNB<4, 2, 8>(a, c, stream);
+    if (nb <= 8) return launchDenseNB<8, 2, 8>(a, c, stream);
+    if (nb <= 13) return launchDenseNB<13, 2, 8>(a, c, stream);
+    if (nb <= 16) return launchDenseNB<16, 2, 8>(a, c, stream);
     return MCMCPP_ERR_UNSUPPORTED;
 }
 

@@ -270,14 +270,15 @@ def test_c5_full_size_linreg_against_sufficient_statistics():
 
 @pytest.mark.parametrize("W,D,steps", [(256, 9, 8), (512, 100, 6), (512, 125, 6), (2048, 500, 3), (2048, 1000, 3), (2100, 1001, 2)])
 def test_dim_shard_kernels_single_rank_bit_exact(port, W, D, steps):
-    """The two-kernel DIM-sharded half-step (partial sums -> table -> rank-ordered sum -> commit) with world = 1 is the
-    single-GPU summation order: bit-exact against the oracle, chain and trace included (even and odd row lengths)."""
+    """The DIM-sharded half-step (draws; fused persistent kernel: partial sums -> slots of the table -> rank-ordered sum ->
+    commit from shared memory) with world = 1 is the single-GPU summation order: bit-exact against the oracle, chain and trace
+    included (even slices: TMA ring; odd slices: plain loads)."""
     iv = 1.0 / (1.0 + (np.arange(D) % 10))
     init, lp = seeded_init(port, "diag_gauss", iv, W, D, 200 + D)
     s = make_sampler("diag_gauss", iv, W, D, seed=1, traceUpdates=W, shardMode="dim")
     s.setInitialWalkerPos(init, lp)
     assert s.runMCMC(steps)
-    assert s.getLaunchCount() == (8 if D % 2 == 0 else 6) * steps    # [draw,] partial, decide, commit per colour
+    assert s.getLaunchCount() == 4 * steps                            # draw + fused kernel per colour
     o = port.run("diag_gauss", iv, init, lp, steps, seed=1, want_trace=True)
     assert np.array_equal(s.getChain()[1:], o["chain"])
     pos, aux = s.getWalkerState()
