@@ -182,6 +182,10 @@ typedef struct mcmcpp_fused_args {
 } mcmcpp_fused_args;
 typedef int (*mcmcpp_fused_fn)(const mcmcpp_fused_args* args, const void* calculator, void* cuda_stream);
 
+/* All ranks of one DIM-sharded ensemble held by ONE process on ONE device (mcmcpp_sampler_run_group): one colour of every rank,
+ * on one stream, with every rank's update kernel in a single cooperative launch (include/mcmcpp_b200/dim_shard_kernels.cuh). */
+typedef int (*mcmcpp_group_fn)(const mcmcpp_halfstep_args* args_per_rank, const void* const* calculators, int count, void* cuda_stream);
+
 /* ---- life cycle: EnsembleSampler ctor/dtor (EnsembleSampler.h:199-218,72) -------------------- */
 /* `calculator` is copied by value (calc_bytes); it must be trivially copyable and any pointers in
  * it must be device pointers (the Calculator "view" convention of targets.h). */
@@ -279,6 +283,15 @@ int mcmcpp_comm_unique_id(void* id128);
 int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128);
 int mcmcpp_sampler_peer_export(mcmcpp_sampler* s, void* handle64);
 int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_ranks);
+/* The ranks of one DIM-sharded ensemble inside ONE process on ONE device (a one-GPU box, tests): samplers[r] was created with
+ * rank r, world `count` (<= 4), shard_mode DIM.  _peer_import_local wires their partial tables together by plain pointers;
+ * _run_group is runMCMC for all of them in lockstep -- per colour one cooperative launch in which CTA b works for rank b % count
+ * (ranks that wait on one another must never be separate launches on one GPU: nothing guarantees they are resident together).
+ * Same results as `count` processes on `count` GPUs.  Built-in Calculators register their group launcher themselves. */
+int mcmcpp_sampler_set_group_launcher(mcmcpp_sampler* s, mcmcpp_group_fn launcher);
+int mcmcpp_sampler_peer_import_local(mcmcpp_sampler* const* samplers, int count);
+int mcmcpp_sampler_run_group(mcmcpp_sampler* const* samplers, int count, int num_steps);
+
 /* DIM sharding: columns [*begin, *begin + *count) of a num_params-wide row held by `rank` (pairs of columns are dealt
  * out so that every slice but possibly the last has even length: 16-byte aligned slices for vector loads). */
 int mcmcpp_dim_slice(int num_params, int rank, int world, int* begin, int* count);

@@ -36,6 +36,7 @@
 #ifndef MCMCPP_B200_DIM_SHARD_KERNELS_CUH
 #define MCMCPP_B200_DIM_SHARD_KERNELS_CUH
 
+#include <cstring>
 #include "mcmcpp_b200/stretch_kernels.cuh"
 
 namespace MCMC
@@ -99,8 +100,9 @@ __device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long 
  * n+P+1 are loaded (lane q <-> walker q of the warp) while tile n is worked on, and the first look at the partial slots
  * of tile n-L is taken before the partial sums of tile n are computed. */
 template <class Calc, int WPW, bool TMA, bool TRACE>
-__global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
-                                                                  const int S, const int P, const int L, const unsigned long long timeoutNs)
+__device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a, const Calc& calcIn, const uint32_t rowStride,
+                                                  const int S, const int P, const int L, const unsigned long long timeoutNs,
+                                                  const int bid, const int nblocks)
 {
     extern __shared__ __align__(128) unsigned char dimSmem[];
     constexpr int NW = DimFusedWarps * WPW;                  /* walkers per tile */
@@ -112,7 +114,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
     double* meta = reinterpret_cast<double*>(barBase + 8u * (size_t)S * NW);            /* [S][NW][4] */
     double* ctaPartial = meta + (size_t)S * NW * 4;                                      /* [2][NW] */
     const int numTiles = (K + NW - 1) / NW;
-    const int myTiles = (int)blockIdx.x < numTiles ? (numTiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const int myTiles = bid < numTiles ? (numTiles - bid + nblocks - 1) / nblocks : 0;
     const int own0 = a.half * K, other0 = (1 - a.half) * K;
     double* const table = a.dim_partial[a.rank] + (size_t)a.half * a.world * K;          /* this rank's slots of the colour */
     const int qpp = 32 / a.world;                            /* walkers whose partials one poll pass of the warp takes */
@@ -127,7 +129,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
     /* scalars of the tile this lane will issue next (lane q < WPW <-> walker q of the warp), loaded one iteration ahead */
     int jN = 0; double zN = 1.0, eN = 0.0, sN = 0.0, pN = 0.0;
     auto prefetch = [&](int n) {
-        const int i = ((int)blockIdx.x + n * (int)gridDim.x) * NW + warp * WPW + lane;
+        const int i = (bid + n * nblocks) * NW + warp * WPW + lane;
         if (n < myTiles && lane < WPW && i < K) {
             jN = __ldg(a.dim_j + i); zN = __ldg(a.dim_z + i); eN = __ldg(a.dim_e + i); sN = __ldg(a.dim_s + i);
             pN = a.logp[own0 + i];
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
     };
     /* walker slot (warp, q) of local tile n lives in stage n % S; uses the scalars prefetch(n) loaded */
     auto issue = [&](int n) {
-        const int tile = (int)blockIdx.x + n * (int)gridDim.x;
+        const int tile = bid + n * nblocks;
         const int st = n % S;
         unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
         const int i = tile * NW + warp * WPW + lane;
@@ -179,13 +181,13 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
         unsigned long long seen = DimEmpty;
         if (finishing) {
             const int ql = lane / a.world, r = lane - ql * a.world;
-            const int ip = ((int)blockIdx.x + m * (int)gridDim.x) * NW + warp * WPW + ql;
+            const int ip = (bid + m * nblocks) * NW + warp * WPW + ql;
             if (ql < qpp && ql < WPW && ip < K) seen = *reinterpret_cast<volatile unsigned long long*>(table + (size_t)r * K + ip);
         }
 
         /* ---- partial(n): proposal slices and their partial sums, one line of NW partials to every rank ---- */
         if (n < myTiles) {
-            const int tile = (int)blockIdx.x + n * (int)gridDim.x;
+            const int tile = bid + n * nblocks;
             const int st = n % S;
             const uint32_t parity = (uint32_t)((n / S) & 1);
             const unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
@@ -232,7 +234,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
 
         /* ---- finish(n - L): rank-ordered sum, Metropolis test, commit from shared memory ---- */
         if (finishing) {
-            const int tile = (int)blockIdx.x + m * (int)gridDim.x;
+            const int tile = bid + m * nblocks;
             const int st = m % S;
             const unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
             const double* mrow = meta + ((size_t)st * NW + warp * WPW) * 4;
@@ -297,7 +299,40 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
             __syncwarp();
         }
     }
-    if (lane == 0 && myAccepted) atomicAdd(a.accept_slots + blockIdx.x, myAccepted);
+    if (lane == 0 && myAccepted) atomicAdd(a.accept_slots + bid, myAccepted);
+}
+
+template <class Calc, int WPW, bool TMA, bool TRACE>
+__global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
+                                                                  const int S, const int P, const int L, const unsigned long long timeoutNs)
+{
+    dimShardFusedBody<Calc, WPW, TMA, TRACE>(a, calcIn, rowStride, S, P, L, timeoutNs, (int)blockIdx.x, (int)gridDim.x);
+}
+
+/* ---- all ranks of a DIM-sharded ensemble in ONE cooperative launch of one process (mcmcpp_sampler_run_group) ------------
+ * The ranks' kernels wait on one another (each polls partial sums the others store), so as separate launches on one GPU
+ * nothing would guarantee that they are resident together.  Here CTA b works as block b / R of rank b % R, on that rank's own
+ * buffers, tables and column slice, with exactly the code of the one-rank kernel: the world > 1 protocol -- slot hand-over,
+ * rank-ordered sums, replicated decisions, per-rank slices (even ones through the TMA ring, odd ones through plain loads) --
+ * runs on a one-GPU box.  A cooperative launch either has every CTA resident or fails. */
+enum { DimGroupMax = 4 };
+template <class Calc>
+struct DimGroupArgs
+{
+    int count;
+    uint32_t rowStride[DimGroupMax];
+    mcmcpp_halfstep_args args[DimGroupMax];
+    alignas(16) unsigned char calc[DimGroupMax][(sizeof(Calc) + 15) / 16 * 16];      /* Calculators by value (they need not be default-constructible) */
+};
+
+template <class Calc, int WPW, bool TRACE>
+__global__ void __launch_bounds__(DimFusedThreads) dimShardFusedGroup(const DimGroupArgs<Calc> g, const int S, const int P, const int L,
+                                                                       const unsigned long long timeoutNs)
+{
+    const int r = (int)blockIdx.x % g.count, bid = (int)blockIdx.x / g.count, nblocks = (int)gridDim.x / g.count;
+    const Calc& calc = *reinterpret_cast<const Calc*>(g.calc[r]);
+    if ((g.args[r].D % 2) == 0) dimShardFusedBody<Calc, WPW, true, TRACE>(g.args[r], calc, g.rowStride[r], S, P, L, timeoutNs, bid, nblocks);
+    else dimShardFusedBody<Calc, WPW, false, TRACE>(g.args[r], calc, g.rowStride[r], S, P, L, timeoutNs, bid, nblocks);
 }
 
 /* Launcher of a DIM-sharded colour for a separable Calculator (a VIEW of this rank's columns: term(x, d) takes the
@@ -345,6 +380,66 @@ struct DimShardLauncher
     static int fusedT(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
     {
         return a.trace ? fused<WPW, TMA, true>(a, calc, stream, rowStride) : fused<WPW, TMA, false>(a, calc, stream, rowStride);
+    }
+
+    template <int WPW, bool TRACE>
+    static int fusedGroup(const DimGroupArgs<Calc>& g, cudaStream_t stream, uint32_t maxStride)
+    {
+        constexpr int NW = DimFusedWarps * WPW;
+        static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
+        int P = 2, L = 2;
+        const size_t stageBytes = (size_t)NW * 2u * maxStride;
+        while (P + L + 1 > 3 && (size_t)(P + L + 1) * (stageBytes + 40u * NW) + 16u * NW > 100u * 1024u) { if (L > P) --L; else if (P > 1) --P; else --L; }
+        const int S = P + L + 1;
+        const size_t smem = (size_t)S * (stageBytes + 40u * NW) + 16u * NW;
+        if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
+        static DynamicSmemOptIn optIn;
+        if (!optIn.ensure(dimShardFusedGroup<Calc, WPW, TRACE>, smem)) return MCMCPP_ERR_CUDA;
+        int perSm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFusedGroup<Calc, WPW, TRACE>, DimFusedThreads, smem) != cudaSuccess || perSm < 1)
+            return MCMCPP_ERR_CUDA;
+        const mcmcpp_halfstep_args& a0 = g.args[0];
+        const int numTiles = (a0.K + NW - 1) / NW;
+        int nblocks = ((a0.sm_count > 0 ? a0.sm_count : 148) * perSm) / g.count;      /* per rank; everything resident at once */
+        if (nblocks > numTiles) nblocks = numTiles;
+        if (nblocks > a0.max_grid) nblocks = a0.max_grid;
+        if (nblocks < 1) return MCMCPP_ERR_UNSUPPORTED;
+        int s_ = S, p_ = P, l_ = L;
+        unsigned long long t_ = timeoutNs;
+        void* params[] = {(void*)&g, &s_, &p_, &l_, &t_};
+        if (cudaLaunchCooperativeKernel((const void*)dimShardFusedGroup<Calc, WPW, TRACE>, dim3(nblocks * g.count), dim3(DimFusedThreads), params, smem,
+                                        stream) != cudaSuccess)
+            return MCMCPP_ERR_CUDA;
+        return launchStatus();
+    }
+
+    /* mcmcpp_group_fn: one colour of `count` ranks that live in this process, on one stream */
+    static int launchGroup(const mcmcpp_halfstep_args* args, const void* const* calculators, int count, void* cudaStream)
+    {
+        if (count < 1 || count > DimGroupMax) return MCMCPP_ERR_UNSUPPORTED;
+        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
+        DimGroupArgs<Calc> g;
+        g.count = count;
+        uint32_t maxStride = 0;
+        bool trace = false;
+        for (int r = 0; r < count; ++r) {
+            const mcmcpp_halfstep_args& a = args[r];
+            if (!a.dim_partial || !a.dim_z || !a.dim_e || !a.dim_j || !a.dim_s || a.world != count || a.rank != r || a.K != args[0].K) return MCMCPP_ERR_STATE;
+            g.args[r] = a;
+            memcpy(g.calc[r], calculators[r], sizeof(Calc));
+            g.rowStride[r] = ((uint32_t)a.D * 8u + 127u) & ~127u;
+            if (g.rowStride[r] > maxStride) maxStride = g.rowStride[r];
+            trace = trace || a.trace != nullptr;
+            dimShardDraw<<<(a.K + 255) / 256, 256, 0, stream>>>(a);                 /* every rank makes the same draws, into its own scratch */
+        }
+        for (int r = count; r < DimGroupMax; ++r) { g.args[r] = args[0]; memcpy(g.calc[r], g.calc[0], sizeof(Calc)); g.rowStride[r] = g.rowStride[0]; }
+        const size_t perWalker = 2u * (size_t)maxStride, stage = 16u * 1024u;
+#define MCMCPP_DIM_GROUP(WPW) (trace ? fusedGroup<WPW, true>(g, stream, maxStride) : fusedGroup<WPW, false>(g, stream, maxStride))
+        if (DimFusedWarps * 8 * perWalker <= stage) return MCMCPP_DIM_GROUP(8);
+        if (DimFusedWarps * 4 * perWalker <= stage) return MCMCPP_DIM_GROUP(4);
+        if (DimFusedWarps * 2 * perWalker <= stage) return MCMCPP_DIM_GROUP(2);
+        return MCMCPP_DIM_GROUP(1);
+#undef MCMCPP_DIM_GROUP
     }
 
     static int launch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)

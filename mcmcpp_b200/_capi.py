@@ -68,6 +68,9 @@ SYMBOLS = {
     "mcmcpp_sampler_comm_init": (C.c_int, [_h, C.c_void_p]),
     "mcmcpp_sampler_peer_export": (C.c_int, [_h, C.c_void_p]),
     "mcmcpp_sampler_peer_import": (C.c_int, [_h, C.c_void_p]),
+    "mcmcpp_sampler_set_group_launcher": (C.c_int, [_h, C.c_void_p]),
+    "mcmcpp_sampler_peer_import_local": (C.c_int, [C.POINTER(_h), C.c_int]),
+    "mcmcpp_sampler_run_group": (C.c_int, [C.POINTER(_h), C.c_int, C.c_int]),
     "mcmcpp_sampler_cov_begin": (C.c_int, [_h, C.c_int, C.c_int]),
     "mcmcpp_sampler_cov_result": (C.c_int, [_h, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_longlong)]),
     "mcmcpp_sampler_cov_end": (C.c_int, [_h]),

@@ -161,4 +161,11 @@ mcmcpp_fused_fn mcmcpp_builtin_fused(int kind, int D, int shardMode)
     }
 }
 
+mcmcpp_group_fn mcmcpp_builtin_group(int kind, int shardMode)
+{
+    using namespace MCMC::Targets;
+    if (shardMode == MCMCPP_SHARD_DIM && kind == MCMCPP_TARGET_DIAG_GAUSS) return &MCMC::Device::DimShardLauncher<DiagGaussian<double> >::launchGroup;
+    return nullptr;
+}
+
 void mcmcpp_builtin_release(void* aux) { mcmcpp_linreg_release(aux); }   /* the only target with scratch */

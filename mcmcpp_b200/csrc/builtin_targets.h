@@ -16,6 +16,8 @@ int mcmcpp_builtin_bind_mover(int moverKind, int kind, int W, int D, const doubl
                               size_t nValues, const double* devParams, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);
 /* the fused small-ensemble launcher that goes with mcmcpp_builtin_bind's generic launcher for this target, or NULL */
 mcmcpp_fused_fn mcmcpp_builtin_fused(int kind, int D, int shardMode);
+/* the rank-group launcher (all ranks of a DIM-sharded ensemble in one cooperative launch) for this target, or NULL */
+mcmcpp_group_fn mcmcpp_builtin_group(int kind, int shardMode);
 void mcmcpp_builtin_release(void* aux);
 /* dense_gauss.cu: FP64 tensor-core half-step for the dense Gaussian; false = use the generic launcher */
 bool mcmcpp_dense_bind(int D, const double* devP, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);

@@ -218,6 +218,8 @@ struct mcmcpp_sampler
     unsigned long long peerEpoch = 0;      /* PEER: barriers issued so far (every rank makes the same calls) */
     bool peerNeedsBarrier = false;         /* PEER: rows changed by the host since the last barrier (set_initial / restore) */
     mcmcpp_fused_fn fusedFn = nullptr;     /* small ensembles: the whole runMCMC loop in one launch */
+    mcmcpp_group_fn groupFn = nullptr;     /* DIM: all ranks of the ensemble in one cooperative launch (mcmcpp_sampler_run_group) */
+    bool tablesWired = false;              /* DIM: every rank's partial table is known (peer_import or peer_import_local) */
     double* dFusedChain = nullptr;         /* [fusedRows][W][D] rows filled by the fused kernel */
     long long fusedRows = 0;
     void* stepCtx = nullptr;
@@ -586,6 +588,7 @@ int mcmcpp_sampler_create_builtin(const mcmcpp_config* cfg, int target_kind, con
                              &s->builtinAux, cfg->shard_mode, s->dimBegin, s->Dl);
     if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "unknown built-in target or bad parameter count"); }
     s->fusedFn = mcmcpp_builtin_fused(target_kind, s->D, cfg->shard_mode);
+    s->groupFn = mcmcpp_builtin_group(target_kind, cfg->shard_mode);
     return MCMCPP_OK;
 }
 
@@ -705,7 +708,7 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
         return fail(MCMCPP_ERR_STATE, "world > 1 but no communicator (mcmcpp_sampler_comm_init)");
     if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_PEER && !s->dPeerPos)
         return fail(MCMCPP_ERR_STATE, "PEER sharding needs mcmcpp_sampler_peer_import");
-    if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_DIM && s->peerOpened.empty())
+    if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_DIM && !s->tablesWired)
         return fail(MCMCPP_ERR_STATE, "DIM sharding needs mcmcpp_sampler_peer_import");
     CUDA_TRY(cudaSetDevice(s->cfg.device));
     const bool chainOn = s->capRows > 0;
@@ -1083,12 +1086,134 @@ int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_rank
     }
     if (dim) {
         CUDA_TRY(cudaMemcpy(s->dDimTable, ptrs.data(), sizeof(double*) * (size_t)s->cfg.world, cudaMemcpyHostToDevice));
+        s->tablesWired = true;
         return MCMCPP_OK;
     }
     CUDA_TRY(cudaMalloc(&s->dPeerPos, sizeof(double*) * (size_t)s->cfg.world));
     CUDA_TRY(cudaMemcpy(s->dPeerPos, ptrs.data(), sizeof(double*) * (size_t)s->cfg.world, cudaMemcpyHostToDevice));
     s->base.peer_pos = s->dPeerPos;
     return MCMCPP_OK;
+}
+
+/* ---- the ranks of one DIM-sharded ensemble inside one process on one device (capi.h) ------------------------------------ */
+int mcmcpp_sampler_set_group_launcher(mcmcpp_sampler* s, mcmcpp_group_fn launcher)
+{
+    if (!s) return fail(MCMCPP_ERR_ARG, "null sampler");
+    s->groupFn = launcher;
+    return MCMCPP_OK;
+}
+
+namespace
+{
+int checkGroup(mcmcpp_sampler* const* ss, int count)
+{
+    if (!ss || count < 2 || count > 4) return fail(MCMCPP_ERR_ARG, "a rank group has 2 to 4 samplers");
+    for (int r = 0; r < count; ++r) {
+        mcmcpp_sampler* s = ss[r];
+        if (!s) return fail(MCMCPP_ERR_ARG, "null sampler in the group");
+        if (s->cfg.shard_mode != MCMCPP_SHARD_DIM || s->cfg.world != count || s->cfg.rank != r)
+            return fail(MCMCPP_ERR_ARG, "samplers[r] must be rank r of a DIM-sharded ensemble of `count` ranks");
+        if (s->W != ss[0]->W || s->D != ss[0]->D || s->cfg.device != ss[0]->cfg.device || s->cfg.seed != ss[0]->cfg.seed ||
+            s->cfg.rng_mode != ss[0]->cfg.rng_mode || s->capRows != ss[0]->capRows || s->dStore || s->cfg.trace_updates != ss[0]->cfg.trace_updates)
+            return fail(MCMCPP_ERR_ARG, "the samplers of a group must agree on walkers, parameters, device, seed, rng mode and chain cap (no device-resident chain)");
+    }
+    return MCMCPP_OK;
+}
+}
+
+int mcmcpp_sampler_peer_import_local(mcmcpp_sampler* const* samplers, int count)
+{
+    int rc = checkGroup(samplers, count);
+    if (rc != MCMCPP_OK) return rc;
+    CUDA_TRY(cudaSetDevice(samplers[0]->cfg.device));
+    std::vector<double*> ptrs((size_t)count);
+    for (int r = 0; r < count; ++r) ptrs[(size_t)r] = samplers[r]->dDimPartial;
+    for (int r = 0; r < count; ++r) {
+        CUDA_TRY(cudaMemcpy(samplers[r]->dDimTable, ptrs.data(), sizeof(double*) * (size_t)count, cudaMemcpyHostToDevice));
+        samplers[r]->tablesWired = true;
+    }
+    return MCMCPP_OK;
+}
+
+int mcmcpp_sampler_run_group(mcmcpp_sampler* const* ss, int count, int num_steps)
+{
+    int rc = checkGroup(ss, count);
+    if (rc != MCMCPP_OK) return rc;
+    if (num_steps <= 0) return fail(MCMCPP_ERR_ARG, "numSteps must be positive");
+    mcmcpp_sampler* lead = ss[0];
+    if (!lead->groupFn) return fail(MCMCPP_ERR_UNSUPPORTED, "this Calculator has no rank-group launcher (mcmcpp_sampler_set_group_launcher)");
+    for (int r = 0; r < count; ++r) {
+        if (!ss[r]->initialised) return fail(MCMCPP_ERR_STATE, "runMCMC before setInitialWalkerPos");
+        if (!ss[r]->tablesWired) return fail(MCMCPP_ERR_STATE, "the group needs mcmcpp_sampler_peer_import_local");
+        if (ss[r]->stored != lead->stored || ss[r]->subSampling != lead->subSampling || ss[r]->interval != lead->interval)
+            return fail(MCMCPP_ERR_STATE, "the samplers of a group must have made the same calls so far");
+    }
+    CUDA_TRY(cudaSetDevice(lead->cfg.device));
+    /* every rank's work goes to the lead's stream for the duration of the call: one stream, one cooperative launch per colour */
+    std::vector<cudaStream_t> own((size_t)count);
+    for (int r = 0; r < count; ++r) { CUDA_TRY(cudaStreamSynchronize(ss[r]->stream)); own[(size_t)r] = ss[r]->stream; ss[r]->stream = lead->stream; }
+    struct Restore { mcmcpp_sampler* const* ss; std::vector<cudaStream_t>& own; int count;
+                     ~Restore() { for (int r = 0; r < count; ++r) ss[r]->stream = own[(size_t)r]; } } restore{ss, own, count};
+    const bool chainOn = lead->capRows > 0;
+    if (chainOn)
+        for (int r = 0; r < count; ++r) {
+            if ((rc = ensureHostChain(ss[r], ss[r]->stored + num_steps)) != MCMCPP_OK) return rc;
+            if ((rc = ensureDeviceChain(ss[r])) != MCMCPP_OK) return rc;
+        }
+    const int perStored = lead->subSampling ? lead->interval : 1;
+    std::vector<mcmcpp_halfstep_args> args((size_t)count);
+    std::vector<const void*> calcs((size_t)count);
+    for (int r = 0; r < count; ++r) calcs[(size_t)r] = ss[r]->calculator.data();
+    auto colour = [&](int half, bool store) -> int {
+        for (int r = 0; r < count; ++r) {
+            mcmcpp_sampler* s = ss[r];
+            mcmcpp_halfstep_args a = s->base;
+            a.half = half;
+            a.chain_row = store ? s->dChain[(int)(s->stored % ChainSlots)] : nullptr;
+            a.trace = nullptr; a.trace_rows = 0;
+            if (s->dTrace) {
+                long long first = s->ensembleSteps * (long long)s->W + (long long)half * s->K;
+                long long rows = (long long)s->cfg.trace_updates - first;
+                if (rows > 0) { a.trace = s->dTrace + first; a.trace_rows = (int32_t)std::min<long long>(rows, s->K); }
+            }
+            args[(size_t)r] = a;
+        }
+        int rcl = lead->groupFn(args.data(), calcs.data(), count, lead->stream);
+        if (rcl != MCMCPP_OK) return fail(rcl, std::string("rank-group launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+        for (int r = 0; r < count; ++r) ss[r]->launches += 2;
+        return MCMCPP_OK;
+    };
+    int status = MCMCPP_OK;
+    for (int i = 0; i < num_steps; ++i) {
+        for (int j = 1; j < perStored; ++j) {
+            if ((rc = colour(0, false)) != MCMCPP_OK) return rc;
+            if ((rc = colour(1, false)) != MCMCPP_OK) return rc;
+            for (int r = 0; r < count; ++r) ++ss[r]->ensembleSteps;
+        }
+        const bool keepRow = chainOn && lead->stored < lead->capRows;
+        const int slot = (int)(lead->stored % ChainSlots);
+        if (keepRow)
+            for (int r = 0; r < count; ++r)
+                if (ss[r]->slotBusy[slot]) { CUDA_TRY(cudaStreamWaitEvent(lead->stream, ss[r]->slotFree[slot], 0)); ss[r]->slotBusy[slot] = false; }
+        if ((rc = colour(0, keepRow)) != MCMCPP_OK) return rc;
+        if ((rc = colour(1, keepRow)) != MCMCPP_OK) return rc;
+        for (int r = 0; r < count; ++r) {
+            mcmcpp_sampler* s = ss[r];
+            ++s->ensembleSteps;
+            if (keepRow && (rc = appendRowFromDeviceSlot(s, slot)) != MCMCPP_OK) return rc;
+            ++s->stored;
+            s->totalSteps += 2ULL * (unsigned long long)s->slotCount * (unsigned long long)perStored;
+        }
+        if (chainOn && lead->stored >= lead->capRows) { status = MCMCPP_CHAIN_FULL; break; }
+    }
+    CUDA_TRY(cudaStreamSynchronize(lead->stream));
+    for (int r = 0; r < count; ++r) {
+        CUDA_TRY(cudaStreamSynchronize(ss[r]->copyStream));
+        int32_t timedOut = 0;
+        CUDA_TRY(cudaMemcpy(&timedOut, ss[r]->dFlags + 1, sizeof timedOut, cudaMemcpyDeviceToHost));
+        if (timedOut) return fail(MCMCPP_ERR_STATE, "a wait on another rank's partial sums timed out inside the rank group");
+    }
+    return status;
 }
 
 /* ---- Analysis::CovarianceMatrix on the device (Analysis/CovarianceMatrix.h:120-215) -------------------------- */

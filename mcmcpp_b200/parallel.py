@@ -91,3 +91,19 @@ def reduce_counts(sampler, group=None):
     v = torch.tensor([a, t], dtype=torch.int64, device=dev)
     dist.all_reduce(v, group=group)
     return int(v[0]), int(v[1])
+
+
+class RankGroup:
+    """All ranks of ONE DIM-sharded ensemble inside one process on one device (a one-GPU box): samplers[r] was created with
+    rank=r, world=len(samplers), shardMode="dim".  runMCMC steps them in lockstep, every rank's update kernel in a single
+    cooperative launch (ranks that wait on one another must not be separate launches on one GPU).  Same results as one process
+    per GPU."""
+
+    def __init__(self, samplers):
+        self.samplers = list(samplers)
+        self._arr = (C.c_void_p * len(self.samplers))(*[s._h for s in self.samplers])
+        _capi.check(_capi.lib().mcmcpp_sampler_peer_import_local(self._arr, len(self.samplers)))
+
+    def runMCMC(self, numSteps):
+        rc = _capi.check(_capi.lib().mcmcpp_sampler_run_group(self._arr, len(self.samplers), int(numSteps)))
+        return rc != _capi.CHAIN_FULL
