@@ -415,7 +415,7 @@ def measure(torch, dist, m, parallel, args, workload, steps, warm, with_e2e, wit
                         + ("; traffic = ncu dram bytes of one launch (profiles/traffic.json), N=1 only" if world == 1 else "")}
     if D <= 8:
         # state is L2-resident: the kernel is bound by instruction issue, not HBM -- report the issue-slot roofline beside it
-        inst = consts.get(workload + "_inst_executed_per_launch")
+        inst = consts.get(workload + ("_per_walker32" if rng_mode == "per_walker32" else "") + "_inst_executed_per_launch")
         sm_hz = (clocks.summary().get("sm_mhz") or 1965) * 1e6
         sms = torch.cuda.get_device_properties(local).multi_processor_count
         if inst and W // 2 > 1024:

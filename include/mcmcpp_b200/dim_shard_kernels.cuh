@@ -95,31 +95,51 @@ __device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long 
  * TMA = rows are 16-byte multiples (even slice): staged with cp.async.bulk; otherwise the warp copies its walkers'
  * rows into the stage itself (odd slices: tests and the last rank of an odd row).
  * Shared memory: S stages x [NW walkers][own row | partner row] (rowStride bytes each), S x NW mbarriers, S x NW x 4 doubles of
- * per-walker scalars {z, log(1-u), log(z)(D-1), current log-prob}, 2 x NW partials.
+ * per-walker scalars {z, log(1-u), log(z)(D-1), current log-prob}, 2 x NW partials.  S stages = P in flight + L waiting for
+ * the other ranks + 1 being worked on; S and P are compile-time so that the ring indices cost no division.
  * Nothing on the per-tile critical path waits for global memory except the staged rows themselves: the scalars of tile
  * n+P+1 are loaded (lane q <-> walker q of the warp) while tile n is worked on, and the first look at the partial slots
- * of tile n-L is taken before the partial sums of tile n are computed. */
-template <class Calc, int WPW, bool TMA, bool TRACE>
+ * of tile n-L is taken before the partial sums of tile n are computed.  At a 1 KB slice the kernel is bound by instruction
+ * issue, not by HBM: all index arithmetic is carried as running pointers. */
+template <class Calc, int WPW, bool TMA, bool TRACE, int S, int P>
 __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a, const Calc& calcIn, const uint32_t rowStride,
-                                                  const int S, const int P, const int L, const unsigned long long timeoutNs,
-                                                  const int bid, const int nblocks)
+                                                  const unsigned long long timeoutNs, const int bid, const int nblocks)
 {
     extern __shared__ __align__(128) unsigned char dimSmem[];
     constexpr int NW = DimFusedWarps * WPW;                  /* walkers per tile */
+    constexpr int L = S - P - 1;
+    static_assert(P >= 1 && L >= 1, "ring: P tiles in flight, L waiting, one in work");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int D = a.D, K = a.K;
     const uint32_t rowBytes = (uint32_t)D * 8u;
-    const size_t stageBytes = (size_t)NW * 2u * rowStride;
-    unsigned char* barBase = dimSmem + (size_t)S * stageBytes;
-    double* meta = reinterpret_cast<double*>(barBase + 8u * (size_t)S * NW);            /* [S][NW][4] */
-    double* ctaPartial = meta + (size_t)S * NW * 4;                                      /* [2][NW] */
+    const uint32_t stageBytes = (uint32_t)NW * 2u * rowStride;
+    unsigned char* const barBase = dimSmem + (size_t)S * stageBytes;
+    double* const meta = reinterpret_cast<double*>(barBase + 8u * S * NW);              /* [S][NW][4] */
+    double* const ctaPartial = meta + S * NW * 4;                                        /* [2][NW] */
     const int numTiles = (K + NW - 1) / NW;
     const int myTiles = bid < numTiles ? (numTiles - bid + nblocks - 1) / nblocks : 0;
     const int own0 = a.half * K, other0 = (1 - a.half) * K;
     double* const table = a.dim_partial[a.rank] + (size_t)a.half * a.world * K;          /* this rank's slots of the colour */
-    const int qpp = 32 / a.world;                            /* walkers whose partials one poll pass of the warp takes */
     Calc calc = calcIn;
     unsigned long long myAccepted = 0;
+
+    /* this warp's part of a stage, as running offsets */
+    unsigned char* const warpRows0 = dimSmem + (size_t)(warp * WPW) * 2u * rowStride;   /* + st * stageBytes */
+    double* const warpMeta0 = meta + warp * WPW * 4;                                     /* + st * NW * 4 */
+    const uint32_t warpBar0 = smemAddr(barBase) + 8u * (uint32_t)(warp * WPW);           /* + st * 8 * NW */
+    const int walkerStep = nblocks * NW;                      /* walker index distance between consecutive tiles of this CTA */
+    const int firstWalker = bid * NW + warp * WPW;            /* walker of slot (warp, 0) of local tile 0 */
+
+    /* who polls what: one pass of the warp takes the partials of qpp walkers, lane (ql * world + r) reads rank r's slot of walker ql */
+    const int qpp = 32 / a.world;
+    const int pollQ = lane / a.world, pollR = lane - pollQ * a.world;
+    const bool pollLane = pollQ < qpp;
+    double* const pollSlot0 = table + (size_t)pollR * K;      /* + walker index */
+    /* who sends what: thread t < world * NW stores partial k = t % NW of the tile into rank t / NW's table */
+    const int sendK = (int)threadIdx.x % NW;
+    const bool sender = (int)threadIdx.x < a.world * NW;
+    double* const sendSlot0 = sender ? a.dim_partial[(int)threadIdx.x / NW] + ((size_t)a.half * a.world + a.rank) * K + sendK : nullptr;   /* + tile * NW */
+    const bool manyRanks = a.world * NW > DimFusedThreads;    /* more than one store pass (world > 8 with wide tiles): generic loop */
 
     if (TMA) {
         for (int b = threadIdx.x; b < S * NW; b += DimFusedThreads) mbarInit(smemAddr(barBase + 8u * b), 1);
@@ -128,35 +148,36 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
 
     /* scalars of the tile this lane will issue next (lane q < WPW <-> walker q of the warp), loaded one iteration ahead */
     int jN = 0; double zN = 1.0, eN = 0.0, sN = 0.0, pN = 0.0;
-    auto prefetch = [&](int n) {
-        const int i = (bid + n * nblocks) * NW + warp * WPW + lane;
-        if (n < myTiles && lane < WPW && i < K) {
-            jN = __ldg(a.dim_j + i); zN = __ldg(a.dim_z + i); eN = __ldg(a.dim_e + i); sN = __ldg(a.dim_s + i);
-            pN = a.logp[own0 + i];
+    int wPre = firstWalker + lane;                            /* walker the next prefetch is for (this lane's) */
+    auto prefetch = [&]() {
+        if (lane < WPW && wPre < K) {
+            jN = __ldg(a.dim_j + wPre); zN = __ldg(a.dim_z + wPre); eN = __ldg(a.dim_e + wPre); sN = __ldg(a.dim_s + wPre);
+            pN = a.logp[own0 + wPre];
         }
+        wPre += walkerStep;
     };
-    /* walker slot (warp, q) of local tile n lives in stage n % S; uses the scalars prefetch(n) loaded */
-    auto issue = [&](int n) {
-        const int tile = bid + n * nblocks;
-        const int st = n % S;
-        unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
-        const int i = tile * NW + warp * WPW + lane;
+    /* issue: walker slot (warp, q) of the next tile goes to stage stI; uses the scalars the last prefetch loaded */
+    int stI = 0, wIss = firstWalker;                          /* stage and first walker (of this warp) of the tile to issue */
+    auto issue = [&]() {
+        unsigned char* rows = warpRows0 + (size_t)stI * stageBytes;
+        const int i = wIss + lane;
         if (lane < WPW && i < K) {
-            double* mrow = meta + ((size_t)st * NW + warp * WPW + lane) * 4;
-            mrow[0] = zN; mrow[1] = eN; mrow[2] = sN; mrow[3] = pN;
+            double2* mrow = reinterpret_cast<double2*>(warpMeta0 + stI * (NW * 4) + lane * 4);
+            mrow[0] = make_double2(zN, eN); mrow[1] = make_double2(sN, pN);
             if (TMA) {
-                const uint32_t bar = smemAddr(barBase + 8u * (st * NW + warp * WPW + lane));
                 /* the stage's last readers were this warp's own lanes, lanes whose loads have returned (their values were used):
                  * program order is enough, and a proxy fence here would wait for the warp's copies already in flight */
+                const uint32_t bar = warpBar0 + 8u * (uint32_t)(stI * NW + lane);
+                const uint32_t dst = smemAddr(rows) + (uint32_t)lane * 2u * rowStride;
                 mbarExpectTx(bar, 2u * rowBytes);
-                bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride), a.pos + (size_t)(own0 + i) * D, rowBytes, bar);
-                bulkLoad(smemAddr(rows + (size_t)lane * 2u * rowStride + rowStride), a.pos + (size_t)(other0 + jN) * D, rowBytes, bar);
+                bulkLoad(dst, a.pos + (size_t)(own0 + i) * D, rowBytes, bar);
+                bulkLoad(dst + rowStride, a.pos + (size_t)(other0 + jN) * D, rowBytes, bar);
             }
         }
         if (!TMA) {
 #pragma unroll
             for (int q = 0; q < WPW; ++q) {
-                const int iq = tile * NW + warp * WPW + q;
+                const int iq = wIss + q;
                 if (iq >= K) break;
                 const int jq = __shfl_sync(0xffffffffu, jN, q);
                 const double* ownRow = a.pos + (size_t)(own0 + iq) * D;
@@ -167,39 +188,37 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
             }
         }
         __syncwarp();
+        stI = stI + 1 == S ? 0 : stI + 1;
+        wIss += walkerStep;
     };
 
-    prefetch(0);
-    for (int n = 0; n < P && n < myTiles; ++n) { issue(n); prefetch(n + 1); }
+    prefetch();
+    int issued = 0;
+    for (; issued < P && issued < myTiles; ++issued) { issue(); prefetch(); }
 
+    int stP = 0, wPart = firstWalker;                         /* stage / first walker of the tile whose partial sums are next */
+    uint32_t parP = 0;                                        /* mbarrier phase parity of that stage's current use */
+    int stF = 0, wFin = firstWalker;                          /* ... of the tile to finish next */
+    int sendOff = bid * NW;                                   /* first walker of the tile being summed (send side) */
     for (int n = 0; n < myTiles + L; ++n) {
-        if (n + P < myTiles) { issue(n + P); prefetch(n + P + 1); }
+        if (issued < myTiles) { issue(); prefetch(); ++issued; }
 
         /* first look at the partial slots of tile n - L (pass 0 of the polls), taken before the arithmetic below */
-        const int m = n - L;
-        const bool finishing = m >= 0 && m < myTiles;
+        const bool finishing = n >= L;
         unsigned long long seen = DimEmpty;
-        if (finishing) {
-            const int ql = lane / a.world, r = lane - ql * a.world;
-            const int ip = (bid + m * nblocks) * NW + warp * WPW + ql;
-            if (ql < qpp && ql < WPW && ip < K) seen = *reinterpret_cast<volatile unsigned long long*>(table + (size_t)r * K + ip);
-        }
+        if (finishing && pollLane && pollQ < WPW && wFin + pollQ < K) seen = *reinterpret_cast<volatile unsigned long long*>(pollSlot0 + wFin + pollQ);
 
         /* ---- partial(n): proposal slices and their partial sums, one line of NW partials to every rank ---- */
         if (n < myTiles) {
-            const int tile = bid + n * nblocks;
-            const int st = n % S;
-            const uint32_t parity = (uint32_t)((n / S) & 1);
-            const unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
-            const double* mrow = meta + ((size_t)st * NW + warp * WPW) * 4;
+            const unsigned char* rows = warpRows0 + (size_t)stP * stageBytes;
+            const double* mrow = warpMeta0 + stP * (NW * 4);
             double s[WPW];
 #pragma unroll
             for (int q = 0; q < WPW; ++q) {
-                const int i = tile * NW + warp * WPW + q;
                 double p0 = 0.0, p1 = 0.0;
-                if (i < K) {                                              /* warp-uniform */
+                if (wPart + q < K) {                                      /* warp-uniform */
                     const double zq = mrow[4 * q];
-                    if (TMA) mbarWait(smemAddr(barBase + 8u * (st * NW + warp * WPW + q)), parity);
+                    if (TMA) mbarWait(warpBar0 + 8u * (uint32_t)(stP * NW + q), parP);
                     const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
                     const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
                     for (int d = 2 * lane; d < D; d += 64) {
@@ -225,41 +244,43 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
             for (int q = 0; q < WPW; ++q)
                 if (lane == 0) mine[warp * WPW + q] = s[q];
             __syncthreads();
-            for (int t = threadIdx.x; t < a.world * NW; t += DimFusedThreads) {
-                const int r = t / NW, k = t - r * NW;
-                if (tile * NW + k < K)
-                    *reinterpret_cast<volatile double*>(a.dim_partial[r] + ((size_t)a.half * a.world + a.rank) * K + (size_t)tile * NW + k) = mine[k];
+            if (!manyRanks) {
+                if (sender && sendOff + sendK < K) *reinterpret_cast<volatile double*>(sendSlot0 + sendOff) = mine[sendK];
+            } else {
+                for (int t = threadIdx.x; t < a.world * NW; t += DimFusedThreads) {
+                    const int r = t / NW, k = t - r * NW;
+                    if (sendOff + k < K)
+                        *reinterpret_cast<volatile double*>(a.dim_partial[r] + ((size_t)a.half * a.world + a.rank) * K + sendOff + k) = mine[k];
+                }
             }
+            sendOff += walkerStep;
+            wPart += walkerStep;
+            if (stP + 1 == S) { stP = 0; parP ^= 1u; } else ++stP;
         }
 
         /* ---- finish(n - L): rank-ordered sum, Metropolis test, commit from shared memory ---- */
         if (finishing) {
-            const int tile = bid + m * nblocks;
-            const int st = m % S;
-            const unsigned char* rows = dimSmem + (size_t)st * stageBytes + (size_t)(warp * WPW) * 2u * rowStride;
-            const double* mrow = meta + ((size_t)st * NW + warp * WPW) * 4;
-            /* one poll pass takes the partials of qpp walkers at once: lane (ql * world + r) reads rank r's slot of walker ql */
+            const unsigned char* rows = warpRows0 + (size_t)stF * stageBytes;
+            const double2* mrow = reinterpret_cast<const double2*>(warpMeta0 + stF * (NW * 4));
             for (int q0 = 0; q0 < WPW; q0 += qpp) {
                 double part = 0.0;
-                {
-                    const int ql = lane / a.world, r = lane - ql * a.world, qi = q0 + ql;
-                    const int ip = tile * NW + warp * WPW + qi;
-                    if (ql < qpp && qi < WPW && ip < K) part = dimTakePartial(table + (size_t)r * K + ip, q0 == 0 ? seen : DimEmpty, timeoutNs, a.flags);
-                }
+                if (pollLane && q0 + pollQ < WPW && wFin + q0 + pollQ < K)
+                    part = dimTakePartial(pollSlot0 + wFin + q0 + pollQ, q0 == 0 ? seen : DimEmpty, timeoutNs, a.flags);
                 for (int q = q0; q < q0 + qpp && q < WPW; ++q) {
-                    const int i = tile * NW + warp * WPW + q;
+                    const int i = wFin + q;
                     if (i >= K) break;                                    /* warp-uniform */
                     const int w = own0 + i;
                     const int src = (q - q0) * a.world;
                     double sum = __shfl_sync(0xffffffffu, part, src);     /* rank order, every lane alike */
                     for (int r = 1; r < a.world; ++r) sum = __dadd_rn(sum, __shfl_sync(0xffffffffu, part, src + r));
-                    const double z = mrow[4 * q], e = mrow[4 * q + 1], scaling = mrow[4 * q + 2], oldp = mrow[4 * q + 3];
+                    const double2 ze = mrow[2 * q], sp = mrow[2 * q + 1];
+                    const double z = ze.x, e = ze.y;
                     const double newp = calc.finish(sum);
-                    const double diff = __dsub_rn(__dadd_rn(scaling, newp), oldp);
+                    const double diff = __dsub_rn(__dadd_rn(sp.x, newp), sp.y);
                     const bool accepted = e < diff;
-                    const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
-                    const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
                     if (accepted || a.chain_row) {
+                        const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
+                        const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
                         double* ownRow = a.pos + (size_t)w * D;
                         double* chainRow = a.chain_row ? a.chain_row + (size_t)w * D : nullptr;
                         for (int d = 2 * lane; d < D; d += 64) {
@@ -297,16 +318,18 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
                 }
             }
             __syncwarp();
+            wFin += walkerStep;
+            stF = stF + 1 == S ? 0 : stF + 1;
         }
     }
     if (lane == 0 && myAccepted) atomicAdd(a.accept_slots + bid, myAccepted);
 }
 
-template <class Calc, int WPW, bool TMA, bool TRACE>
+template <class Calc, int WPW, bool TMA, bool TRACE, int S, int P>
 __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
-                                                                  const int S, const int P, const int L, const unsigned long long timeoutNs)
+                                                                  const unsigned long long timeoutNs)
 {
-    dimShardFusedBody<Calc, WPW, TMA, TRACE>(a, calcIn, rowStride, S, P, L, timeoutNs, (int)blockIdx.x, (int)gridDim.x);
+    dimShardFusedBody<Calc, WPW, TMA, TRACE, S, P>(a, calcIn, rowStride, timeoutNs, (int)blockIdx.x, (int)gridDim.x);
 }
 
 /* ---- all ranks of a DIM-sharded ensemble in ONE cooperative launch of one process (mcmcpp_sampler_run_group) ------------
@@ -325,14 +348,16 @@ struct DimGroupArgs
     alignas(16) unsigned char calc[DimGroupMax][(sizeof(Calc) + 15) / 16 * 16];      /* Calculators by value (they need not be default-constructible) */
 };
 
+enum { DimGroupStages = 4, DimGroupPrefetch = 2 };          /* the ring of the emulation kernel: small, so that all ranks fit */
 template <class Calc, int WPW, bool TRACE>
-__global__ void __launch_bounds__(DimFusedThreads) dimShardFusedGroup(const DimGroupArgs<Calc> g, const int S, const int P, const int L,
-                                                                       const unsigned long long timeoutNs)
+__global__ void __launch_bounds__(DimFusedThreads) dimShardFusedGroup(const DimGroupArgs<Calc> g, const unsigned long long timeoutNs)
 {
     const int r = (int)blockIdx.x % g.count, bid = (int)blockIdx.x / g.count, nblocks = (int)gridDim.x / g.count;
     const Calc& calc = *reinterpret_cast<const Calc*>(g.calc[r]);
-    if ((g.args[r].D % 2) == 0) dimShardFusedBody<Calc, WPW, true, TRACE>(g.args[r], calc, g.rowStride[r], S, P, L, timeoutNs, bid, nblocks);
-    else dimShardFusedBody<Calc, WPW, false, TRACE>(g.args[r], calc, g.rowStride[r], S, P, L, timeoutNs, bid, nblocks);
+    if ((g.args[r].D % 2) == 0)
+        dimShardFusedBody<Calc, WPW, true, TRACE, DimGroupStages, DimGroupPrefetch>(g.args[r], calc, g.rowStride[r], timeoutNs, bid, nblocks);
+    else
+        dimShardFusedBody<Calc, WPW, false, TRACE, DimGroupStages, DimGroupPrefetch>(g.args[r], calc, g.rowStride[r], timeoutNs, bid, nblocks);
 }
 
 /* Launcher of a DIM-sharded colour for a separable Calculator (a VIEW of this rank's columns: term(x, d) takes the
@@ -348,32 +373,41 @@ struct DimShardLauncher
         return e ? atoi(e) : dflt;
     }
 
-    template <int WPW, bool TMA, bool TRACE>
-    static int fused(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
+    template <int WPW, bool TMA, bool TRACE, int S, int P>
+    static int fusedSP(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
     {
         constexpr int NW = DimFusedWarps * WPW;
-        /* P tiles in flight, L tiles waiting for the other ranks' partials, one being worked on */
-        static const int envP = envInt("MCMCPP_B200_DIM_PREFETCH", 2), envL = envInt("MCMCPP_B200_DIM_LAG", 2);
         static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
-        int P = envP < 1 ? 1 : envP, L = envL < 1 ? 1 : envL;
         const size_t stageBytes = (size_t)NW * 2u * rowStride;
-        while (P + L + 1 > 3 && (size_t)(P + L + 1) * (stageBytes + 40u * NW) + 16u * NW > 200u * 1024u) {
-            if (L > P) --L; else if (P > 1) --P; else --L;   /* wide slices: fewer stages */
-        }
-        const int S = P + L + 1;
         const size_t smem = (size_t)S * (stageBytes + 40u * NW) + 16u * NW;      /* rows + mbarrier + 4 scalars per walker slot */
         if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
         static DynamicSmemOptIn optIn;
-        if (!optIn.ensure(dimShardFused<Calc, WPW, TMA, TRACE>, smem)) return MCMCPP_ERR_CUDA;
+        if (!optIn.ensure(dimShardFused<Calc, WPW, TMA, TRACE, S, P>, smem)) return MCMCPP_ERR_CUDA;
         int perSm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFused<Calc, WPW, TMA, TRACE>, DimFusedThreads, smem) != cudaSuccess || perSm < 1)
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFused<Calc, WPW, TMA, TRACE, S, P>, DimFusedThreads, smem) != cudaSuccess || perSm < 1)
             perSm = 1;
         const int numTiles = (a.K + NW - 1) / NW;
         int grid = (a.sm_count > 0 ? a.sm_count : 148) * perSm;           /* persistent: everything resident at once */
         if (grid > numTiles) grid = numTiles;
         if (grid > a.max_grid) grid = a.max_grid;
-        dimShardFused<Calc, WPW, TMA, TRACE><<<grid, DimFusedThreads, smem, stream>>>(a, calc, rowStride, S, P, L, timeoutNs);
+        dimShardFused<Calc, WPW, TMA, TRACE, S, P><<<grid, DimFusedThreads, smem, stream>>>(a, calc, rowStride, timeoutNs);
         return launchStatus();
+    }
+
+    /* ring shapes: S stages = P tiles in flight + L waiting for the other ranks' partials + one being worked on */
+    template <int WPW, bool TMA, bool TRACE>
+    static int fused(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
+    {
+        constexpr int NW = DimFusedWarps * WPW;
+        static const int ring = envInt("MCMCPP_B200_DIM_RING", 52);        /* two digits: stages, in flight */
+        const size_t perStage = (size_t)NW * 2u * rowStride + 40u * NW;
+        if (TMA && !TRACE) {
+            if (ring == 42 && 4 * perStage <= 200u * 1024u) return fusedSP<WPW, TMA, TRACE, 4, 2>(a, calc, stream, rowStride);
+            if (ring == 63 && 6 * perStage <= 200u * 1024u) return fusedSP<WPW, TMA, TRACE, 6, 3>(a, calc, stream, rowStride);
+            if (ring == 74 && 7 * perStage <= 200u * 1024u) return fusedSP<WPW, TMA, TRACE, 7, 4>(a, calc, stream, rowStride);
+        }
+        if (5 * perStage <= 200u * 1024u) return fusedSP<WPW, TMA, TRACE, 5, 2>(a, calc, stream, rowStride);
+        return fusedSP<WPW, TMA, TRACE, 3, 1>(a, calc, stream, rowStride);      /* wide slices: fewer stages */
     }
 
     template <int WPW, bool TMA>
@@ -387,11 +421,8 @@ struct DimShardLauncher
     {
         constexpr int NW = DimFusedWarps * WPW;
         static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
-        int P = 2, L = 2;
         const size_t stageBytes = (size_t)NW * 2u * maxStride;
-        while (P + L + 1 > 3 && (size_t)(P + L + 1) * (stageBytes + 40u * NW) + 16u * NW > 100u * 1024u) { if (L > P) --L; else if (P > 1) --P; else --L; }
-        const int S = P + L + 1;
-        const size_t smem = (size_t)S * (stageBytes + 40u * NW) + 16u * NW;
+        const size_t smem = (size_t)DimGroupStages * (stageBytes + 40u * NW) + 16u * NW;
         if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
         static DynamicSmemOptIn optIn;
         if (!optIn.ensure(dimShardFusedGroup<Calc, WPW, TRACE>, smem)) return MCMCPP_ERR_CUDA;
@@ -404,9 +435,8 @@ struct DimShardLauncher
         if (nblocks > numTiles) nblocks = numTiles;
         if (nblocks > a0.max_grid) nblocks = a0.max_grid;
         if (nblocks < 1) return MCMCPP_ERR_UNSUPPORTED;
-        int s_ = S, p_ = P, l_ = L;
         unsigned long long t_ = timeoutNs;
-        void* params[] = {(void*)&g, &s_, &p_, &l_, &t_};
+        void* params[] = {(void*)&g, &t_};
         if (cudaLaunchCooperativeKernel((const void*)dimShardFusedGroup<Calc, WPW, TRACE>, dim3(nblocks * g.count), dim3(DimFusedThreads), params, smem,
                                         stream) != cudaSuccess)
             return MCMCPP_ERR_CUDA;

@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(256) denseDrawKernel(const mcmcpp_halfstep_arg
  * the decisions. */
 template <int NB, int GROUPS, int GW, bool TRACE>
 __global__ void __launch_bounds__(32 * GW * GROUPS, 1) denseGaussHalfStep(const mcmcpp_halfstep_args a, const double* __restrict__ P, const int useToken,
-                                                                         const int passEarly)
+                                                                         const int passEarly, const int earlyDependents)
 {
     constexpr int DenseGroupWarps = GW, DenseGroupThreads = 32 * GW, FR = 8 / GW;
     static_assert(GW == 4 || GW == 8, "a group is 4 or 8 warps");
@@ -146,13 +146,18 @@ __global__ void __launch_bounds__(32 * GW * GROUPS, 1) denseGaussHalfStep(const 
     /* programmatic dependent launch: P is constant; the draws, rows and log-probs are read from here on.  The launch right
      * before this one is the draw kernel of this colour, which itself completes only after the previous colour's update. */
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    /* The dependents (the NEXT colour's draw kernel, then its update kernel's P load) are released late: a draw kernel running
+     * beside the MMA loops sends its FP64 logs through the same pipe as the DMMAs.  Every group signals when it starts its last
+     * tile, so the draws fall into this launch's tail.  MCMCPP_B200_DENSE_EARLY_DEPENDENTS=1: right here instead. */
+    if (earlyDependents || myTiles == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     bool pReady = !bulkP;
     unsigned long long myAccepted = 0;                        /* lane 0 of every warp counts its own rows */
 
+    if (!earlyDependents && myTiles > 0 && group >= myTiles) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   /* a group without a tile */
     for (int n = group; n < myTiles; n += GROUPS) {
         const int tile = (int)blockIdx.x + n * (int)gridDim.x;
         const int row0 = tile * DenseTileRows;
+        if (!earlyDependents && n + GROUPS >= myTiles) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");         /* this group's last tile */
         /* (a) the tile's draws and partner rows */
         if (tid < DenseTileRows) {
             const int i = row0 + tid;
@@ -324,6 +329,7 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     static const int useToken = [] { const char* e = getenv("MCMCPP_B200_DENSE_TOKEN"); return (e && e[0] == '0') ? 0 : 1; }();
     static const int passEnv = [] { const char* e = getenv("MCMCPP_B200_DENSE_PASS_EARLY"); return e ? atoi(e) : -1; }();
     const int passEarly = passEnv >= 0 ? passEnv : (GW == 4 ? 1 : 0);
+    static const int earlyDependents = [] { const char* e = getenv("MCMCPP_B200_DENSE_EARLY_DEPENDENTS"); return (e && e[0] == '1') ? 1 : 0; }();
     static DynamicSmemOptIn optedIn[2];                       /* keyed by device inside */
     static const bool pdl = [] { const char* e = getenv("MCMCPP_B200_PDL"); return !(e && e[0] == '0'); }();
     if (!a.dim_z || !a.dim_e || !a.dim_j) return MCMCPP_ERR_STATE;
@@ -342,10 +348,10 @@ int launchDenseNB(const mcmcpp_halfstep_args& a, const DenseCalc& c, cudaStream_
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
     if (a.trace) {
         if (!optedIn[1].ensure(denseGaussHalfStep<NB, GROUPS, GW, true>, smem)) return MCMCPP_ERR_CUDA;
-        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, GW, true>, a, c.P, useToken, passEarly) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, GW, true>, a, c.P, useToken, passEarly, earlyDependents) != cudaSuccess) return MCMCPP_ERR_CUDA;
     } else {
         if (!optedIn[0].ensure(denseGaussHalfStep<NB, GROUPS, GW, false>, smem)) return MCMCPP_ERR_CUDA;
-        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, GW, false>, a, c.P, useToken, passEarly) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if (cudaLaunchKernelEx(&cfg, denseGaussHalfStep<NB, GROUPS, GW, false>, a, c.P, useToken, passEarly, earlyDependents) != cudaSuccess) return MCMCPP_ERR_CUDA;
     }
     return launchStatus();
 }

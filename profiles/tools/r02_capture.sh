@@ -37,6 +37,7 @@ if [ "$stage" = "bench" ] || [ "$stage" = "all" ]; then
 fi
 
 if [ "$stage" = "ncu" ] || [ "$stage" = "all" ]; then
+  rm -f $O/*.ncu-rep
   B="python bench.py --steps 2 --warmup 3 --no-cpu --no-others"
   $B > $O/plain_c4.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $O/r02_c4_launches.csv $B > $O/ncu_c4_list.log 2>&1
   $B > $O/plain_c4.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:stretchHalfStepBulk -s 4 -c 1 -o $O/r02_c4_bulk $B > $O/ncu_c4.log 2>&1
@@ -55,5 +56,11 @@ if [ "$stage" = "ncu" ] || [ "$stage" = "all" ]; then
     $B > $O/plain_c2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:stretchHalfStepThread -s 6 -c 1 -o $O/r02_c2_thread_$rng $B > $O/ncu_c2_$rng.log 2>&1
   done
   ls -la $O/*.ncu-rep
+  # summaries are made on the box (the reports carry the source and are ~30 MB each; gpurun_out/ comes back only below 64 MiB)
+  for rep in $O/*.ncu-rep; do
+    pre=${rep%.ncu-rep}
+    python profiles/tools/summarise_ncu.py $rep $pre > ${pre}_summary.txt 2>&1
+  done
+  if [ "${KEEP_REPS:-}" != "" ]; then for rep in $O/*.ncu-rep; do case "$rep" in *${KEEP_REPS}*) ;; *) rm -f $rep;; esac; done; else rm -f $O/*.ncu-rep; fi
 fi
 echo done
