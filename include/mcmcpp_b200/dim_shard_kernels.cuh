@@ -137,30 +137,35 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
         }
     }
 
-    /* ---- 2. finish tile t - LAG while those copies are in flight ---- */
+    /* ---- 2. finish tile t - LAG while those copies are in flight -- if its partial sums are all here already; otherwise after
+     *         this tile's own sums have gone out (step 3), so that nobody downstream waits for a CTA that is itself waiting ---- */
     const int f = t - lagTiles;
-    if (f >= 0 && f < numTiles) {
-        const int i = f * NW + warp * WPW + lane;            /* lane q < WPW decides walker q of the warp */
-        const bool mine = lane < WPW && i < K;
+    const bool finishing = f >= 0 && f < numTiles;
+    const int iF = f * NW + warp * WPW + lane;                /* lane q < WPW decides walker q of the warp */
+    const bool mine = finishing && lane < WPW && iF < K;
+    double* const slot0 = a.dim_partial[a.rank] + (size_t)a.half * a.world * K + (mine ? iF : 0);      /* + r * K */
+    unsigned long long seen[DimPollUnroll];
+    bool ready = true;
+#pragma unroll
+    for (int r = 0; r < DimPollUnroll; ++r) {                 /* all the ranks' slots at once (independent loads) */
+        seen[r] = (mine && r < a.world) ? *reinterpret_cast<volatile unsigned long long*>(slot0 + (size_t)r * K) : 0ULL;
+        ready = ready && seen[r] != DimEmpty;
+    }
+    if (a.world > DimPollUnroll) ready = false;
+    auto finishTile = [&](const bool useSeen) {
         bool accepted = false;
         double z = 1.0;
         int j = 0;
         if (mine) {
-            double* slot0 = a.dim_partial[a.rank] + (size_t)a.half * a.world * K + i;      /* + r * K */
-            /* all the ranks' slots at once (independent loads), then whatever was still empty */
-            unsigned long long v[DimPollUnroll];
-#pragma unroll
-            for (int r = 0; r < DimPollUnroll; ++r)
-                v[r] = r < a.world ? *reinterpret_cast<volatile unsigned long long*>(slot0 + (size_t)r * K) : 0ULL;
-            const int w = own0 + i;
-            z = __ldg(a.dim_z + i);
-            j = __ldg(a.dim_j + i);
-            const double e = __ldg(a.dim_e + i), scaling = __ldg(a.dim_s + i), oldp = a.logp[w];
+            const int w = own0 + iF;
+            z = __ldg(a.dim_z + iF);
+            j = __ldg(a.dim_j + iF);
+            const double e = __ldg(a.dim_e + iF), scaling = __ldg(a.dim_s + iF), oldp = a.logp[w];
             double sum = 0.0;
 #pragma unroll
             for (int r = 0; r < DimPollUnroll; ++r) {
                 if (r < a.world) {
-                    const double p = dimTakePartial(slot0 + (size_t)r * K, v[r], timeoutNs, a.flags);
+                    const double p = dimTakePartial(slot0 + (size_t)r * K, useSeen ? seen[r] : DimEmpty, timeoutNs, a.flags);
                     sum = r == 0 ? p : __dadd_rn(sum, p);            /* rank order */
                 }
             }
@@ -170,10 +175,10 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
             accepted = e < diff;
             if (accepted) a.logp[w] = newp;
             if (TRACE) {
-                if (i < a.trace_rows) {
+                if (iF < a.trace_rows) {
                     mcmcpp_trace tr;
                     tr.j = j; tr.accept = accepted ? 1 : 0; tr.z = z; tr.e = e; tr.newp = newp; tr.diff = diff;
-                    a.trace[i] = tr;
+                    a.trace[iF] = tr;
                 }
             }
         }
@@ -224,7 +229,9 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
                 }
             }
         }
-    }
+    };
+    const bool finishNow = finishing && __all_sync(0xffffffffu, ready);       /* warp-uniform */
+    if (finishNow) finishTile(true);
 
     /* ---- 3. partial sums of tile t, one line of NW partials to every rank ---- */
     if (summing) {
@@ -272,6 +279,7 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
                 *reinterpret_cast<volatile double*>(a.dim_partial[r] + ((size_t)a.half * a.world + a.rank) * K + (size_t)t * NW + k) = ctaPartial[k];
         }
     }
+    if (finishing && !finishNow) finishTile(false);                           /* its partial sums were not all here before: wait for them now */
     if (threadIdx.x == 0 && t == totalTickets - 1) a.flags[2] = 0;        /* every ticket of this launch has been taken */
 }
 
@@ -326,8 +334,8 @@ struct DimShardLauncher
      * have had time to cross NVLink */
     static int lagFor(int residentCtas)
     {
-        static const int extra = envInt("MCMCPP_B200_DIM_LAG_EXTRA", 64);
-        return residentCtas + (extra < 0 ? 0 : extra);
+        static const int extra = envInt("MCMCPP_B200_DIM_LAG_EXTRA", -1);
+        return residentCtas + (extra < 0 ? residentCtas : extra);          /* default: two residencies */
     }
 
     template <int WPW, bool TMA, bool TRACE>
