@@ -17,9 +17,10 @@
  *                        them at D = 1000; their rows were streamed LAG tiles ago and are still in L2);
  *                     3. reduces tile t's proposals to canonical 64-way partial sums and stores them, one line of NW partials per
  *                        rank, straight into EVERY rank's table over NVLink (peer-mapped stores).
- *                   LAG >= the number of CTAs resident at once, so a tile is only waited for after the CTA that sums it has started
- *                   (on this rank; on the other ranks it is at most a launch skew away) -- nobody waits for work that cannot run.
- *                   The hardware's CTA scheduler does the pipelining: 3 CTAs x 64 KB of rows in flight per SM.
+ *                   If tile t - LAG's sums are not all there at step 2, the CTA finishes it after step 3 instead: it never keeps
+ *                   its own sums back while it waits, and everything it waits for comes from CTAs that have already started
+ *                   (lower tickets) or from ranks that cannot be waiting for more than this rank has sent -- no deadlock for any LAG.
+ *                   The hardware's CTA scheduler does the pipelining: 200+ KB of rows in flight per SM.
  *
  * Exchange protocol: a table slot holds either the all-ones NaN (`DimEmpty`, no arithmetic produces it) or a partial
  * sum.  Writers store 8-byte values (single, indivisible stores); the one reader of a slot spins until it is not
@@ -295,9 +296,8 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
  * nothing would guarantee that they run at the same time.  Here CTA b works for rank b % R, takes its ticket from that rank's
  * counter and runs exactly the code of the one-rank kernel on that rank's own buffers, tables and column slice: the world > 1
  * protocol -- slot hand-over, rank-ordered sums, replicated decisions, per-rank slices (even ones through TMA, odd ones through
- * plain loads) -- runs on a one-GPU box.  Progress: a CTA only ever waits for tiles of LOWER tickets than its own minus LAG,
- * LAG >= the number of CTAs resident at once, so the CTAs it waits for (on any rank) have started and wait for nothing
- * themselves before they send. */
+ * plain loads) -- runs on a one-GPU box.  Progress: a CTA sends before it ever blocks, and only blocks on tiles of LOWER tickets
+ * of any rank (see lagFor below), so the CTAs it waits for have started or will start as resident ones retire. */
 enum { DimGroupMax = 4 };
 template <class Calc>
 struct DimGroupArgs
@@ -330,12 +330,15 @@ struct DimShardLauncher
         return e ? atoi(e) : dflt;
     }
 
-    /* LAG in tiles: at least the CTAs resident at once (see the header comment), a little more so that the other ranks' partials
-     * have had time to cross NVLink */
+    /* LAG in tiles.  Any value >= 0 is safe: a CTA sends its own sums before it ever blocks, and what it blocks on comes from CTAs
+     * with lower tickets -- which have started, because tickets are handed out at CTA start -- or from the other ranks, which
+     * cannot be blocked on more than this rank has already sent.  Small: the finished walkers' rows are still in L2 and the finish
+     * runs under this tile's TMA latency; too small: the other ranks' sums have not crossed NVLink yet and the finish moves behind
+     * the tile's own work.  Default: a quarter of the CTAs resident at once. */
     static int lagFor(int residentCtas)
     {
-        static const int extra = envInt("MCMCPP_B200_DIM_LAG_EXTRA", -1);
-        return residentCtas + (extra < 0 ? residentCtas : extra);          /* default: two residencies */
+        static const int lag = envInt("MCMCPP_B200_DIM_LAG", -1);
+        return lag >= 0 ? lag : (residentCtas + 3) / 4;
     }
 
     template <int WPW, bool TMA, bool TRACE>
