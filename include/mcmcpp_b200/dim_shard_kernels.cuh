@@ -8,8 +8,8 @@
  * over its columns.  One colour = two launches:
  *
  *   dimShardDraw    one thread per walker: the three draws of the update (j, z, log(1-u)) and log(z)(D-1) into the draw scratch.
- *   dimShardFused   one-shot CTAs, one TILE of NW walkers each, in ticket order (an atomic counter, so "earlier tile" means
- *                   "CTA that started earlier").  The CTA with ticket t
+ *   dimShardFused   one-shot CTAs, one TILE of NW walkers each; CTA t (= blockIdx.x: the hardware hands CTAs out in index order,
+ *                   so a lower tile's CTA has started earlier)
  *                     1. issues the TMA bulk copies of tile t (own slice + partner slice of every walker, one mbarrier per walker);
  *                     2. while they are in flight FINISHES tile t - LAG: takes the `world` partial sums of each of its walkers
  *                        from this rank's table, adds them in rank order -- the same bits on every rank, so every rank takes the
@@ -18,8 +18,10 @@
  *                     3. reduces tile t's proposals to canonical 64-way partial sums and stores them, one line of NW partials per
  *                        rank, straight into EVERY rank's table over NVLink (peer-mapped stores).
  *                   If tile t - LAG's sums are not all there at step 2, the CTA finishes it after step 3 instead: it never keeps
- *                   its own sums back while it waits, and everything it waits for comes from CTAs that have already started
- *                   (lower tickets) or from ranks that cannot be waiting for more than this rank has sent -- no deadlock for any LAG.
+ *                   its own sums back while it waits, and everything it waits for comes from CTAs of lower index (started
+ *                   earlier) or from ranks that cannot be waiting for more than this rank has sent.  (A global ticket counter
+ *                   would make "started earlier" independent of the dispatch order, at the price of 32,768 atomics on one
+ *                   address and a barrier per CTA; every wait is bounded by the timeout either way.)
  *                   The hardware's CTA scheduler does the pipelining: 200+ KB of rows in flight per SM.
  *
  * Exchange protocol: a table slot holds either the all-ones NaN (`DimEmpty`, no arithmetic produces it) or a partial
@@ -96,15 +98,14 @@ __device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long 
  * TMA = rows are 16-byte multiples (even slice): staged with cp.async.bulk; otherwise the warps read their walkers' rows
  * straight from global memory (odd slices: tests and the last rank of an odd row).
  * Shared memory: [NW walkers][own row | partner row] (rowStride bytes each), NW mbarriers, NW partials.
- * `ticket` points at this rank's ticket counter (0 at launch; the CTA with the last ticket puts 0 back). */
+ * `t` is the CTA's tile (its block index; in the rank-group kernel block index / ranks). */
 enum { DimPollUnroll = 8 };
 
 template <class Calc, int WPW, bool TMA, bool TRACE>
 __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a, const Calc& calcIn, const uint32_t rowStride,
-                                                  const int lagTiles, const int totalTickets, const unsigned long long timeoutNs)
+                                                  const int lagTiles, const int t, const unsigned long long timeoutNs)
 {
     extern __shared__ __align__(128) unsigned char dimSmem[];
-    __shared__ int sTicket;
     constexpr int NW = DimFusedWarps * WPW;                  /* walkers per tile */
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int D = a.D, K = a.K;
@@ -116,10 +117,10 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
     const int own0 = a.half * K, other0 = (1 - a.half) * K;
     Calc calc = calcIn;
 
-    if (threadIdx.x == 0) sTicket = atomicAdd(a.flags + 2, 1);
-    if (TMA && threadIdx.x < NW) mbarInit(smemAddr(barBase + 8u * threadIdx.x), 1);
-    __syncthreads();
-    const int t = sTicket;
+    if (TMA) {
+        if (threadIdx.x < NW) mbarInit(smemAddr(barBase + 8u * threadIdx.x), 1);
+        __syncthreads();
+    }
     const bool summing = t < numTiles;                        /* CTA-uniform */
 
     /* ---- 1. tile t: lane q < WPW starts walker q's two copies ---- */
@@ -281,14 +282,13 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
         }
     }
     if (finishing && !finishNow) finishTile(false);                           /* its partial sums were not all here before: wait for them now */
-    if (threadIdx.x == 0 && t == totalTickets - 1) a.flags[2] = 0;        /* every ticket of this launch has been taken */
 }
 
 template <class Calc, int WPW, bool TMA, bool TRACE>
 __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
                                                                   const int lagTiles, const unsigned long long timeoutNs)
 {
-    dimShardFusedBody<Calc, WPW, TMA, TRACE>(a, calcIn, rowStride, lagTiles, (int)gridDim.x, timeoutNs);
+    dimShardFusedBody<Calc, WPW, TMA, TRACE>(a, calcIn, rowStride, lagTiles, (int)blockIdx.x, timeoutNs);
 }
 
 /* ---- all ranks of a DIM-sharded ensemble in ONE launch of one process (mcmcpp_sampler_run_group) ------------------------
@@ -296,8 +296,8 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_ha
  * nothing would guarantee that they run at the same time.  Here CTA b works for rank b % R, takes its ticket from that rank's
  * counter and runs exactly the code of the one-rank kernel on that rank's own buffers, tables and column slice: the world > 1
  * protocol -- slot hand-over, rank-ordered sums, replicated decisions, per-rank slices (even ones through TMA, odd ones through
- * plain loads) -- runs on a one-GPU box.  Progress: a CTA sends before it ever blocks, and only blocks on tiles of LOWER tickets
- * of any rank (see lagFor below), so the CTAs it waits for have started or will start as resident ones retire. */
+ * plain loads) -- runs on a one-GPU box.  Progress: a CTA sends before it ever blocks, and only blocks on LOWER tiles of any rank
+ * (see lagFor below), whose CTAs have lower block indices: they have started or will start as resident ones retire. */
 enum { DimGroupMax = 4 };
 template <class Calc>
 struct DimGroupArgs
@@ -311,10 +311,10 @@ struct DimGroupArgs
 template <class Calc, int WPW, bool TRACE>
 __global__ void __launch_bounds__(DimFusedThreads) dimShardFusedGroup(const DimGroupArgs<Calc> g, const int lagTiles, const unsigned long long timeoutNs)
 {
-    const int r = (int)blockIdx.x % g.count, perRank = (int)gridDim.x / g.count;
+    const int r = (int)blockIdx.x % g.count, t = (int)blockIdx.x / g.count;
     const Calc& calc = *reinterpret_cast<const Calc*>(g.calc[r]);
-    if ((g.args[r].D % 2) == 0) dimShardFusedBody<Calc, WPW, true, TRACE>(g.args[r], calc, g.rowStride[r], lagTiles, perRank, timeoutNs);
-    else dimShardFusedBody<Calc, WPW, false, TRACE>(g.args[r], calc, g.rowStride[r], lagTiles, perRank, timeoutNs);
+    if ((g.args[r].D % 2) == 0) dimShardFusedBody<Calc, WPW, true, TRACE>(g.args[r], calc, g.rowStride[r], lagTiles, t, timeoutNs);
+    else dimShardFusedBody<Calc, WPW, false, TRACE>(g.args[r], calc, g.rowStride[r], lagTiles, t, timeoutNs);
 }
 
 /* Launcher of a DIM-sharded colour for a separable Calculator (a VIEW of this rank's columns: term(x, d) takes the
@@ -331,8 +331,8 @@ struct DimShardLauncher
     }
 
     /* LAG in tiles.  Any value >= 0 is safe: a CTA sends its own sums before it ever blocks, and what it blocks on comes from CTAs
-     * with lower tickets -- which have started, because tickets are handed out at CTA start -- or from the other ranks, which
-     * cannot be blocked on more than this rank has already sent.  Small: the finished walkers' rows are still in L2 and the finish
+     * of lower index -- handed out earlier by the hardware -- or from the other ranks, which cannot be blocked on more than this
+     * rank has already sent.  Small: the finished walkers' rows are still in L2 and the finish
      * runs under this tile's TMA latency; too small: the other ranks' sums have not crossed NVLink yet and the finish moves behind
      * the tile's own work.  Default: a quarter of the CTAs resident at once. */
     static int lagFor(int residentCtas)
