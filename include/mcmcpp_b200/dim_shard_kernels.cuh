@@ -10,18 +10,18 @@
  *   dimShardDraw    one thread per walker: the three draws of the update (j, z, log(1-u)) and log(z)(D-1) into the draw scratch.
  *   dimShardFused   one-shot CTAs, one TILE of NW walkers each; CTA t (= blockIdx.x: the hardware hands CTAs out in index order,
  *                   so a lower tile's CTA has started earlier)
- *                     1. issues the TMA bulk copies of tile t (own slice + partner slice of every walker, one mbarrier per walker);
- *                     2. while they are in flight FINISHES tile t - LAG: takes the `world` partial sums of each of its walkers
- *                        from this rank's table, adds them in rank order -- the same bits on every rank, so every rank takes the
- *                        same Metropolis decision (StretchMove.h:112-122) -- and rebuilds the accepted walkers' slices (13 % of
- *                        them at D = 1000; their rows were streamed LAG tiles ago and are still in L2);
- *                     3. reduces tile t's proposals to canonical 64-way partial sums and stores them, one line of NW partials per
- *                        rank, straight into EVERY rank's table over NVLink (peer-mapped stores).
- *                   If tile t - LAG's sums are not all there at step 2, the CTA finishes it after step 3 instead: it never keeps
- *                   its own sums back while it waits, and everything it waits for comes from CTAs of lower index (started
- *                   earlier) or from ranks that cannot be waiting for more than this rank has sent.  (A global ticket counter
- *                   would make "started earlier" independent of the dispatch order, at the price of 32,768 atomics on one
- *                   address and a barrier per CTA; every wait is bounded by the timeout either way.)
+ *                   has two kinds of warps that never wait for each other:
+ *                     SUMMING (4 warps)  issue the TMA bulk copies of tile t (own slice + partner slice of every walker, one
+ *                        mbarrier per walker), reduce the proposals to canonical 64-way partial sums and store them, one line of
+ *                        NW partials per rank, straight into EVERY rank's table over NVLink (peer-mapped stores);
+ *                     FINISHING (1-2 warps)  tile t - LAG: take the `world` partial sums of each of its walkers from this rank's
+ *                        table, add them in rank order -- the same bits on every rank, so every rank takes the same Metropolis
+ *                        decision (StretchMove.h:112-122) -- and rebuild the accepted walkers' slices (8-13 % of them at
+ *                        D = 1000; their rows were streamed LAG tiles ago and are still in L2).
+ *                   A CTA's sums never wait for anything but its own copies, and what a finishing warp waits for comes from CTAs
+ *                   of lower index (started earlier) or from ranks that cannot be waiting for more than this rank has sent.
+ *                   (A global ticket counter would make "started earlier" independent of the dispatch order, at the price of
+ *                   32,768 atomics on one address and a barrier per CTA; every wait is bounded by the timeout either way.)
  *                   The hardware's CTA scheduler does the pipelining: 200+ KB of rows in flight per SM.
  *
  * Exchange protocol: a table slot holds either the all-ones NaN (`DimEmpty`, no arithmetic produces it) or a partial
@@ -101,7 +101,12 @@ __device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long 
  * `t` is the CTA's tile (its block index; in the rank-group kernel block index / ranks). */
 enum { DimPollUnroll = 8 };
 
-template <class Calc, int WPW, bool TMA, bool TRACE>
+__device__ __forceinline__ void dimSumWarpsSync()
+{
+    asm volatile("bar.sync 1, 128;" ::: "memory");            /* the four summing warps only (DimFusedThreads) */
+}
+
+template <class Calc, int WPW, bool TMA, bool TRACE, int FW>
 __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a, const Calc& calcIn, const uint32_t rowStride,
                                                   const int lagTiles, const int t, const unsigned long long timeoutNs)
 {
@@ -109,56 +114,28 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
     constexpr int NW = DimFusedWarps * WPW;                  /* walkers per tile */
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int D = a.D, K = a.K;
-    const uint32_t rowBytes = (uint32_t)D * 8u;
-    unsigned char* const rows = dimSmem + (size_t)(warp * WPW) * 2u * rowStride;
-    unsigned char* const barBase = dimSmem + (TMA ? (size_t)NW * 2u * rowStride : 0);     /* no staged rows without TMA */
-    double* const ctaPartial = reinterpret_cast<double*>(barBase + 8u * NW);
     const int numTiles = (K + NW - 1) / NW;
     const int own0 = a.half * K, other0 = (1 - a.half) * K;
     Calc calc = calcIn;
 
-    if (TMA) {
-        if (threadIdx.x < NW) mbarInit(smemAddr(barBase + 8u * threadIdx.x), 1);
-        __syncthreads();
-    }
-    const bool summing = t < numTiles;                        /* CTA-uniform */
-
-    /* ---- 1. tile t: lane q < WPW starts walker q's two copies ---- */
-    const int iA = t * NW + warp * WPW + lane;               /* this lane's walker of tile t */
-    int jA = 0;
-    double zA = 1.0;
-    if (summing && lane < WPW && iA < K) {
-        jA = __ldg(a.dim_j + iA);
-        zA = __ldg(a.dim_z + iA);
-        if (TMA) {
-            const uint32_t bar = smemAddr(barBase + 8u * (warp * WPW + lane));
-            const uint32_t dst = smemAddr(rows + (size_t)lane * 2u * rowStride);
-            mbarExpectTx(bar, 2u * rowBytes);
-            bulkLoad(dst, a.pos + (size_t)(own0 + iA) * D, rowBytes, bar);
-            bulkLoad(dst + rowStride, a.pos + (size_t)(other0 + jA) * D, rowBytes, bar);
-        }
-    }
-
-    /* ---- 2. finish tile t - LAG while those copies are in flight -- if its partial sums are all here already; otherwise after
-     *         this tile's own sums have gone out (step 3), so that nobody downstream waits for a CTA that is itself waiting ---- */
-    const int f = t - lagTiles;
-    const bool finishing = f >= 0 && f < numTiles;
-    const int iF = f * NW + warp * WPW + lane;                /* lane q < WPW decides walker q of the warp */
-    const bool mine = finishing && lane < WPW && iF < K;
-    double* const slot0 = a.dim_partial[a.rank] + (size_t)a.half * a.world * K + (mine ? iF : 0);      /* + r * K */
-    unsigned long long seen[DimPollUnroll];
-    bool ready = true;
-#pragma unroll
-    for (int r = 0; r < DimPollUnroll; ++r) {                 /* all the ranks' slots at once (independent loads) */
-        seen[r] = (mine && r < a.world) ? *reinterpret_cast<volatile unsigned long long*>(slot0 + (size_t)r * K) : 0ULL;
-        ready = ready && seen[r] != DimEmpty;
-    }
-    if (a.world > DimPollUnroll) ready = false;
-    auto finishTile = [&](const bool useSeen) {
+    if (warp >= DimFusedWarps) {
+        /* ================= FINISHING warps: tile t - LAG, independent of the summing warps of this CTA ================= */
+        constexpr int PER = (NW + FW - 1) / FW;              /* walkers of the tile per finishing warp, one per lane */
+        static_assert(PER <= 32, "a finishing warp decides at most 32 walkers");
+        const int f = t - lagTiles;
+        if (f < 0 || f >= numTiles) return;
+        const int k0 = (warp - DimFusedWarps) * PER;
+        const int iF = f * NW + k0 + lane;
+        const bool mine = lane < PER && k0 + lane < NW && iF < K;
         bool accepted = false;
         double z = 1.0;
         int j = 0;
         if (mine) {
+            double* const slot0 = a.dim_partial[a.rank] + (size_t)a.half * a.world * K + iF;        /* + r * K */
+            unsigned long long seen[DimPollUnroll];
+#pragma unroll
+            for (int r = 0; r < DimPollUnroll; ++r)              /* all the ranks' slots at once (independent loads) */
+                seen[r] = r < a.world ? *reinterpret_cast<volatile unsigned long long*>(slot0 + (size_t)r * K) : 0ULL;
             const int w = own0 + iF;
             z = __ldg(a.dim_z + iF);
             j = __ldg(a.dim_j + iF);
@@ -167,7 +144,7 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
 #pragma unroll
             for (int r = 0; r < DimPollUnroll; ++r) {
                 if (r < a.world) {
-                    const double p = dimTakePartial(slot0 + (size_t)r * K, useSeen ? seen[r] : DimEmpty, timeoutNs, a.flags);
+                    const double p = dimTakePartial(slot0 + (size_t)r * K, seen[r], timeoutNs, a.flags);
                     sum = r == 0 ? p : __dadd_rn(sum, p);            /* rank order */
                 }
             }
@@ -192,7 +169,7 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
             const int q = __ffs(work) - 1;
             work &= work - 1;
             const bool acc = (accMask >> q) & 1u;
-            const int iq = f * NW + warp * WPW + q;
+            const int iq = f * NW + k0 + q;
             const double zq = __shfl_sync(0xffffffffu, z, q);
             const int jq = __shfl_sync(0xffffffffu, j, q);
             double* ownRow = a.pos + (size_t)(own0 + iq) * D;
@@ -231,64 +208,86 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
                 }
             }
         }
-    };
-    const bool finishNow = finishing && __all_sync(0xffffffffu, ready);       /* warp-uniform */
-    if (finishNow) finishTile(true);
+        return;
+    }
 
-    /* ---- 3. partial sums of tile t, one line of NW partials to every rank ---- */
-    if (summing) {
-        double s[WPW];
-#pragma unroll
-        for (int q = 0; q < WPW; ++q) {
-            const int i = t * NW + warp * WPW + q;
-            const double zq = __shfl_sync(0xffffffffu, zA, q);
-            double p0 = 0.0, p1 = 0.0;
-            if (i < K) {                                                  /* warp-uniform */
-                if (TMA) {
-                    mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
-                    const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
-                    const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
-                    for (int d = 2 * lane; d < D; d += 64) {
-                        const double2 c = *reinterpret_cast<const double2*>(ownS + d);
-                        const double2 sl = *reinterpret_cast<const double2*>(selS + d);
-                        p0 = __dadd_rn(p0, calc.term(stretchPoint(sl.x, c.x, zq), d));
-                        p1 = __dadd_rn(p1, calc.term(stretchPoint(sl.y, c.y, zq), d + 1));
-                    }
-                } else {
-                    const int jq = __shfl_sync(0xffffffffu, jA, q);
-                    const double* ownRow = a.pos + (size_t)(own0 + i) * D;
-                    const double* selRow = a.pos + (size_t)(other0 + jq) * D;
-                    for (int d = 2 * lane; d < D; d += 64) {
-                        p0 = __dadd_rn(p0, calc.term(stretchPoint(selRow[d], ownRow[d], zq), d));
-                        if (d + 1 < D) p1 = __dadd_rn(p1, calc.term(stretchPoint(selRow[d + 1], ownRow[d + 1], zq), d + 1));
-                    }
-                }
-            }
-            s[q] = __dadd_rn(p0, p1);
-        }
-#pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) {
-#pragma unroll
-            for (int q = 0; q < WPW; ++q) s[q] = __dadd_rn(s[q], __shfl_xor_sync(0xffffffffu, s[q], off));
-        }
-#pragma unroll
-        for (int q = 0; q < WPW; ++q)
-            if (lane == 0) ctaPartial[warp * WPW + q] = s[q];
-        __syncthreads();
-        for (int u = threadIdx.x; u < a.world * NW; u += DimFusedThreads) {
-            const int r = u / NW, k = u - r * NW;
-            if (t * NW + k < K)
-                *reinterpret_cast<volatile double*>(a.dim_partial[r] + ((size_t)a.half * a.world + a.rank) * K + (size_t)t * NW + k) = ctaPartial[k];
+    /* ================= SUMMING warps: tile t ================= */
+    if (t >= numTiles) return;                                /* CTA-uniform: the finish-only CTAs behind the last tile */
+    const uint32_t rowBytes = (uint32_t)D * 8u;
+    unsigned char* const rows = dimSmem + (size_t)(warp * WPW) * 2u * rowStride;
+    unsigned char* const barBase = dimSmem + (TMA ? (size_t)NW * 2u * rowStride : 0);     /* no staged rows without TMA */
+    double* const ctaPartial = reinterpret_cast<double*>(barBase + 8u * NW);
+    if (TMA) {
+        if (threadIdx.x < NW) mbarInit(smemAddr(barBase + 8u * threadIdx.x), 1);
+        dimSumWarpsSync();
+    }
+    /* lane q < WPW starts walker q's two copies */
+    const int iA = t * NW + warp * WPW + lane;               /* this lane's walker of tile t */
+    int jA = 0;
+    double zA = 1.0;
+    if (lane < WPW && iA < K) {
+        jA = __ldg(a.dim_j + iA);
+        zA = __ldg(a.dim_z + iA);
+        if (TMA) {
+            const uint32_t bar = smemAddr(barBase + 8u * (warp * WPW + lane));
+            const uint32_t dst = smemAddr(rows + (size_t)lane * 2u * rowStride);
+            mbarExpectTx(bar, 2u * rowBytes);
+            bulkLoad(dst, a.pos + (size_t)(own0 + iA) * D, rowBytes, bar);
+            bulkLoad(dst + rowStride, a.pos + (size_t)(other0 + jA) * D, rowBytes, bar);
         }
     }
-    if (finishing && !finishNow) finishTile(false);                           /* its partial sums were not all here before: wait for them now */
+    /* partial sums of the warp's walkers; the WPW butterflies run interleaved (independent dependency chains) */
+    double s[WPW];
+#pragma unroll
+    for (int q = 0; q < WPW; ++q) {
+        const int i = t * NW + warp * WPW + q;
+        const double zq = __shfl_sync(0xffffffffu, zA, q);
+        double p0 = 0.0, p1 = 0.0;
+        if (i < K) {                                                  /* warp-uniform */
+            if (TMA) {
+                mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
+                const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
+                const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
+                for (int d = 2 * lane; d < D; d += 64) {
+                    const double2 c = *reinterpret_cast<const double2*>(ownS + d);
+                    const double2 sl = *reinterpret_cast<const double2*>(selS + d);
+                    p0 = __dadd_rn(p0, calc.term(stretchPoint(sl.x, c.x, zq), d));
+                    p1 = __dadd_rn(p1, calc.term(stretchPoint(sl.y, c.y, zq), d + 1));
+                }
+            } else {
+                const int jq = __shfl_sync(0xffffffffu, jA, q);
+                const double* ownRow = a.pos + (size_t)(own0 + i) * D;
+                const double* selRow = a.pos + (size_t)(other0 + jq) * D;
+                for (int d = 2 * lane; d < D; d += 64) {
+                    p0 = __dadd_rn(p0, calc.term(stretchPoint(selRow[d], ownRow[d], zq), d));
+                    if (d + 1 < D) p1 = __dadd_rn(p1, calc.term(stretchPoint(selRow[d + 1], ownRow[d + 1], zq), d + 1));
+                }
+            }
+        }
+        s[q] = __dadd_rn(p0, p1);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+#pragma unroll
+        for (int q = 0; q < WPW; ++q) s[q] = __dadd_rn(s[q], __shfl_xor_sync(0xffffffffu, s[q], off));
+    }
+#pragma unroll
+    for (int q = 0; q < WPW; ++q)
+        if (lane == 0) ctaPartial[warp * WPW + q] = s[q];
+    dimSumWarpsSync();
+    /* one line of NW partials to every rank */
+    for (int u = threadIdx.x; u < a.world * NW; u += DimFusedThreads) {
+        const int r = u / NW, k = u - r * NW;
+        if (t * NW + k < K)
+            *reinterpret_cast<volatile double*>(a.dim_partial[r] + ((size_t)a.half * a.world + a.rank) * K + (size_t)t * NW + k) = ctaPartial[k];
+    }
 }
 
-template <class Calc, int WPW, bool TMA, bool TRACE>
-__global__ void __launch_bounds__(DimFusedThreads) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
-                                                                  const int lagTiles, const unsigned long long timeoutNs)
+template <class Calc, int WPW, bool TMA, bool TRACE, int FW>
+__global__ void __launch_bounds__(DimFusedThreads + 32 * FW) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
+                                                                            const int lagTiles, const unsigned long long timeoutNs)
 {
-    dimShardFusedBody<Calc, WPW, TMA, TRACE>(a, calcIn, rowStride, lagTiles, (int)blockIdx.x, timeoutNs);
+    dimShardFusedBody<Calc, WPW, TMA, TRACE, FW>(a, calcIn, rowStride, lagTiles, (int)blockIdx.x, timeoutNs);
 }
 
 /* ---- all ranks of a DIM-sharded ensemble in ONE launch of one process (mcmcpp_sampler_run_group) ------------------------
@@ -308,13 +307,13 @@ struct DimGroupArgs
     alignas(16) unsigned char calc[DimGroupMax][(sizeof(Calc) + 15) / 16 * 16];      /* Calculators by value (they need not be default-constructible) */
 };
 
-template <class Calc, int WPW, bool TRACE>
-__global__ void __launch_bounds__(DimFusedThreads) dimShardFusedGroup(const DimGroupArgs<Calc> g, const int lagTiles, const unsigned long long timeoutNs)
+template <class Calc, int WPW, bool TRACE, int FW>
+__global__ void __launch_bounds__(DimFusedThreads + 32 * FW) dimShardFusedGroup(const DimGroupArgs<Calc> g, const int lagTiles, const unsigned long long timeoutNs)
 {
     const int r = (int)blockIdx.x % g.count, t = (int)blockIdx.x / g.count;
     const Calc& calc = *reinterpret_cast<const Calc*>(g.calc[r]);
-    if ((g.args[r].D % 2) == 0) dimShardFusedBody<Calc, WPW, true, TRACE>(g.args[r], calc, g.rowStride[r], lagTiles, t, timeoutNs);
-    else dimShardFusedBody<Calc, WPW, false, TRACE>(g.args[r], calc, g.rowStride[r], lagTiles, t, timeoutNs);
+    if ((g.args[r].D % 2) == 0) dimShardFusedBody<Calc, WPW, true, TRACE, FW>(g.args[r], calc, g.rowStride[r], lagTiles, t, timeoutNs);
+    else dimShardFusedBody<Calc, WPW, false, TRACE, FW>(g.args[r], calc, g.rowStride[r], lagTiles, t, timeoutNs);
 }
 
 /* Launcher of a DIM-sharded colour for a separable Calculator (a VIEW of this rank's columns: term(x, d) takes the
@@ -348,14 +347,15 @@ struct DimShardLauncher
         static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
         const size_t smem = TMA ? (size_t)NW * 2u * rowStride + 16u * NW : 16u * NW;      /* rows, mbarriers, partials */
         if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
+        constexpr int FW = NW >= 16 ? 2 : 1;                  /* finishing warps beside the four summing warps */
         static DynamicSmemOptIn optIn;
-        if (!optIn.ensure(dimShardFused<Calc, WPW, TMA, TRACE>, smem)) return MCMCPP_ERR_CUDA;
+        if (!optIn.ensure(dimShardFused<Calc, WPW, TMA, TRACE, FW>, smem)) return MCMCPP_ERR_CUDA;
         int perSm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFused<Calc, WPW, TMA, TRACE>, DimFusedThreads, smem) != cudaSuccess || perSm < 1)
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFused<Calc, WPW, TMA, TRACE, FW>, DimFusedThreads + 32 * FW, smem) != cudaSuccess || perSm < 1)
             return MCMCPP_ERR_CUDA;
         const int lag = lagFor((a.sm_count > 0 ? a.sm_count : 148) * perSm);
         const int numTiles = (a.K + NW - 1) / NW;
-        dimShardFused<Calc, WPW, TMA, TRACE><<<numTiles + lag, DimFusedThreads, smem, stream>>>(a, calc, rowStride, lag, timeoutNs);
+        dimShardFused<Calc, WPW, TMA, TRACE, FW><<<numTiles + lag, DimFusedThreads + 32 * FW, smem, stream>>>(a, calc, rowStride, lag, timeoutNs);
         return launchStatus();
     }
 
@@ -372,15 +372,16 @@ struct DimShardLauncher
         static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
         const size_t smem = (size_t)NW * 2u * maxStride + 16u * NW;
         if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
+        constexpr int FW = NW >= 16 ? 2 : 1;
         static DynamicSmemOptIn optIn;
-        if (!optIn.ensure(dimShardFusedGroup<Calc, WPW, TRACE>, smem)) return MCMCPP_ERR_CUDA;
+        if (!optIn.ensure(dimShardFusedGroup<Calc, WPW, TRACE, FW>, smem)) return MCMCPP_ERR_CUDA;
         int perSm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFusedGroup<Calc, WPW, TRACE>, DimFusedThreads, smem) != cudaSuccess || perSm < 1)
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFusedGroup<Calc, WPW, TRACE, FW>, DimFusedThreads + 32 * FW, smem) != cudaSuccess || perSm < 1)
             return MCMCPP_ERR_CUDA;
         const mcmcpp_halfstep_args& a0 = g.args[0];
         const int lag = lagFor((a0.sm_count > 0 ? a0.sm_count : 148) * perSm);       /* resident CTAs of ALL ranks together */
         const int numTiles = (a0.K + NW - 1) / NW;
-        dimShardFusedGroup<Calc, WPW, TRACE><<<(numTiles + lag) * g.count, DimFusedThreads, smem, stream>>>(g, lag, timeoutNs);
+        dimShardFusedGroup<Calc, WPW, TRACE, FW><<<(numTiles + lag) * g.count, DimFusedThreads + 32 * FW, smem, stream>>>(g, lag, timeoutNs);
         return launchStatus();
     }
 
