@@ -236,7 +236,12 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
             bulkLoad(dst + rowStride, a.pos + (size_t)(other0 + jA) * D, rowBytes, bar);
         }
     }
-    /* partial sums of the warp's walkers; the WPW butterflies run interleaved (independent dependency chains) */
+    /* partial sums of the warp's walkers: all copies awaited first, then WPW independent dependency chains side by side */
+    if (TMA) {
+#pragma unroll
+        for (int q = 0; q < WPW; ++q)
+            if (t * NW + warp * WPW + q < K) mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
+    }
     double s[WPW];
 #pragma unroll
     for (int q = 0; q < WPW; ++q) {
@@ -245,7 +250,6 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
         double p0 = 0.0, p1 = 0.0;
         if (i < K) {                                                  /* warp-uniform */
             if (TMA) {
-                mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
                 const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
                 const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
                 for (int d = 2 * lane; d < D; d += 64) {
@@ -283,8 +287,8 @@ __device__ __forceinline__ void dimShardFusedBody(const mcmcpp_halfstep_args& a,
     }
 }
 
-template <class Calc, int WPW, bool TMA, bool TRACE, int FW>
-__global__ void __launch_bounds__(DimFusedThreads + 32 * FW) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
+template <class Calc, int WPW, bool TMA, bool TRACE, int FW, int MINB>
+__global__ void __launch_bounds__(DimFusedThreads + 32 * FW, MINB) dimShardFused(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride,
                                                                             const int lagTiles, const unsigned long long timeoutNs)
 {
     dimShardFusedBody<Calc, WPW, TMA, TRACE, FW>(a, calcIn, rowStride, lagTiles, (int)blockIdx.x, timeoutNs);
@@ -340,23 +344,39 @@ struct DimShardLauncher
         return lag >= 0 ? lag : (residentCtas + 3) / 4;
     }
 
+    template <int WPW, bool TMA, bool TRACE, int FW, int MINB>
+    static int fusedFM(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride, size_t smem)
+    {
+        constexpr int NW = DimFusedWarps * WPW;
+        static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
+        static DynamicSmemOptIn optIn;
+        if (!optIn.ensure(dimShardFused<Calc, WPW, TMA, TRACE, FW, MINB>, smem)) return MCMCPP_ERR_CUDA;
+        int perSm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFused<Calc, WPW, TMA, TRACE, FW, MINB>, DimFusedThreads + 32 * FW, smem) != cudaSuccess || perSm < 1)
+            return MCMCPP_ERR_CUDA;
+        const int lag = lagFor((a.sm_count > 0 ? a.sm_count : 148) * perSm);
+        const int numTiles = (a.K + NW - 1) / NW;
+        dimShardFused<Calc, WPW, TMA, TRACE, FW, MINB><<<numTiles + lag, DimFusedThreads + 32 * FW, smem, stream>>>(a, calc, rowStride, lag, timeoutNs);
+        return launchStatus();
+    }
+
     template <int WPW, bool TMA, bool TRACE>
     static int fused(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride)
     {
         constexpr int NW = DimFusedWarps * WPW;
-        static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
         const size_t smem = TMA ? (size_t)NW * 2u * rowStride + 16u * NW : 16u * NW;      /* rows, mbarriers, partials */
         if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
-        constexpr int FW = NW >= 16 ? 2 : 1;                  /* finishing warps beside the four summing warps */
-        static DynamicSmemOptIn optIn;
-        if (!optIn.ensure(dimShardFused<Calc, WPW, TMA, TRACE, FW>, smem)) return MCMCPP_ERR_CUDA;
-        int perSm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dimShardFused<Calc, WPW, TMA, TRACE, FW>, DimFusedThreads + 32 * FW, smem) != cudaSuccess || perSm < 1)
-            return MCMCPP_ERR_CUDA;
-        const int lag = lagFor((a.sm_count > 0 ? a.sm_count : 148) * perSm);
-        const int numTiles = (a.K + NW - 1) / NW;
-        dimShardFused<Calc, WPW, TMA, TRACE, FW><<<numTiles + lag, DimFusedThreads + 32 * FW, smem, stream>>>(a, calc, rowStride, lag, timeoutNs);
-        return launchStatus();
+        /* finishing warps beside the four summing warps; CTAs per SM the register allocation is asked to allow (short slices need many
+         * CTAs in flight: the per-CTA chain load index -> copy -> sum -> send is latency, not bandwidth) */
+        static const int fwEnv = envInt("MCMCPP_B200_DIM_FW", 0), minbEnv = envInt("MCMCPP_B200_DIM_MINB", 0);
+        const bool two = fwEnv ? fwEnv == 2 : NW >= 16;
+        const bool dense = (minbEnv ? minbEnv > 1 : true) && TMA && !TRACE && smem <= 33u * 1024u;
+        if (NW >= 8 && two) {
+            if (dense) return fusedFM<WPW, TMA, TRACE, 2, 6>(a, calc, stream, rowStride, smem);
+            return fusedFM<WPW, TMA, TRACE, 2, 1>(a, calc, stream, rowStride, smem);
+        }
+        if (dense) return fusedFM<WPW, TMA, TRACE, 1, 7>(a, calc, stream, rowStride, smem);
+        return fusedFM<WPW, TMA, TRACE, 1, 1>(a, calc, stream, rowStride, smem);
     }
 
     template <int WPW, bool TMA>
