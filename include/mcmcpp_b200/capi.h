@@ -166,6 +166,8 @@ typedef struct {
     double* dim_s;             /* [2K] log(z) (D_total - 1) of the draws (DIM), second half free for a launcher's own use */
     int32_t sm_count;          /* multiprocessors of the device (persistent grids) */
     double* mover_state;       /* [W * mover_state_doubles] per-walker mover state, or NULL */
+    void* side_stream;         /* DIM: a second cudaStream_t of the sampler -- the finishing kernel runs on it beside the summing kernel */
+    void* side_event[2];       /* DIM: two cudaEvent_t (timing disabled) the launcher orders the two streams with */
 } mcmcpp_halfstep_args;
 
 typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);
@@ -182,8 +184,9 @@ typedef struct mcmcpp_fused_args {
 } mcmcpp_fused_args;
 typedef int (*mcmcpp_fused_fn)(const mcmcpp_fused_args* args, const void* calculator, void* cuda_stream);
 
-/* All ranks of one DIM-sharded ensemble held by ONE process on ONE device (mcmcpp_sampler_run_group): one colour of every rank,
- * on one stream, with every rank's update kernel in a single cooperative launch (include/mcmcpp_b200/dim_shard_kernels.cuh). */
+/* All ranks of one DIM-sharded ensemble held by ONE process on ONE device (mcmcpp_sampler_run_group): one colour of every rank --
+ * every rank's draws and summing kernel on `cuda_stream`, then every rank's finishing kernel on its side stream
+ * (include/mcmcpp_b200/dim_shard_kernels.cuh: finishing kernels wait for summing kernels only, which wait for nobody). */
 typedef int (*mcmcpp_group_fn)(const mcmcpp_halfstep_args* args_per_rank, const void* const* calculators, int count, void* cuda_stream);
 
 /* ---- life cycle: EnsembleSampler ctor/dtor (EnsembleSampler.h:199-218,72) -------------------- */
@@ -284,9 +287,9 @@ int mcmcpp_sampler_comm_init(mcmcpp_sampler* s, const void* id128);
 int mcmcpp_sampler_peer_export(mcmcpp_sampler* s, void* handle64);
 int mcmcpp_sampler_peer_import(mcmcpp_sampler* s, const void* handles64_all_ranks);
 /* The ranks of one DIM-sharded ensemble inside ONE process on ONE device (a one-GPU box, tests): samplers[r] was created with
- * rank r, world `count` (<= 4), shard_mode DIM.  _peer_import_local wires their partial tables together by plain pointers;
- * _run_group is runMCMC for all of them in lockstep -- per colour one cooperative launch in which CTA b works for rank b % count
- * (ranks that wait on one another must never be separate launches on one GPU: nothing guarantees they are resident together).
+ * rank r, world `count` (<= 8), shard_mode DIM.  _peer_import_local wires their partial tables together by plain pointers;
+ * _run_group is runMCMC for all of them in lockstep -- per colour every rank's summing kernel is launched before any rank's finishing
+ * kernel (the only kernels that wait: for summing kernels, which wait for nobody), with exactly the kernels one process per GPU runs.
  * Same results as `count` processes on `count` GPUs.  Built-in Calculators register their group launcher themselves. */
 int mcmcpp_sampler_set_group_launcher(mcmcpp_sampler* s, mcmcpp_group_fn launcher);
 int mcmcpp_sampler_peer_import_local(mcmcpp_sampler* const* samplers, int count);

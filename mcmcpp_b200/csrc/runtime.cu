@@ -175,7 +175,8 @@ struct mcmcpp_sampler
     double* dParams = nullptr;             /* built-in target parameters */
     void* builtinAux = nullptr;            /* built-in target scratch (dense kernels) */
 
-    cudaStream_t stream = nullptr, copyStream = nullptr;
+    cudaStream_t stream = nullptr, copyStream = nullptr, sideStream = nullptr;     /* sideStream: DIM finishing kernels */
+    cudaEvent_t sideEvent[2] = {nullptr, nullptr};
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     cudaEvent_t slotReady[ChainSlots] = {nullptr, nullptr}, slotFree[ChainSlots] = {nullptr, nullptr};
     bool slotBusy[ChainSlots] = {false, false};
@@ -479,6 +480,8 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
         CUDA_TRY(cudaMemset(s->dDimPartial, 0xFF, sizeof(double) * tableDoubles));
         CUDA_TRY(cudaMalloc(&s->dDimTable, sizeof(double*) * (size_t)cfg->world));
         if (cfg->world == 1) CUDA_TRY(cudaMemcpy(s->dDimTable, &s->dDimPartial, sizeof(double*), cudaMemcpyHostToDevice));
+        CUDA_TRY(cudaStreamCreateWithFlags(&s->sideStream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) CUDA_TRY(cudaEventCreateWithFlags(&s->sideEvent[i], cudaEventDisableTiming));
     }
     if (cfg->trace_updates > 0) {
         CUDA_TRY(cudaMalloc(&s->dTrace, sizeof(mcmcpp_trace) * (size_t)cfg->trace_updates));
@@ -494,6 +497,7 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     a.D_total = D; a.dim_begin = s->dimBegin; a.rank = cfg->rank; a.world = cfg->world;
     a.dim_partial = s->dDimTable; a.dim_z = s->dDimZ; a.dim_e = s->dDimE; a.dim_j = s->dDimJ; a.dim_s = s->dDimS;
     a.mover_state = s->dMoverState;
+    a.side_stream = s->sideStream; a.side_event[0] = s->sideEvent[0]; a.side_event[1] = s->sideEvent[1];
     { int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device); a.sm_count = sms; }
     a.slot_begin = s->slotBegin; a.slot_count = s->slotCount; a.slots_per_rank = s->slotCount;
     a.rng_mode = cfg->rng_mode;
@@ -626,6 +630,8 @@ int mcmcpp_sampler_destroy(mcmcpp_sampler* s)
     cudaSetDevice(s->cfg.device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->copyStream) cudaStreamSynchronize(s->copyStream);
+    if (s->sideStream) { cudaStreamSynchronize(s->sideStream); cudaStreamDestroy(s->sideStream); }
+    for (int i = 0; i < 2; ++i) if (s->sideEvent[i]) cudaEventDestroy(s->sideEvent[i]);
     if (s->comm && nccl().ok) nccl().CommDestroy(s->comm);
     for (void* p : s->peerOpened) cudaIpcCloseMemHandle(p);
     cudaFree(s->dPeerPos);
@@ -1107,7 +1113,7 @@ namespace
 {
 int checkGroup(mcmcpp_sampler* const* ss, int count)
 {
-    if (!ss || count < 2 || count > 4) return fail(MCMCPP_ERR_ARG, "a rank group has 2 to 4 samplers");
+    if (!ss || count < 2 || count > 8) return fail(MCMCPP_ERR_ARG, "a rank group has 2 to 8 samplers");
     for (int r = 0; r < count; ++r) {
         mcmcpp_sampler* s = ss[r];
         if (!s) return fail(MCMCPP_ERR_ARG, "null sampler in the group");
@@ -1180,7 +1186,7 @@ int mcmcpp_sampler_run_group(mcmcpp_sampler* const* ss, int count, int num_steps
         }
         int rcl = lead->groupFn(args.data(), calcs.data(), count, lead->stream);
         if (rcl != MCMCPP_OK) return fail(rcl, std::string("rank-group launch failed: ") + cudaGetErrorString(cudaGetLastError()));
-        for (int r = 0; r < count; ++r) ss[r]->launches += 2;
+        for (int r = 0; r < count; ++r) ss[r]->launches += 3;
         return MCMCPP_OK;
     };
     int status = MCMCPP_OK;

@@ -278,7 +278,7 @@ def test_dim_shard_kernels_single_rank_bit_exact(port, W, D, steps):
     s = make_sampler("diag_gauss", iv, W, D, seed=1, traceUpdates=W, shardMode="dim")
     s.setInitialWalkerPos(init, lp)
     assert s.runMCMC(steps)
-    assert s.getLaunchCount() == 4 * steps                            # draw + fused kernel per colour
+    assert s.getLaunchCount() == 6 * steps                            # draw, summing and finishing kernel per colour
     o = port.run("diag_gauss", iv, init, lp, steps, seed=1, want_trace=True)
     assert np.array_equal(s.getChain()[1:], o["chain"])
     pos, aux = s.getWalkerState()
