@@ -166,8 +166,8 @@ typedef struct {
     double* dim_s;             /* [2K] log(z) (D_total - 1) of the draws (DIM), second half free for a launcher's own use */
     int32_t sm_count;          /* multiprocessors of the device (persistent grids) */
     double* mover_state;       /* [W * mover_state_doubles] per-walker mover state, or NULL */
-    void* side_stream;         /* DIM: a second cudaStream_t of the sampler -- the finishing kernel runs on it beside the summing kernel */
-    void* side_event[2];       /* DIM: two cudaEvent_t (timing disabled) the launcher orders the two streams with */
+    void* side_stream;         /* a second cudaStream_t of the sampler and two cudaEvent_t (timing disabled) for launchers that want to */
+    void* side_event[2];       /* run part of a half-step beside the rest; the built-in launchers do not use them (DIM: measured slower) */
 } mcmcpp_halfstep_args;
 
 typedef int (*mcmcpp_halfstep_fn)(const mcmcpp_halfstep_args* args, const void* calculator, void* cuda_stream);

@@ -5,30 +5,29 @@
  * Every rank holds all W walkers but only its columns [dim_begin, dim_begin + D) of each row, makes the SAME draws
  * (j, z, log(1-u)) from the sampler's pcg64 stream, builds its slice of every proposal
  * (MCMCpp/Movers/StretchMove.h:103-109) and the partial sum of a separable Calculator (term()/finish(), targets.h)
- * over its columns.  One colour = three launches on two streams:
+ * over its columns.  One colour = three launches:
  *
- *   dimShardDraw    (main stream) one thread per walker: the three draws of the update (j, z, log(1-u)) and log(z)(D-1).
- *   dimShardSum     (main stream) one-shot CTAs, one tile of NW walkers each: lane q of a warp issues walker q's two TMA bulk
+ *   dimShardDraw    one thread per walker: the three draws of the update (j, z, log(1-u)) and log(z)(D-1).
+ *   dimShardSum     one-shot CTAs, one tile of NW walkers each: lane q of a warp issues walker q's two TMA bulk
  *                   copies (own slice, partner slice) onto the walker's mbarrier; the warp reduces the proposals to canonical
  *                   64-way partial sums; the CTA stores them, one line of NW partials per rank, straight into EVERY rank's
  *                   table over NVLink (peer-mapped stores).  It never waits for anything but its own copies.
- *   dimShardFinish  (side stream, CONCURRENT with dimShardSum) a few persistent warps per SM walk the colour in groups of 32
- *                   walkers: each lane takes the `world` partial sums of its walker from this rank's table -- waiting for
- *                   them if they are not there yet --, adds them in rank order (the same bits on every rank, so every rank
- *                   takes the same Metropolis decision, StretchMove.h:112-122), and the warp rebuilds the accepted walkers'
- *                   slices (8-13 % of them at D = 1000; their rows were streamed moments ago and come from L2).
- *                   The next colour's launches wait for it through an event.
+ *   dimShardFinish  one warp per group of 32 walkers: each lane takes the `world` partial sums of its walker from this rank's
+ *                   table -- waiting for the other ranks' if they are not there yet --, adds them in rank order (the same bits
+ *                   on every rank, so every rank takes the same Metropolis decision, StretchMove.h:112-122), and the warp
+ *                   rebuilds the accepted walkers' slices (8-13 % of them at D = 1000).  Decision and commit in one kernel,
+ *                   no work list, no atomics (round 1: decide kernel + list + commit kernel, behind a rendezvous).
  * Who waits for whom: finishing kernels wait for summing kernels (of every rank); summing kernels wait for nobody.  So there
  * is no cycle, on any number of GPUs -- and none either when all the ranks live in one process on one GPU
  * (mcmcpp_sampler_run_group, tests/test_gpu_rank_group.py): the summing kernels of all ranks are launched before any
- * finishing kernel, and a finishing kernel occupies a fraction of each SM only.
+ * finishing kernel.
  *
  * Exchange protocol: a table slot holds either the all-ones NaN (`DimEmpty`, no arithmetic produces it) or a partial
  * sum.  Writers store 8-byte values (single, indivisible stores); the one reader of a slot spins until it is not
  * DimEmpty, takes the value and puts DimEmpty back.  No flag, no fence, no rendezvous kernel and no NCCL call.
  * The table has a half per colour; a rank cannot write a slot of colour c again before its reader has emptied it: it
  * would have to be two half-steps ahead, and it cannot finish the half-step in between without this rank's partials of
- * that half-step, which this rank only sends after the kernel that emptied the slot has completed (event order).
+ * that half-step, which this rank only sends after the kernel that emptied the slot has completed (stream order).
  * A poll that sees nothing for `timeout_ns` sets flags[1] and gives up (mcmcpp_sampler_run then returns
  * MCMCPP_ERR_STATE): a dead peer cannot wedge the other GPUs.
  *
@@ -191,7 +190,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
 enum { DimFinishWarps = 4, DimPollUnroll = 8 };   /* 4 warps x 93 registers: fits beside 7 summing CTAs of 48 registers */
 
 template <class Calc, bool VEC, bool TRACE>
-__global__ void __launch_bounds__(DimFinishWarps * 32) dimShardFinish(const mcmcpp_halfstep_args a, const Calc calcIn, const unsigned long long timeoutNs)
+__global__ void __launch_bounds__(DimFinishWarps * 32, 8) dimShardFinish(const mcmcpp_halfstep_args a, const Calc calcIn, const unsigned long long timeoutNs)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int D = a.D, K = a.K;
@@ -314,14 +313,12 @@ struct DimShardLauncher
         return launchStatus();
     }
 
-    /* finishing kernel of one rank on `stream`: a fraction of each SM, so that it runs beside the summing kernel */
+    /* finishing kernel of one rank on `stream`: one warp per group of 32 walkers */
     static int finish(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream)
     {
         static const unsigned long long timeoutNs = (unsigned long long)envInt("MCMCPP_B200_RDV_TIMEOUT_MS", 20000) * 1000000ULL;
-        static const int perSm = envInt("MCMCPP_B200_DIM_FINISH_CTAS", 1);
-        int grid = (a.sm_count > 0 ? a.sm_count : 148) * (perSm < 1 ? 1 : perSm);
         const int numGroups = (a.K + 31) / 32;
-        if (grid * DimFinishWarps > numGroups) grid = (numGroups + DimFinishWarps - 1) / DimFinishWarps;
+        const int grid = (numGroups + DimFinishWarps - 1) / DimFinishWarps;
         const bool vec = (a.D % 2) == 0;
         if (a.trace) {
             if (vec) dimShardFinish<Calc, true, true><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs);
@@ -336,47 +333,34 @@ struct DimShardLauncher
     static int launch(const mcmcpp_halfstep_args* args, const void* calculator, void* cudaStream)
     {
         const mcmcpp_halfstep_args& a = *args;
-        if (!a.dim_partial || !a.dim_z || !a.dim_e || !a.dim_j || !a.dim_s || !a.side_stream || !a.side_event[0] || !a.side_event[1]) return MCMCPP_ERR_STATE;
+        if (!a.dim_partial || !a.dim_z || !a.dim_e || !a.dim_j || !a.dim_s) return MCMCPP_ERR_STATE;
         if (a.world > 32) return MCMCPP_ERR_UNSUPPORTED;
         const Calc& calc = *static_cast<const Calc*>(calculator);
-        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream), side = static_cast<cudaStream_t>(a.side_stream);
-        cudaEvent_t drawn = static_cast<cudaEvent_t>(a.side_event[0]), finished = static_cast<cudaEvent_t>(a.side_event[1]);
-        /* main: draw, [drawn], sum ...................... wait [finished]
-         * side:         wait [drawn], finish, [finished]                        (finish runs beside sum) */
+        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
         dimShardDraw<<<(a.K + 255) / 256, 256, 0, stream>>>(a);
-        if (cudaEventRecord(drawn, stream) != cudaSuccess || cudaStreamWaitEvent(side, drawn, 0) != cudaSuccess) return MCMCPP_ERR_CUDA;
         int rc = sumOnly(a, calc, stream);
         if (rc != MCMCPP_OK) return rc;
-        if ((rc = finish(a, calc, side)) != MCMCPP_OK) return rc;
-        if (cudaEventRecord(finished, side) != cudaSuccess || cudaStreamWaitEvent(stream, finished, 0) != cudaSuccess) return MCMCPP_ERR_CUDA;
+        if ((rc = finish(a, calc, stream)) != MCMCPP_OK) return rc;
         if (a.launch_count) *a.launch_count += 2;
         return MCMCPP_OK;
     }
 
-    /* mcmcpp_group_fn: one colour of `count` ranks that live in this process, all on one stream except the finishing kernels:
-     * every rank's draws and summing kernel first (they wait for nobody), then every rank's finishing kernel on its side stream */
+    /* mcmcpp_group_fn: one colour of `count` ranks that live in this process, on one stream: every rank's draws and summing
+     * kernel first (they wait for nobody), then every rank's finishing kernel */
     static int launchGroup(const mcmcpp_halfstep_args* args, const void* const* calculators, int count, void* cudaStream)
     {
         if (count < 1 || count > 8) return MCMCPP_ERR_UNSUPPORTED;
         cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
         for (int r = 0; r < count; ++r) {
             const mcmcpp_halfstep_args& a = args[r];
-            if (!a.dim_partial || !a.dim_z || !a.dim_e || !a.dim_j || !a.dim_s || !a.side_stream || !a.side_event[0] || !a.side_event[1] ||
-                a.world != count || a.rank != r || a.K != args[0].K)
-                return MCMCPP_ERR_STATE;
+            if (!a.dim_partial || !a.dim_z || !a.dim_e || !a.dim_j || !a.dim_s || a.world != count || a.rank != r || a.K != args[0].K) return MCMCPP_ERR_STATE;
             dimShardDraw<<<(a.K + 255) / 256, 256, 0, stream>>>(a);
             int rc = sumOnly(a, *static_cast<const Calc*>(calculators[r]), stream);
             if (rc != MCMCPP_OK) return rc;
         }
-        cudaEvent_t summed = static_cast<cudaEvent_t>(args[0].side_event[0]);
-        if (cudaEventRecord(summed, stream) != cudaSuccess) return MCMCPP_ERR_CUDA;
         for (int r = 0; r < count; ++r) {
-            cudaStream_t side = static_cast<cudaStream_t>(args[r].side_stream);
-            cudaEvent_t finished = static_cast<cudaEvent_t>(args[r].side_event[1]);
-            if (cudaStreamWaitEvent(side, summed, 0) != cudaSuccess) return MCMCPP_ERR_CUDA;
-            int rc = finish(args[r], *static_cast<const Calc*>(calculators[r]), side);
+            int rc = finish(args[r], *static_cast<const Calc*>(calculators[r]), stream);
             if (rc != MCMCPP_OK) return rc;
-            if (cudaEventRecord(finished, side) != cudaSuccess || cudaStreamWaitEvent(stream, finished, 0) != cudaSuccess) return MCMCPP_ERR_CUDA;
         }
         return MCMCPP_OK;
     }
