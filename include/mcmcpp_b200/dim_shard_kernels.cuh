@@ -189,8 +189,8 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
 /* ---- the finishing kernel: persistent warps, groups of 32 walkers in index order (warp g of the grid takes groups g, g + G, ...) */
 enum { DimFinishWarps = 4, DimPollUnroll = 8 };   /* 4 warps x 93 registers: fits beside 7 summing CTAs of 48 registers */
 
-template <class Calc, bool VEC, bool TRACE>
-__global__ void __launch_bounds__(DimFinishWarps * 32, 8) dimShardFinish(const mcmcpp_halfstep_args a, const Calc calcIn, const unsigned long long timeoutNs)
+template <class Calc, bool VEC, bool TRACE, int WALK, int CH>
+__global__ void __launch_bounds__(DimFinishWarps * 32, 4) dimShardFinish(const mcmcpp_halfstep_args a, const Calc calcIn, const unsigned long long timeoutNs)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int D = a.D, K = a.K;
@@ -240,47 +240,75 @@ __global__ void __launch_bounds__(DimFinishWarps * 32, 8) dimShardFinish(const m
         const unsigned accMask = __ballot_sync(0xffffffffu, accepted);
         unsigned work = a.chain_row ? __ballot_sync(0xffffffffu, mine) : accMask;         /* stored steps: every walker's chain row */
         myAccepted += (unsigned long long)__popc(accMask);
-        /* rebuild the slices of the walkers in `work`, the whole warp on one walker at a time (rows come from L2) */
+        /* rebuild the slices of the walkers in `work`: the whole warp on WALK walkers at a time, CH 64-element chunks of each
+         * in flight per lane (short slices: 4 walkers x 2 chunks, so that one memory latency covers four walkers) */
         while (work) {
-            const int q = __ffs(work) - 1;
-            work &= work - 1;
-            const bool acc = (accMask >> q) & 1u;
-            const int iq = g * 32 + q;
-            const double zq = __shfl_sync(0xffffffffu, z, q);
-            const int jq = __shfl_sync(0xffffffffu, j, q);
-            double* ownRow = a.pos + (size_t)(own0 + iq) * D;
-            const double* selRow = a.pos + (size_t)(other0 + jq) * D;
-            double* chainRow = a.chain_row ? a.chain_row + (size_t)(own0 + iq) * D : nullptr;
-            if (VEC) {
-                for (int d0 = 0; d0 < D; d0 += 256) {                      /* four vector loads per row in flight per lane */
-                    double2 c[4], sl[4];
+            int qs[WALK];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int d = d0 + 64 * u + 2 * lane;
-                        if (d < D) {
-                            c[u] = *reinterpret_cast<const double2*>(ownRow + d);
-                            if (acc) sl[u] = *reinterpret_cast<const double2*>(selRow + d);
+            for (int k = 0; k < WALK; ++k) {
+                qs[k] = work ? __ffs(work) - 1 : -1;
+                if (work) work &= work - 1;
+            }
+            if (VEC) {
+                double* ownRow[WALK];
+                const double* selRow[WALK];
+                double zq[WALK];
+                bool acc[WALK];
+#pragma unroll
+                for (int k = 0; k < WALK; ++k) {
+                    const int q = qs[k] < 0 ? 0 : qs[k];
+                    acc[k] = qs[k] >= 0 && ((accMask >> q) & 1u);
+                    zq[k] = __shfl_sync(0xffffffffu, z, q);
+                    const int jq = __shfl_sync(0xffffffffu, j, q);
+                    ownRow[k] = a.pos + (size_t)(own0 + g * 32 + q) * D;
+                    selRow[k] = a.pos + (size_t)(other0 + jq) * D;
+                }
+                for (int d0 = 0; d0 < D; d0 += 64 * CH) {
+                    double2 c[WALK][CH], sl[WALK][CH];
+#pragma unroll
+                    for (int k = 0; k < WALK; ++k) {
+#pragma unroll
+                        for (int u = 0; u < CH; ++u) {
+                            const int d = d0 + 64 * u + 2 * lane;
+                            if (qs[k] >= 0 && d < D) {
+                                c[k][u] = *reinterpret_cast<const double2*>(ownRow[k] + d);
+                                if (acc[k]) sl[k][u] = *reinterpret_cast<const double2*>(selRow[k] + d);
+                            }
                         }
                     }
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int d = d0 + 64 * u + 2 * lane;
-                        if (d < D) {
-                            double2 v2 = c[u];
-                            if (acc) {
-                                v2.x = stretchPoint(sl[u].x, c[u].x, zq);
-                                v2.y = stretchPoint(sl[u].y, c[u].y, zq);
-                                *reinterpret_cast<double2*>(ownRow + d) = v2;
+                    for (int k = 0; k < WALK; ++k) {
+#pragma unroll
+                        for (int u = 0; u < CH; ++u) {
+                            const int d = d0 + 64 * u + 2 * lane;
+                            if (qs[k] >= 0 && d < D) {
+                                double2 v2 = c[k][u];
+                                if (acc[k]) {
+                                    v2.x = stretchPoint(sl[k][u].x, c[k][u].x, zq[k]);
+                                    v2.y = stretchPoint(sl[k][u].y, c[k][u].y, zq[k]);
+                                    *reinterpret_cast<double2*>(ownRow[k] + d) = v2;
+                                }
+                                if (a.chain_row) *reinterpret_cast<double2*>(a.chain_row + (ownRow[k] - a.pos) + d) = v2;
                             }
-                            if (chainRow) *reinterpret_cast<double2*>(chainRow + d) = v2;
                         }
                     }
                 }
             } else {
-                for (int d = lane; d < D; d += 32) {
-                    double v1 = ownRow[d];
-                    if (acc) { v1 = stretchPoint(selRow[d], v1, zq); ownRow[d] = v1; }
-                    if (chainRow) chainRow[d] = v1;
+#pragma unroll
+                for (int k = 0; k < WALK; ++k) {
+                    if (qs[k] < 0) continue;
+                    const int q = qs[k];
+                    const bool acc = (accMask >> q) & 1u;
+                    const double zq = __shfl_sync(0xffffffffu, z, q);
+                    const int jq = __shfl_sync(0xffffffffu, j, q);
+                    double* ownRow = a.pos + (size_t)(own0 + g * 32 + q) * D;
+                    const double* selRow = a.pos + (size_t)(other0 + jq) * D;
+                    double* chainRow = a.chain_row ? a.chain_row + (size_t)(own0 + g * 32 + q) * D : nullptr;
+                    for (int d = lane; d < D; d += 32) {
+                        double v1 = ownRow[d];
+                        if (acc) { v1 = stretchPoint(selRow[d], v1, zq); ownRow[d] = v1; }
+                        if (chainRow) chainRow[d] = v1;
+                    }
                 }
             }
         }
@@ -320,13 +348,19 @@ struct DimShardLauncher
         const int numGroups = (a.K + 31) / 32;
         const int grid = (numGroups + DimFinishWarps - 1) / DimFinishWarps;
         const bool vec = (a.D % 2) == 0;
+#define MCMCPP_DIM_FINISH(V, T, WALK, CH) dimShardFinish<Calc, V, T, WALK, CH><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs)
         if (a.trace) {
-            if (vec) dimShardFinish<Calc, true, true><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs);
-            else dimShardFinish<Calc, false, true><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs);
+            if (vec) MCMCPP_DIM_FINISH(true, true, 1, 4); else MCMCPP_DIM_FINISH(false, true, 1, 1);
+        } else if (!vec) {
+            MCMCPP_DIM_FINISH(false, false, 1, 1);
+        } else if (a.D <= 128) {
+            MCMCPP_DIM_FINISH(true, false, 4, 2);
+        } else if (a.D <= 256) {
+            MCMCPP_DIM_FINISH(true, false, 2, 4);
         } else {
-            if (vec) dimShardFinish<Calc, true, false><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs);
-            else dimShardFinish<Calc, false, false><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs);
+            MCMCPP_DIM_FINISH(true, false, 1, 4);
         }
+#undef MCMCPP_DIM_FINISH
         return launchStatus();
     }
 
