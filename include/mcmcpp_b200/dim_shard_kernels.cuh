@@ -98,7 +98,7 @@ __device__ __forceinline__ double dimTakePartial(double* slotPtr, unsigned long 
  * straight from global memory (odd slices: tests and the last rank of an odd row).
  * Shared memory: [NW walkers][own row | partner row] (rowStride bytes each), NW mbarriers, NW partials. */
 template <class Calc, int WPW, bool TMA>
-__global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride)
+__global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride, const int waitAll)
 {
     extern __shared__ __align__(128) unsigned char dimSmem[];
     constexpr int NW = DimFusedWarps * WPW;                  /* walkers per tile */
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
     double* const sendSlot = ((int)threadIdx.x < a.world * NW && t * NW + sendK < K)
                                  ? a.dim_partial[(int)threadIdx.x / NW] + ((size_t)a.half * a.world + a.rank) * K + (size_t)t * NW + sendK : nullptr;
     /* partial sums of the warp's walkers: all copies awaited first, then WPW independent dependency chains side by side */
-    if (TMA) {
+    if (TMA && waitAll) {
 #pragma unroll
         for (int q = 0; q < WPW; ++q)
             if (t * NW + warp * WPW + q < K) mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
@@ -149,6 +149,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
         double p0 = 0.0, p1 = 0.0;
         if (i < K) {                                                  /* warp-uniform */
             if (TMA) {
+                if (!waitAll) mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
                 const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
                 const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
                 for (int d = 2 * lane; d < D; d += 64) {
@@ -337,7 +338,8 @@ struct DimShardLauncher
         if (smem > 227u * 1024u) return MCMCPP_ERR_UNSUPPORTED;
         static DynamicSmemOptIn optIn;
         if (!optIn.ensure(dimShardSum<Calc, WPW, TMA>, smem)) return MCMCPP_ERR_CUDA;
-        dimShardSum<Calc, WPW, TMA><<<(a.K + NW - 1) / NW, DimFusedThreads, smem, stream>>>(a, calc, rowStride);
+        static const int waitAll = envInt("MCMCPP_B200_DIM_WAIT_ALL", 0);
+        dimShardSum<Calc, WPW, TMA><<<(a.K + NW - 1) / NW, DimFusedThreads, smem, stream>>>(a, calc, rowStride, waitAll);
         return launchStatus();
     }
 
