@@ -8,8 +8,12 @@ nvidia-smi -L | head -8
 timeout 900 $TR --master-port 29611 tests/multigpu_check.py > $O/r02_multigpu_check_n$N.log 2>&1; tail -4 $O/r02_multigpu_check_n$N.log
 timeout 600 $TR --master-port 29612 bench.py --gpus $N --steps 20 --warmup 5 > $O/r02_bench_c4_n${N}_dim.json 2> $O/bench_n$N.err; tail -c 400 $O/bench_n$N.err
 timeout 600 $TR --master-port 29613 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu > $O/r02_bench_c4_n${N}_dim_b.json 2>> $O/bench_n$N.err
-MCMCPP_B200_DIM_LAG=1024 timeout 600 $TR --master-port 29617 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu > $O/r02_bench_c4_n${N}_dim_lag1024.json 2>> $O/bench_n$N.err
-MCMCPP_B200_DIM_LAG=64 timeout 600 $TR --master-port 29618 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu > $O/r02_bench_c4_n${N}_dim_lag64.json 2>> $O/bench_n$N.err
+if [ "${QUICK:-}" = "1" ]; then
+  for f in $O/r02_bench_c4_n${N}_dim.json $O/r02_bench_c4_n${N}_dim_b.json; do python -c "
+import json,sys
+d=json.loads([l for l in open('$f') if l.startswith('{')][-1]); print('$f value %.4g ms/step %.4f e2e %.4g accepted %s' % (d['value'], d['ms_per_step'], d['e2e']['value'], d['acceptance']['accepted']))"; done
+  echo done; exit 0
+fi
 timeout 600 $TR --master-port 29614 bench.py --gpus $N --shard peer --steps 10 --warmup 3 --no-cpu > $O/r02_bench_c4_n${N}_peer.json 2>> $O/bench_n$N.err
 timeout 600 $TR --master-port 29615 bench.py --gpus $N --shard allgather --steps 6 --warmup 3 --no-cpu > $O/r02_bench_c4_n${N}_allgather.json 2>> $O/bench_n$N.err
 timeout 600 $TR --master-port 29616 bench.py --gpus $N --workload c5 --steps 5 --warmup 3 --no-cpu > $O/r02_bench_c5_n${N}_data.json 2>> $O/bench_n$N.err
