@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
     double* const sendSlot = ((int)threadIdx.x < a.world * NW && t * NW + sendK < K)
                                  ? a.dim_partial[(int)threadIdx.x / NW] + ((size_t)a.half * a.world + a.rank) * K + (size_t)t * NW + sendK : nullptr;
     /* partial sums of the warp's walkers: all copies awaited first, then WPW independent dependency chains side by side */
-    if (TMA && waitAll) {
+    if (TMA && (waitAll & 1)) {
 #pragma unroll
         for (int q = 0; q < WPW; ++q)
             if (t * NW + warp * WPW + q < K) mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
         double p0 = 0.0, p1 = 0.0;
         if (i < K) {                                                  /* warp-uniform */
             if (TMA) {
-                if (!waitAll) mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
+                if (!(waitAll & 1)) mbarWait(smemAddr(barBase + 8u * (warp * WPW + q)), 0);
                 const double* ownS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride);
                 const double* selS = reinterpret_cast<const double*>(rows + (size_t)q * 2u * rowStride + rowStride);
                 for (int d = 2 * lane; d < D; d += 64) {
@@ -179,7 +179,10 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
     for (int q = 0; q < WPW; ++q)
         if (lane == 0) ctaPartial[warp * WPW + q] = s[q];
     __syncthreads();
-    if (sendSlot) *reinterpret_cast<volatile double*>(sendSlot) = ctaPartial[sendK];
+    if (sendSlot) {
+        if (waitAll & 2) *sendSlot = ctaPartial[sendK];                                    /* experiment: plain store */
+        else *reinterpret_cast<volatile double*>(sendSlot) = ctaPartial[sendK];
+    }
     for (int u = threadIdx.x + DimFusedThreads; u < a.world * NW; u += DimFusedThreads) {            /* world * NW > 128: the rest of the line */
         const int r = u / NW, k = u - r * NW;
         if (t * NW + k < K)
