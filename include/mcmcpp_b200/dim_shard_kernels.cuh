@@ -193,8 +193,8 @@ __global__ void __launch_bounds__(DimFusedThreads) dimShardSum(const mcmcpp_half
 /* ---- the finishing kernel: persistent warps, groups of 32 walkers in index order (warp g of the grid takes groups g, g + G, ...) */
 enum { DimFinishWarps = 4, DimPollUnroll = 8 };   /* 4 warps x 93 registers: fits beside 7 summing CTAs of 48 registers */
 
-template <class Calc, bool VEC, bool TRACE, int WALK, int CH>
-__global__ void __launch_bounds__(DimFinishWarps * 32, 4) dimShardFinish(const mcmcpp_halfstep_args a, const Calc calcIn, const unsigned long long timeoutNs)
+template <class Calc, bool VEC, bool TRACE, int WALK, int CH, int MINB>
+__global__ void __launch_bounds__(DimFinishWarps * 32, MINB) dimShardFinish(const mcmcpp_halfstep_args a, const Calc calcIn, const unsigned long long timeoutNs)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int D = a.D, K = a.K;
@@ -353,17 +353,22 @@ struct DimShardLauncher
         const int numGroups = (a.K + 31) / 32;
         const int grid = (numGroups + DimFinishWarps - 1) / DimFinishWarps;
         const bool vec = (a.D % 2) == 0;
-#define MCMCPP_DIM_FINISH(V, T, WALK, CH) dimShardFinish<Calc, V, T, WALK, CH><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs)
+#define MCMCPP_DIM_FINISH(V, T, WALK, CH, MINB) dimShardFinish<Calc, V, T, WALK, CH, MINB><<<grid, DimFinishWarps * 32, 0, stream>>>(a, calc, timeoutNs)
+        static const int variant = envInt("MCMCPP_B200_DIM_FINISH_VARIANT", 0);
         if (a.trace) {
-            if (vec) MCMCPP_DIM_FINISH(true, true, 1, 4); else MCMCPP_DIM_FINISH(false, true, 1, 1);
+            if (vec) MCMCPP_DIM_FINISH(true, true, 1, 4, 4); else MCMCPP_DIM_FINISH(false, true, 1, 1, 4);
         } else if (!vec) {
-            MCMCPP_DIM_FINISH(false, false, 1, 1);
+            MCMCPP_DIM_FINISH(false, false, 1, 1, 4);
+        } else if (variant == 1) {
+            MCMCPP_DIM_FINISH(true, false, 1, 4, 8);
+        } else if (variant == 2) {
+            MCMCPP_DIM_FINISH(true, false, 2, 2, 6);
         } else if (a.D <= 128) {
-            MCMCPP_DIM_FINISH(true, false, 4, 2);
+            MCMCPP_DIM_FINISH(true, false, 4, 2, 4);
         } else if (a.D <= 256) {
-            MCMCPP_DIM_FINISH(true, false, 2, 4);
+            MCMCPP_DIM_FINISH(true, false, 2, 4, 4);
         } else {
-            MCMCPP_DIM_FINISH(true, false, 1, 4);
+            MCMCPP_DIM_FINISH(true, false, 1, 4, 4);
         }
 #undef MCMCPP_DIM_FINISH
         return launchStatus();
