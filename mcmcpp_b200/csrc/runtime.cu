@@ -220,6 +220,7 @@ struct mcmcpp_sampler
     bool peerNeedsBarrier = false;         /* PEER: rows changed by the host since the last barrier (set_initial / restore) */
     mcmcpp_fused_fn fusedFn = nullptr;     /* small ensembles: the whole runMCMC loop in one launch */
     mcmcpp_group_fn groupFn = nullptr;     /* DIM: all ranks of the ensemble in one cooperative launch (mcmcpp_sampler_run_group) */
+    int groupDepth = 0;                    /* > 0 while mcmcpp_sampler_run_group drives this sampler (no cross-process rendezvous then) */
     bool tablesWired = false;              /* DIM: every rank's partial table is known (peer_import or peer_import_local) */
     double* dFusedChain = nullptr;         /* [fusedRows][W][D] rows filled by the fused kernel */
     long long fusedRows = 0;
@@ -326,6 +327,10 @@ int nextDeviceSlot(mcmcpp_sampler* s, double** slot)
 
 int peerBarrier(mcmcpp_sampler* s)
 {
+    if (s->cfg.shard_mode == MCMCPP_SHARD_DIM)      /* the epoch words sit behind the partial table */
+        peerBarrierKernel<<<1, 32, 0, s->stream>>>(s->dDimTable, 2 * (size_t)s->cfg.world * (size_t)s->K, s->cfg.rank, s->cfg.world, ++s->peerEpoch,
+                                                   s->dFlags, rendezvousTimeoutNs());
+    else
     peerBarrierKernel<<<1, 32, 0, s->stream>>>(s->dPeerPos, devRowDoubles(s), s->cfg.rank, s->cfg.world, ++s->peerEpoch, s->dFlags,
                                                rendezvousTimeoutNs());
     CUDA_TRY(cudaGetLastError());
@@ -475,9 +480,10 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     CUDA_TRY(cudaMalloc(&s->dDimS, sizeof(double) * 2 * (size_t)s->K));
     if (cfg->shard_mode == MCMCPP_SHARD_DIM) {
         /* partial table [2 colours][world][K]; every slot starts EMPTY (all-ones, dim_shard_kernels.cuh) */
-        const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K;
-        CUDA_TRY(cudaMalloc(&s->dDimPartial, sizeof(double) * tableDoubles));
+        const size_t tableDoubles = 2 * (size_t)cfg->world * (size_t)s->K, tail = (size_t)cfg->world + 2;   /* + epoch words of the start-of-run rendezvous */
+        CUDA_TRY(cudaMalloc(&s->dDimPartial, sizeof(double) * (tableDoubles + tail)));
         CUDA_TRY(cudaMemset(s->dDimPartial, 0xFF, sizeof(double) * tableDoubles));
+        CUDA_TRY(cudaMemset(s->dDimPartial + tableDoubles, 0, sizeof(double) * tail));
         CUDA_TRY(cudaMalloc(&s->dDimTable, sizeof(double*) * (size_t)cfg->world));
         if (cfg->world == 1) CUDA_TRY(cudaMemcpy(s->dDimTable, &s->dDimPartial, sizeof(double*), cudaMemcpyHostToDevice));
         CUDA_TRY(cudaStreamCreateWithFlags(&s->sideStream, cudaStreamNonBlocking));
@@ -729,6 +735,11 @@ int mcmcpp_sampler_run(mcmcpp_sampler* s, int num_steps, float* device_ms)
         /* the first colour reads partner rows from the other ranks: their setInitialWalkerPos / restore copies must have landed */
         if ((rc = peerBarrier(s)) != MCMCPP_OK) return rc;
         s->peerNeedsBarrier = false;
+    }
+    if (s->cfg.world > 1 && s->cfg.shard_mode == MCMCPP_SHARD_DIM && s->groupDepth == 0) {
+        /* every rank has entered runMCMC before the clock of this call starts: the ranks' host threads arrive at different times, and
+         * a rank that is early would otherwise spend that time inside its first finishing kernel (device-side barrier, bounded) */
+        if ((rc = peerBarrier(s)) != MCMCPP_OK) return rc;
     }
     CUDA_TRY(cudaEventRecord(s->evStart, s->stream));
     static const bool fusedAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED"); return !(e && e[0] == '0'); }();
