@@ -399,7 +399,7 @@ def measure(torch, dist, m, parallel, args, workload, steps, warm, with_e2e, wit
     # bytes that MUST move: both rows read, the own row written only when the proposal is accepted (+ chain row, log-probs)
     actual_per_update = 8.0 * Dloc * (2.0 + acc_frac + stored_frac) + 16.0
     achieved_actual = per_launch_updates * actual_per_update / (launch_ms * 1e-3) / 1e9
-    kernel = ("dimShardDraw + dimShardFused (TMA ring, partials over NVLink)" if shard == "dim" else "stretchDrawKernel + stretchHalfStepBulk (TMA)"
+    kernel = ("dimShardDraw + dimShardSum (TMA, partial sums over NVLink) + dimShardFinish" if shard == "dim" else "stretchDrawKernel + stretchHalfStepBulk (TMA)"
               if (D >= 130 and D % 2 == 0) else "stretchHalfStepWarp" if D > 8 else
               "stretchFusedSmall (whole runMCMC in one launch)" if (W // 2 <= 1024 and world == 1) else "stretchHalfStepThread")
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
