@@ -329,6 +329,20 @@ int mcmcpp_sampler_cov_end(mcmcpp_sampler* s);
 int mcmcpp_covariance(const double* chain_host, long long steps, int num_walkers, int num_params, int slice_interval, int device,
                       double* mean, double* cov, double* corr, long long* points);
 
+/* ---- covariance of rows already in device memory, WITHOUT any allocation.  No counterpart in the reference: added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ *      loops, harnesses that forbid it).  Same kernels, definitions and tolerance tier as mcmcpp_covariance; the per-CTA Kahan
+ *      pairs and the totals live in a file-scope `static __device__` array of the library (csrc/analysis.cu; about 2.7 MB, held
+ *      by every GPU that loads the library until the process exits) instead of cudaMalloc'ed memory.
+ *      rows_dev: DEVICE pointer, [num_points][num_params] doubles on `device`; mean[D], cov[D*D], corr[D*D]: HOST outputs,
+ *      any may be NULL; cuda_stream: the cudaStream_t to work on (NULL = the default stream); the call returns after the
+ *      stream has drained.  num_params <= MCMCPP_NOALLOC_COV_MAX_PARAMS, else MCMCPP_ERR_UNSUPPORTED with a message.
+ *      Calls no cudaMalloc / cudaFree / allocating routine.  Every call on a device shares the one array (cleared at the
+ *      start of each call): calls that overlap on the same GPU -- two host threads, two streams -- race; serialise them. */
+#define MCMCPP_NOALLOC_COV_MAX_PARAMS 32
+int mcmcpp_covariance_device_noalloc(const double* rows_dev, long long num_points, int num_params, int device,
+                                     double* mean, double* cov, double* corr, void* cuda_stream);
+
 /* ---- Analysis::AutoCorrCalc::calcAutoCorrTimes + retrieveAutoCorrelationTime (Analysis/AutoCorrCalc.h:77,89,150-203;
  *      Detail/AutoCov.h:131-290) over a host chain [steps][num_walkers][num_params], all walkers: iat_out[num_params].
  *      The reference's own arithmetic in its own order (radix-2 circular FFT autocovariance, its twiddles, its

@@ -10,7 +10,9 @@
  *   D <= 4   covSmallKernel: one thread per point, items in registers, CTA tree, one Kahan step per CTA per call
  *   D <= 128 covItemKernel:  one thread per item (i, j<=i), 32-point chunks staged in shared memory
  */
+#include <atomic>
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <vector>
 #include "analysis.h"
@@ -430,4 +432,105 @@ extern "C" int mcmcpp_autocorr_times(const double* chain_host, long long steps, 
     if (rc == MCMCPP_OK) rc = mcmcpp_autocorr_device(dChain, steps, num_walkers, num_params, window_scaling, reference_buffer_reuse, iat_out);
     cudaFree(dChain);
     return rc;
+}
+
+/* =====================================================================================================================
+ * mcmcpp_covariance_device_noalloc (capi.h): the covariance kernels above on scratch that is NOT allocated.  No counterpart
+ * in the reference; added for callers that cannot call cudaMalloc.
+ *
+ * The per-CTA Kahan pairs and the totals live in one file-scope device array.  Its name is only a stand-in in host code:
+ * the address the kernels get is taken with cudaGetSymbolAddress, once per device, with that device current.  Every call
+ * on a device uses the same array, which keeps the previous call's contents: it is cleared on the caller's stream first.
+ * Calls that overlap on one GPU race on it.
+ * ===================================================================================================================== */
+namespace
+{
+enum {
+    NoAllocMaxD = MCMCPP_NOALLOC_COV_MAX_PARAMS,
+    NoAllocMaxItems = NoAllocMaxD + NoAllocMaxD * (NoAllocMaxD + 1) / 2,        /* 560 */
+    NoAllocBlocksSmall = 148 * 8, NoAllocItemsSmall = 4 + 4 * 5 / 2,            /* D <= 4: 1184 CTAs x 14 items */
+    NoAllocBlocks = 148 * 2,                                                    /* D > 4:   296 CTAs x <= 560 items */
+    NoAllocPairs = NoAllocBlocks * NoAllocMaxItems,                             /* 165,760 >= 1184 x 14 */
+    NoAllocDevices = 64
+};
+static_assert(NoAllocPairs >= NoAllocBlocksSmall * NoAllocItemsSmall, "scratch must hold the small-D layout too");
+
+/* [NoAllocPairs] (sum, compensation) pairs, then [NoAllocMaxItems] totals: 2,656,640 bytes */
+static __device__ __align__(256) double2 g_noAllocScratch[NoAllocPairs + (NoAllocMaxItems + 1) / 2];
+
+/* device address of the array on each device (0 = not asked yet); the same value whichever thread stores it */
+std::atomic<uintptr_t> g_noAllocAddress[NoAllocDevices];
+}  // namespace
+
+int mcmcpp_covariance_device_noalloc(const double* rows_dev, long long num_points, int num_params, int device,
+                                     double* mean, double* cov, double* corr, void* cuda_stream)
+{
+    if (!rows_dev || num_points <= 0 || num_params <= 0) return mcmcpp_internal_fail(MCMCPP_ERR_ARG, "bad argument");
+    if (num_params > NoAllocMaxD) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "mcmcpp_covariance_device_noalloc: num_params = %d exceeds MCMCPP_NOALLOC_COV_MAX_PARAMS = %d "
+                                  "(the static scratch array is sized for that)", num_params, (int)NoAllocMaxD);
+        return mcmcpp_internal_fail(MCMCPP_ERR_UNSUPPORTED, msg);
+    }
+    if (device < 0 || device >= NoAllocDevices) return mcmcpp_internal_fail(MCMCPP_ERR_ARG, "device ordinal out of range");
+    if (cudaSetDevice(device) != cudaSuccess) return mcmcpp_internal_fail(MCMCPP_ERR_CUDA, "cudaSetDevice failed");
+    uintptr_t address = g_noAllocAddress[device].load(std::memory_order_acquire);
+    if (!address) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noAllocScratch);       /* this device is current */
+        if (e != cudaSuccess || !p) {
+            char msg[160];
+            snprintf(msg, sizeof msg, "cudaGetSymbolAddress of the static scratch failed on device %d: %s", device, cudaGetErrorString(e));
+            return mcmcpp_internal_fail(MCMCPP_ERR_CUDA, msg);
+        }
+        address = (uintptr_t)p;
+        g_noAllocAddress[device].store(address, std::memory_order_release);
+    }
+    double2* acc = reinterpret_cast<double2*>(address);
+    double* totals = reinterpret_cast<double*>(acc + NoAllocPairs);
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    const int D = num_params, nItems = D + D * (D + 1) / 2;
+    const int nBlocks = D <= 4 ? NoAllocBlocksSmall : NoAllocBlocks;
+
+    /* the array holds the last call's pairs: the ones this call reads must start at zero */
+    if (cudaMemsetAsync(acc, 0, sizeof(double2) * (size_t)nBlocks * nItems, stream) != cudaSuccess)
+        return mcmcpp_internal_fail(MCMCPP_ERR_CUDA, "clearing the static scratch failed");
+    switch (D) {
+    case 1: covSmallKernel<1><<<nBlocks, CovSmallThreads, 0, stream>>>(rows_dev, num_points, acc); break;
+    case 2: covSmallKernel<2><<<nBlocks, CovSmallThreads, 0, stream>>>(rows_dev, num_points, acc); break;
+    case 3: covSmallKernel<3><<<nBlocks, CovSmallThreads, 0, stream>>>(rows_dev, num_points, acc); break;
+    case 4: covSmallKernel<4><<<nBlocks, CovSmallThreads, 0, stream>>>(rows_dev, num_points, acc); break;
+    default: covItemKernel<<<nBlocks, CovThreads, sizeof(double) * CovChunk * D, stream>>>(rows_dev, num_points, D, nItems, acc);
+    }
+    covTotalsKernel<<<(nItems + 255) / 256, 256, 0, stream>>>(acc, nBlocks, nItems, totals);
+    if (cudaGetLastError() != cudaSuccess) return mcmcpp_internal_fail(MCMCPP_ERR_CUDA, "covariance kernel launch failed");
+
+    double t[NoAllocMaxItems];                                                  /* host stack: nothing is allocated */
+    if (cudaMemcpyAsync(t, totals, sizeof(double) * (size_t)nItems, cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+        cudaStreamSynchronize(stream) != cudaSuccess) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "covariance on the static scratch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return mcmcpp_internal_fail(MCMCPP_ERR_CUDA, msg);
+    }
+    /* finalizeMatrix, CovarianceMatrix.h:143-185 (as mcmcpp_cov_finalize, on fixed-size arrays) */
+    const double ptCount = (double)num_points;
+    double avg[NoAllocMaxD], cv[NoAllocMaxD * NoAllocMaxD], cr[NoAllocMaxD * NoAllocMaxD];
+    for (int i = 0; i < D; ++i) avg[i] = t[i] / ptCount;
+    for (int i = 0; i < D; ++i)
+        for (int j = 0; j <= i; ++j) {
+            const double temp = (t[D + i * (i + 1) / 2 + j] / ptCount) - (avg[i] * avg[j]);
+            cv[i * D + j] = temp;
+            cv[j * D + i] = temp;
+        }
+    for (int i = 0; i < D; ++i) {
+        const double sv = std::sqrt(cv[i * D + i]);
+        for (int j = 0; j < D; ++j) cr[i * D + j] = cv[i * D + j] / sv;
+    }
+    for (int j = 0; j < D; ++j) {
+        const double sv = std::sqrt(cv[j * D + j]);
+        for (int i = 0; i < D; ++i) cr[i * D + j] /= sv;
+    }
+    for (int i = 0; i < D; ++i) if (mean) mean[i] = avg[i];
+    for (int k = 0; k < D * D; ++k) { if (cov) cov[k] = cv[k]; if (corr) corr[k] = cr[k]; }
+    return MCMCPP_OK;
 }

@@ -19,4 +19,6 @@ int mcmcpp_cov_accumulate(mcmcpp_cov_accum* c, const double* devRows, long long 
 int mcmcpp_cov_finalize(mcmcpp_cov_accum* c, long long nPoints, double* mean, double* cov, double* corr, cudaStream_t stream);
 /* AutoCorrCalc::calcAutoCorrTimes over a DEVICE chain [steps][W][D] (all walkers) -> host iat[D]; see mcmcpp_autocorr_times */
 int mcmcpp_autocorr_device(const double* chain_dev, long long steps, int W, int D, int window_scaling, int reference_buffer_reuse, double* iat_out);
+/* sets the message mcmcpp_last_error returns (runtime.cu) and hands `code` back */
+int mcmcpp_internal_fail(int code, const char* what);
 #endif

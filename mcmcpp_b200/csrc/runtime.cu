@@ -559,6 +559,9 @@ int afterInitialState(mcmcpp_sampler* s, const double* hostRowOrNull)
 
 }  // namespace
 
+/* internal (analysis.h): lets the other translation units of the library leave a message for mcmcpp_last_error */
+int mcmcpp_internal_fail(int code, const char* what) { return fail(code, what ? what : ""); }
+
 extern "C" {
 
 const char* mcmcpp_last_error(void) { return g_lastError.c_str(); }
