@@ -143,7 +143,7 @@ typedef struct {
     int32_t slot_count;        /* owned slots */
     int32_t slots_per_rank;    /* K / world (PEER owner lookup) */
     int32_t rng_mode;
-    uint64_t bound_threshold;  /* (2^64 - K) mod K   (pcg_extras.hpp:517) */
+    uint64_t bound_threshold;  /* (2^64 - K) mod K   (pcg_extras.hpp:517); with the 32-bit engine (PER_WALKER32): (2^32 - K) mod K */
     uint64_t bound_recip;      /* floor(2^64 / K) */
     uint64_t skip_mult[2];     /* SEQUENTIAL: affine jump by 3W-3 draws applied after a walker's 3 draws */
     uint64_t skip_plus[2];
@@ -276,6 +276,9 @@ const char* mcmcpp_last_error(void);
 int mcmcpp_device_count(void);
 /* measured FP64 tensor-core (DMMA m8n8k4) peak of `device` in TFLOP/s: the roofline denominator of the dense-likelihood kernels */
 int mcmcpp_fp64_tensor_peak(int device, double* tflops);
+/* self-check of the kernels' log (device_rng.cuh logOfNormal) against CUDA's log() on `device`: both evaluated on x[0..n), which must
+ * be positive, finite and normal; the outputs are host arrays of n doubles.  Test infrastructure for the "same bits" claim. */
+int mcmcpp_device_log_check(int device, const double* x, size_t n, double* kernel_log, double* cuda_log);
 
 /* ---- multi-GPU plumbing (one process per GPU) -------------------------------------------------
  *      ALLGATHER / DATA: rank 0 makes an id, the host layer broadcasts the 128 bytes, every rank joins (NCCL).

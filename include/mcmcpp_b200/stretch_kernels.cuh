@@ -137,7 +137,7 @@ __device__ __forceinline__ GwConstants gwOf(const mcmcpp_halfstep_args& a)
 /* the three draws of an update from whichever engine the sampler runs (uniform branch on a launch argument) */
 __device__ __forceinline__ StretchDraws drawStretchFor(const mcmcpp_halfstep_args& a, WalkerRng& rng)
 {
-    if (a.rng_mode == MCMCPP_RNG_PER_WALKER32) return drawStretch32(rng.state.lo, rng.inc.lo, (uint32_t)a.K, gwOf(a));
+    if (a.rng_mode == MCMCPP_RNG_PER_WALKER32) return drawStretch32(rng.state.lo, rng.inc.lo, (uint32_t)a.K, (uint32_t)a.bound_threshold, a.bound_recip, gwOf(a));
     return drawStretch(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, gwOf(a));
 }
 
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 14 : 1)) stretc
         loadRow<D>(ownRow, cur);
         const double oldp = a.logp[w];
         StretchDraws dr;
-        if (RNG32) { dr.redraws = 0; dr.j = drawPartner32(rng.state.lo, rng.inc.lo, (uint32_t)a.K); }
+        if (RNG32) { dr.redraws = 0; dr.j = drawPartner32(rng.state.lo, rng.inc.lo, (uint32_t)a.K, (uint32_t)a.bound_threshold, a.bound_recip); }
         else dr.j = drawPartner(rng.state, rng.inc, (uint64_t)a.K, a.bound_threshold, a.bound_recip, dr.redraws);
         /* Programmatic dependent launch: everything above reads what THIS colour's previous launch (two launches back,
          * complete) wrote; only the partner rows come from the launch right before.  Wait for it here, then let the next
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 14 : 1)) stretc
 #pragma unroll
         for (int d = 0; d < D; ++d) prop[d] = stretchPoint(prop[d], cur[d], dr.z);
 
-        const double scaling = __dmul_rn(log(dr.z), (double)(D - 1));
+        const double scaling = __dmul_rn(RNG32 ? logOfNormal(dr.z) : log(dr.z), (double)(D - 1));   /* the same bits (device_rng.cuh) */
         const double newp = calc.calcLogPostProb(prop);
         const double diff = __dsub_rn(__dadd_rn(scaling, newp), oldp);
         accepted = dr.logOneMinusU < diff ? 1 : 0;

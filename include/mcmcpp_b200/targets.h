@@ -46,6 +46,29 @@ public:
     ParamType epsilon;
 };
 
+namespace Detail
+{
+/* v / -20 as an IEEE division, any type */
+template <class ParamType>
+MCMCPP_HD ParamType overMinusTwenty(ParamType v) { return v / static_cast<ParamType>(-20); }
+
+/* ... and for double on the device without the generic division sequence (a MUFU, four Newton DFMAs and a range check to divide
+ * by a constant): q = RN(v c), r = v + 20 q (exact in one FMA), RN(q + r c) with c = RN(1/-20) is the correctly rounded
+ * quotient (Markstein), i.e. the very bits of v / -20.0 wherever nothing leaves the normal range; outside it the division itself. */
+MCMCPP_HD double overMinusTwenty(double v)
+{
+#if defined(__CUDA_ARCH__)
+    const unsigned h = (unsigned)__double2hiint(v) & 0x7fffffffu;
+    if (h - 0x07000000u < 0x70000000u) {                 /* 2^-911 <= |v| < 2^881 */
+        const double c = -0x1.999999999999ap-5;
+        const double q = __dmul_rn(v, c);
+        return fma(fma(20.0, q, v), c, q);
+    }
+#endif
+    return v / -20.0;
+}
+}
+
 /* BASELINE config 2: Goodman-Weare banana, -(100 (y-x^2)^2 + (1-x)^2)/20 */
 template <class ParamType>
 class RosenbrockTwoDim
@@ -56,7 +79,7 @@ public:
     {
         ParamType t1 = paramSet[1] - paramSet[0] * paramSet[0];
         ParamType t2 = static_cast<ParamType>(1) - paramSet[0];
-        return ((static_cast<ParamType>(100) * (t1 * t1)) + (t2 * t2)) / static_cast<ParamType>(-20);
+        return Detail::overMinusTwenty((static_cast<ParamType>(100) * (t1 * t1)) + (t2 * t2));
     }
 };
 

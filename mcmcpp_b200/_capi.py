@@ -64,6 +64,7 @@ SYMBOLS = {
     "mcmcpp_device_count": (C.c_int, []),
     "mcmcpp_sampler_set_fused_launcher": (C.c_int, [C.c_void_p, C.c_void_p]),
     "mcmcpp_fp64_tensor_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
+    "mcmcpp_device_log_check": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
     "mcmcpp_covariance_device_noalloc": (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                   C.c_void_p]),
     "mcmcpp_comm_unique_id": (C.c_int, [C.c_void_p]),

@@ -509,6 +509,7 @@ int createCommon(const mcmcpp_config* cfg, mcmcpp_sampler** out)
     a.rng_mode = cfg->rng_mode;
     const uint64_t K64 = (uint64_t)s->K;
     a.bound_threshold = (0ULL - K64) % K64;                                    /* pcg_extras.hpp:517 */
+    if (cfg->rng_mode == MCMCPP_RNG_PER_WALKER32) a.bound_threshold = (uint64_t)((0u - (uint32_t)K64) % (uint32_t)K64);   /* the same in 32 bits */
     a.bound_recip = (K64 == 1) ? ~0ULL : (uint64_t)((((unsigned __int128)1) << 64) / K64);
     U128 inc; inc.lo = 1; inc.hi = 0;                                          /* stream 0 */
     MCMC::Device::Affine128 skip = MCMC::Device::pcg64AdvanceMap(inc, 3ULL * (uint64_t)W - 3ULL, 0);
@@ -559,6 +560,15 @@ int afterInitialState(mcmcpp_sampler* s, const double* hostRowOrNull)
 
 }  // namespace
 
+/* both logs on the same inputs (mcmcpp_device_log_check) */
+static __global__ void logCheckKernel(const double* x, size_t n, double* kernelLog, double* cudaLog)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    kernelLog[i] = MCMC::Device::logOfNormal(x[i]);
+    cudaLog[i] = log(x[i]);
+}
+
 /* internal (analysis.h): lets the other translation units of the library leave a message for mcmcpp_last_error */
 int mcmcpp_internal_fail(int code, const char* what) { return fail(code, what ? what : ""); }
 
@@ -571,6 +581,23 @@ int mcmcpp_device_count(void)
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
     return count;
+}
+
+int mcmcpp_device_log_check(int device, const double* x, size_t n, double* kernel_log, double* cuda_log)
+{
+    if (!x || !kernel_log || !cuda_log || n == 0) return fail(MCMCPP_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(device));
+    double* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, sizeof(double) * 3 * n));
+    int rc = MCMCPP_OK;
+    if (cudaMemcpy(d, x, sizeof(double) * n, cudaMemcpyHostToDevice) != cudaSuccess) rc = MCMCPP_ERR_CUDA;
+    if (rc == MCMCPP_OK) {
+        logCheckKernel<<<(unsigned)((n + 255) / 256), 256>>>(d, n, d + n, d + 2 * n);
+        if (cudaMemcpy(kernel_log, d + n, sizeof(double) * n, cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(cuda_log, d + 2 * n, sizeof(double) * n, cudaMemcpyDeviceToHost) != cudaSuccess) rc = MCMCPP_ERR_CUDA;
+    }
+    cudaFree(d);
+    return rc == MCMCPP_OK ? rc : fail(rc, std::string("log check failed: ") + cudaGetErrorString(cudaGetLastError()));
 }
 
 int mcmcpp_sampler_create(const mcmcpp_config* cfg, mcmcpp_halfstep_fn launcher, const void* calculator, size_t calc_bytes,

@@ -277,3 +277,30 @@ def test_c2_million_walker_iat_without_the_chain_crossing_pcie(port):
     assert np.allclose(np.abs(iat), np.abs(ref), rtol=0.15), (iat, ref)
     assert np.allclose(mean, full.reshape(-1, D).mean(axis=0), rtol=1e-9, atol=1e-12)      # the same 2e8 points
     s.close()
+
+
+def test_device_log_matches_cuda_log():
+    """device_rng.cuh logOfNormal (the log the pcg32 draws call on z and on 1-u) returns the bits of CUDA's log() on its whole
+    domain of use -- positive normal doubles -- and is within 1 ulp of the host libm (the oracle's log)."""
+    from mcmcpp_b200 import _capi
+    lib = _capi.lib()
+    rng = np.random.default_rng(20240607)
+    n = 1 << 21
+    u = rng.random(n)
+    parts = [
+        1.0 - u[: n // 4],                                             # 1 - u as the Metropolis test makes it
+        (0.7071067811865475 * u[n // 4: n // 2] + 0.7071067811865476) ** 2,   # z = g(u), alpha = 2
+        np.exp(rng.uniform(-700.0, 700.0, n // 4)),                      # the whole normal range
+        rng.integers(1, 1 << 62, n // 4 - 8).astype(np.uint64).view(np.float64),
+        np.array([1.0, 2.0 ** -53, np.nextafter(1.0, 0.0), np.nextafter(1.0, 2.0), 2.2250738585072014e-308,
+                  1.7976931348623157e308, 0.5, 2.0]),
+    ]
+    x = np.ascontiguousarray(np.concatenate(parts))
+    x = np.ascontiguousarray(x[np.isfinite(x) & (x >= 2.2250738585072014e-308)])
+    mine = np.empty_like(x)
+    ref = np.empty_like(x)
+    _capi.check(lib.mcmcpp_device_log_check(0, x.ctypes.data, x.size, mine.ctypes.data, ref.ctypes.data))
+    assert np.array_equal(mine.view(np.uint64), ref.view(np.uint64)), int((mine.view(np.uint64) != ref.view(np.uint64)).sum())
+    host = np.log(x)
+    ulp = np.abs(mine - host) / np.spacing(np.abs(host) + 1e-300)
+    assert ulp.max() <= 1.0
