@@ -492,6 +492,16 @@ def gpu_arm(args):
     if world != args.gpus and rank == 0:
         print("bench.py: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
     warm = max(3, args.warmup)
+    if args.shard_list:
+        # analysis: several shard modes in ONE launch (one start-up on an N-GPU box), device-timed value only, one line per mode
+        for mode in args.shard_list.split(","):
+            args.shard = mode
+            line = measure(torch, dist, m, parallel, args, args.workload, args.steps, warm, False, False)
+            if rank == 0:
+                print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
     line = measure(torch, dist, m, parallel, args, args.workload, args.steps, warm, True, not args.no_cpu)
     if rank == 0 and world == 1 and args.workload == "c4" and not args.no_others and not os.environ.get("MCMCPP_BENCH_D") \
             and args.shard is None and args.mover == "stretch" and args.store_every == 0:
@@ -520,6 +530,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--shard", default=None, choices=["allgather", "peer", "dim"])
+    ap.add_argument("--shard-list", default=None, help="analysis: comma-separated shard modes measured one after the other in this launch (no e2e / cpu legs), one JSON line each")
     ap.add_argument("--rng", default="sequential", choices=["sequential", "per_walker", "per_walker32"])
     ap.add_argument("--mover", default="stretch", choices=["stretch", "de"], help="de: Mover::DifferentialEvolution (analysis runs; not the BASELINE metric)")
     ap.add_argument("--store-every", type=int, default=0, help="N > 0: chain on, every N-th step stored (SURVEY s.8(d): C2's second run stores every 100th); single GPU")

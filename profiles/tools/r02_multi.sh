@@ -5,6 +5,17 @@ N=${1:-2}
 O=gpurun_out; mkdir -p $O
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 nvidia-smi -L | head -8
+if [ "${ONLY:-}" = "walker" ]; then      # the walker-sharded modes north_star words (all-gather) and its row-gather variant, one launch
+  timeout 600 $TR --master-port 29617 bench.py --gpus $N --shard-list peer,allgather --steps 6 --warmup 3 > $O/r02_bench_c4_n${N}_walker_shards.jsonl 2> $O/bench_walker_n$N.err
+  tail -c 600 $O/bench_walker_n$N.err
+  python - $O/r02_bench_c4_n${N}_walker_shards.jsonl <<'PY'
+import json, sys
+for l in open(sys.argv[1]):
+    if l.startswith('{'):
+        d = json.loads(l); print('shard %s value %.4g ms/step %.4f accepted %s' % (d['config']['shard'], d['value'], d['ms_per_step'], d['acceptance']['accepted']))
+PY
+  echo done; exit 0
+fi
 timeout 900 $TR --master-port 29611 tests/multigpu_check.py > $O/r02_multigpu_check_n$N.log 2>&1; tail -4 $O/r02_multigpu_check_n$N.log
 timeout 600 $TR --master-port 29612 bench.py --gpus $N --steps 20 --warmup 5 > $O/r02_bench_c4_n${N}_dim.json 2> $O/bench_n$N.err; tail -c 400 $O/bench_n$N.err
 timeout 600 $TR --master-port 29613 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu > $O/r02_bench_c4_n${N}_dim_b.json 2>> $O/bench_n$N.err
