@@ -701,6 +701,118 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedSmall(const mc
     if ((t & 31) == 0 && accepted) atomicAdd(a.accept_slots, accepted);
 }
 
+/* ---- the same, with the draws made AHEAD by the whole CTA (sequential stream, W <= 1024) --------------------------------
+ * In stretchFusedSmall one thread makes a walker's three draws and then its update: ~450 dependent instructions per colour on
+ * ONE warp for a 32-walker ensemble (0.8 us per colour).  But in the sequential stream the draws of update (step s, walker w)
+ * are the base stream advanced by 3 (s W + w) -- they depend on nothing the chain does.  So the CTA works in windows of B steps
+ * (B = 1024 / W): first ALL B W threads make one update's draws each (thread (b, w): steps b, b + B, ... of walker w, its state
+ * jumping 3 W B draws per window) into shared memory, then the K walker threads run the 2 B colours of the window, whose
+ * dependent chain is now draws-from-shared-memory -> partner row -> proposal -> log-prob -> test.  The arithmetic of every draw
+ * and update is stretchFusedSmall's; chains, counters and final rng states are bit-identical (tests/test_gpu_parity.py fused
+ * cases run both).  One difference, outside parity: after a bounded_rand rejection (probability K / 2^64 per update; counted in
+ * flags[0] as everywhere) the later draws of that walker do not shift by one. */
+template <class Calc, int D>
+__global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mcmcpp_fused_args f, const Calc calcIn, const int stepsPerWindow)
+{
+    extern __shared__ double fusedSmem[];
+    const mcmcpp_halfstep_args& a = f.base;
+    const int K = a.K, W = 2 * K, t = threadIdx.x, B = stepsPerWindow, T = W * B;
+    double* sPos = fusedSmem;                                 /* [W][D] */
+    double* sLogp = sPos + (size_t)W * D;                     /* [W] */
+    double* sZ = sLogp + W;                                   /* [B][W] z, log(1-u), log(z) (D-1), partner */
+    double* sE = sZ + T;
+    double* sS = sE + T;
+    int* sJ = reinterpret_cast<int*>(sS + T);
+    for (int idx = t; idx < W * D; idx += blockDim.x) sPos[idx] = a.pos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) sLogp[idx] = a.logp[idx];
+    Calc calc = calcIn;
+    const long long total = (long long)f.stored_steps * f.interval;
+
+    /* drawing role: thread (b, w) owns steps b, b + B, ... of walker w */
+    const bool drawer = t < T;
+    const int b = t / W, w = t - b * W;
+    U128 inc; inc.lo = 1ULL; inc.hi = 0;                      /* the sampler's stream 0 (EnsembleSampler.h:217) */
+    U128 base; base.lo = 0; base.hi = 0;
+    Affine128 window; window.mult = base; window.plus = base;
+    long long next = b;
+    unsigned redraws = 0;
+    if (drawer) {
+        const ulonglong2 s0 = reinterpret_cast<const ulonglong2*>(a.rng_state)[w];
+        base.lo = s0.x; base.hi = s0.y;
+        base = applyAffine(pcg64AdvanceMap(inc, 3ULL * (uint64_t)W * (uint64_t)b, 0), base);
+        window = pcg64AdvanceMap(inc, 3ULL * (uint64_t)W * (uint64_t)B, 0);
+    }
+    /* walker role: thread t < K owns red walker t and black walker K + t; their warps meet at barrier 1 after every colour */
+    const int walkerThreads = ((K + 31) / 32) * 32;
+    const bool live = t < K;
+    unsigned long long accepted = 0;
+    int sinceStore = 0;
+    long long row = 0;
+    __syncthreads();
+    for (long long first = 0; first < total; first += B) {
+        if (drawer && next < total) {
+            U128 st = base;
+            const StretchDraws dr = drawStretch(st, inc, (uint64_t)K, a.bound_threshold, a.bound_recip, gwOf(a));
+            redraws += (unsigned)dr.redraws;
+            sJ[t] = dr.j; sZ[t] = dr.z; sE[t] = dr.logOneMinusU;
+            sS[t] = __dmul_rn(log(dr.z), (double)(D - 1));
+            base = applyAffine(window, base);
+            next += B;
+        }
+        __syncthreads();
+        if (t < walkerThreads) {
+            const int steps = (int)((total - first) < (long long)B ? (total - first) : (long long)B);
+            for (int bb = 0; bb < steps; ++bb) {
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    if (live) {
+                        const int ww = half * K + t, other0 = (1 - half) * K, item = bb * W + ww;
+                        const int j = sJ[item];
+                        const double z = sZ[item];
+                        double cur[D], prop[D];
+#pragma unroll
+                        for (int d = 0; d < D; ++d) { cur[d] = sPos[(size_t)ww * D + d]; prop[d] = sPos[(size_t)(other0 + j) * D + d]; }
+#pragma unroll
+                        for (int d = 0; d < D; ++d) prop[d] = stretchPoint(prop[d], cur[d], z);
+                        const double newp = calc.calcLogPostProb(prop);
+                        const double diff = __dsub_rn(__dadd_rn(sS[item], newp), sLogp[ww]);
+                        if (sE[item] < diff) {
+#pragma unroll
+                            for (int d = 0; d < D; ++d) sPos[(size_t)ww * D + d] = prop[d];
+                            sLogp[ww] = newp;
+                            ++accepted;
+                        }
+                    }
+                    asm volatile("bar.sync 1, %0;" :: "r"(walkerThreads) : "memory");
+                }
+                if (++sinceStore == f.interval) {
+                    sinceStore = 0;
+                    if (f.chain_rows && live) {
+                        double* out = f.chain_rows + (size_t)row * W * D;
+#pragma unroll
+                        for (int d = 0; d < D; ++d) {
+                            out[(size_t)t * D + d] = sPos[(size_t)t * D + d];
+                            out[(size_t)(K + t) * D + d] = sPos[(size_t)(K + t) * D + d];
+                        }
+                    }
+                    ++row;
+                }
+            }
+        }
+        __syncthreads();
+    }
+    for (int idx = t; idx < W * D; idx += blockDim.x) a.pos[idx] = sPos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) a.logp[idx] = sLogp[idx];
+    if (drawer) {
+        /* walker w's state at rest = the stream at ITS next draw: the base of the item (step total, walker w) */
+        if (next == total) reinterpret_cast<ulonglong2*>(a.rng_state)[w] = make_ulonglong2(base.lo, base.hi);
+        if (redraws) atomicAdd(a.flags, redraws);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) accepted += __shfl_xor_sync(0xffffffffu, accepted, off);
+    if ((t & 31) == 0 && accepted) atomicAdd(a.accept_slots, accepted);
+}
+
 /* Pass &FusedLauncher<Calc>::launch to mcmcpp_sampler_set_fused_launcher (stretch move, any Calculator). */
 template <class Calc, int FixedD = 0>
 struct FusedLauncher
@@ -709,6 +821,16 @@ struct FusedLauncher
     static int run(const mcmcpp_fused_args& f, const Calc& calc, cudaStream_t stream)
     {
         const mcmcpp_halfstep_args& a = f.base;
+        /* sequential stream and W <= 1024: the draws are made ahead by the whole CTA (MCMCPP_B200_FUSED_AHEAD=0: never) */
+        static const bool aheadAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED_AHEAD"); return !(e && e[0] == '0'); }();
+        if (aheadAllowed && a.rng_mode == MCMCPP_RNG_SEQUENTIAL && 2 * a.K <= FusedMaxThreads) {
+            const int W = 2 * a.K, B = FusedMaxThreads / W, T = W * B;
+            const size_t smemAhead = sizeof(double) * ((size_t)W * D + (size_t)W + 3 * (size_t)T) + sizeof(int) * (size_t)T;
+            static DynamicSmemOptIn optInAhead;
+            if (smemAhead > 48 * 1024 && !optInAhead.ensure(stretchFusedAhead<Calc, D>, smemAhead)) return MCMCPP_ERR_CUDA;
+            stretchFusedAhead<Calc, D><<<1, ((T + 31) / 32) * 32, smemAhead, stream>>>(f, calc, B);
+            return launchStatus();
+        }
         const size_t smem = sizeof(double) * ((size_t)2 * a.K * D + (size_t)2 * a.K);
         static DynamicSmemOptIn optIn;
         if (smem > 48 * 1024 && !optIn.ensure(stretchFusedSmall<Calc, D>, smem)) return MCMCPP_ERR_CUDA;

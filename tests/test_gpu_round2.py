@@ -304,3 +304,31 @@ def test_device_log_matches_cuda_log():
     host = np.log(x)
     ulp = np.abs(mine - host) / np.spacing(np.abs(host) + 1e-300)
     assert ulp.max() <= 1.0
+
+
+# ---- the fused small-ensemble kernel with the draws made ahead (stretchFusedAhead) -----------------------------------------
+@pytest.mark.parametrize("kind,W,D,calls,interval", [
+    ("skewed_gauss_2d", 32, 2, (1, 31, 32, 33, 100), 1),        # B = 32 steps per window: less than, exactly, more than a window
+    ("skewed_gauss_2d", 320, 2, (7, 2, 50), 1),                 # the reference's own test size: B = 3, 960 drawing threads
+    ("rosenbrock_2d", 44, 2, (45, 1, 23), 2),                   # B = 23, T = 1012: a ragged last warp; subsampling
+    ("diag_gauss", 1024, 5, (3, 4), 1),                         # B = 1
+    ("diag_gauss", 600, 8, (5, 5), 3),                          # B = 1, T = 600 < 1024; > 48 KB of shared memory
+    ("dense_gauss", 12, 5, (70, 9), 1)])                        # B = 85
+def test_fused_kernel_with_draws_made_ahead(port, monkeypatch, kind, W, D, calls, interval):
+    """Several runMCMC calls of awkward lengths (each call is one launch and leaves every walker's rng state behind for the next):
+    chain, final state and counters equal to the oracle's."""
+    params = {"skewed_gauss_2d": [0.13], "rosenbrock_2d": [], "diag_gauss": 1.0 / (1.0 + (np.arange(D) % 10)),
+              "dense_gauss": np.linalg.inv(0.9 ** np.abs(np.subtract.outer(np.arange(D), np.arange(D)))).reshape(-1)}[kind]
+    init, lp = seeded_init(port, kind, params if len(params) else None, W, D, 15)
+    s = make_sampler(kind, params, W, D, seed=4)
+    s.setSlicingMode(interval > 1, interval)
+    s.setInitialWalkerPos(init, lp)
+    for n in calls:
+        assert s.runMCMC(n)
+    assert s.getLaunchCount() == len(calls)
+    assert s.getRngRedraws() == 0
+    o = port.run(kind, params if len(params) else None, init, lp, sum(calls), interval=interval, seed=4)
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(np.array(s.getChain())[1:], o["chain"]) and np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+    assert (s.getAcceptedSteps(), s.getTotalSteps()) == (int(o["acc"].sum()), int(o["tot"].sum()))
+    s.close()
