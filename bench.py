@@ -278,6 +278,9 @@ def measure(torch, dist, m, parallel, args, workload, steps, warm, with_e2e, wit
     if os.environ.get("MCMCPP_BENCH_D"):          # analysis only (e.g. one rank's slice of C4 on one GPU); named in config
         D = int(os.environ["MCMCPP_BENCH_D"])
         desc += " [params overridden to %d]" % D
+    if os.environ.get("MCMCPP_BENCH_W"):          # analysis only (size sweeps); named in config
+        W = int(os.environ["MCMCPP_BENCH_W"])
+        desc += " [walkers overridden to %d]" % W
     params = target_params(kind, D)
     # default sharding per workload: C5 shards its data rows, C4 (separable) its parameter dimension, the rest walkers
     shard = args.shard or ("data" if kind == "linreg" else "dim" if kind == "diag_gauss" else "peer")
@@ -503,7 +506,7 @@ def gpu_arm(args):
             dist.destroy_process_group()
         return 0
     line = measure(torch, dist, m, parallel, args, args.workload, args.steps, warm, True, not args.no_cpu)
-    if rank == 0 and world == 1 and args.workload == "c4" and not args.no_others and not os.environ.get("MCMCPP_BENCH_D") \
+    if rank == 0 and world == 1 and args.workload == "c4" and not args.no_others and not os.environ.get("MCMCPP_BENCH_D") and not os.environ.get("MCMCPP_BENCH_W") \
             and args.shard is None and args.mover == "stretch" and args.store_every == 0:
         # the other BASELINE configs, short runs, one GPU: driver-visible numbers for C1/C2/C3/C5
         others = {}

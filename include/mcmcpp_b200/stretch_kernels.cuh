@@ -712,25 +712,32 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedSmall(const mc
  * cases run both).  One difference, outside parity: after a bounded_rand rejection (probability K / 2^64 per update; counted in
  * flags[0] as everywhere) the later draws of that walker do not shift by one. */
 template <class Calc, int D>
-__global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mcmcpp_fused_args f, const Calc calcIn, const int stepsPerWindow)
+__global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mcmcpp_fused_args f, const Calc calcIn, const int stepsPerWindow,
+                                                                        const int overlap)
 {
     extern __shared__ double fusedSmem[];
     const mcmcpp_halfstep_args& a = f.base;
     const int K = a.K, W = 2 * K, t = threadIdx.x, B = stepsPerWindow, T = W * B;
+    const int buffers = overlap ? 2 : 1;
     double* sPos = fusedSmem;                                 /* [W][D] */
     double* sLogp = sPos + (size_t)W * D;                     /* [W] */
-    double* sZ = sLogp + W;                                   /* [B][W] z, log(1-u), log(z) (D-1), partner */
-    double* sE = sZ + T;
-    double* sS = sE + T;
-    int* sJ = reinterpret_cast<int*>(sS + T);
+    double* sZ = sLogp + W;                                   /* [buffers][B][W] z, log(1-u), log(z) (D-1), partner */
+    double* sE = sZ + (size_t)buffers * T;
+    double* sS = sE + (size_t)buffers * T;
+    int* sJ = reinterpret_cast<int*>(sS + (size_t)buffers * T);
     for (int idx = t; idx < W * D; idx += blockDim.x) sPos[idx] = a.pos[idx];
     for (int idx = t; idx < W; idx += blockDim.x) sLogp[idx] = a.logp[idx];
     Calc calc = calcIn;
     const long long total = (long long)f.stored_steps * f.interval;
 
-    /* drawing role: thread (b, w) owns steps b, b + B, ... of walker w */
-    const bool drawer = t < T;
-    const int b = t / W, w = t - b * W;
+    /* walker role: thread t < K owns red walker t and black walker K + t; their warps meet at barrier 1 after every colour.
+     * drawing role: thread (b, w) owns steps b, b + B, ... of walker w.  overlap: the warps after the walker warps draw window
+     * k + 1 while the walker warps run window k (two draw buffers); otherwise every thread draws, then the walkers run. */
+    const int walkerThreads = ((K + 31) / 32) * 32;
+    const bool live = t < K;
+    const int u = t - (overlap ? walkerThreads : 0);
+    const bool drawer = u >= 0 && u < T;
+    const int b = drawer ? u / W : 0, w = drawer ? u - b * W : 0;
     U128 inc; inc.lo = 1ULL; inc.hi = 0;                      /* the sampler's stream 0 (EnsembleSampler.h:217) */
     U128 base; base.lo = 0; base.hi = 0;
     Affine128 window; window.mult = base; window.plus = base;
@@ -742,64 +749,76 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mc
         base = applyAffine(pcg64AdvanceMap(inc, 3ULL * (uint64_t)W * (uint64_t)b, 0), base);
         window = pcg64AdvanceMap(inc, 3ULL * (uint64_t)W * (uint64_t)B, 0);
     }
-    /* walker role: thread t < K owns red walker t and black walker K + t; their warps meet at barrier 1 after every colour */
-    const int walkerThreads = ((K + 31) / 32) * 32;
-    const bool live = t < K;
     unsigned long long accepted = 0;
     int sinceStore = 0;
     long long row = 0;
-    __syncthreads();
-    for (long long first = 0; first < total; first += B) {
+
+    auto draw = [&](int buffer) {
         if (drawer && next < total) {
             U128 st = base;
             const StretchDraws dr = drawStretch(st, inc, (uint64_t)K, a.bound_threshold, a.bound_recip, gwOf(a));
             redraws += (unsigned)dr.redraws;
-            sJ[t] = dr.j; sZ[t] = dr.z; sE[t] = dr.logOneMinusU;
-            sS[t] = __dmul_rn(log(dr.z), (double)(D - 1));
+            const int slot = buffer * T + u;
+            sJ[slot] = dr.j; sZ[slot] = dr.z; sE[slot] = dr.logOneMinusU;
+            sS[slot] = __dmul_rn(log(dr.z), (double)(D - 1));
             base = applyAffine(window, base);
             next += B;
         }
-        __syncthreads();
-        if (t < walkerThreads) {
-            const int steps = (int)((total - first) < (long long)B ? (total - first) : (long long)B);
-            for (int bb = 0; bb < steps; ++bb) {
+    };
+    auto walk = [&](long long first, int buffer) {
+        const int steps = (int)((total - first) < (long long)B ? (total - first) : (long long)B);
+        for (int bb = 0; bb < steps; ++bb) {
 #pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    if (live) {
-                        const int ww = half * K + t, other0 = (1 - half) * K, item = bb * W + ww;
-                        const int j = sJ[item];
-                        const double z = sZ[item];
-                        double cur[D], prop[D];
+            for (int half = 0; half < 2; ++half) {
+                if (live) {
+                    const int ww = half * K + t, other0 = (1 - half) * K, item = buffer * T + bb * W + ww;
+                    const int j = sJ[item];
+                    const double z = sZ[item];
+                    double cur[D], prop[D];
 #pragma unroll
-                        for (int d = 0; d < D; ++d) { cur[d] = sPos[(size_t)ww * D + d]; prop[d] = sPos[(size_t)(other0 + j) * D + d]; }
+                    for (int d = 0; d < D; ++d) { cur[d] = sPos[(size_t)ww * D + d]; prop[d] = sPos[(size_t)(other0 + j) * D + d]; }
 #pragma unroll
-                        for (int d = 0; d < D; ++d) prop[d] = stretchPoint(prop[d], cur[d], z);
-                        const double newp = calc.calcLogPostProb(prop);
-                        const double diff = __dsub_rn(__dadd_rn(sS[item], newp), sLogp[ww]);
-                        if (sE[item] < diff) {
+                    for (int d = 0; d < D; ++d) prop[d] = stretchPoint(prop[d], cur[d], z);
+                    const double newp = calc.calcLogPostProb(prop);
+                    const double diff = __dsub_rn(__dadd_rn(sS[item], newp), sLogp[ww]);
+                    if (sE[item] < diff) {
 #pragma unroll
-                            for (int d = 0; d < D; ++d) sPos[(size_t)ww * D + d] = prop[d];
-                            sLogp[ww] = newp;
-                            ++accepted;
-                        }
+                        for (int d = 0; d < D; ++d) sPos[(size_t)ww * D + d] = prop[d];
+                        sLogp[ww] = newp;
+                        ++accepted;
                     }
-                    asm volatile("bar.sync 1, %0;" :: "r"(walkerThreads) : "memory");
                 }
-                if (++sinceStore == f.interval) {
-                    sinceStore = 0;
-                    if (f.chain_rows && live) {
-                        double* out = f.chain_rows + (size_t)row * W * D;
+                asm volatile("bar.sync 1, %0;" :: "r"(walkerThreads) : "memory");
+            }
+            if (++sinceStore == f.interval) {
+                sinceStore = 0;
+                if (f.chain_rows && live) {
+                    double* out = f.chain_rows + (size_t)row * W * D;
 #pragma unroll
-                        for (int d = 0; d < D; ++d) {
-                            out[(size_t)t * D + d] = sPos[(size_t)t * D + d];
-                            out[(size_t)(K + t) * D + d] = sPos[(size_t)(K + t) * D + d];
-                        }
+                    for (int d = 0; d < D; ++d) {
+                        out[(size_t)t * D + d] = sPos[(size_t)t * D + d];
+                        out[(size_t)(K + t) * D + d] = sPos[(size_t)(K + t) * D + d];
                     }
-                    ++row;
                 }
+                ++row;
             }
         }
-        __syncthreads();
+    };
+
+    draw(0);
+    __syncthreads();
+    int parity = 0;
+    for (long long first = 0; first < total; first += B) {
+        if (overlap) {
+            if (t < walkerThreads) walk(first, parity); else draw(parity ^ 1);
+            __syncthreads();
+            parity ^= 1;
+        } else {
+            if (t < walkerThreads) walk(first, 0);
+            __syncthreads();
+            draw(0);
+            __syncthreads();
+        }
     }
     for (int idx = t; idx < W * D; idx += blockDim.x) a.pos[idx] = sPos[idx];
     for (int idx = t; idx < W; idx += blockDim.x) a.logp[idx] = sLogp[idx];
@@ -824,11 +843,17 @@ struct FusedLauncher
         /* sequential stream and W <= 1024: the draws are made ahead by the whole CTA (MCMCPP_B200_FUSED_AHEAD=0: never) */
         static const bool aheadAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED_AHEAD"); return !(e && e[0] == '0'); }();
         if (aheadAllowed && a.rng_mode == MCMCPP_RNG_SEQUENTIAL && 2 * a.K <= FusedMaxThreads) {
-            const int W = 2 * a.K, B = FusedMaxThreads / W, T = W * B;
-            const size_t smemAhead = sizeof(double) * ((size_t)W * D + (size_t)W + 3 * (size_t)T) + sizeof(int) * (size_t)T;
+            /* enough threads beside the walker warps to draw at least one step per window: they draw window k + 1 while window k
+             * runs (MCMCPP_B200_FUSED_OVERLAP=0: draw, then run) */
+            static const bool overlapAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED_OVERLAP"); return !(e && e[0] == '0'); }();
+            const int W = 2 * a.K, walkerThreads = ((a.K + 31) / 32) * 32;
+            const int overlap = overlapAllowed && (FusedMaxThreads - walkerThreads) / W >= 1 ? 1 : 0;
+            const int B = overlap ? (FusedMaxThreads - walkerThreads) / W : FusedMaxThreads / W, T = W * B;
+            const int threads = overlap ? walkerThreads + ((T + 31) / 32) * 32 : ((T + 31) / 32) * 32;
+            const size_t smemAhead = sizeof(double) * ((size_t)W * D + (size_t)W + 3 * (size_t)T * (overlap + 1)) + sizeof(int) * (size_t)T * (overlap + 1);
             static DynamicSmemOptIn optInAhead;
             if (smemAhead > 48 * 1024 && !optInAhead.ensure(stretchFusedAhead<Calc, D>, smemAhead)) return MCMCPP_ERR_CUDA;
-            stretchFusedAhead<Calc, D><<<1, ((T + 31) / 32) * 32, smemAhead, stream>>>(f, calc, B);
+            stretchFusedAhead<Calc, D><<<1, threads, smemAhead, stream>>>(f, calc, B, overlap);
             return launchStatus();
         }
         const size_t smem = sizeof(double) * ((size_t)2 * a.K * D + (size_t)2 * a.K);
