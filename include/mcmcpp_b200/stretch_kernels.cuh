@@ -788,7 +788,8 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mc
                         ++accepted;
                     }
                 }
-                asm volatile("bar.sync 1, %0;" :: "r"(walkerThreads) : "memory");
+                if (walkerThreads == 32) __syncwarp();      /* one warp of walkers: no CTA barrier needed */
+                else asm volatile("bar.sync 1, %0;" :: "r"(walkerThreads) : "memory");
             }
             if (++sinceStore == f.interval) {
                 sinceStore = 0;

@@ -175,7 +175,7 @@ struct mcmcpp_sampler
     double* dParams = nullptr;             /* built-in target parameters */
     void* builtinAux = nullptr;            /* built-in target scratch (dense kernels) */
 
-    cudaStream_t stream = nullptr, copyStream = nullptr, sideStream = nullptr;     /* sideStream: DIM finishing kernels */
+    cudaStream_t stream = nullptr, copyStream = nullptr, sideStream = nullptr;     /* sideStream + sideEvent: handed to launchers (capi.h side_stream); the built-in ones do not use them */
     cudaEvent_t sideEvent[2] = {nullptr, nullptr};
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     cudaEvent_t slotReady[ChainSlots] = {nullptr, nullptr}, slotFree[ChainSlots] = {nullptr, nullptr};
