@@ -16,6 +16,14 @@ for l in open(sys.argv[1]):
 PY
   echo done; exit 0
 fi
+if [ "${ONLY:-}" = "check" ]; then       # regression check of a later tree: the four shard modes against the oracle + one DIM line
+  timeout 900 $TR --master-port 29611 tests/multigpu_check.py > $O/r02_multigpu_check_n${N}_final.log 2>&1; tail -4 $O/r02_multigpu_check_n${N}_final.log
+  timeout 600 $TR --master-port 29613 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu > $O/r02_bench_c4_n${N}_dim_final.json 2> $O/bench_n$N.err
+  python -c "
+import json
+d=json.loads([l for l in open('$O/r02_bench_c4_n${N}_dim_final.json') if l.startswith('{')][-1]); print('value %.4g ms/step %.4f e2e %.4g accepted %s' % (d['value'], d['ms_per_step'], d['e2e']['value'], d['acceptance']['accepted']))"
+  echo done; exit 0
+fi
 timeout 900 $TR --master-port 29611 tests/multigpu_check.py > $O/r02_multigpu_check_n$N.log 2>&1; tail -4 $O/r02_multigpu_check_n$N.log
 timeout 600 $TR --master-port 29612 bench.py --gpus $N --steps 20 --warmup 5 > $O/r02_bench_c4_n${N}_dim.json 2> $O/bench_n$N.err; tail -c 400 $O/bench_n$N.err
 timeout 600 $TR --master-port 29613 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu > $O/r02_bench_c4_n${N}_dim_b.json 2>> $O/bench_n$N.err
