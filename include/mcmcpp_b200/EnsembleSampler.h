@@ -189,7 +189,10 @@ public:
     {
         Device::DiffEvoBlob<Calculator> blob = {calc, {gamma, smallRandLowEdge, smallRandWidth}};
         cfg.rng_mode = MCMCPP_RNG_PER_WALKER;
-        return mcmcpp_sampler_create(&cfg, &Device::DiffEvoLauncher<Calculator>::launch, &blob, sizeof(blob), out);
+        int rc = mcmcpp_sampler_create(&cfg, &Device::DiffEvoLauncher<Calculator>::launch, &blob, sizeof(blob), out);
+        if (rc == MCMCPP_OK && paramCount <= Device::ThreadKernelMaxDim)     /* small ensembles: the whole runMCMC call in one launch */
+            rc = mcmcpp_sampler_set_fused_launcher(*out, &Device::DiffEvoFusedLauncher<Calculator>::launch);
+        return rc;
     }
 private:
     int paramCount;
@@ -216,7 +219,10 @@ public:
         Device::WalkMoveBlob<Calculator> blob = {calc, numPoints};
         cfg.rng_mode = MCMCPP_RNG_PER_WALKER;
         cfg.mover_state_doubles = 2;
-        return mcmcpp_sampler_create(&cfg, &Device::WalkMoveLauncher<Calculator>::launch, &blob, sizeof(blob), out);
+        int rc = mcmcpp_sampler_create(&cfg, &Device::WalkMoveLauncher<Calculator>::launch, &blob, sizeof(blob), out);
+        if (rc == MCMCPP_OK && paramCount <= Device::ThreadKernelMaxDim)     /* small ensembles: the whole runMCMC call in one launch */
+            rc = mcmcpp_sampler_set_fused_launcher(*out, &Device::WalkMoveFusedLauncher<Calculator>::launch);
+        return rc;
     }
 private:
     int paramCount, numPoints;

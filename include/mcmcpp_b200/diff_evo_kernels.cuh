@@ -123,6 +123,120 @@ __global__ void __launch_bounds__(ThreadKernelThreads, (D <= 2 ? 12 : 1)) diffEv
     if ((threadIdx.x & 31) == 0 && ballot) atomicAdd(a.accept_slots + blockIdx.x, (unsigned long long)__popc(ballot));
 }
 
+/* ---- small ensembles: the whole runMCMC loop in one launch (mcmcpp_fused_args), as stretchFusedSmall ------------------------
+ * One CTA; thread t owns red walker t and black walker K + t (both engines in registers for the whole call); the ensemble
+ * lives in shared memory; __syncthreads() is the colour boundary.  Per update exactly the arithmetic of diffEvoThread, so
+ * chains, counters and rng states are the ones the launch-per-colour path produces (tests/test_gpu_movers.py runs both). */
+template <class Calc, int D>
+__global__ void __launch_bounds__(FusedMaxThreads, 1) diffEvoFusedSmall(const mcmcpp_fused_args f, const DiffEvoBlob<Calc> blob)
+{
+    extern __shared__ double fusedSmem[];
+    const mcmcpp_halfstep_args& a = f.base;
+    const int K = a.K, W = 2 * K, t = threadIdx.x;
+    double* sPos = fusedSmem;                                 /* [W][D] */
+    double* sLogp = fusedSmem + (size_t)W * D;                /* [W] */
+    for (int idx = t; idx < W * D; idx += blockDim.x) sPos[idx] = a.pos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) sLogp[idx] = a.logp[idx];
+    Calc calc = blob.calc;
+    const bool live = t < K;
+    WalkerRng rng[2];
+    if (live) { rng[0] = loadRng(a, t); rng[1] = loadRng(a, K + t); }
+    unsigned long long accepted = 0;
+    __syncthreads();
+    const long long total = (long long)f.stored_steps * f.interval;
+    int sinceStore = 0;
+    long long row = 0;
+    for (long long step = 0; step < total; ++step) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            if (live) {
+                const int w = half * K + t, other0 = (1 - half) * K;
+                const int ind1 = deBounded(rng[half].state, rng[half].inc, a);
+                int ind2;
+                do { ind2 = deBounded(rng[half].state, rng[half].inc, a); } while (ind2 == ind1);
+                double prop[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d)
+                    prop[d] = deProposal(sPos[(size_t)w * D + d], sPos[(size_t)(other0 + ind1) * D + d], sPos[(size_t)(other0 + ind2) * D + d],
+                                         unitFromU64(pcg64Next(rng[half].state, rng[half].inc)), blob.mv);
+                const double newp = calc.calcLogPostProb(prop);
+                const double diff = __dsub_rn(newp, sLogp[w]);
+                const double e = log(1.0 - unitFromU64(pcg64Next(rng[half].state, rng[half].inc)));
+                if (diff > e) {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) sPos[(size_t)w * D + d] = prop[d];
+                    sLogp[w] = newp;
+                    ++accepted;
+                }
+            }
+            __syncthreads();
+        }
+        if (++sinceStore == f.interval) {
+            sinceStore = 0;
+            if (f.chain_rows && live) {
+                double* out = f.chain_rows + (size_t)row * W * D;
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    out[(size_t)t * D + d] = sPos[(size_t)t * D + d];
+                    out[(size_t)(K + t) * D + d] = sPos[(size_t)(K + t) * D + d];
+                }
+            }
+            ++row;
+        }
+    }
+    for (int idx = t; idx < W * D; idx += blockDim.x) a.pos[idx] = sPos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) a.logp[idx] = sLogp[idx];
+    if (live) {
+        reinterpret_cast<ulonglong2*>(a.rng_state)[t] = make_ulonglong2(rng[0].state.lo, rng[0].state.hi);
+        reinterpret_cast<ulonglong2*>(a.rng_state)[K + t] = make_ulonglong2(rng[1].state.lo, rng[1].state.hi);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) accepted += __shfl_xor_sync(0xffffffffu, accepted, off);
+    if ((t & 31) == 0 && accepted) atomicAdd(a.accept_slots, accepted);
+}
+
+/* Pass &DiffEvoFusedLauncher<Calc>::launch to mcmcpp_sampler_set_fused_launcher (the sampler's calculator is a DiffEvoBlob<Calc>). */
+template <class Calc, int FixedD = 0>
+struct DiffEvoFusedLauncher
+{
+    template <int D>
+    static int run(const mcmcpp_fused_args& f, const DiffEvoBlob<Calc>& blob, cudaStream_t stream)
+    {
+        const mcmcpp_halfstep_args& a = f.base;
+        const size_t smem = sizeof(double) * ((size_t)2 * a.K * D + (size_t)2 * a.K);
+        static DynamicSmemOptIn optIn;
+        if (smem > 48 * 1024 && !optIn.ensure(diffEvoFusedSmall<Calc, D>, smem)) return MCMCPP_ERR_CUDA;
+        diffEvoFusedSmall<Calc, D><<<1, ((a.K + 31) / 32) * 32, smem, stream>>>(f, blob);
+        return launchStatus();
+    }
+
+    static int launch(const mcmcpp_fused_args* args, const void* calculator, void* cudaStream)
+    {
+        const mcmcpp_fused_args& f = *args;
+        const DiffEvoBlob<Calc>& blob = *static_cast<const DiffEvoBlob<Calc>*>(calculator);
+        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
+        if (f.base.rng_mode != MCMCPP_RNG_PER_WALKER) return MCMCPP_ERR_UNSUPPORTED;
+        if (f.base.K > FusedMaxThreads || f.base.K < 2 || f.base.D > ThreadKernelMaxDim || f.base.slot_count != f.base.K) return MCMCPP_ERR_UNSUPPORTED;
+        if (f.stored_steps <= 0 || f.interval <= 0) return MCMCPP_ERR_ARG;
+        if constexpr (FixedD > 0) {
+            if (f.base.D != FixedD) return MCMCPP_ERR_ARG;
+            return run<FixedD>(f, blob, stream);
+        } else {
+            switch (f.base.D) {
+            case 1: return run<1>(f, blob, stream);
+            case 2: return run<2>(f, blob, stream);
+            case 3: return run<3>(f, blob, stream);
+            case 4: return run<4>(f, blob, stream);
+            case 5: return run<5>(f, blob, stream);
+            case 6: return run<6>(f, blob, stream);
+            case 7: return run<7>(f, blob, stream);
+            case 8: return run<8>(f, blob, stream);
+            default: return MCMCPP_ERR_UNSUPPORTED;
+            }
+        }
+    }
+};
+
 enum { DiffEvoWarps = 4 };
 
 template <class Calc, bool TRACE>

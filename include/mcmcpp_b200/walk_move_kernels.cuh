@@ -134,6 +134,148 @@ __global__ void __launch_bounds__(WalkMoveWarps * 32) walkMoveWarp(const mcmcpp_
     }
 }
 
+/* ---- small ensembles: the whole runMCMC loop in one launch (mcmcpp_fused_args), as stretchFusedSmall ------------------------
+ * One CTA; thread t owns red walker t and black walker K + t (engines and the normal distribution's saved value in registers
+ * for the whole call); the ensemble lives in shared memory; __syncthreads() is the colour boundary.  Per update the draws and
+ * the arithmetic of walkMoveWarp in its order (selection, S normals and their sum in order j; per parameter the two sums over
+ * j; the Calculator's own evaluation order), so the results are the launch-per-colour path's bit for bit. */
+template <class Calc, int D>
+__global__ void __launch_bounds__(FusedMaxThreads, 1) walkMoveFusedSmall(const mcmcpp_fused_args f, const WalkMoveBlob<Calc> blob)
+{
+    extern __shared__ double fusedSmem[];
+    const mcmcpp_halfstep_args& a = f.base;
+    const int K = a.K, W = 2 * K, t = threadIdx.x, S = blob.numPoints;
+    double* sPos = fusedSmem;                                 /* [W][D] */
+    double* sLogp = fusedSmem + (size_t)W * D;                /* [W] */
+    for (int idx = t; idx < W * D; idx += blockDim.x) sPos[idx] = a.pos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) sLogp[idx] = a.logp[idx];
+    Calc calc = blob.calc;
+    const bool live = t < K;
+    const double ptCount = (double)S;
+    WalkerRng rng[2];
+    double saved[2] = {0.0, 0.0}, available[2] = {0.0, 0.0};
+    if (live) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            rng[h] = loadRng(a, h * K + t);
+            saved[h] = a.mover_state[2 * (size_t)(h * K + t)]; available[h] = a.mover_state[2 * (size_t)(h * K + t) + 1];
+        }
+    }
+    unsigned long long accepted = 0;
+    __syncthreads();
+    const long long total = (long long)f.stored_steps * f.interval;
+    int sinceStore = 0;
+    long long row = 0;
+    for (long long step = 0; step < total; ++step) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            if (live) {
+                const int w = half * K + t, other0 = (1 - half) * K;
+                int sel[WalkMoveMaxPoints];
+                int numSelected = 0, examined = 0;                    /* selectWalkers */
+                while (numSelected < S) {
+                    const double u = unitFromU64(pcg64Next(rng[half].state, rng[half].inc));
+                    if (__dmul_rn((double)(K - examined), u) >= __dsub_rn(ptCount, (double)numSelected)) ++examined;
+                    else { sel[numSelected] = examined; ++examined; ++numSelected; }
+                }
+                double i0[D], i2[D], sumR = 0.0;
+#pragma unroll
+                for (int d = 0; d < D; ++d) { i0[d] = 0.0; i2[d] = 0.0; }
+                for (int j = 0; j < S; ++j) {
+                    const double r = walkStdNormal(rng[half].state, rng[half].inc, saved[half], available[half]);
+                    sumR = __dadd_rn(sumR, r);
+                    const double* partner = sPos + (size_t)(other0 + sel[j]) * D;
+#pragma unroll
+                    for (int d = 0; d < D; ++d) {
+                        i0[d] = __dadd_rn(i0[d], __dmul_rn(r, partner[d]));
+                        i2[d] = __dadd_rn(i2[d], partner[d]);
+                    }
+                }
+                double prop[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) prop[d] = __dadd_rn(sPos[(size_t)w * D + d], __dsub_rn(i0[d], __dmul_rn(sumR, __ddiv_rn(i2[d], ptCount))));
+                const double newp = calc.calcLogPostProb(prop);
+                const double diff = __dsub_rn(newp, sLogp[w]);
+                const double e = log(1.0 - unitFromU64(pcg64Next(rng[half].state, rng[half].inc)));
+                if (e < diff) {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) sPos[(size_t)w * D + d] = prop[d];
+                    sLogp[w] = newp;
+                    ++accepted;
+                }
+            }
+            __syncthreads();
+        }
+        if (++sinceStore == f.interval) {
+            sinceStore = 0;
+            if (f.chain_rows && live) {
+                double* out = f.chain_rows + (size_t)row * W * D;
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    out[(size_t)t * D + d] = sPos[(size_t)t * D + d];
+                    out[(size_t)(K + t) * D + d] = sPos[(size_t)(K + t) * D + d];
+                }
+            }
+            ++row;
+        }
+    }
+    for (int idx = t; idx < W * D; idx += blockDim.x) a.pos[idx] = sPos[idx];
+    for (int idx = t; idx < W; idx += blockDim.x) a.logp[idx] = sLogp[idx];
+    if (live) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            reinterpret_cast<ulonglong2*>(a.rng_state)[h * K + t] = make_ulonglong2(rng[h].state.lo, rng[h].state.hi);
+            a.mover_state[2 * (size_t)(h * K + t)] = saved[h]; a.mover_state[2 * (size_t)(h * K + t) + 1] = available[h];
+        }
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) accepted += __shfl_xor_sync(0xffffffffu, accepted, off);
+    if ((t & 31) == 0 && accepted) atomicAdd(a.accept_slots, accepted);
+}
+
+/* Pass &WalkMoveFusedLauncher<Calc>::launch to mcmcpp_sampler_set_fused_launcher (the sampler's calculator is a WalkMoveBlob<Calc>). */
+template <class Calc, int FixedD = 0>
+struct WalkMoveFusedLauncher
+{
+    template <int D>
+    static int run(const mcmcpp_fused_args& f, const WalkMoveBlob<Calc>& blob, cudaStream_t stream)
+    {
+        const mcmcpp_halfstep_args& a = f.base;
+        const size_t smem = sizeof(double) * ((size_t)2 * a.K * D + (size_t)2 * a.K);
+        static DynamicSmemOptIn optIn;
+        if (smem > 48 * 1024 && !optIn.ensure(walkMoveFusedSmall<Calc, D>, smem)) return MCMCPP_ERR_CUDA;
+        walkMoveFusedSmall<Calc, D><<<1, ((a.K + 31) / 32) * 32, smem, stream>>>(f, blob);
+        return launchStatus();
+    }
+
+    static int launch(const mcmcpp_fused_args* args, const void* calculator, void* cudaStream)
+    {
+        const mcmcpp_fused_args& f = *args;
+        const WalkMoveBlob<Calc>& blob = *static_cast<const WalkMoveBlob<Calc>*>(calculator);
+        cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
+        if (f.base.rng_mode != MCMCPP_RNG_PER_WALKER || !f.base.mover_state) return MCMCPP_ERR_UNSUPPORTED;
+        if (blob.numPoints < 1 || blob.numPoints > WalkMoveMaxPoints || blob.numPoints > f.base.K) return MCMCPP_ERR_ARG;
+        if (f.base.K > FusedMaxThreads || f.base.D > ThreadKernelMaxDim || f.base.slot_count != f.base.K) return MCMCPP_ERR_UNSUPPORTED;
+        if (f.stored_steps <= 0 || f.interval <= 0) return MCMCPP_ERR_ARG;
+        if constexpr (FixedD > 0) {
+            if (f.base.D != FixedD) return MCMCPP_ERR_ARG;
+            return run<FixedD>(f, blob, stream);
+        } else {
+            switch (f.base.D) {
+            case 1: return run<1>(f, blob, stream);
+            case 2: return run<2>(f, blob, stream);
+            case 3: return run<3>(f, blob, stream);
+            case 4: return run<4>(f, blob, stream);
+            case 5: return run<5>(f, blob, stream);
+            case 6: return run<6>(f, blob, stream);
+            case 7: return run<7>(f, blob, stream);
+            case 8: return run<8>(f, blob, stream);
+            default: return MCMCPP_ERR_UNSUPPORTED;
+            }
+        }
+    }
+};
+
 /* Launcher: pass &WalkMoveLauncher<Calc>::launch and a WalkMoveBlob<Calc> to mcmcpp_sampler_create (rng_mode PER_WALKER;
  * the runtime must have been asked for mover state: mcmcpp_config.mover_state_doubles = 2). */
 template <class Calc>

@@ -13,7 +13,8 @@
 int mcmcpp_builtin_bind(int kind, int W, int D, const double* hostParams, size_t nValues, const double* devParams,
                         mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator, void** aux, int shardMode, int dimBegin, int dimCount);
 int mcmcpp_builtin_bind_mover(int moverKind, int kind, int W, int D, const double* moverParams, size_t nMover, const double* hostParams,
-                              size_t nValues, const double* devParams, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator);
+                              size_t nValues, const double* devParams, mcmcpp_halfstep_fn* launcher, std::vector<char>* calculator,
+                              mcmcpp_fused_fn* fused);     /* *fused: the mover's small-ensemble launcher (D <= 8), or NULL */
 /* the fused small-ensemble launcher that goes with mcmcpp_builtin_bind's generic launcher for this target, or NULL */
 mcmcpp_fused_fn mcmcpp_builtin_fused(int kind, int D, int shardMode);
 /* the rank-group launcher (all ranks of a DIM-sharded ensemble in one cooperative launch) for this target, or NULL */

@@ -655,7 +655,7 @@ int mcmcpp_sampler_create_builtin_mover(const mcmcpp_config* cfg, int mover_kind
         if (e != cudaSuccess) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(MCMCPP_ERR_CUDA, cudaGetErrorString(e)); }
     }
     rc = mcmcpp_builtin_bind_mover(mover_kind, target_kind, s->W, s->D, mover_params, num_mover_params, params, num_params_values, s->dParams,
-                                   &s->launcher, &s->calculator);
+                                   &s->launcher, &s->calculator, &s->fusedFn);
     if (rc != MCMCPP_OK) { mcmcpp_sampler_destroy(s); *out = nullptr; return fail(rc, "mover: unsupported target or bad parameters"); }
     return MCMCPP_OK;
 }

@@ -137,3 +137,60 @@ def test_walk_move_checkpoint_carries_the_normal_distribution_state(port):
     pa, la = a.getWalkerState(); pc, lc = c.getWalkerState()
     assert np.array_equal(pa, pc) and np.array_equal(la, lc)
     a.close(); c.close()
+
+
+# ---- small ensembles: the movers' whole runMCMC call in one launch (diffEvoFusedSmall, walkMoveFusedSmall) ---------------------
+@pytest.mark.parametrize("kind,W,D,calls,interval", [("skewed_gauss_2d", 16, 2, (120, 7), 1), ("skewed_gauss_2d", 320, 2, (40, 3), 3),
+                                                     ("rosenbrock_2d", 2048, 2, (12, 5), 1), ("diag_gauss", 64, 5, (30, 30), 2),
+                                                     ("dense_gauss", 40, 8, (25, 2), 1)])
+def test_diff_evo_fused_small_ensemble(port, kind, W, D, calls, interval):
+    """One launch per runMCMC call (no trace requested) against the launch-per-colour path (a trace request selects it) and the
+    oracle: chains, final state, counters bit-exact; the second call continues every walker's stream."""
+    import mcmcpp_b200 as m
+    params = np.asarray({"skewed_gauss_2d": [0.13], "rosenbrock_2d": [], "diag_gauss": 1.0 / (1.0 + (np.arange(D) % 10)),
+                         "dense_gauss": np.linalg.inv(0.9 ** np.abs(np.arange(D)[:, None] - np.arange(D)[None, :])).reshape(-1)}[kind])
+    init = np.random.default_rng(W + D).standard_normal((W, D))
+    lp = port.logp(kind, params if params.size else None, init)
+    runs = []
+    for trace in (0, 1):
+        s = m.EnsembleSampler(11, W, D, m.DifferentialEvolution(D, 11, CALC[kind](m, params, D)), traceUpdates=trace)
+        s.setSlicingMode(interval > 1, interval)
+        s.setInitialWalkerPos(init, lp)
+        for n in calls:
+            assert s.runMCMC(n)
+        assert s.getLaunchCount() == (len(calls) if trace == 0 else 2 * sum(calls) * interval)
+        runs.append((np.array(s.getChain()), s.getWalkerState(), s.getAcceptedSteps(), s.getTotalSteps()))
+        s.close()
+    (c0, (p0, a0), acc0, tot0), (c1, (p1, a1), acc1, tot1) = runs
+    assert np.array_equal(c0, c1) and np.array_equal(p0, p1) and np.array_equal(a0, a1) and (acc0, tot0) == (acc1, tot1)
+    o = port.run_de(kind, params if params.size else None, init, lp, sum(calls), interval=interval, seed=11, per_walker=True)
+    assert np.array_equal(c0[1:], o["chain"]) and np.array_equal(p0, o["pos"]) and np.array_equal(a0, o["logp"])
+    assert (acc0, tot0) == (int(o["acc"].sum()), int(o["tot"].sum()))
+
+
+@pytest.mark.parametrize("kind,W,D,S,calls", [("skewed_gauss_2d", 16, 2, 3, (50, 9)), ("skewed_gauss_2d", 32, 2, 16, (20, 11)),
+                                              ("skewed_gauss_2d", 320, 2, 5, (15, 4)), ("rosenbrock_2d", 2048, 2, 4, (6, 3)),
+                                              ("diag_gauss", 64, 5, 7, (20, 5)), ("dense_gauss", 40, 8, 64 // 4, (10, 3))])
+def test_walk_move_fused_small_ensemble(port, kind, W, D, S, calls):
+    """The same for Mover::WalkMove (odd numbers of points: the normal distribution's saved value crosses updates and calls):
+    one launch per call, bit-identical to the launch-per-colour path; against the oracle in the mover's tolerance tier."""
+    import mcmcpp_b200 as m
+    params = np.asarray({"skewed_gauss_2d": [0.13], "rosenbrock_2d": [], "diag_gauss": 1.0 / (1.0 + (np.arange(D) % 10)),
+                         "dense_gauss": np.linalg.inv(0.9 ** np.abs(np.arange(D)[:, None] - np.arange(D)[None, :])).reshape(-1)}[kind])
+    init = np.random.default_rng(W + D + S).standard_normal((W, D))
+    lp = port.logp(kind, params if params.size else None, init)
+    runs = []
+    for trace in (0, 1):
+        s = m.EnsembleSampler(6, W, D, m.WalkMove(D, 6, CALC[kind](m, params, D), S), traceUpdates=trace)
+        s.setInitialWalkerPos(init, lp)
+        for n in calls:
+            assert s.runMCMC(n)
+        assert s.getLaunchCount() == (len(calls) if trace == 0 else 2 * sum(calls))
+        runs.append((np.array(s.getChain()), s.getWalkerState(), s.getAcceptedSteps(), s.getTotalSteps()))
+        s.close()
+    (c0, (p0, a0), acc0, tot0), (c1, (p1, a1), acc1, tot1) = runs
+    assert np.array_equal(c0, c1) and np.array_equal(p0, p1) and np.array_equal(a0, a1) and (acc0, tot0) == (acc1, tot1)
+    o = port.run_walk(kind, params if params.size else None, init, lp, sum(calls), S, seed=6, per_walker=True)
+    scale = np.abs(o["pos"]) + np.abs(o["pos"]).max()
+    assert np.all(np.abs(p0 - o["pos"]) <= 1e-12 * scale) and np.allclose(a0, o["logp"], rtol=1e-11, atol=1e-12)
+    assert (acc0, tot0) == (int(o["acc"].sum()), int(o["tot"].sum()))
