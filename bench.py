@@ -490,6 +490,10 @@ def gpu_arm(args):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    bound = None
+    if world > 1 and os.environ.get("MCMCPP_BENCH_BIND", "1") != "0":
+        # one process per GPU: onto the GPU's own NUMA node before anything is pinned (rank 0's cpu legs run at N=1 only)
+        bound = parallel.bind_host_to_device(bus_id_of(torch, local))
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     if world != args.gpus and rank == 0:
@@ -506,6 +510,8 @@ def gpu_arm(args):
             dist.destroy_process_group()
         return 0
     line = measure(torch, dist, m, parallel, args, args.workload, args.steps, warm, True, not args.no_cpu)
+    if rank == 0 and world > 1:
+        line["config"]["host_binding"] = ("rank processes bound to their GPU's NUMA-local cores (rank 0: %d cores)" % len(bound)) if bound else "none"
     if rank == 0 and world == 1 and args.workload == "c4" and not args.no_others and not os.environ.get("MCMCPP_BENCH_D") and not os.environ.get("MCMCPP_BENCH_W") \
             and args.shard is None and args.mover == "stretch" and args.store_every == 0:
         # the other BASELINE configs, short runs, one GPU: driver-visible numbers for C1/C2/C3/C5

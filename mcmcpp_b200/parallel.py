@@ -11,6 +11,28 @@ import os
 from . import _capi
 
 
+def bind_host_to_device(pci_bus_id):
+    """One process per GPU: run this process on the CPU cores NVML reports as local to its GPU (the GPU's NUMA node), so that
+    host buffers pinned AFTERWARDS are allocated there and the rank's host<->device copies do not cross the socket link.
+    With 4-8 ranks on a two-socket box whose buffers all sit on one node, the copies of an end-to-end call share one node's memory
+    and the inter-socket link.  Returns the cores bound to, or None when NVML, the device or an allowed core is not there (nothing
+    is changed then)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByPciBusId(pci_bus_id.encode() if isinstance(pci_bus_id, str) else pci_bus_id)
+        words = (max(os.cpu_count() or 1, 1) + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cores = {64 * i + b for i, word in enumerate(mask) for b in range(64) if (int(word) >> b) & 1}
+        cores &= set(os.sched_getaffinity(0))
+        if not cores:
+            return None
+        os.sched_setaffinity(0, cores)
+        return sorted(cores)
+    except Exception:
+        return None
+
+
 def shard_slots(num_walkers, rank, world):
     """Owned slots [begin, end) of each colour for `rank`: contiguous walker-index shards of
     the K = W/2 walkers per colour (MCMCpp/EnsembleSampler.h:225-226 numbering)."""

@@ -203,3 +203,12 @@ def test_two_rank_data_sharded_ensemble(tmp_path, port):
     assert np.array_equal(z[0]["pos"], z[1]["pos"]) and np.array_equal(z[0]["logp"], z[1]["logp"])   # replicas stay identical
     assert np.array_equal(z[0]["pos"], o["pos"]) and int(z[0]["acc"]) == int(o["acc"].sum())
     assert np.allclose(z[0]["logp"], o["logp"], rtol=1e-12, atol=0)
+
+
+def test_bind_host_to_device_changes_nothing_without_nvml_device():
+    """No GPU here: the NUMA binding helper must leave the process where it is and say so."""
+    import os
+    from mcmcpp_b200 import parallel
+    before = os.sched_getaffinity(0)
+    assert parallel.bind_host_to_device("00000000:01:00.0") is None
+    assert os.sched_getaffinity(0) == before
