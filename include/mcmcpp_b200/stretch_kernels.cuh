@@ -428,7 +428,7 @@ static __global__ void __launch_bounds__(256) stretchDrawKernel(const mcmcpp_hal
     a.dim_z[i] = dr.z; a.dim_e[i] = dr.logOneMinusU; a.dim_j[i] = dr.j;
 }
 
-template <class Calc, int WARPS, bool TRACE, bool PRE>
+template <class Calc, int WARPS, bool TRACE, bool PRE, bool ODD = false>
 __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_halfstep_args a, const Calc calcIn, const uint32_t rowStride)
 {
     extern __shared__ __align__(128) unsigned char bulkSmem[];
@@ -456,7 +456,12 @@ __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_h
     }
     double* ownRow = a.pos + (size_t)w * D;
     const double* selRow = partnerBase(a, dr.j) + (size_t)(other0 + dr.j) * D;
-    if (lane == 0) {
+    if (ODD) {
+        /* odd numParams: every second row starts 8 bytes off the 16-byte grid a bulk copy needs -- plain coalesced loads stage
+         * the rows instead (rows past 1024 odd parameters, which the register-resident warp kernel cannot hold) */
+        for (int d = lane; d < D; d += 32) { ownS[d] = ownRow[d]; selS[d] = __ldg(selRow + d); }
+        if (lane == 0) { ownS[D] = 0.0; selS[D] = 0.0; }      /* the pair partner of the last element (the row stride leaves room) */
+    } else if (lane == 0) {
         mbarInit(bar, 1);
         mbarExpectTx(bar, 2u * rowBytes);
         bulkLoad(smemAddr(ownS), ownRow, rowBytes, bar);
@@ -466,7 +471,7 @@ __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_h
     /* overlapped with the copies: the scalar part of the update */
     const double scaling = __dmul_rn(log(dr.z), (double)(D - 1));
     const double oldp = a.logp[w];
-    mbarWait(bar, 0);
+    if (!ODD) mbarWait(bar, 0);
 
     double p0 = 0.0, p1 = 0.0;
     for (int d = 2 * lane; d < D; d += 64) {
@@ -478,7 +483,7 @@ __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_h
         *reinterpret_cast<double2*>(selS + d) = p;       /* the proposal replaces the partner row */
         if constexpr (IsSeparable<Calc>::value) {
             p0 = __dadd_rn(p0, calc.term(p.x, d));
-            p1 = __dadd_rn(p1, calc.term(p.y, d + 1));
+            if (!ODD || d + 1 < D) p1 = __dadd_rn(p1, calc.term(p.y, d + 1));
         }
     }
     double newp;
@@ -496,13 +501,23 @@ __global__ void __launch_bounds__(WARPS * 32) stretchHalfStepBulk(const mcmcpp_h
     const double diff = __dsub_rn(__dadd_rn(scaling, newp), oldp);
     const bool accepted = dr.logOneMinusU < diff;
 
-    if (accepted) {
-        for (int d = 2 * lane; d < D; d += 64) *reinterpret_cast<double2*>(ownRow + d) = *reinterpret_cast<const double2*>(selS + d);
-    }
-    if (a.chain_row) {
-        double* chainRow = a.chain_row + (size_t)w * D;
-        const double* src = accepted ? selS : ownS;
-        for (int d = 2 * lane; d < D; d += 64) *reinterpret_cast<double2*>(chainRow + d) = *reinterpret_cast<const double2*>(src + d);
+    if (ODD) {
+        __syncwarp();
+        if (accepted) for (int d = lane; d < D; d += 32) ownRow[d] = selS[d];
+        if (a.chain_row) {
+            double* chainRow = a.chain_row + (size_t)w * D;
+            const double* src = accepted ? selS : ownS;
+            for (int d = lane; d < D; d += 32) chainRow[d] = src[d];
+        }
+    } else {
+        if (accepted) {
+            for (int d = 2 * lane; d < D; d += 64) *reinterpret_cast<double2*>(ownRow + d) = *reinterpret_cast<const double2*>(selS + d);
+        }
+        if (a.chain_row) {
+            double* chainRow = a.chain_row + (size_t)w * D;
+            const double* src = accepted ? selS : ownS;
+            for (int d = 2 * lane; d < D; d += 64) *reinterpret_cast<double2*>(chainRow + d) = *reinterpret_cast<const double2*>(src + d);
+        }
     }
     if (lane == 0) {
         if (!PRE) {
@@ -578,12 +593,12 @@ int launchWarpKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream
     return launchStatus();
 }
 
-template <class Calc, int WARPS, bool TRACE, bool PRE>
+template <class Calc, int WARPS, bool TRACE, bool PRE, bool ODD = false>
 int launchBulkKernelWTP(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream, uint32_t rowStride, int grid, size_t smem)
 {
     static DynamicSmemOptIn optIn;
-    if (!optIn.ensure(stretchHalfStepBulk<Calc, WARPS, TRACE, PRE>, 227 * 1024)) return MCMCPP_ERR_CUDA;
-    stretchHalfStepBulk<Calc, WARPS, TRACE, PRE><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
+    if (!optIn.ensure(stretchHalfStepBulk<Calc, WARPS, TRACE, PRE, ODD>, 227 * 1024)) return MCMCPP_ERR_CUDA;
+    stretchHalfStepBulk<Calc, WARPS, TRACE, PRE, ODD><<<grid, WARPS * 32, smem, stream>>>(a, calc, rowStride);
     return launchStatus();
 }
 
@@ -593,6 +608,9 @@ int launchBulkKernelW(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStrea
     const int grid = (a.slot_count + WARPS - 1) / WARPS;
     if (grid > a.max_grid) return MCMCPP_ERR_ARG;
     const size_t smem = (size_t)WARPS * 2u * rowStride + 8u * WARPS;
+    if (a.D & 1)                             /* odd numParams: rows staged by plain loads, draws in the kernel */
+        return a.trace ? launchBulkKernelWTP<Calc, WARPS, true, false, true>(a, calc, stream, rowStride, grid, smem)
+                       : launchBulkKernelWTP<Calc, WARPS, false, false, true>(a, calc, stream, rowStride, grid, smem);
     if (a.dim_z && a.dim_e && a.dim_j) {     /* draw scratch available: draws in their own kernel */
         stretchDrawKernel<<<(a.slot_count + 255) / 256, 256, 0, stream>>>(a);
         if (a.launch_count) *a.launch_count += 1;
@@ -607,7 +625,7 @@ int launchBulkKernelW(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStrea
 template <class Calc>
 int launchBulkKernel(const mcmcpp_halfstep_args& a, const Calc& calc, cudaStream_t stream)
 {
-    const uint32_t rowStride = ((uint32_t)a.D * 8u + 127u) & ~127u;
+    const uint32_t rowStride = (((uint32_t)a.D + ((uint32_t)a.D & 1u)) * 8u + 127u) & ~127u;      /* an odd row's last element gets a pair partner */
     const size_t perWarp = 2u * (size_t)rowStride + 8u;
     if (4 * perWarp <= 74 * 1024) return launchBulkKernelW<Calc, 4>(a, calc, stream, rowStride);
     if (2 * perWarp <= 74 * 1024) return launchBulkKernelW<Calc, 2>(a, calc, stream, rowStride);
@@ -923,7 +941,7 @@ struct HalfStepLauncher
             if (chunks <= 4) return launchWarpKernel<Calc, 4>(a, calc, stream);
             if (chunks <= 8) return launchWarpKernel<Calc, 8>(a, calc, stream);
             if (chunks <= 16) return launchWarpKernel<Calc, 16>(a, calc, stream);
-            return MCMCPP_ERR_UNSUPPORTED;   /* D > 1024: not built yet */
+            return launchBulkKernel<Calc>(a, calc, stream);   /* odd D > 1024 (or the bulk kernel switched off): rows staged in shared memory */
         }
     }
 };

@@ -95,9 +95,11 @@ def test_rosenbrock_thread_kernel(port, W, D, steps, interval):
 
 
 @pytest.mark.parametrize("W,D,steps", [(64, 3, 20), (64, 8, 20), (256, 9, 10), (256, 64, 10), (256, 65, 10), (256, 127, 6),
-                                       (512, 200, 6), (2048, 500, 3), (4096, 1000, 3), (4096, 1023, 2), (4096, 1024, 2)])
+                                       (512, 200, 6), (2048, 500, 3), (4096, 1000, 3), (4096, 1023, 2), (4096, 1024, 2),
+                                       (2100, 1025, 2), (2400, 1191, 2), (4200, 2049, 1)])
 def test_diag_gauss_every_kernel_shape(port, W, D, steps):
-    """thread kernel (D<=8), warp kernel with 1..16 chunks, odd D (scalar loads) and ragged tails:
+    """thread kernel (D<=8), warp kernel with 1..16 chunks, odd D (scalar loads) and ragged tails, odd D past 1024 (rows staged in
+    shared memory by plain loads):
     the separable log-posterior is reduced in the canonical order, so everything is bit-exact."""
     iv = 1.0 / (1.0 + (np.arange(D) % 10))
     init, lp = seeded_init(port, "diag_gauss", iv, W, D, 100 + D)

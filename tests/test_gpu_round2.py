@@ -332,3 +332,21 @@ def test_fused_kernel_with_draws_made_ahead(port, monkeypatch, kind, W, D, calls
     assert np.array_equal(np.array(s.getChain())[1:], o["chain"]) and np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
     assert (s.getAcceptedSteps(), s.getTotalSteps()) == (int(o["acc"].sum()), int(o["tot"].sum()))
     s.close()
+
+
+@pytest.mark.parametrize("rng", ["sequential", "per_walker32"])
+def test_odd_rows_past_1024_parameters_without_a_trace(port, rng):
+    """numParams odd and > 1024 (no bulk copies possible, too long for the register-resident warp kernel): the shared-memory
+    kernel with plain loads; chain on, subsampling, no trace."""
+    W, D, steps, interval = 2300, 1111, 2, 2
+    iv = 1.0 / (1.0 + (np.arange(D) % 10))
+    init, lp = seeded_init(port, "diag_gauss", iv, W, D, 8)
+    s = make_sampler("diag_gauss", iv, W, D, seed=3, rngMode=rng)
+    s.setSlicingMode(True, interval)
+    s.setInitialWalkerPos(init, lp)
+    assert s.runMCMC(steps)
+    o = port.run("diag_gauss", iv, init, lp, steps, interval=interval, seed=3, per_walker=32 if rng == "per_walker32" else False)
+    pos, aux = s.getWalkerState()
+    assert np.array_equal(np.array(s.getChain())[1:], o["chain"]) and np.array_equal(pos, o["pos"]) and np.array_equal(aux, o["logp"])
+    assert s.getAcceptedSteps() == int(o["acc"].sum())
+    s.close()
