@@ -30,6 +30,8 @@
 #define MCMCPP_B200_STRETCH_KERNELS_CUH
 
 #include <cuda_runtime.h>
+#include <cooperative_groups.h>
+#include <algorithm>
 #include <atomic>
 #include <cstdlib>
 #include "mcmcpp_b200/capi.h"
@@ -729,7 +731,7 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedSmall(const mc
  * and update is stretchFusedSmall's; chains, counters and final rng states are bit-identical (tests/test_gpu_parity.py fused
  * cases run both).  One difference, outside parity: after a bounded_rand rejection (probability K / 2^64 per update; counted in
  * flags[0] as everywhere) the later draws of that walker do not shift by one. */
-template <class Calc, int D>
+template <class Calc, int D, bool CLUSTER>
 __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mcmcpp_fused_args f, const Calc calcIn, const int stepsPerWindow,
                                                                         const int overlap)
 {
@@ -743,8 +745,21 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mc
     double* sE = sZ + (size_t)buffers * T;
     double* sS = sE + (size_t)buffers * T;
     int* sJ = reinterpret_cast<int*>(sS + (size_t)buffers * T);
-    for (int idx = t; idx < W * D; idx += blockDim.x) sPos[idx] = a.pos[idx];
-    for (int idx = t; idx < W; idx += blockDim.x) sLogp[idx] = a.logp[idx];
+    /* CLUSTER: a thread-block cluster; CTA 0 holds the ensemble and runs the walkers, every other thread of the cluster draws,
+     * storing its draws into CTA 0's buffers through distributed shared memory; the cluster barrier ends a window */
+    int crank = 0;
+    double *wZ = sZ, *wE = sE, *wS = sS;
+    int* wJ = sJ;
+    if (CLUSTER) {
+        cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+        crank = (int)cluster.block_rank();
+        wZ = cluster.map_shared_rank(sZ, 0); wE = cluster.map_shared_rank(sE, 0); wS = cluster.map_shared_rank(sS, 0);
+        wJ = cluster.map_shared_rank(sJ, 0);
+    }
+    if (crank == 0) {
+        for (int idx = t; idx < W * D; idx += blockDim.x) sPos[idx] = a.pos[idx];
+        for (int idx = t; idx < W; idx += blockDim.x) sLogp[idx] = a.logp[idx];
+    }
     Calc calc = calcIn;
     const long long total = (long long)f.stored_steps * f.interval;
 
@@ -752,8 +767,9 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mc
      * drawing role: thread (b, w) owns steps b, b + B, ... of walker w.  overlap: the warps after the walker warps draw window
      * k + 1 while the walker warps run window k (two draw buffers); otherwise every thread draws, then the walkers run. */
     const int walkerThreads = ((K + 31) / 32) * 32;
-    const bool live = t < K;
-    const int u = t - (overlap ? walkerThreads : 0);
+    const bool live = crank == 0 && t < K;
+    const int u = CLUSTER ? (crank == 0 ? t - walkerThreads : (FusedMaxThreads - walkerThreads) + (crank - 1) * FusedMaxThreads + t)
+                          : t - (overlap ? walkerThreads : 0);
     const bool drawer = u >= 0 && u < T;
     const int b = drawer ? u / W : 0, w = drawer ? u - b * W : 0;
     U128 inc; inc.lo = 1ULL; inc.hi = 0;                      /* the sampler's stream 0 (EnsembleSampler.h:217) */
@@ -777,8 +793,8 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mc
             const StretchDraws dr = drawStretch(st, inc, (uint64_t)K, a.bound_threshold, a.bound_recip, gwOf(a));
             redraws += (unsigned)dr.redraws;
             const int slot = buffer * T + u;
-            sJ[slot] = dr.j; sZ[slot] = dr.z; sE[slot] = dr.logOneMinusU;
-            sS[slot] = __dmul_rn(log(dr.z), (double)(D - 1));
+            wJ[slot] = dr.j; wZ[slot] = dr.z; wE[slot] = dr.logOneMinusU;
+            wS[slot] = __dmul_rn(log(dr.z), (double)(D - 1));
             base = applyAffine(window, base);
             next += B;
         }
@@ -824,13 +840,17 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mc
         }
     };
 
+    auto windowEnd = [&]() {
+        if (CLUSTER) cooperative_groups::this_cluster().sync(); else __syncthreads();
+    };
+    if (CLUSTER) cooperative_groups::this_cluster().sync();       /* CTA 0's shared memory exists before anybody stores into it */
     draw(0);
-    __syncthreads();
+    windowEnd();
     int parity = 0;
     for (long long first = 0; first < total; first += B) {
         if (overlap) {
-            if (t < walkerThreads) walk(first, parity); else draw(parity ^ 1);
-            __syncthreads();
+            if (crank == 0 && t < walkerThreads) walk(first, parity); else draw(parity ^ 1);
+            windowEnd();
             parity ^= 1;
         } else {
             if (t < walkerThreads) walk(first, 0);
@@ -839,8 +859,10 @@ __global__ void __launch_bounds__(FusedMaxThreads, 1) stretchFusedAhead(const mc
             __syncthreads();
         }
     }
-    for (int idx = t; idx < W * D; idx += blockDim.x) a.pos[idx] = sPos[idx];
-    for (int idx = t; idx < W; idx += blockDim.x) a.logp[idx] = sLogp[idx];
+    if (crank == 0) {
+        for (int idx = t; idx < W * D; idx += blockDim.x) a.pos[idx] = sPos[idx];
+        for (int idx = t; idx < W; idx += blockDim.x) a.logp[idx] = sLogp[idx];
+    }
     if (drawer) {
         /* walker w's state at rest = the stream at ITS next draw: the base of the item (step total, walker w) */
         if (next == total) reinterpret_cast<ulonglong2*>(a.rng_state)[w] = make_ulonglong2(base.lo, base.hi);
@@ -861,18 +883,44 @@ struct FusedLauncher
         const mcmcpp_halfstep_args& a = f.base;
         /* sequential stream and W <= 1024: the draws are made ahead by the whole CTA (MCMCPP_B200_FUSED_AHEAD=0: never) */
         static const bool aheadAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED_AHEAD"); return !(e && e[0] == '0'); }();
-        if (aheadAllowed && a.rng_mode == MCMCPP_RNG_SEQUENTIAL && 2 * a.K <= FusedMaxThreads) {
+        if (aheadAllowed && a.rng_mode == MCMCPP_RNG_SEQUENTIAL && 2 * a.K <= FusedMaxThreads) {      /* W <= 1024 */
             /* enough threads beside the walker warps to draw at least one step per window: they draw window k + 1 while window k
              * runs (MCMCPP_B200_FUSED_OVERLAP=0: draw, then run) */
             static const bool overlapAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED_OVERLAP"); return !(e && e[0] == '0'); }();
+            static const bool clusterAllowed = [] { const char* e = getenv("MCMCPP_B200_FUSED_CLUSTER"); return !(e && e[0] == '0'); }();
             const int W = 2 * a.K, walkerThreads = ((a.K + 31) / 32) * 32;
+            const size_t stateBytes = sizeof(double) * ((size_t)W * D + (size_t)W), perDraw = 3 * sizeof(double) + sizeof(int);
+            /* from 256 walkers on the draws are most of a step on one SM (3.5 W cycles of issue against ~900 of walker latency):
+             * a thread-block cluster of 2, 4 or 8 CTAs draws, CTA 0 runs the walkers (distributed shared memory) */
+            if (overlapAllowed && clusterAllowed && W >= 256 && stateBytes + 2 * perDraw * (size_t)W <= 160 * 1024) {
+                int B = (int)std::min<size_t>(8, (160 * 1024 - stateBytes) / (2 * perDraw * (size_t)W));
+                int ctas = 0;
+                for (;; --B) {
+                    const int beside = FusedMaxThreads - walkerThreads, need = W * B - beside;
+                    ctas = 1 + (need > 0 ? (need + FusedMaxThreads - 1) / FusedMaxThreads : 0);
+                    ctas = ctas <= 2 ? 2 : (ctas <= 4 ? 4 : 8);
+                    if (1 + (need > 0 ? (need + FusedMaxThreads - 1) / FusedMaxThreads : 0) <= 8 || B == 1) break;
+                }
+                const int T = W * B;
+                const size_t smemCluster = stateBytes + 2 * perDraw * (size_t)T;
+                static DynamicSmemOptIn optInCluster;
+                if (smemCluster > 48 * 1024 && !optInCluster.ensure(stretchFusedAhead<Calc, D, true>, smemCluster)) return MCMCPP_ERR_CUDA;
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(FusedMaxThreads); cfg.dynamicSmemBytes = smemCluster; cfg.stream = stream;
+                cudaLaunchAttribute attr[1];
+                attr[0].id = cudaLaunchAttributeClusterDimension;
+                attr[0].val.clusterDim.x = ctas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+                cfg.attrs = attr; cfg.numAttrs = 1;
+                if (cudaLaunchKernelEx(&cfg, stretchFusedAhead<Calc, D, true>, f, calc, B, 1) != cudaSuccess) return MCMCPP_ERR_CUDA;
+                return launchStatus();
+            }
             const int overlap = overlapAllowed && (FusedMaxThreads - walkerThreads) / W >= 1 ? 1 : 0;
             const int B = overlap ? (FusedMaxThreads - walkerThreads) / W : FusedMaxThreads / W, T = W * B;
             const int threads = overlap ? walkerThreads + ((T + 31) / 32) * 32 : ((T + 31) / 32) * 32;
             const size_t smemAhead = sizeof(double) * ((size_t)W * D + (size_t)W + 3 * (size_t)T * (overlap + 1)) + sizeof(int) * (size_t)T * (overlap + 1);
             static DynamicSmemOptIn optInAhead;
-            if (smemAhead > 48 * 1024 && !optInAhead.ensure(stretchFusedAhead<Calc, D>, smemAhead)) return MCMCPP_ERR_CUDA;
-            stretchFusedAhead<Calc, D><<<1, threads, smemAhead, stream>>>(f, calc, B, overlap);
+            if (smemAhead > 48 * 1024 && !optInAhead.ensure(stretchFusedAhead<Calc, D, false>, smemAhead)) return MCMCPP_ERR_CUDA;
+            stretchFusedAhead<Calc, D, false><<<1, threads, smemAhead, stream>>>(f, calc, B, overlap);
             return launchStatus();
         }
         const size_t smem = sizeof(double) * ((size_t)2 * a.K * D + (size_t)2 * a.K);

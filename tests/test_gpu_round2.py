@@ -309,11 +309,13 @@ def test_device_log_matches_cuda_log():
 # ---- the fused small-ensemble kernel with the draws made ahead (stretchFusedAhead) -----------------------------------------
 @pytest.mark.parametrize("kind,W,D,calls,interval", [
     ("skewed_gauss_2d", 32, 2, (1, 31, 32, 33, 100), 1),        # B = 32 steps per window: less than, exactly, more than a window
-    ("skewed_gauss_2d", 320, 2, (7, 2, 50), 1),                 # the reference's own test size: B = 3, 960 drawing threads
+    ("skewed_gauss_2d", 320, 2, (7, 2, 50), 1),                 # the reference's own test size: cluster of 4 CTAs, B = 8
     ("rosenbrock_2d", 44, 2, (45, 1, 23), 2),                   # B = 23, T = 1012: a ragged last warp; subsampling
-    ("diag_gauss", 1024, 5, (3, 4), 1),                         # B = 1
-    ("diag_gauss", 600, 8, (5, 5), 3),                          # B = 1, T = 600 < 1024; > 48 KB of shared memory
-    ("dense_gauss", 12, 5, (70, 9), 1)])                        # B = 85
+    ("diag_gauss", 1024, 5, (3, 4), 1),                         # cluster, B = 2
+    ("diag_gauss", 600, 8, (5, 5), 3),                          # cluster, B = 3; > 48 KB of shared memory
+    ("dense_gauss", 12, 5, (70, 9), 1),                         # B = 82
+    ("rosenbrock_2d", 256, 2, (9, 8, 1, 30), 1),                # from 256 walkers: a cluster of CTAs draws (B = 8, 4 CTAs)
+    ("diag_gauss", 1000, 3, (5, 2, 6), 2)])                     # cluster, B = 2, 1000 walkers
 def test_fused_kernel_with_draws_made_ahead(port, monkeypatch, kind, W, D, calls, interval):
     """Several runMCMC calls of awkward lengths (each call is one launch and leaves every walker's rng state behind for the next):
     chain, final state and counters equal to the oracle's."""
