@@ -348,8 +348,8 @@ struct DiffEvoLauncher
         default: break;
         }
         if (a.D > 4096) return MCMCPP_ERR_UNSUPPORTED;
-        static int cachedD = -1;
-        static DiffEvoJumps jumps;
+        static thread_local int cachedD = -1;          /* per host thread: samplers of different D may launch from different threads */
+        static thread_local DiffEvoJumps jumps;
         if (cachedD != a.D) { jumps = makeDiffEvoJumps(a.D); cachedD = a.D; }
         const int grid = (a.slot_count + DiffEvoWarps - 1) / DiffEvoWarps;
         if (grid > a.max_grid) return MCMCPP_ERR_ARG;
