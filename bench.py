@@ -523,6 +523,18 @@ def gpu_arm(args):
                                                  "roofline", "cpu_baseline", "acceptance")}
             except Exception as exc:                    # a failure here must not take the headline line with it
                 others[name] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+        # C2 once more on the fast engine (one pcg32 per walker, its own pinned oracle): the device-timed value and its rooflines
+        try:
+            saved = args.rng
+            args.rng = "per_walker32"
+            k_steps, k_warm = OTHERS["c2"][0], OTHERS["c2"][1]
+            r = measure(torch, dist, m, parallel, args, "c2", k_steps, k_warm, False, False)
+            others["c2_per_walker32"] = {k: r[k] for k in ("value", "unit", "steps", "warmup", "ms_per_step", "config", "clocks", "gpu_launches",
+                                                            "roofline", "acceptance")}
+        except Exception as exc:
+            others["c2_per_walker32"] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+        finally:
+            args.rng = saved
         line["other_workloads"] = others
     if rank == 0:
         print(json.dumps(line), flush=True)

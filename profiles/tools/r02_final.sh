@@ -18,7 +18,7 @@ import json
 d = json.loads([l for l in open('gpurun_out/r02_bench_default_n1.json') if l.startswith('{')][-1])
 print('C4 value %.4g ms/step %.4f frac_actual %.3f e2e %.4g clocks %s' % (d['value'], d['ms_per_step'], d['roofline']['frac_actual'], d['e2e']['value'], d['clocks']))
 for k, v in d['other_workloads'].items():
-    print(k, v.get('error') or ('%.4g' % v['value'], v['roofline'].get('frac'), v['roofline'].get('issue', {}).get('frac'), '%.4g' % v['cpu_baseline']['value']))
+    print(k, v.get('error') or ('%.4g' % v['value'], v['roofline'].get('frac'), v['roofline'].get('issue', {}).get('frac'), '%.4g' % (v.get('cpu_baseline') or {'value': float('nan')})['value']))
 r = json.loads([l for l in open('gpurun_out/r02_bench_reference_arm.json') if l.startswith('{')][-1]); print('reference arm %.4g' % r['value'])
 PY
 tail -3 $O/final.err
